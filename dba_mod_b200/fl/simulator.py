@@ -1,0 +1,563 @@
+"""The experiment driver: round loop, client training, aggregation, evaluation, recording, checkpoints.
+
+Public API (what ``main.py --params X.yaml`` and ``bench.py`` call):
+
+    sim = Simulator(Params.from_yaml(path))      # loads data, builds / resumes the global model
+    sim.run()                                     # all rounds  (reference main.py:135-235)
+    sim.run_round(epoch)                          # one round, returns a RoundReport
+
+Reference flow reproduced per round (main.py:135-235, image_train.py:12-315, loan_train.py:11-261, test.py):
+select clients -> local training of every selected client from the current global model (benign or poisoned, with
+scaling) -> per-client evaluations (Q16) -> aggregation (mean / geom_median / foolsgold) -> global evaluations
+(clean, combined trigger, per-trigger) -> checkpoint -> CSV dump.  What differs is *how*: the clients of a rank
+train as one batched group over flat slabs, all evaluations of a round that share inputs are batched over models,
+metrics stay on the device until the end of the phase, and with several ranks (one process per GPU) the clients are
+sharded over ranks and aggregation runs as collectives (fused peer-memory kernels on B200, ``torch.distributed`` as
+the baseline / CPU path).
+"""
+from __future__ import annotations
+
+import logging
+import os
+import random
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .. import config as C
+from ..config import Params
+from ..data import ImageData, LoanData
+from ..models import display_name, initial_state
+from ..utils import checkpoint as ckpt
+from ..utils.csv_record import Recorder
+from ..utils.logging_utils import close_logger, make_run_folder, now_tag, open_logger
+from ..utils.metrics import MetricsStream, dict_html
+from ..utils.timing import PhaseTimer
+from . import aggregation as agg
+from .schedule import ClientPlan, build_schedule, plan_clients
+from .selection import select_clients
+
+logger = logging.getLogger("logger")
+
+
+@dataclass
+class RoundReport:
+    epoch: int
+    names: List
+    adversaries: List
+    global_acc: float = 0.0
+    global_loss: float = 0.0
+    poison_acc: Optional[float] = None
+    poison_loss: Optional[float] = None
+    trigger_acc: Dict[str, float] = field(default_factory=dict)
+    agg_weights: Optional[List[float]] = None
+    agg_alphas: Optional[List[float]] = None
+    steps: int = 0
+    nan_clients: List = field(default_factory=list)
+    seconds: float = 0.0
+
+
+def pick_device(params) -> torch.device:
+    if params["backend"] == "torch" and not torch.cuda.is_available():
+        return torch.device("cpu")
+    if torch.cuda.is_available():
+        return torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    return torch.device("cpu")
+
+
+class Simulator:
+    def __init__(self, params: Params, device: Optional[torch.device] = None, comm=None, out_root: str = "saved_models",
+                 quiet: bool = False, data=None, write_files: bool = True) -> None:
+        self.params = params
+        self.device = device if device is not None else pick_device(params)
+        self.comm = comm if comm is not None else agg.LocalComm()
+        self.rank, self.world = self.comm.rank, self.comm.world
+        self.is_main = self.rank == 0
+        self.write_files = write_files and self.is_main
+        seed = int(params["seed"])
+        # main.py:36-38,86 — one python / numpy stream drives partition shuffles, Dirichlet draws and selection
+        self.py_rng = random.Random(seed)
+        self.np_rng = np.random.RandomState(seed)
+        self.torch_gen = torch.Generator(device=self.device).manual_seed(seed + 7919 * self.rank)
+        self.noise_gen = torch.Generator(device=self.device).manual_seed(seed + 104729)
+
+        name = params.get("name") or C.DEFAULT_NAME[params["type"]]
+        self.name = name
+        self.current_time = now_tag()
+        if self.write_files:
+            self.folder_path = make_run_folder(name, self.current_time, out_root)
+            self._log_handlers = open_logger(self.folder_path, stream=not quiet)
+        else:
+            self.folder_path = None
+            self._log_handlers = []
+            logging.getLogger("logger").setLevel(logging.WARNING if quiet else logging.INFO)
+        if not params.get("environment_name"):
+            params["environment_name"] = name
+        params["current_time"] = self.current_time
+        params["folder_path"] = self.folder_path
+        logger.info(f"current path: {self.folder_path}")
+
+        self.recorder = Recorder()
+        self.metrics = MetricsStream(self.folder_path, enabled=self.write_files)
+        self.ckpt_writer = ckpt.CheckpointWriter(params)
+        self.timer = PhaseTimer(self.device)
+
+        # ---- data (image_helper.load_data / loan_helper.load_data)
+        if data is not None:
+            self.data = data
+        elif params.is_image:
+            self.data = ImageData(params, self.device, self.py_rng, self.np_rng)
+        else:
+            self.data = LoanData(params, self.device)
+        logger.info("load data done")
+
+        # ---- model (create_model + resume; image_helper.py:32-70, loan_helper.py:85-109)
+        self.spec, flat, cnt = initial_state(params["type"], seed)
+        self.start_epoch = 1
+        if params["resumed_model"]:
+            path = ckpt.resume_path(params, out_root if os.path.isdir(out_root) else "saved_models")
+            sd, ep, lr = ckpt.load_checkpoint(path)
+            flat, cnt = self.spec.flatten(sd)
+            self.start_epoch = ep + 1
+            if lr is not None:
+                params["lr"] = lr
+            logger.info(f"Loaded parameters from saved model: LR is {params['lr']} and current epoch is "
+                        f"{self.start_epoch}")
+        self.G = flat.to(self.device)
+        self.G_cnt = cnt[: max(self.spec.n_counters, 0)].to(self.device) if self.spec.n_counters else \
+            torch.zeros(0, dtype=torch.long, device=self.device)
+        logger.info("create model done")
+        self.local_name = display_name(params["type"], "Local")
+        self.target_name = display_name(params["type"], "Target")
+
+        self.backend = self._make_backend()
+        self.fg = agg.FoolsGoldState(use_memory=bool(params["fg_use_memory"]))
+        self._loan_local_epoch = self.start_epoch - 1
+        self.stream_inputs = False          # bench end-to-end mode: re-upload the round's inputs from pinned host
+        self._pinned = None
+        self.h2d_bytes_last = 0
+        self.d2h_bytes_last = 0
+
+        if params["is_poison"]:
+            logger.info(f"Poisoned following participants: {params['adversary_list']}")
+        if self.write_files:
+            params.dump_yaml(os.path.join(self.folder_path, "params.yaml"))
+            with open(os.path.join(self.folder_path, "params.html"), "w") as f:
+                f.write(dict_html(params, self.current_time))
+        unknown = params.unknown_keys()
+        if unknown:
+            logger.info(f"ignoring unknown parameters: {unknown}")
+
+    # ------------------------------------------------------------------------------------------ set-up
+    def _make_backend(self):
+        want = self.params["backend"]
+        if want == "auto":
+            want = "cuda" if self.device.type == "cuda" else "torch"
+        if want == "cuda":
+            from .cuda_backend import CudaBackend
+            return CudaBackend(self.params, self.spec, self.data, self.device)
+        from .torch_backend import TorchBackend
+        return TorchBackend(self.params, self.spec, self.data, self.device)
+
+    def state_dict(self):
+        return self.spec.unflatten(self.G.detach().cpu(), self.G_cnt.detach().cpu() if self.G_cnt.numel() else None)
+
+    def load_state_dict(self, sd) -> None:
+        flat, cnt = self.spec.flatten(sd)
+        self.G.copy_(flat.to(self.device))
+        if self.spec.n_counters:
+            self.G_cnt.copy_(cnt[: self.spec.n_counters].to(self.device))
+
+    def close(self) -> None:
+        self.metrics.close()
+        close_logger(self._log_handlers)
+        self._log_handlers = []
+
+    # ------------------------------------------------------------------------------------- client sharding
+    def _shard(self, names: List) -> List[int]:
+        """Slots of this rank.  Greedy longest-processing-time placement on the estimated step count, so the
+        attacker (3-10x more steps) does not share a GPU with many benign clients."""
+        if self.world == 1:
+            return list(range(len(names)))
+        p = self.params
+        cost = []
+        for s, nm in enumerate(names):
+            adv = p.adversary_index(nm) if (p["is_poison"] and nm in p["adversary_list"]) else -1
+            ne = p["internal_poison_epochs"] if adv >= 0 else p["internal_epochs"]
+            cost.append((self.data.batches_per_epoch(nm) * ne, s))
+        load = [0] * self.world
+        owner = {}
+        for c, s in sorted(cost, key=lambda t: (-t[0], t[1])):
+            r = min(range(self.world), key=lambda i: (load[i], i))
+            load[r] += c
+            owner[s] = r
+        return [s for s in range(len(names)) if owner[s] == self.rank]
+
+    def _owner_counts(self, names: List) -> Tuple[List[int], List[int]]:
+        """(rows per rank, global-slot order of the concatenated rank shards)."""
+        if self.world == 1:
+            return [len(names)], list(range(len(names)))
+        saved = self.rank
+        counts, order = [], []
+        for r in range(self.world):
+            self.rank = r
+            sl = self._shard(names)
+            counts.append(len(sl))
+            order += sl
+        self.rank = saved
+        return counts, order
+
+    # ------------------------------------------------------------------------------------------ the loop
+    def run(self, max_rounds: Optional[int] = None) -> List[RoundReport]:
+        p = self.params
+        reports = []
+        for i, epoch in enumerate(range(self.start_epoch, p["epochs"] + 1, p["aggr_epoch_interval"])):
+            if max_rounds is not None and i >= max_rounds:
+                break
+            reports.append(self.run_round(epoch))
+        logger.info("Saving all the graphs.")
+        logger.info(f"This run has a label: {p['current_time']}. Metrics stream: {self.metrics.path}")
+        return reports
+
+    def _stage_inputs(self, names: List) -> None:
+        """End-to-end mode: the round's inputs (selected clients' training samples + the test split) come from
+        pinned host memory every round, like the reference's DataLoader -> .to(device) path."""
+        d = self.data
+        if self._pinned is None:
+            self._pinned = {"train": d.train_x_host.pin_memory(), "test": d.test_x_host.pin_memory()}
+        idx = torch.cat([d.client_index_tensor(n) for n in names]) if names else None
+        nbytes = 0
+        if idx is not None and idx.numel():
+            host_idx = idx.cpu()
+            rows = self._pinned["train"][host_idx].pin_memory()
+            dev_rows = rows.to(self.device, non_blocking=True)
+            d.train_x.index_copy_(0, idx, dev_rows)
+            nbytes += rows.numel() * rows.element_size()
+        d.test_x.copy_(self._pinned["test"], non_blocking=True)
+        nbytes += d.test_x.numel() * d.test_x.element_size()
+        self.h2d_bytes_last = nbytes
+
+    def run_round(self, epoch: int) -> RoundReport:
+        p, be, dev = self.params, self.backend, self.device
+        t0 = time.time()
+        names, adversaries = select_clients(p, epoch, self.data.participants_list, self.data.benign_namelist,
+                                            self.py_rng)
+        logger.info(f"Server Epoch:{epoch} choose agents : {names}.")
+        rep = RoundReport(epoch, list(names), list(adversaries))
+        self._round_epoch, self._loan_tle = epoch, {}
+        my_slots = self._shard(names)
+        my_names = [names[s] for s in my_slots]
+        counts, order = self._owner_counts(names)
+        if self.stream_inputs:
+            self._stage_inputs(my_names)
+        K, Df = len(my_names), self.spec.Df
+        use_fg = p["aggregation_methods"] == C.AGGR_FOOLSGOLD
+
+        # R1: global -> client broadcast (image_train.py:26-32)
+        W = self.G.unsqueeze(0).repeat(K, 1)
+        cnt = self.G_cnt.unsqueeze(0).repeat(K, 1) if self.spec.n_counters else torch.zeros(K, 0, dtype=torch.long,
+                                                                                             device=dev)
+        grad_sum = None
+        num_samples = [0] * K
+        rows_local: List[Tuple[int, str, list]] = []     # (slot, table, row) emitted in reference order later
+
+        with self.timer.phase("train"):
+            for seg_epoch in range(epoch, epoch + p["aggr_epoch_interval"]):
+                anchor, anchor_cnt = W.clone(), cnt.clone()
+                lr_override = self._loan_adaptive_lr(my_names, seg_epoch, W)
+                plans = plan_clients(p, self.data, my_names, seg_epoch, lr_override)
+                sch = build_schedule(p, self.data, plans, seg_epoch, dev, self.torch_gen)
+                res = be.train(sch, W, cnt, anchor, use_fg, generator=self.torch_gen)
+                rep.steps += sch.T
+                if use_fg:
+                    grad_sum = res.grad_sum     # "only works for aggr_epoch_interval=1" (image_train.py:24)
+                self._after_training(seg_epoch, plans, my_slots, sch, res, W, cnt, anchor, anchor_cnt, rows_local,
+                                     num_samples, rep)
+        # emit per-client rows in the reference's order (client by client)
+        self._emit_rows(rows_local, counts)
+
+        # ---------------- aggregation (main.py:172-191)
+        with self.timer.phase("aggregate"):
+            self._aggregate(epoch, names, adversaries, my_slots, counts, order, W, cnt, grad_sum, num_samples, rep)
+
+        # ---------------- global evaluation (main.py:195-231)
+        with self.timer.phase("global_eval"):
+            self._global_eval(epoch, rep)
+
+        if self.write_files:
+            self.ckpt_writer.save_model(self.state_dict(), epoch, rep.poison_loss if p["is_poison"] else rep.global_loss)
+            self.recorder.save_result_csv(epoch, p["is_poison"], self.folder_path)
+            self.metrics.flush()
+        rep.seconds = time.time() - t0
+        logger.info(f"Done in {rep.seconds} sec.")
+        return rep
+
+    # -------------------------------------------------------------------------------------- local phase
+    def _loan_adaptive_lr(self, my_names, seg_epoch, W) -> Optional[dict]:
+        """Q18 (loan_train.py:65-75): a LOAN attacker first measures the backdoor accuracy of the model it starts
+        from and shrinks ``poison_lr`` (/5 above 20 %, a further /10 above 60 %) unless ``baseline``."""
+        p = self.params
+        if p["type"] != C.TYPE_LOAN or not p["is_poison"]:
+            return None
+        ks = [k for k, nm in enumerate(my_names)
+              if nm in p["adversary_list"] and seg_epoch in p.poison_epochs_of(p.adversary_index(nm))]
+        if not ks:
+            return None
+        loss, correct, n = self.backend.evaluate(W[ks], "poison", 0)
+        out = {}
+        for j, k in enumerate(ks):
+            acc_p = 100.0 * float(correct[j]) / n if n else 0.0
+            logger.info(acc_p)
+            lr = float(p["poison_lr"])
+            if not p["baseline"]:
+                if acc_p > 20:
+                    lr /= 5
+                if acc_p > 60:
+                    lr /= 10
+            out[my_names[k]] = lr
+        return out
+
+    def _after_training(self, epoch, plans: List[ClientPlan], my_slots, sch, res, W, cnt, anchor, anchor_cnt,
+                        rows, num_samples, rep) -> None:
+        p, be = self.params, self.backend
+        is_loan = p["type"] == C.TYPE_LOAN
+        K = len(plans)
+        # ---- one D2H of the phase's metric block
+        loss_sum = res.loss_sum.cpu()
+        correct = res.correct.cpu()
+        count = res.count.cpu()
+        pcount = res.poison_count.cpu()
+        nan = res.nan_flag.cpu()
+        self.d2h_bytes_last = sum(t.numel() * t.element_size() for t in (loss_sum, correct, count, pcount, nan))
+        for k, pl in enumerate(plans):
+            if bool(nan[k]):
+                rep.nan_clients.append(pl.name)
+                if is_loan:
+                    raise ValueError(f"NaN in the outputs of client {pl.name}")   # loan_model.py:25-26
+        # ---- train rows / logs
+        for k, pl in enumerate(plans):
+            slot = my_slots[k]
+            for e in range(pl.n_epochs):
+                n = int(count[k, e])
+                acc = 100.0 * float(correct[k, e]) / n if n else 0.0
+                tl = float(loss_sum[k, e]) / n if n else 0.0
+                if is_loan:   # loan_train.py:32: starts at (round start epoch - 1), +1 per internal epoch
+                    tle = self._loan_tle.get(pl.name, self._round_epoch - 1) + 1
+                    self._loan_tle[pl.name] = tle
+                else:
+                    tle = (epoch - 1) * pl.n_epochs + e + 1
+                tag = "___PoisonTrain" if pl.poisoning else "___Train"
+                extra = f", train_poison_data_count: {int(pcount[k, e])}" if pl.poisoning else ""
+                logger.info("{} {},  epoch {:3d}, local model {}, internal_epoch {:3d},  Average loss: {:.4f}, "
+                            "Accuracy: {}/{} ({:.4f}%){}".format(tag, self.local_name, epoch, pl.name, e + 1, tl,
+                                                                 int(correct[k, e]), n, acc, extra))
+                rows.append((slot, "train", [pl.name, tle, epoch, e + 1, tl, acc, int(correct[k, e]), n]))
+                if p["vis_train"]:
+                    self.metrics.train_vis(tle, acc, tl, str(pl.name), pl.poisoning)
+            if pl.n_epochs:
+                num_samples[k] = int(count[k, pl.n_epochs - 1])
+
+        # ---- evaluations + scaling; jobs are batched over models that share the same inputs
+        scaling = [k for k, pl in enumerate(plans) if pl.poisoning and not p["baseline"]]
+        jobs: List[Tuple[str, int, torch.Tensor, int, str]] = []   # (split, trig_row, model_row, k, tag)
+        if scaling:
+            logger.info(f"Global model norm: {float(be.global_norm(self.G[None])[0])}.")
+            gn, dn = be.global_norm(W[scaling]).cpu(), be.dist_norm(W[scaling], anchor[scaling]).cpu()
+            for j, k in enumerate(scaling):
+                logger.info(f"Norm before scaling: {float(gn[j])}. Distance: {float(dn[j])}")
+        do_eval = bool(p["client_eval"])
+        pre = W[scaling].clone() if scaling else None
+        if do_eval and not is_loan:
+            for j, k in enumerate(scaling):         # image_train.py:148-164: tests of the unscaled poisoned model
+                jobs.append(("clean", -1, pre[j], k, "pre_clean"))
+                jobs.append(("poison", 0, pre[j], k, "pre_poison"))
+        if scaling:
+            sc = torch.tensor([plans[k].scale for k in scaling], device=self.device)
+            sub = W[scaling]
+            be.scale_(sub, anchor[scaling], sc)
+            W[scaling] = sub
+            if cnt.numel():
+                for k in scaling:       # counters scale too (integer arithmetic under torch<=1.4)
+                    cnt[k] = anchor_cnt[k] + ((cnt[k] - anchor_cnt[k]).double() * plans[k].scale).trunc().long()
+            gn, dn = be.global_norm(W[scaling]).cpu(), be.dist_norm(W[scaling], anchor[scaling]).cpu()
+            for j, k in enumerate(scaling):
+                logger.info(f"Scaling by  {plans[k].scale}")
+                logger.info(f"Scaled Norm after poisoning: {float(gn[j])}, distance: {float(dn[j])}")
+                if not is_loan:
+                    rows.append((my_slots[k], "scale", [epoch, float(dn[j])]))
+        if do_eval:
+            for k, pl in enumerate(plans):
+                if is_loan or not pl.poisoning:                       # loan_train.py:198-201 / image_train.py:268-271
+                    jobs.append(("clean", -1, W[k], k, "clean"))
+                if p["is_poison"] and pl.poisoning:                   # image_train.py:274-282
+                    jobs.append(("poison", 0, W[k], k, "poison"))
+                if p["is_poison"] and pl.adv_index >= 0:              # image_train.py:285-295
+                    jobs.append(("poison", pl.adv_index + 1, W[k], k, "agent"))
+        results = self._run_eval_jobs(jobs)
+        order_tags = ["pre_clean", "pre_poison", "clean", "poison", "agent"]
+        for k, pl in enumerate(plans):
+            slot = my_slots[k]
+            for tag in order_tags:
+                r = results.get((k, tag))
+                if r is None:
+                    continue
+                loss, acc, corr, n = r
+                poisoned = tag in ("pre_poison", "poison")
+                if tag != "agent":
+                    logger.info("___Test {} poisoned: {}, epoch: {}: Average loss: {:.4f}, Accuracy: {}/{} ({:.4f}%)"
+                                .format(self.local_name, poisoned, epoch, loss, corr, n, acc))
+                if tag in ("pre_clean", "clean"):
+                    rows.append((slot, "test", [pl.name, epoch, loss, acc, corr, n]))
+                    if tag == "clean":
+                        self.metrics.test_vis(epoch, acc, None, str(pl.name))
+                elif poisoned:
+                    rows.append((slot, "poison", [pl.name, epoch, loss, acc, corr, n]))
+                    if tag == "poison":
+                        self.metrics.poison_test_vis(epoch, acc, None, str(pl.name))
+                else:
+                    rows.append((slot, "trigger", [pl.name, f"{pl.name}_trigger", "", epoch, loss, acc, corr, n]))
+                    if p["vis_trigger_split_test"]:
+                        self.metrics.trigger_agent_test_vis(epoch, acc, f"{pl.name}_trigger")
+
+    def _run_eval_jobs(self, jobs) -> Dict[Tuple[int, str], Tuple[float, float, int, int]]:
+        groups: Dict[Tuple[str, int], list] = {}
+        for split, trig, row, k, tag in jobs:
+            groups.setdefault((split, trig), []).append((row, k, tag))
+        out = {}
+        for (split, trig), items in groups.items():
+            models = torch.stack([it[0] for it in items])
+            loss, correct, n = self.backend.evaluate(models, split, max(trig, 0))
+            loss, correct = loss.cpu(), correct.cpu()
+            for j, (_, k, tag) in enumerate(items):
+                acc = 100.0 * float(correct[j]) / n if n else 0
+                out[(k, tag)] = (float(loss[j]) / n if n else 0, acc, int(correct[j]), n)
+        return out
+
+    def _emit_rows(self, rows_local, counts) -> None:
+        rows = rows_local
+        if self.world > 1:
+            import torch.distributed as dist
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, rows_local)
+            rows = [r for part in gathered for r in part]
+        if not self.is_main:
+            return
+        rows = sorted(rows, key=lambda r: r[0])     # stable: keeps each client's internal order
+        rec = self.recorder
+        for _, table, row in rows:
+            if table == "train":
+                rec.train_result.append(row)
+            elif table == "test":
+                rec.test_result.append(row)
+            elif table == "poison":
+                rec.posiontest_result.append(row)
+            elif table == "trigger":
+                rec.poisontriggertest_result.append(row)
+            elif table == "scale":
+                rec.add_scale(row[0], row[1])
+
+    # ---------------------------------------------------------------------------------------- aggregation
+    def _aggregate(self, epoch, names, adversaries, my_slots, counts, order, W, cnt, grad_sum, num_samples,
+                   rep) -> None:
+        p, be, comm = self.params, self.backend, self.comm
+        method = p["aggregation_methods"]
+        sigma = float(p["sigma"]) if p["diff_privacy"] else None
+        all_ns = self._gather_num_samples(num_samples, counts, order, len(names))
+        names_in_order = [names[s] for s in order]
+        if method == C.AGGR_MEAN:
+            delta = W - self.G[None, :]
+            dcnt = (cnt - self.G_cnt[None, :]) if cnt.numel() else None
+            if hasattr(be, "fedavg_update_"):
+                be.fedavg_update_(self.G, self.G_cnt, delta, dcnt, float(p["eta"]), int(p["no_models"]), comm, sigma,
+                                  self.noise_gen)
+            else:
+                agg.fedavg_update_(self.G, self.G_cnt, delta, dcnt, float(p["eta"]), int(p["no_models"]), comm,
+                                   sigma, self.noise_gen)
+            return
+        self._log_poison_ratio("rfa" if method == C.AGGR_GEO_MED else "foolsgold", names, all_ns)
+        if method == C.AGGR_GEO_MED:
+            delta = W - self.G[None, :]
+            ns = torch.tensor(num_samples, dtype=torch.float64, device=self.device)
+            fn = getattr(be, "geometric_median", None) or agg.geometric_median
+            res = fn(delta, ns, [all_ns[s] for s in order], counts, maxiter=int(p["geom_median_maxiter"]), comm=comm)
+            agg.rfa_update_(self.G, res, float(p["eta"]), sigma, comm, self.noise_gen)
+            logger.info(f"[rfa agg] iters: {res.iters}, objective: {res.objective}, weight: {res.wv}")
+            wv, alphas = res.wv, res.distances
+        else:
+            feats_local = grad_sum[:, self.spec.fg_slice] if grad_sum is not None and grad_sum.shape[0] else \
+                torch.zeros(0, self.spec.fg_len, device=self.device)
+            feats = comm.all_gather_rows(feats_local.contiguous(), counts)
+            fmat = self.fg.features(names_in_order, feats)
+            wv_t, alpha_t = agg.foolsgold_weights(fmat)
+            logger.info(f"[foolsgold agg] wv: {wv_t.tolist()}")
+            self.fg.wv_history.append(wv_t.tolist())
+            lo = sum(counts[: self.rank])
+            wv_local = wv_t[lo: lo + counts[self.rank]].to(self.device)
+            gs = grad_sum if grad_sum is not None else torch.zeros(0, self.spec.Dp, device=self.device)
+            agg.foolsgold_update_(self.G, self.spec.Dp, gs, wv_local, len(names), float(p["eta"]), float(p["lr"]),
+                                  float(p["decay"]), comm)
+            wv, alphas = [float(v) for v in wv_t.tolist()], [float(v) for v in alpha_t.tolist()]
+        rep.agg_weights, rep.agg_alphas = wv, alphas
+        if self.is_main:
+            self.recorder.add_weight_result(names_in_order, wv, alphas)
+            for nm, w_, a_ in zip(names_in_order, wv, alphas):
+                self.metrics.weight_vis(epoch, w_, str(nm), nm in adversaries)
+                self.metrics.alpha_vis(epoch, a_, str(nm), nm in adversaries)
+
+    def _gather_num_samples(self, num_samples, counts, order, n) -> Dict[int, float]:
+        t = torch.tensor(num_samples, dtype=torch.float64, device=self.device).reshape(-1, 1)
+        allv = self.comm.all_gather_rows(t, counts).reshape(-1).tolist()
+        return {s: v for s, v in zip(order, allv)}
+
+    def _log_poison_ratio(self, tag, names, all_ns) -> None:
+        p = self.params
+        tot = sum(all_ns.values()) or 1.0
+        adv = sum(all_ns[s] for s, nm in enumerate(names) if nm in p["adversary_list"]) / tot
+        logger.info(f"[{tag} agg] training data poison_ratio: {adv}  data num: {[all_ns[s] for s in range(len(names))]}")
+        logger.info(f"[{tag} agg] considering poison per batch poison_fraction: "
+                    f"{adv * p['poisoning_per_batch'] / p['batch_size']}")
+
+    # ---------------------------------------------------------------------------------------- global eval
+    def _eval_global(self, split: str, trig: int) -> Tuple[float, float, int, int]:
+        loss, correct, n = self.backend.evaluate(self.G[None, :], split, trig)
+        c = int(correct[0])
+        return (float(loss[0]) / n if n else 0, 100.0 * c / n if n else 0, c, n)
+
+    def _global_eval(self, epoch: int, rep: RoundReport) -> None:
+        p, rec = self.params, self.recorder
+        tge = epoch + p["aggr_epoch_interval"] - 1
+        loss, acc, corr, n = self._eval_global("clean", 0)
+        logger.info("___Test {} poisoned: {}, epoch: {}: Average loss: {:.4f}, Accuracy: {}/{} ({:.4f}%)".format(
+            self.target_name, False, tge, loss, corr, n, acc))
+        rep.global_loss, rep.global_acc = loss, acc
+        if self.is_main:
+            rec.add_test("global", tge, loss, acc, corr, n)
+            rec.close_scale_row(acc)
+            self.metrics.test_vis(tge, acc, None, "global")
+        if not p["is_poison"]:
+            return
+        loss, acc_p, corr, n = self._eval_global("poison", 0)
+        logger.info("___Test {} poisoned: {}, epoch: {}: Average loss: {:.4f}, Accuracy: {}/{} ({:.4f}%)".format(
+            self.target_name, True, tge, loss, corr, n, acc_p))
+        rep.poison_loss, rep.poison_acc = loss, acc_p
+        if self.is_main:
+            rec.add_poison_test("global", tge, loss, acc_p, corr, n)
+            rec.add_trigger_test("global", "combine", "", tge, loss, acc_p, corr, n)
+            if p["vis_trigger_split_test"]:
+                self.metrics.trigger_agent_test_vis(epoch, acc_p, "global_combine")
+        tests = []
+        if p.is_centralized_attack:
+            if p["centralized_test_trigger"]:
+                tests = [(f"global_in_index_{j}_trigger", j + 1) for j in range(int(p["trigger_num"]))]
+        else:
+            tests = [(f"global_in_{a}_trigger", p.adversary_index(a) + 1) for a in p["adversary_list"]]
+        for tname, row in tests:
+            l_, a_, c_, n_ = self._eval_global("poison", row)
+            rep.trigger_acc[tname] = a_
+            if self.is_main:
+                rec.add_trigger_test("global", tname, "", epoch, l_, a_, c_, n_)
+                if p["vis_trigger_split_test"]:
+                    self.metrics.trigger_agent_test_vis(epoch, a_, tname)
