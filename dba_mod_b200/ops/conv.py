@@ -1,0 +1,31 @@
+"""Tensor-level wrapper of the tcgen05 implicit-GEMM convolution (csrc/conv_tc.cu)."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import native
+from .layout import Geom
+
+
+def conv_tc(x: torch.Tensor, wt: torch.Tensor, K: int, B: int, H: int, W: int, ksize: int, sub: int = 1,
+            relu: bool = False, res: Optional[torch.Tensor] = None, scale: Optional[torch.Tensor] = None,
+            shift: Optional[torch.Tensor] = None, stats: Optional[torch.Tensor] = None,
+            out: Optional[torch.Tensor] = None, x_shared: bool = False, debug_swap: int = 0) -> torch.Tensor:
+    """x planar bf16 [Kx, Cin/8, R, 8]; wt packed bf16 [K, taps, Cin/8, Cout, 8] -> planar bf16 [K, Cout/8, Ro, 8].
+
+    ``out`` must be a buffer whose halo rows are zero (they are never written).  ``stats`` [K, Cout, 2] fp32 is
+    accumulated into (caller zeroes it)."""
+    lib = native.load()
+    Cin, Cout = wt.shape[2] * 8, wt.shape[3]
+    assert x.dtype == torch.bfloat16 and wt.dtype == torch.bfloat16 and x.is_contiguous() and wt.is_contiguous()
+    assert x.shape[1] * 8 == Cin and x.shape[2] == Geom(B, H, W).rows, (x.shape, Cin, Geom(B, H, W).rows)
+    go = Geom(B, H // sub, W // sub)
+    if out is None:
+        out = torch.zeros(K, Cout // 8, go.rows, 8, dtype=torch.bfloat16, device=x.device)
+    assert out.shape == (K, Cout // 8, go.rows, 8) and out.is_contiguous()
+    native.check(lib.dba_conv_tc(native.ptr(x), native.ptr(wt), native.ptr(out), native.ptr(res), native.ptr(scale),
+                                 native.ptr(shift), native.ptr(stats), K, B, H, W, Cin, Cout, ksize, sub, int(relu),
+                                 int(x_shared), int(debug_swap), native.stream()))
+    return out

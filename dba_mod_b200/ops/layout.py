@@ -1,0 +1,84 @@
+"""Planar-8 / shared-halo activation layout and packed weight layouts used by the tensor-core kernels
+(csrc/conv_tc.cu has the rationale).  These torch implementations are the reference packers used by the tests and by
+cold paths (checkpoint import, oracle comparisons); the hot path packs with kernels.
+
+  activation  X[k][c8][row][8] bf16,  row(b,h,w) = lead + b*S + h*Wp + w,  Wp = W+1, S = (H+1)*Wp, lead = Wp+1
+  conv weight [k][tap][cin8][cout][8] bf16  (tap = kh*3+kw), i.e. K-major rows of 8 input channels per output channel
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+
+@dataclass(frozen=True)
+class Geom:
+    B: int
+    H: int
+    W: int
+
+    @property
+    def Wp(self) -> int:
+        return self.W + 1
+
+    @property
+    def S(self) -> int:
+        return (self.H + 1) * self.Wp
+
+    @property
+    def lead(self) -> int:
+        return self.Wp + 1
+
+    @property
+    def rows(self) -> int:
+        body = (self.B * self.S + 511) // 512 * 512
+        return self.lead + body + self.Wp + 2
+
+
+def to_planar(x: torch.Tensor, cpad: int = None) -> torch.Tensor:
+    """x [K, B, C, H, W] float -> bf16 [K, Cp/8, R, 8] (channels zero-padded to ``cpad``)."""
+    K, B, C, H, W = x.shape
+    Cp = cpad or ((C + 7) // 8 * 8)
+    g = Geom(B, H, W)
+    buf = torch.zeros(K, Cp // 8, g.rows, 8, dtype=torch.bfloat16, device=x.device)
+    body = torch.zeros(K, B, H + 1, g.Wp, Cp, dtype=torch.bfloat16, device=x.device)
+    body[:, :, :H, :W, :C] = x.permute(0, 1, 3, 4, 2).to(torch.bfloat16)
+    body = body.reshape(K, B * g.S, Cp // 8, 8).permute(0, 2, 1, 3)
+    buf[:, :, g.lead:g.lead + B * g.S] = body
+    return buf
+
+
+def from_planar(y: torch.Tensor, B: int, H: int, W: int, C: int = None) -> torch.Tensor:
+    """bf16 [K, Cp/8, R, 8] -> float [K, B, C, H, W]."""
+    K, C8 = y.shape[:2]
+    g = Geom(B, H, W)
+    body = y[:, :, g.lead:g.lead + B * g.S].permute(0, 2, 1, 3).reshape(K, B, H + 1, g.Wp, C8 * 8)
+    out = body[:, :, :H, :W].permute(0, 1, 4, 2, 3).float()
+    return out[:, :, :C] if C is not None else out
+
+
+def halo_is_zero(y: torch.Tensor, B: int, H: int, W: int) -> bool:
+    K, C8 = y.shape[:2]
+    g = Geom(B, H, W)
+    t = y.clone()
+    body = t[:, :, g.lead:g.lead + B * g.S].reshape(K, C8, B, H + 1, g.Wp, 8)
+    body[:, :, :, :H, :W] = 0
+    return bool((t == 0).all())
+
+
+def pack_conv_weight(w: torch.Tensor, cin_pad: int = None, cout_pad: int = None) -> torch.Tensor:
+    """w [K, Cout, Cin, kh, kw] -> bf16 [K, kh*kw, Cin_p/8, Cout_p, 8]."""
+    K, Co, Ci, kh, kw = w.shape
+    Cip = cin_pad or ((Ci + 15) // 16 * 16)
+    Cop = cout_pad or ((Co + 31) // 32 * 32)
+    wp = torch.zeros(K, Cop, Cip, kh, kw, dtype=torch.float32, device=w.device)
+    wp[:, :Co, :Ci] = w
+    t = wp.permute(0, 3, 4, 2, 1).reshape(K, kh * kw, Cip // 8, 8, Cop).permute(0, 1, 2, 4, 3)
+    return t.contiguous().to(torch.bfloat16)
+
+
+def pack_conv_weight_T(w: torch.Tensor) -> torch.Tensor:
+    """Weights for the input-gradient (dgrad) pass run as a forward convolution: roles of Cin/Cout swapped and the
+    3x3 taps flipped:  w'[k][ci][co][2-kh][2-kw] = w[k][co][ci][kh][kw]."""
+    return pack_conv_weight(w.transpose(1, 2).flip(-1, -2))

@@ -1,0 +1,81 @@
+"""ctypes binding of the in-tree native library ``libdba_b200.so`` (built by ``__graft_entry__.build()`` /
+``tools/build_native.py`` with nvcc for sm_100a).  Declarations mirror include/dba_b200.h.
+
+On a machine with a GPU a missing library is an error (no silent fallback to library kernels); on a CPU-only
+machine ``available()`` is simply False and the torch backend is used.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_double, c_float, c_int, c_longlong, c_ulonglong, c_void_p
+from typing import Optional
+
+import torch
+
+_LIB: Optional[ctypes.CDLL] = None
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdba_b200.so")
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def _sig(lib, name, argtypes, restype=c_int):
+    fn = getattr(lib, name)
+    fn.argtypes = argtypes
+    fn.restype = restype
+    return fn
+
+
+def load() -> ctypes.CDLL:
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not available():
+        raise NativeError(f"{_LIB_PATH} not found - run `python -c 'import __graft_entry__ as g; g.build()'`")
+    lib = ctypes.CDLL(_LIB_PATH)
+    P, I, L, F, D, U = c_void_p, c_int, c_longlong, c_float, c_double, c_ulonglong
+    _sig(lib, "dba_last_error", [], ctypes.c_char_p)
+    _sig(lib, "dba_launch_count", [], c_ulonglong)
+    _sig(lib, "dba_reset_launch_count", [], None)
+    _sig(lib, "dba_sgd_step", [P, L, P, P, P, L, P, P, I, L, F, F, P])
+    _sig(lib, "dba_scale_rows", [P, L, P, L, P, I, L, P])
+    _sig(lib, "dba_rows_sqdist_scratch_elems", [I], c_longlong)
+    _sig(lib, "dba_rows_sqdist", [P, L, P, L, P, I, L, P, I, P, L, P])
+    _sig(lib, "dba_fedavg_update", [P, P, L, I, L, F, F, U, I, P])
+    _sig(lib, "dba_weiszfeld", [P, L, P, I, L, P, I, F, D, P, P, P, P, P, P, P, L, P])
+    _sig(lib, "dba_foolsgold_weights", [P, L, P, P, L, I, L, I, P, P, P, P, P, P])
+    _sig(lib, "dba_foolsgold_apply", [P, P, L, P, I, L, F, F, F, P])
+    _sig(lib, "dba_conv_rows", [I, I, I], c_longlong)
+    _sig(lib, "dba_conv_tc", [P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
+    _LIB = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = load().dba_last_error().decode(errors="replace")
+        raise NativeError(f"native call failed (code {rc}): {msg}")
+
+
+def ptr(t: Optional[torch.Tensor]) -> c_void_p:
+    if t is None:
+        return c_void_p(0)
+    return c_void_p(t.data_ptr())
+
+
+def stream() -> c_void_p:
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def launch_count() -> int:
+    return int(load().dba_launch_count()) if _LIB is not None or available() else 0
