@@ -57,7 +57,13 @@ def _install_stubs():
         except Exception:  # noqa: BLE001
             mpl = types.ModuleType("matplotlib")
             plt = types.ModuleType("matplotlib.pyplot")
-            plt.__getattr__ = lambda name: (lambda *a, **k: None)  # type: ignore[attr-defined]
+
+            def _plt_getattr(name):
+                if name.startswith("__"):
+                    raise AttributeError(name)
+                return lambda *a, **k: None
+
+            plt.__getattr__ = _plt_getattr  # type: ignore[attr-defined]
             mpl.pyplot = plt
             sys.modules["matplotlib"] = mpl
             sys.modules["matplotlib.pyplot"] = plt

@@ -1,0 +1,277 @@
+// Training-mode BatchNorm on planar-8 activations for K client replicas at once (K3/K4 in SURVEY §2.4; reference
+// nn.BatchNorm2d + F.relu + residual add in models/resnet_cifar.py:20-35).
+//
+//   forward : the per-channel sum / sum-of-squares come out of the convolution epilogue (conv_tc.cu); bn_apply turns
+//             them into mean / rstd (saved for backward), updates running_mean / running_var (momentum 0.1, unbiased
+//             variance, only for clients active in this step), and writes relu(y*scale + shift (+ residual)).
+//   backward: bn_bwd_reduce -> per-channel sums of g' and g'*xhat (g' = upstream gradient masked by the ReLU);
+//             bn_bwd_apply  -> dy = gamma*rstd*(g' - mean(g') - xhat*mean(g'*xhat)), d_gamma, d_beta; can scatter dy
+//             onto the even positions of the 2x finer grid (input-gradient / weight-gradient of stride-2 convolutions
+//             are computed at full resolution) and can emit g' for the identity-shortcut path.
+// Ragged batches: samples b >= nvalid[k] are padding; they are excluded from the statistics (count = nvalid*H*W),
+// produce zero activations and zero gradients.  Halo rows of every buffer are never written.
+#include "common.cuh"
+
+using namespace dba;
+
+namespace {
+
+struct BnArgs {
+  const __nv_bfloat16* y;      // raw conv output      [K][C/8][R][8]
+  const __nv_bfloat16* res;    // residual (fwd) or null
+  __nv_bfloat16* out;          // fwd: activation;  bwd: dy
+  const __nv_bfloat16* g;      // bwd: upstream gradient
+  const __nv_bfloat16* act;    // bwd: post-ReLU output of this BN (mask) or null
+  __nv_bfloat16* gmask;        // bwd: optional copy of g' (same geometry as g)
+  float* stats;                // fwd: [K][ld_stats] (sum, sumsq) pairs;  bwd: (sum g', sum g'*xhat) pairs
+  float* saved;                // [K][ld_saved] (mean, rstd) pairs
+  float* Wflat;                // [K][ldw] state rows (gamma, beta, running stats)
+  float* Gflat;                // [K][ldg] gradient rows (bwd) or null
+  const int* nvalid;           // [K]
+  const unsigned char* active; // [K] or null
+  long long ld_stats, ld_saved, ldw, ldg, R, Rup;
+  int stats_off, saved_off, g_off, b_off, rm_off, rv_off;
+  int K, C, B, H, W, relu, up;
+  float momentum, eps;
+};
+
+__device__ __forceinline__ void unpack8(const uint4 u, float (&f)[8]) {
+  f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
+  f[4] = bf16lo(u.z); f[5] = bf16hi(u.z); f[6] = bf16lo(u.w); f[7] = bf16hi(u.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 p;
+  p.x = pack_bf16x2(f[0], f[1]); p.y = pack_bf16x2(f[2], f[3]);
+  p.z = pack_bf16x2(f[4], f[5]); p.w = pack_bf16x2(f[6], f[7]);
+  return p;
+}
+
+// grid (row blocks, C/8, K), 256 threads; each thread walks rows of one 8-channel plane.
+__global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
+  __shared__ float s_scale[8], s_shift[8];
+  const int chunk = blockIdx.y, k = blockIdx.z;
+  const int nv = a.nvalid[k];
+  const float n = (float)nv * (float)(a.H * a.W);
+  if (threadIdx.x < 8) {
+    const int c = chunk * 8 + threadIdx.x;
+    float* w = a.Wflat + (long long)k * a.ldw;
+    const float s1 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c];
+    const float s2 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
+    const float mean = n > 0.f ? s1 / n : 0.f;
+    const float var = n > 0.f ? fmaxf(s2 / n - mean * mean, 0.f) : 0.f;
+    const float rstd = rsqrtf(var + a.eps);
+    const float sc = w[a.g_off + c] * rstd;
+    s_scale[threadIdx.x] = sc;
+    s_shift[threadIdx.x] = w[a.b_off + c] - mean * sc;
+    if (blockIdx.x == 0) {
+      a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c] = mean;
+      a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c + 1] = rstd;
+      if (nv > 0 && (!a.active || a.active[k])) {
+        const float unb = n > 1.f ? var * n / (n - 1.f) : var;
+        w[a.rm_off + c] = (1.f - a.momentum) * w[a.rm_off + c] + a.momentum * mean;
+        w[a.rv_off + c] = (1.f - a.momentum) * w[a.rv_off + c] + a.momentum * unb;
+      }
+    }
+  }
+  __syncthreads();
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
+  const int total = a.B * S;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+    if (h >= a.H || w >= a.W) continue;
+    const long long off = (plane + lead + q) * 8;
+    float o[8];
+    if (b < nv) {
+      float v[8];
+      unpack8(*reinterpret_cast<const uint4*>(a.y + off), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = v[j] * s_scale[j] + s_shift[j];
+      if (a.res) {
+        float r[8];
+        unpack8(*reinterpret_cast<const uint4*>(a.res + off), r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += r[j];
+      }
+      if (a.relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = 0.f;
+    }
+    *reinterpret_cast<uint4*>(a.out + off) = pack8(o);
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
+  __shared__ float red[2][8][8];
+  const int chunk = blockIdx.y, k = blockIdx.z;
+  const int nv = a.nvalid[k];
+  float mean[8], rstd[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mean[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * 8 + j)];
+    rstd[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * 8 + j) + 1];
+  }
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
+  const int total = min(a.B, nv) * S;
+  float sg[8], sgx[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sg[j] = sgx[j] = 0.f;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+    if (h >= a.H || w >= a.W) continue;
+    const long long off = (plane + lead + q) * 8;
+    float g[8], y[8];
+    unpack8(*reinterpret_cast<const uint4*>(a.g + off), g);
+    unpack8(*reinterpret_cast<const uint4*>(a.y + off), y);
+    if (a.act) {
+      float o[8];
+      unpack8(*reinterpret_cast<const uint4*>(a.act + off), o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sg[j] += g[j];
+      sgx[j] += g[j] * (y[j] - mean[j]) * rstd[j];
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sg[j] = warp_sum(sg[j]);
+    sgx[j] = warp_sum(sgx[j]);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { red[0][warp][j] = sg[j]; red[1][warp][j] = sgx[j]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 16) {
+    const int which = threadIdx.x >> 3, j = threadIdx.x & 7;
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += red[which][w][j];
+    if (t != 0.f) atomicAdd(&a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * (chunk * 8 + j) + which], t);
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
+  __shared__ float s_sc[8], s_mg[8], s_mgx[8], s_mean[8], s_rstd[8];
+  const int chunk = blockIdx.y, k = blockIdx.z;
+  const int nv = a.nvalid[k];
+  const float n = (float)nv * (float)(a.H * a.W);
+  if (threadIdx.x < 8) {
+    const int c = chunk * 8 + threadIdx.x;
+    const float sg = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c];
+    const float sgx = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
+    const float mean = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c];
+    const float rstd = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c + 1];
+    const float gamma = a.Wflat[(long long)k * a.ldw + a.g_off + c];
+    s_sc[threadIdx.x] = gamma * rstd;
+    s_mg[threadIdx.x] = n > 0.f ? sg / n : 0.f;
+    s_mgx[threadIdx.x] = n > 0.f ? sgx / n : 0.f;
+    s_mean[threadIdx.x] = mean;
+    s_rstd[threadIdx.x] = rstd;
+    if (blockIdx.x == 0 && a.Gflat) {
+      a.Gflat[(long long)k * a.ldg + a.g_off + c] = sgx;   // d gamma
+      a.Gflat[(long long)k * a.ldg + a.b_off + c] = sg;    // d beta
+    }
+  }
+  __syncthreads();
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const int Wpu = 2 * a.W + 1, Su = (2 * a.H + 1) * Wpu, leadu = Wpu + 1;
+  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
+  const long long plane_up = ((long long)k * (a.C >> 3) + chunk) * a.Rup;
+  const int total = a.B * S;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+    if (h >= a.H || w >= a.W) continue;
+    const long long off = (plane + lead + q) * 8;
+    float d[8], gm[8];
+    if (b < nv) {
+      float g[8], y[8];
+      unpack8(*reinterpret_cast<const uint4*>(a.g + off), g);
+      unpack8(*reinterpret_cast<const uint4*>(a.y + off), y);
+      if (a.act) {
+        float o[8];
+        unpack8(*reinterpret_cast<const uint4*>(a.act + off), o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (y[j] - s_mean[j]) * s_rstd[j];
+        gm[j] = g[j];
+        d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = gm[j] = 0.f;
+    }
+    if (a.gmask) *reinterpret_cast<uint4*>(a.gmask + off) = pack8(gm);
+    long long doff = off;
+    if (a.up) doff = (plane_up + leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w) * 8;
+    *reinterpret_cast<uint4*>(a.out + doff) = pack8(d);
+  }
+}
+
+inline dim3 bn_grid(int B, int H, int W, int C, int K) {
+  const int total = B * (H + 1) * (W + 1);
+  int rb = (total + 1023) / 1024;
+  if (rb < 1) rb = 1;
+  if (rb > 64) rb = 64;
+  return dim3(rb, C / 8, K);
+}
+
+}  // namespace
+
+extern "C" {
+
+// out = relu?( (y - mean)*rstd*gamma + beta (+ res) ); also saves (mean, rstd) and updates the running statistics.
+// stats: pairs (sum, sumsq) at stats[k*ld_stats + stats_off + 2c]; saved likewise.  Offsets g/b/rm/rv index Wflat rows.
+int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long long ld_stats, int stats_off,
+                 float* saved, long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off,
+                 int rm_off, int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H,
+                 int W, long long R, int relu, float momentum, float eps, void* stream) {
+  DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_bn_apply: K=%d C=%d B=%d", K, C, B);
+  BnArgs a{};
+  a.y = (const __nv_bfloat16*)y; a.res = (const __nv_bfloat16*)res; a.out = (__nv_bfloat16*)out;
+  a.stats = stats; a.saved = saved; a.Wflat = Wflat; a.nvalid = nvalid; a.active = active;
+  a.ld_stats = ld_stats; a.ld_saved = ld_saved; a.ldw = ldw; a.R = R;
+  a.stats_off = stats_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off; a.rm_off = rm_off; a.rv_off = rv_off;
+  a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.relu = relu; a.momentum = momentum; a.eps = eps;
+  bn_apply_kernel<<<bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// Backward of the above.  g: upstream gradient (geometry of y); act: this BN's post-ReLU output (null = no ReLU);
+// dy: output, written on the (2H, 2W) grid at even positions when up != 0 (Rup = rows of that grid);
+// gmask: optional copy of the ReLU-masked upstream gradient; sums: scratch pairs [K][ld_sums] zeroed by the caller;
+// Gflat: d_gamma / d_beta are stored at g_off / b_off of the gradient rows.
+int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, void* gmask, float* sums,
+                    long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
+                    long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
+                    int B, int H, int W, long long R, int up, long long Rup, void* stream) {
+  DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_bn_backward: K=%d C=%d B=%d", K, C, B);
+  BnArgs a{};
+  a.g = (const __nv_bfloat16*)g; a.y = (const __nv_bfloat16*)y; a.act = (const __nv_bfloat16*)act;
+  a.out = (__nv_bfloat16*)dy; a.gmask = (__nv_bfloat16*)gmask; a.stats = sums; a.saved = saved; a.Wflat = Wflat;
+  a.Gflat = Gflat; a.nvalid = nvalid;
+  a.ld_stats = ld_sums; a.ld_saved = ld_saved; a.ldw = ldw; a.ldg = ldg; a.R = R; a.Rup = Rup;
+  a.stats_off = sums_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off;
+  a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.up = up;
+  const dim3 grid = bn_grid(B, H, W, C, K);
+  bn_bwd_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  bn_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(2);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+}  // extern "C"

@@ -35,7 +35,6 @@ namespace {
 
 constexpr int kTileM = 128;
 constexpr int kThreads = 192;
-constexpr int kMaxTaps = 9;
 
 struct ConvArgs {
   const __nv_bfloat16* X;      // [Kx][Cin/8][R][8]
@@ -48,6 +47,9 @@ struct ConvArgs {
   long long x_client_stride;   // elements; 0 = all clients read the same input (shared evaluation batch)
   long long x_plane_stride;    // elements between channel-chunk planes (= R*8)
   long long y_client_stride, y_plane_stride;
+  long long w_client_stride;   // elements between the clients' packed weight sets
+  long long ss_stride;         // floats between the clients' scale / shift rows
+  long long stats_stride;      // floats between the clients' statistics rows
   int K, Cin, Cout, taps;      // taps = 1 (1x1) or 9 (3x3, pad 1)
   int H, W, Wp, S, lead, B;    // input (= compute) geometry
   int T;                       // row tiles per pass
@@ -134,7 +136,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
         const int k = item / (nnb * a.num_pass);
         const long long row0 = (long long)a.lead + (long long)pass * a.T * kTileM - a.halo;
         const __nv_bfloat16* xk = a.X + (long long)k * a.x_client_stride;
-        const __nv_bfloat16* wk = a.Wt + (long long)k * a.taps * (long long)a.Cin * a.Cout;
+        const __nv_bfloat16* wk = a.Wt + (long long)k * a.w_client_stride;
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = pa.stage(a.SA);
           mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
@@ -223,8 +225,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       }
       mbar_wait(&acc_full[as], pacc.phase(a.NS));
       tc_fence_after();
-      const float* sc = a.scale ? a.scale + (long long)k * a.Cout + nb * a.NB : nullptr;
-      const float* sh = a.shift ? a.shift + (long long)k * a.Cout + nb * a.NB : nullptr;
+      const float* sc = a.scale ? a.scale + (long long)k * a.ss_stride + nb * a.NB : nullptr;
+      const float* sh = a.shift ? a.shift + (long long)k * a.ss_stride + nb * a.NB : nullptr;
       __nv_bfloat16* yk = a.Y + (long long)k * a.y_client_stride;
       const __nv_bfloat16* rk = a.Res ? a.Res + (long long)k * a.y_client_stride : nullptr;
       for (int t = 0; t < a.T; ++t) {
@@ -310,7 +312,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       ++pacc.it;
       if (a.stats) {
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        float* gs = a.stats + ((long long)k * a.Cout + nb * a.NB) * 2;
+        float* gs = a.stats + (long long)k * a.stats_stride + (long long)nb * a.NB * 2;
         for (int i = threadIdx.x - 64; i < 2 * a.NB; i += 128) {
           const float v = stat_s[i];
           if (v != 0.f) atomicAdd(gs + i, v);
@@ -344,9 +346,11 @@ long long dba_conv_rows(int B, int H, int W) {
 // Wt: [K][taps][Cin/8][Cout][8]; Y (and Res): [K][Cout/8][Ro][8], Ro = dba_conv_rows(B,Ho,Wo), Ho = H/sub.
 // scale/shift (nullable together): per (client, out-channel) affine = folded BatchNorm.  stats (nullable): [K][Cout][2]
 // accumulated (+=) with sum / sum-of-squares of the stored outputs.  x_shared != 0: every client reads client 0's X.
-int dba_conv_tc(const void* X, const void* Wt, void* Y, const void* Res, const float* scale, const float* shift,
-                float* stats, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub, int relu,
-                int x_shared, int debug_swap, void* stream) {
+int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                        const float* scale, const float* shift, long long ss_stride, float* stats,
+                        long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                        int relu, int x_shared, void* stream) {
+  const int debug_swap = 0;
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
   DBA_REQUIRE(ksize == 1 || ksize == 3, "dba_conv_tc: ksize must be 1 or 3, got %d", ksize);
   DBA_REQUIRE(Cin % 16 == 0 && Cout % 16 == 0, "dba_conv_tc: Cin (%d) and Cout (%d) must be multiples of 16", Cin, Cout);
@@ -364,6 +368,9 @@ int dba_conv_tc(const void* X, const void* Wt, void* Y, const void* Res, const f
   a.x_client_stride = x_shared ? 0 : (long long)(Cin / 8) * R * 8;
   a.y_plane_stride = Ro * 8;
   a.y_client_stride = (long long)(Cout / 8) * Ro * 8;
+  a.w_client_stride = w_client_stride;
+  a.ss_stride = ss_stride;
+  a.stats_stride = stats_stride;
   a.NB = Cout <= 256 ? Cout : 256;
   DBA_REQUIRE(Cout % a.NB == 0, "dba_conv_tc: Cout=%d not a multiple of the n-block %d", Cout, a.NB);
   a.KB = Cin >= 64 ? 64 : Cin;
@@ -406,6 +413,15 @@ int dba_conv_tc(const void* X, const void* Wt, void* Y, const void* Res, const f
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
+}
+
+// Dense-stride convenience form: Wt [K][taps][Cin/8][Cout][8], scale/shift [K][Cout], stats [K][Cout][2].
+int dba_conv_tc(const void* X, const void* Wt, void* Y, const void* Res, const float* scale, const float* shift,
+                float* stats, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub, int relu,
+                int x_shared, int reserved, void* stream) {
+  (void)reserved;
+  return dba_conv_tc_strided(X, Wt, (long long)ksize * ksize * Cin * Cout, Y, Res, scale, shift, Cout, stats,
+                             2LL * Cout, K, B, H, W, Cin, Cout, ksize, sub, relu, x_shared, stream);
 }
 
 }  // extern "C"

@@ -1,0 +1,318 @@
+// Network plumbing kernels around the tensor-core convolution: weight packing, BatchNorm folding for evaluation,
+// the fused input stage (gather + /255 + trigger stamping + flip + stem im2col) and the fused classifier head
+// (avg-pool + linear + cross-entropy + metrics, forward and backward).
+//
+// Reference ops: image batches + triggers image_helper.py:289-350 (K12); F.avg_pool2d / Linear / cross_entropy /
+// argmax accuracy resnet_cifar.py:94-96, image_train.py:85,104-105, test.py:20-24 (K5, K6, K8).
+#include "common.cuh"
+
+using namespace dba;
+
+// ------------------------------------------------------------------------------------------- weight packing
+// Table entry per convolution (all ints): [0] src offset in the flat parameter vector (weights stored
+// [Cout][taps][Cin]), [1] Cout, [2] Cin, [3] taps, [4] dst offset (elements) of the forward pack
+// [taps'][CinP/8][CoutP][8], [5] dst offset of the transposed pack [taps][CoutP/8][CinP][8] with flipped taps (-1 =
+// none), [6] CinP, [7] CoutP, [8] fold: 1 = treat (taps, Cin) as one K axis of length taps*Cin padded to CinP (stem).
+#define PACK_FIELDS 9
+__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ W, long long ldw,
+                                                           const int* __restrict__ table,
+                                                           __nv_bfloat16* __restrict__ dst, long long dst_client_stride) {
+  const int* e = table + blockIdx.y * PACK_FIELDS;
+  const int k = blockIdx.z;
+  const int Cout = e[1], Cin = e[2], taps = e[3], CinP = e[6], CoutP = e[7], fold = e[8];
+  const float* src = W + (long long)k * ldw + e[0];
+  __nv_bfloat16* d = dst + (long long)k * dst_client_stride;
+  const int ptaps = fold ? 1 : taps;             // taps as seen by the kernel
+  const int kreal = fold ? taps * Cin : Cin;     // real reduction length per packed tap
+  // forward pack: one thread per (tap, ci8, co) 16-byte group
+  const long long nf = (long long)ptaps * (CinP >> 3) * CoutP;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nf; i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % (CinP >> 3));
+    const int co = (int)((i / (CinP >> 3)) % CoutP);
+    const int tap = (int)(i / ((long long)(CinP >> 3) * CoutP));
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int ci = c8 * 8 + j;
+      v[j] = (co < Cout && ci < kreal) ? src[((long long)co * ptaps + tap) * kreal + ci] : 0.f;
+    }
+    uint4 pk;
+    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(d + e[4] + (((long long)tap * (CinP >> 3) + c8) * CoutP + co) * 8) = pk;
+  }
+  if (e[5] < 0 || fold) return;
+  // transposed pack for the input-gradient convolution: out channels become the reduction axis, taps are flipped
+  const long long nt = (long long)taps * (CoutP >> 3) * CinP;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nt; i += (long long)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % CinP);
+    const int o8 = (int)((i / CinP) % (CoutP >> 3));
+    const int tap = (int)(i / ((long long)CinP * (CoutP >> 3)));
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int co = o8 * 8 + j;
+      v[j] = (co < Cout && ci < Cin) ? src[((long long)co * taps + tap) * Cin + ci] : 0.f;
+    }
+    uint4 pk;
+    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+    const int ftap = taps - 1 - tap;
+    *reinterpret_cast<uint4*>(d + e[5] + (((long long)ftap * (CoutP >> 3) + o8) * CinP + ci) * 8) = pk;
+  }
+}
+extern "C" int dba_pack_weights(const float* W, long long ldw, const int* table, int n_layers, int K, void* dst,
+                                long long dst_client_stride, void* stream) {
+  DBA_REQUIRE(n_layers > 0 && K > 0, "dba_pack_weights: n_layers=%d K=%d", n_layers, K);
+  dim3 g(32, n_layers, K);
+  pack_weights_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, (__nv_bfloat16*)dst, dst_client_stride);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// ------------------------------------------------------------------------------- BatchNorm folding (evaluation)
+// Table entry per BN layer: [0] gamma offset, [1] beta offset, [2] running-mean offset, [3] running-var offset (all
+// into the flat state row), [4] C, [5] dst offset into scale/shift rows.  scale = g/sqrt(rv+eps), shift = b - rm*scale.
+#define FOLD_FIELDS 6
+__global__ void bn_fold_kernel(const float* __restrict__ W, long long ldw, const int* __restrict__ table,
+                               float* __restrict__ scale, float* __restrict__ shift, long long ld_out, float eps) {
+  const int* e = table + blockIdx.y * FOLD_FIELDS;
+  const int k = blockIdx.z;
+  const float* w = W + (long long)k * ldw;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < e[4]; c += gridDim.x * blockDim.x) {
+    const float s = w[e[0] + c] * rsqrtf(w[e[3] + c] + eps);
+    scale[(long long)k * ld_out + e[5] + c] = s;
+    shift[(long long)k * ld_out + e[5] + c] = w[e[1] + c] - w[e[2] + c] * s;
+  }
+}
+extern "C" int dba_bn_fold(const float* W, long long ldw, const int* table, int n_layers, int K, float* scale,
+                           float* shift, long long ld_out, float eps, void* stream) {
+  DBA_REQUIRE(n_layers > 0 && K > 0, "dba_bn_fold: n_layers=%d K=%d", n_layers, K);
+  dim3 g(2, n_layers, K);
+  bn_fold_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, scale, shift, ld_out, eps);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ input stage
+// Builds the stem convolution's A operand straight from the uint8 dataset: for every (client, sample, output pixel)
+// the ks x ks x C input patch (zero padded, /255, trigger pixels forced to 1.0 for poisoned samples, optional
+// horizontal flip of the source image) is written as KP = roundup(ks*ks*C, 16) bf16 values in planar-8 layout, so the
+// stem becomes a 1x1 convolution on the tensor cores.  Also emits the (possibly swapped) labels.
+// idx [K][B] dataset indices (-1 = padding sample -> zero rows, label -1).  Samples b < poison_n[k] are poisoned with
+// trigger mask row trig_row[k].  With shared != 0 there is one input set (K = 1 here) used by all models.
+struct InputArgs {
+  const unsigned char* data;     // [N][Hi][Wi][C]
+  const long long* labels;       // [N]
+  const long long* idx;          // [K][ld_idx] (+ t*B offset applied by the caller through idx pointer)
+  long long ld_idx;
+  const unsigned char* trig;     // [T][Hi][Wi]
+  const long long* trig_row;     // [K]
+  const long long* poison_n;     // [K]
+  const unsigned char* flip;     // [K][ld_idx] or null
+  __nv_bfloat16* out;            // [K][KP/8][R][8]
+  int* labels_out;               // [K][B]
+  int K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo, KP, label_swap;
+  long long R;
+};
+__global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
+  const int Wp = a.Wo + 1, S = (a.Ho + 1) * Wp, lead = Wp + 1;
+  const int nchunk = a.KP >> 3;
+  const long long total = (long long)a.K * a.B * a.Ho * a.Wo * nchunk;
+  const int kreal = a.ks * a.ks * a.C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    // pixel index fastest -> 16-byte stores of consecutive threads are contiguous inside one chunk plane
+    const int wo = (int)(i % a.Wo);
+    const int ho = (int)((i / a.Wo) % a.Ho);
+    const int b = (int)((i / ((long long)a.Wo * a.Ho)) % a.B);
+    const int chunk = (int)((i / ((long long)a.Wo * a.Ho * a.B)) % nchunk);
+    const int k = (int)(i / ((long long)a.Wo * a.Ho * a.B * nchunk));
+    const long long id = a.idx[(long long)k * a.ld_idx + b];
+    const bool poisoned = id >= 0 && b < a.poison_n[k];
+    const bool flip = a.flip && a.flip[(long long)k * a.ld_idx + b];
+    const unsigned char* img = a.data + (id < 0 ? 0 : id) * (long long)a.Hi * a.Wi * a.C;
+    const unsigned char* tm = a.trig + a.trig_row[k] * (long long)a.Hi * a.Wi;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int e = chunk * 8 + j;
+      float x = 0.f;
+      if (id >= 0 && e < kreal) {
+        const int tap = e / a.C, c = e - tap * a.C;
+        const int kh = tap / a.ks, kw = tap - kh * a.ks;
+        const int hi = ho * a.stride + kh - a.pad, wi = wo * a.stride + kw - a.pad;
+        if (hi >= 0 && hi < a.Hi && wi >= 0 && wi < a.Wi) {
+          if (poisoned && tm[hi * a.Wi + wi]) x = 1.f;
+          else x = (float)img[((long long)hi * a.Wi + (flip ? a.Wi - 1 - wi : wi)) * a.C + c] * (1.f / 255.f);
+        }
+      }
+      v[j] = x;
+    }
+    uint4 pk;
+    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+    const long long row = lead + (long long)b * S + ho * Wp + wo;
+    *reinterpret_cast<uint4*>(a.out + (((long long)k * nchunk + chunk) * a.R + row) * 8) = pk;
+    if (a.labels_out && chunk == 0 && ho == 0 && wo == 0)
+      a.labels_out[k * a.B + b] = id < 0 ? -1 : (poisoned ? a.label_swap : (int)a.labels[id]);
+  }
+}
+extern "C" int dba_input_stage_image(const void* data, const long long* labels, const long long* idx, long long ld_idx,
+                                     const void* trig, const long long* trig_row, const long long* poison_n,
+                                     const void* flip, void* out, int* labels_out, int K, int B, int Hi, int Wi, int C,
+                                     int ks, int stride, int pad, int Ho, int Wo, int KP, int label_swap, long long R,
+                                     void* stream) {
+  DBA_REQUIRE(K > 0 && B > 0 && KP % 16 == 0 && KP >= ks * ks * C, "dba_input_stage_image: K=%d B=%d KP=%d", K, B, KP);
+  InputArgs a{(const unsigned char*)data, labels, idx, ld_idx, (const unsigned char*)trig, trig_row, poison_n,
+              (const unsigned char*)flip, (__nv_bfloat16*)out, labels_out, K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo,
+              KP, label_swap, R};
+  const long long total = (long long)K * B * Ho * Wo * (KP / 8);
+  long long g = (total + 255) / 256;
+  if (g > kNumSMs * 16) g = kNumSMs * 16;
+  input_stage_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// ------------------------------------------------------------------------------------------- classifier head
+// One warp per (client, sample): global average pool over the HxW interior rows of the planar activation, linear
+// layer (fp32 master weights straight from the flat slab), softmax cross-entropy, argmax -> device-side metric
+// accumulators (no host sync per batch).  In training mode also the backward pass of all three: gradient of the
+// activation (planar bf16, scaled by 1/(n_valid*H*W)), and fp32 atomics into the flat gradient slab for the linear
+// weight / bias.  Metric slots: metrics_f[k][slot] += loss, metrics_i[k][slot][0] += correct, [1] += count.
+struct HeadArgs {
+  const __nv_bfloat16* act;  // [K][C/8][R][8]
+  const float* Wflat;        // [K][ldw]
+  float* Gflat;              // [K][ldg] or null (evaluation)
+  __nv_bfloat16* dact;       // [K][C/8][R][8] or null
+  const int* labels;         // [Kl][B]   (Kl = 1 when labels are shared by all models)
+  const int* nvalid;         // [K] or null (=> every sample with label >= 0 counts, loss is a SUM)
+  const long long* slot;     // [K] metric column (internal epoch) or null -> column 0
+  float* metrics_f;          // [K][ld_m]
+  int* metrics_i;            // [K][ld_m][2]
+  unsigned char* nan_flag;   // [K] or null
+  long long ldw, ldg, R;
+  int w_off, b_off, K, B, C, H, W, ncls, ld_m, shared_labels;
+};
+template <int MAXC, int MAXCLS>
+__global__ void __launch_bounds__(256) head_kernel(const HeadArgs a) {
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp_global >= a.K * a.B) return;
+  const int k = warp_global / a.B, b = warp_global - k * a.B;
+  const int label = a.labels[(a.shared_labels ? 0 : k) * a.B + b];
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const long long plane = a.R * 8;
+  const __nv_bfloat16* act = a.act + (long long)k * (a.C >> 3) * plane;
+  constexpr int PER = MAXC / 32;
+  float pooled[PER];
+  const float inv_hw = 1.f / (float)(a.H * a.W);
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int c = lane + 32 * i;
+    float s = 0.f;
+    if (c < a.C && label >= 0) {
+      const __nv_bfloat16* p = act + (long long)(c >> 3) * plane + (c & 7);
+      for (int h = 0; h < a.H; ++h)
+        for (int w = 0; w < a.W; ++w) s += __bfloat162float(p[((long long)lead + (long long)b * S + h * Wp + w) * 8]);
+    }
+    pooled[i] = s * inv_hw;
+  }
+  if (label < 0) {            // padding sample: contributes nothing, but its gradient rows must be zero
+    if (a.dact) {
+      __nv_bfloat16* d = a.dact + (long long)k * (a.C >> 3) * plane;
+      for (int i = 0; i < PER; ++i) {
+        const int c = lane + 32 * i;
+        if (c < a.C)
+          for (int h = 0; h < a.H; ++h)
+            for (int w = 0; w < a.W; ++w)
+              d[(long long)(c >> 3) * plane + ((long long)lead + (long long)b * S + h * Wp + w) * 8 + (c & 7)] =
+                  __float2bfloat16(0.f);
+      }
+    }
+    return;
+  }
+  const float* Wl = a.Wflat + (long long)k * a.ldw + a.w_off;
+  const float* bl = a.Wflat + (long long)k * a.ldw + a.b_off;
+  float logit[MAXCLS];           // every lane ends up holding all logits
+  float mx = -INFINITY;
+  int arg = 0;
+  for (int j = 0; j < a.ncls; ++j) {
+    float part = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int c = lane + 32 * i;
+      if (c < a.C) part += Wl[(long long)j * a.C + c] * pooled[i];
+    }
+    part = warp_sum(part) + bl[j];
+    logit[j] = part;
+    if (part > mx) { mx = part; arg = j; }
+  }
+  float se = 0.f;
+  for (int j = 0; j < a.ncls; ++j) se += __expf(logit[j] - mx);
+  const float lse = mx + __logf(se);
+  const float loss = lse - logit[label];
+  const int slot = a.slot ? (int)a.slot[k] : 0;
+  const bool finite = isfinite(lse);
+  if (lane == 0) {
+    const float scale = a.nvalid ? 1.f / (float)max(a.nvalid[k], 1) : 1.f;   // training logs the batch-MEAN loss (Q6)
+    atomicAdd(&a.metrics_f[(long long)k * a.ld_m + slot], loss * scale);
+    atomicAdd(&a.metrics_i[((long long)k * a.ld_m + slot) * 2], arg == label ? 1 : 0);
+    atomicAdd(&a.metrics_i[((long long)k * a.ld_m + slot) * 2 + 1], 1);
+    if (a.nan_flag && !finite) a.nan_flag[k] = 1;
+  }
+  if (!a.Gflat) return;
+  // ---- backward
+  const float inv_n = 1.f / (float)max(a.nvalid ? a.nvalid[k] : 1, 1);
+  float* Gw = a.Gflat + (long long)k * a.ldg + a.w_off;
+  float* Gb = a.Gflat + (long long)k * a.ldg + a.b_off;
+  float dpooled[PER];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) dpooled[i] = 0.f;
+  for (int j = 0; j < a.ncls; ++j) {
+    const float dl = (__expf(logit[j] - lse) - (j == label ? 1.f : 0.f)) * inv_n;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int c = lane + 32 * i;
+      if (c < a.C) {
+        dpooled[i] += dl * Wl[(long long)j * a.C + c];
+        atomicAdd(&Gw[(long long)j * a.C + c], dl * pooled[i]);
+      }
+    }
+    if (lane == 0) atomicAdd(&Gb[j], dl);
+  }
+  if (a.dact) {
+    __nv_bfloat16* d = a.dact + (long long)k * (a.C >> 3) * plane;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int c = lane + 32 * i;
+      if (c < a.C) {
+        const __nv_bfloat16 g = __float2bfloat16(dpooled[i] * inv_hw);
+        for (int h = 0; h < a.H; ++h)
+          for (int w = 0; w < a.W; ++w)
+            d[(long long)(c >> 3) * plane + ((long long)lead + (long long)b * S + h * Wp + w) * 8 + (c & 7)] = g;
+      }
+    }
+  }
+}
+extern "C" int dba_head(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat,
+                        long long ldg, void* dact, const int* labels, int shared_labels, const int* nvalid,
+                        const long long* slot, float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag,
+                        int K, int B, int C, int H, int W, int ncls, long long R, void* stream) {
+  DBA_REQUIRE(K > 0 && B > 0 && C <= 512 && ncls <= 200, "dba_head: K=%d B=%d C=%d ncls=%d", K, B, C, ncls);
+  HeadArgs a{(const __nv_bfloat16*)act, Wflat, Gflat, (__nv_bfloat16*)dact, labels, nvalid, slot, metrics_f, metrics_i,
+             nan_flag, ldw, ldg, R, w_off, b_off, K, B, C, H, W, ncls, ld_m, shared_labels};
+  const long long warps = (long long)K * B;
+  const int blocks = (int)((warps * 32 + 255) / 256);
+  if (C <= 256 && ncls <= 16)
+    head_kernel<256, 16><<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  else
+    head_kernel<512, 200><<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}

@@ -1,0 +1,244 @@
+// Convolution weight gradient on tcgen05 tensor cores for K client replicas (K2 "wgrad" in SURVEY §2.4; the autograd
+// of nn.Conv2d that the reference gets from cuDNN, image_train.py:91,209).
+//
+//   dW[k][co][tap][ci] += sum_rows  dY[k][co][row] * X[k][ci][row + shift(tap)]
+//
+// Both operands are consumed in the SAME planar-8 / shared-halo layout the forward pass uses: a [c8][row][8] block
+// is the SWIZZLE_NONE canonical *MN-major* UMMA operand (8 consecutive channels per 16 bytes, reduction rows at a
+// 16-byte pitch), so dY is the A operand (M = output channels), X the B operand (N = input channels), the reduction
+// axis is the pixel-row axis, and a 3x3 tap is once more just a row-shifted descriptor into the same X block.
+// Per stage a CTA loads 128 rows of dY (all M planes) and 128+halo rows of X (all N planes) with bulk async copies and
+// issues  taps_in_group x 8  MMAs (M=128, N=Cin, K=16) into taps_in_group accumulators living side by side in TMEM.
+// Work item = (client, 128-wide block of Cout, tap group, slice of the row range); partial results are added into
+// the fp32 gradient slab with vector reductions (red.global.add.v4.f32), rows of Cin being contiguous thanks to the
+// [Cout][tap][Cin] internal weight order.
+#include "common.cuh"
+
+using namespace dba;
+
+namespace {
+
+constexpr int kRowsK = 128;     // reduction rows per pipeline stage
+constexpr int kThreadsW = 192;
+
+struct WgArgs {
+  const __nv_bfloat16* dY;     // [K][Cout/8][R][8]  (zero on halo rows and on padding samples)
+  const __nv_bfloat16* X;      // [K][Cin/8][R][8]
+  float* G;                    // [K][ldg] gradient rows; this layer's weights at w_off, layout [Cout][taps][cin_real]
+  long long dy_plane, dy_client, x_plane, x_client, ldg;
+  int w_off;
+  int K, Cout, Cin, cin_real, cout_real, taps, Wp, lead, halo;
+  int body_chunks;             // number of 128-row chunks covering the body rows
+  int nsplit;                  // row-range slices
+  int tpg;                     // taps per group
+  int ngroups;                 // tap groups
+  int nmb;                     // Cout blocks of 128
+  int stages;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mplanes = 16;                                   // M = 128 -> 16 planes of 8 output channels
+  const int nplanes = a.Cin >> 3;
+  const uint32_t pitchA = kRowsK * 16u;
+  const uint32_t bytesA = mplanes * pitchA;
+  const uint32_t rowsB = kRowsK + 2 * a.halo;
+  const uint32_t pitchB = rowsB * 16u;
+  const uint32_t bytesB = nplanes * pitchB;
+  uint8_t* smA = smem;
+  uint8_t* smB = smA + (size_t)a.stages * bytesA;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smB + (size_t)a.stages * bytesB);
+  uint64_t* empty = full + a.stages;
+  uint64_t* acc_full = empty + a.stages;
+  uint64_t* acc_empty = acc_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < a.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init(acc_empty, 4);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int items = a.K * a.nmb * a.ngroups * a.nsplit;
+  // real planes of dY available for this M block (the rest of the 16 planes stays unloaded: rows >= Cout of D are
+  // never read back)
+  if (warp == 0) {
+    if (elect_one()) {
+      int it = 0;
+      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int sp = item % a.nsplit;
+        const int mb = (item / (a.nsplit * a.ngroups)) % a.nmb;
+        const int k = item / (a.nsplit * a.ngroups * a.nmb);
+        const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
+        const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
+        const int mreal = min(16, (a.Cout >> 3) - mb * 16);
+        for (int ch = c0; ch < c1; ++ch, ++it) {
+          const int s = it % a.stages;
+          mbar_wait(&empty[s], ((it / a.stages) & 1) ^ 1u);
+          mbar_arrive_expect_tx(&full[s], (uint32_t)mreal * pitchA + bytesB);
+          const long long row = (long long)a.lead + (long long)ch * kRowsK;
+          for (int p = 0; p < mreal; ++p)
+            bulk_g2s(smA + (size_t)s * bytesA + (size_t)p * pitchA,
+                     a.dY + (long long)k * a.dy_client + (long long)(mb * 16 + p) * a.dy_plane + row * 8, pitchA,
+                     &full[s]);
+          for (int p = 0; p < nplanes; ++p)
+            bulk_g2s(smB + (size_t)s * bytesB + (size_t)p * pitchB,
+                     a.X + (long long)k * a.x_client + (long long)p * a.x_plane + (row - a.halo) * 8, pitchB, &full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(128, a.Cin, 1, 1);     // both operands MN-major
+      int it = 0, acc_it = 0;
+      for (int item = blockIdx.x; item < items; item += gridDim.x, ++acc_it) {
+        const int sp = item % a.nsplit;
+        const int grp = (item / a.nsplit) % a.ngroups;
+        const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
+        const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
+        const int t0 = grp * a.tpg, t1 = min(a.taps, t0 + a.tpg);
+        mbar_wait(acc_empty, (acc_it & 1) ^ 1u);
+        tc_fence_after();
+        for (int ch = c0; ch < c1; ++ch, ++it) {
+          const int s = it % a.stages;
+          mbar_wait(&full[s], (it / a.stages) & 1);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smA + (size_t)s * bytesA);
+          const uint32_t b_base = smem_u32(smB + (size_t)s * bytesB);
+          for (int tap = t0; tap < t1; ++tap) {
+            int shift = 0;
+            if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
+            const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.Cin);
+#pragma unroll 1
+            for (int ks = 0; ks < kRowsK / 16; ++ks) {
+              const uint64_t da = umma_desc_noswz(a_base + (uint32_t)ks * 256u, 128, pitchA);
+              const uint64_t db = umma_desc_noswz(b_base + (uint32_t)(ks * 16 + a.halo + shift) * 16u, 128, pitchB);
+              umma_f16(d_tmem, da, db, idesc, (ch != c0 || ks != 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(&empty[s]);
+        }
+        umma_commit(acc_full);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    int acc_it = 0;
+    for (int item = blockIdx.x; item < items; item += gridDim.x, ++acc_it) {
+      const int sp = item % a.nsplit;
+      const int grp = (item / a.nsplit) % a.ngroups;
+      const int mb = (item / (a.nsplit * a.ngroups)) % a.nmb;
+      const int k = item / (a.nsplit * a.ngroups * a.nmb);
+      const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
+      const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
+      const int t0 = grp * a.tpg, t1 = min(a.taps, t0 + a.tpg);
+      mbar_wait(acc_full, acc_it & 1);
+      tc_fence_after();
+      const int co = mb * 128 + q * 32 + lane;
+      float* gk = a.G + (long long)k * a.ldg + a.w_off;
+      const bool vec = ((a.cin_real | a.w_off) & 3) == 0 && (a.ldg & 3) == 0;
+      if (c1 > c0) {
+        for (int tap = t0; tap < t1; ++tap) {
+          float* dst = gk + ((long long)co * a.taps + tap) * a.cin_real;
+          for (int n0 = 0; n0 < a.Cin; n0 += 16) {
+            uint32_t v[16];
+            tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tap - t0) * a.Cin + n0), v);
+            tmem_ld_wait();
+            if (co < a.cout_real) {
+              if (vec) {
+#pragma unroll
+                for (int j = 0; j < 16; j += 4)
+                  if (n0 + j < a.cin_real)
+                    red_add_v4(dst + n0 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                               __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  if (n0 + j < a.cin_real) atomicAdd(dst + n0 + j, __uint_as_float(v[j]));
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// dY: [K][Cout/8][R][8] (zero outside the stored outputs), X: [K][Cin/8][R][8], both on the B x H x W grid
+// (R = dba_conv_rows(B,H,W)).  Adds the weight gradient of a ksize x ksize convolution (ksize 1 or 3, pad ksize/2) into
+// G[k*ldg + w_off + (co*taps + tap)*cin_real + ci] for co < cout_real, ci < cin_real (the gradient slab is zeroed by
+// the caller once per step).  Cin / Cout are the padded channel counts of the planar buffers.
+int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
+                 int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
+  DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
+  DBA_REQUIRE(Cin % 16 == 0 && Cin <= 256 && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d (<=256, %%16) Cout=%d", Cin, Cout);
+  WgArgs a{};
+  a.dY = (const __nv_bfloat16*)dY; a.X = (const __nv_bfloat16*)X; a.G = G; a.ldg = ldg; a.w_off = w_off;
+  a.K = K; a.Cout = Cout; a.Cin = Cin; a.cin_real = cin_real; a.cout_real = cout_real; a.taps = ksize * ksize;
+  a.Wp = W + 1; a.lead = a.Wp + 1; a.halo = ksize == 3 ? a.Wp + 1 : 0;
+  const long long S = (long long)(H + 1) * a.Wp;
+  long long body = (long long)B * S;
+  body = (body + 511) / 512 * 512;
+  const long long R = a.lead + body + a.Wp + 2;
+  a.dy_plane = R * 8; a.dy_client = (long long)(Cout / 8) * R * 8;
+  a.x_plane = R * 8; a.x_client = (long long)(Cin / 8) * R * 8;
+  a.body_chunks = (int)(((long long)B * S + kRowsK - 1) / kRowsK);
+  a.nmb = (Cout + 127) / 128;
+  a.tpg = 512 / Cin;
+  if (a.tpg > a.taps) a.tpg = a.taps;
+  a.ngroups = (a.taps + a.tpg - 1) / a.tpg;
+  a.tpg = (a.taps + a.ngroups - 1) / a.ngroups;            // balance the groups (e.g. 9 taps, 4 max -> 3+3+3)
+  const int base_items = K * a.nmb * a.ngroups;
+  int nsplit = (2 * kNumSMs + base_items - 1) / base_items;
+  if (nsplit > a.body_chunks) nsplit = a.body_chunks;
+  if (nsplit < 1) nsplit = 1;
+  a.nsplit = nsplit;
+  const size_t bytesA = 16 * kRowsK * 16, bytesB = (size_t)(Cin / 8) * (kRowsK + 2 * a.halo) * 16;
+  a.stages = 3;
+  size_t need = a.stages * (bytesA + bytesB) + 1024;
+  if (need > 220 * 1024) { a.stages = 2; need = a.stages * (bytesA + bytesB) + 1024; }
+  DBA_REQUIRE(need <= 220 * 1024, "dba_wgrad_tc: shared memory need %zu too large", need);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DBA_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    attr_set[dev] = true;
+  }
+  if (need < 120 * 1024) need = 120 * 1024;
+  const int items = base_items * nsplit;
+  const int grid = items < kNumSMs ? items : kNumSMs;
+  wgrad_tc_kernel<<<grid, kThreadsW, need, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,92 @@
+"""CUDA backend: the engine's compute interface on hand-written sm_100a kernels (csrc/, loaded through ctypes).
+
+Fails loudly when the native library is missing - there is no silent fallback to library kernels on a GPU box.
+What runs where:
+  * flat-slab work (SGD + FoolsGold grad-sum, poison scaling, norms, FedAvg, Weiszfeld loop, FoolsGold weights and
+    server step): csrc/flat_ops.cu
+  * ResNet-18 (CIFAR / Tiny-ImageNet) evaluation and training: native executor over the tcgen05 implicit-GEMM
+    convolution (csrc/conv_tc.cu) + fused BatchNorm / head kernels (``NativeResNet``), when available for the model
+  * anything the native executor does not cover yet falls back to the batched torch formulation *explicitly*
+    (``self.native_train`` / ``self.native_eval`` say which path is active; bench.py reports them).
+"""
+from __future__ import annotations
+
+import logging
+from typing import List, Optional
+
+import torch
+
+from .. import config as C
+from ..ops import flat, native
+from . import aggregation as agg
+from .torch_backend import TorchBackend
+
+logger = logging.getLogger("logger")
+
+
+class CudaBackend(TorchBackend):
+    name = "cuda"
+
+    def __init__(self, params, spec, data, device) -> None:
+        if device.type != "cuda":
+            raise RuntimeError("CudaBackend needs a CUDA device")
+        native.load()                       # raises NativeError when libdba_b200.so is absent
+        super().__init__(params, spec, data, device)
+        self.native_train = False
+        self.native_eval = False
+        self.exec = None
+        if params["type"] in (C.TYPE_CIFAR, C.TYPE_TINYIMAGENET) and params.get("native_net", True):
+            try:
+                from .native_resnet import NativeResNet
+                self.exec = NativeResNet(params, spec, data, device)
+                self.native_eval = self.exec.can_eval
+                self.native_train = self.exec.can_train
+            except ImportError:
+                self.exec = None
+
+    # ---------------------------------------------------------------------------------------- flat ops
+    def _sgd_update(self, W, V, g, lr_t, act, grad_sum, mu, wd) -> None:
+        g = g.contiguous()
+        flat.sgd_step_(W, V, g, lr_t.contiguous(), act.to(torch.uint8), self.spec.Dp, mu, wd, grad_sum)
+
+    @staticmethod
+    def scale_(W, anchor, scale) -> None:
+        flat.scale_rows_(W, anchor, scale.float().contiguous())
+
+    def dist_norm(self, W, anchor):
+        return flat.rows_dist(W, anchor, n=self.spec.Dp).float()
+
+    def global_norm(self, W):
+        return flat.rows_dist(W, None, n=self.spec.Dp).float()
+
+    # ------------------------------------------------------------------------------------- aggregation
+    def fedavg_from_states_(self, G, G_cnt, W, cnt, eta, no_models, comm, sigma, seed) -> bool:
+        """G += eta/no_models * sum_k (W[k] - G): delta extraction + reduce + apply (+ DP noise) in one launch.
+        Returns False when the caller must use the collective path (several ranks)."""
+        if comm.world != 1:
+            return False
+        flat.fedavg_update_(G, W, eta / no_models, sigma or 0.0, seed, bcast=False)
+        if cnt is not None and cnt.numel() and G_cnt.numel():
+            d = (cnt - G_cnt[None, :]).sum(0).double()
+            G_cnt.add_((d * (eta / no_models)).trunc().long())
+        return True
+
+    def geometric_median_states(self, W, G, num_samples: List[float], maxiter: int):
+        """Device-resident Weiszfeld loop over the deltas W[c] - G (single rank)."""
+        ns = torch.tensor(num_samples, dtype=torch.float64, device=W.device)
+        alphas = (ns / ns.sum()).float()
+        med, dist, wv, obj, state = flat.weiszfeld(W, G, alphas, maxiter)
+        st = state.cpu()
+        return agg.RFAResult(int(st[2]), [float(v) for v in wv.cpu().tolist()],
+                             [float(v) for v in dist.cpu().tolist()], med, float(obj.cpu()[0]), int(st[1]))
+
+    # -------------------------------------------------------------------------------- train / evaluate
+    def train(self, sch, W, cnt, anchor, want_grad_sum, generator=None):
+        if self.native_train:
+            return self.exec.train(sch, W, cnt, anchor, want_grad_sum)
+        return super().train(sch, W, cnt, anchor, want_grad_sum, generator)
+
+    def evaluate(self, models, split, trig_row):
+        if self.native_eval:
+            return self.exec.evaluate(models, split, trig_row)
+        return super().evaluate(models, split, trig_row)

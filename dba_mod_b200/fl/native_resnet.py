@@ -1,0 +1,412 @@
+"""Native executor for the CIFAR ResNet-18 family: evaluation and training of K client replicas (or M models
+under test) as chains of hand-written sm_100a kernels.
+
+  input stage (uint8 gather, /255, trigger, stem im2col)      csrc/net_ops.cu   dba_input_stage_image
+  every convolution, fwd and input-gradient                   csrc/conv_tc.cu   dba_conv_tc   (tcgen05 / TMEM / UBLKCP)
+  weight gradients                                            csrc/wgrad_tc.cu  dba_wgrad_tc  (tcgen05, MN-major operands)
+  BatchNorm (train: stats from the conv epilogue; apply+residual+ReLU; backward)   csrc/bn_ops.cu
+  avg-pool + linear + cross-entropy + metrics (+ backward)    csrc/net_ops.cu   dba_head
+  SGD / FoolsGold grad-sum                                    csrc/flat_ops.cu  dba_sgd_step
+
+Reference behaviour: models/resnet_cifar.py:67-104 run per client by image_train.py:191-271 (training) and
+test.py:7-239 (evaluation).  Evaluation folds BatchNorm into the convolution epilogue (scale/shift + residual + ReLU),
+so a forward pass is 20 convolution launches + input stage + head for ALL models at once.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from .. import config as C
+from ..ops import conv as convop
+from ..ops import native
+from ..ops.layout import Geom
+
+BN_EPS = 1e-5
+
+
+@dataclass
+class ConvL:
+    name: str          # weight key
+    bn: str            # BatchNorm prefix
+    cin: int
+    cout: int
+    ks: int
+    H: int             # input resolution (square)
+    sub: int
+    fold: bool = False
+    cin_p: int = 0
+    cout_p: int = 0
+    w_off: int = 0     # forward pack offset (elements, per client)
+    wt_off: int = -1   # transposed pack offset
+    bn_off: int = 0    # offset into the per-model scale/shift rows
+
+
+class NativeResNet:
+    def __init__(self, params, spec, data, device) -> None:
+        self.params, self.spec, self.data, self.device = params, spec, data, device
+        self.lib = native.load()
+        self.kind = params["type"]
+        if self.kind != C.TYPE_CIFAR:
+            raise ImportError("native executor currently covers the CIFAR ResNet-18")
+        self.B = int(params["batch_size"])
+        self.label_swap = int(params["poison_label_swap"])
+        self.ncls = 10
+        self._plan()
+        self.can_eval = True
+        self.can_train = bool(params.get("native_train", True))
+        self._train_bufs: Dict[int, dict] = {}
+        self.mu, self.wd = float(params["momentum"]), float(params["decay"])
+        self.eval_chunk = int(params.get("native_eval_chunk", 500))
+        self._eval_bufs: Dict[Tuple[int, int], dict] = {}
+        d = data
+        self.trig_u8 = d.trigger_masks.to(torch.uint8).contiguous()
+
+    # ----------------------------------------------------------------------------------------------- plan
+    def _plan(self) -> None:
+        sp = self.spec
+        L: List[ConvL] = [ConvL("conv1.weight", "bn1", 3, 32, 3, 32, 1, fold=True)]
+        widths = [32, 64, 128, 256]
+        res = 32
+        cin = 32
+        self.blocks = []
+        for li, w in enumerate(widths, start=1):
+            for bi in range(2):
+                pre = f"layer{li}.{bi}"
+                sub = 2 if (li > 1 and bi == 0) else 1
+                c1 = ConvL(f"{pre}.conv1.weight", f"{pre}.bn1", cin, w, 3, res, sub)
+                c2 = ConvL(f"{pre}.conv2.weight", f"{pre}.bn2", w, w, 3, res // sub, 1)
+                sc = None
+                if f"{pre}.shortcut.0.weight" in sp.entries:
+                    sc = ConvL(f"{pre}.shortcut.0.weight", f"{pre}.shortcut.1", cin, w, 1, res, sub)
+                L += [c1, c2] + ([sc] if sc else [])
+                self.blocks.append((c1, c2, sc))
+                res //= sub
+                cin = w
+        off = 0
+        bn_off = 0
+        rows = []
+        fold_rows = []
+        for l in L:
+            taps = l.ks * l.ks
+            if l.fold:
+                l.cin_p, l.cout_p = (taps * l.cin + 15) // 16 * 16, (l.cout + 31) // 32 * 32
+                n_f = l.cin_p * l.cout_p
+            else:
+                l.cin_p, l.cout_p = (l.cin + 15) // 16 * 16, (l.cout + 31) // 32 * 32
+                n_f = taps * l.cin_p * l.cout_p
+            l.w_off = off
+            off += n_f
+            if not l.fold:
+                l.wt_off = off
+                off += n_f
+            l.bn_off = bn_off
+            bn_off += l.cout
+            e = sp.entries[l.name]
+            rows.append([e.offset, l.cout, l.cin, taps, l.w_off, l.wt_off, l.cin_p, l.cout_p, int(l.fold)])
+            ent = sp.entries
+            fold_rows.append([ent[l.bn + ".weight"].offset, ent[l.bn + ".bias"].offset,
+                              ent[l.bn + ".running_mean"].offset, ent[l.bn + ".running_var"].offset, l.cout, l.bn_off])
+        self.layers = L
+        self.pack_elems = off
+        self.bn_total = bn_off
+        self.pack_table = torch.tensor(rows, dtype=torch.int32, device=self.device).contiguous()
+        self.fold_table = torch.tensor(fold_rows, dtype=torch.int32, device=self.device).contiguous()
+        self.head_w_off = sp.entries["linear.weight"].offset
+        self.head_b_off = sp.entries["linear.bias"].offset
+
+    # ------------------------------------------------------------------------------------------ helpers
+    def pack_weights(self, W: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        K = W.shape[0]
+        if out is None:
+            out = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=self.device)
+        native.check(self.lib.dba_pack_weights(native.ptr(W), W.stride(0), native.ptr(self.pack_table),
+                                               len(self.layers), K, native.ptr(out), out.stride(0), native.stream()))
+        return out
+
+    def _wt(self, pack: torch.Tensor, l: ConvL, transposed: bool = False) -> torch.Tensor:
+        K = pack.shape[0]
+        if l.fold:
+            return pack[:, l.w_off:l.w_off + l.cin_p * l.cout_p].unflatten(1, (1, l.cin_p // 8, l.cout_p, 8))
+        taps = l.ks * l.ks
+        n = taps * l.cin_p * l.cout_p
+        if transposed:
+            return pack[:, l.wt_off:l.wt_off + n].unflatten(1, (taps, l.cout_p // 8, l.cin_p, 8))
+        return pack[:, l.w_off:l.w_off + n].unflatten(1, (taps, l.cin_p // 8, l.cout_p, 8))
+
+    def _conv(self, x, pack, l: ConvL, K, B, out, res=None, scale=None, shift=None, relu=False, stats=None,
+              x_shared=False):
+        """Forward convolution of layer l.  pack rows are strided views -> pass raw pointers."""
+        wt = self._wt(pack, l)
+        ks = 1 if l.fold else l.ks
+        cin = l.cin_p
+        native.check(self.lib.dba_conv_tc_strided(
+            native.ptr(x), native.ptr(wt), pack.stride(0), native.ptr(out), native.ptr(res),
+            native.ptr(scale), native.ptr(shift), scale.stride(0) if scale is not None else 0, native.ptr(stats),
+            stats.stride(0) if stats is not None else 0, K, B, l.H, l.H, cin, l.cout_p, ks, l.sub, int(relu),
+            int(x_shared), native.stream()))
+        return out
+
+    # ------------------------------------------------------------------------------------------ evaluation
+    def _ebufs(self, M: int, Bt: int) -> dict:
+        key = (M, Bt)
+        if key in self._eval_bufs:
+            return self._eval_bufs[key]
+        dev = self.device
+        z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
+        bufs = {"stem_in": z(1, 32, 32), "lv": {}}
+        for w, r in zip([32, 64, 128, 256], [32, 16, 8, 4]):
+            bufs["lv"][r] = [z(M, w, r) for _ in range(4)]
+        bufs["labels"] = torch.zeros(1, Bt, dtype=torch.int32, device=dev)
+        bufs["idx"] = torch.full((1, Bt), -1, dtype=torch.long, device=dev)
+        self._eval_bufs[key] = bufs
+        return bufs
+
+    @torch.no_grad()
+    def evaluate(self, models: torch.Tensor, split: str, trig_row: int):
+        d, dev, lib = self.data, self.device, self.lib
+        M = models.shape[0]
+        Bt = self.eval_chunk
+        ids_all = d.all_test_idx if split == "clean" else d.poison_test_idx
+        n = int(ids_all.numel())
+        models = models.contiguous()
+        pack = self.pack_weights(models)
+        scale = torch.empty(M, self.bn_total, device=dev)
+        shift = torch.empty(M, self.bn_total, device=dev)
+        native.check(lib.dba_bn_fold(native.ptr(models), models.stride(0), native.ptr(self.fold_table),
+                                     len(self.layers), M, native.ptr(scale), native.ptr(shift), scale.stride(0),
+                                     BN_EPS, native.stream()))
+        bufs = self._ebufs(M, Bt)
+        mf = torch.zeros(M, 1, device=dev)
+        mi = torch.zeros(M, 1, 2, dtype=torch.int32, device=dev)
+        trow = torch.tensor([max(trig_row, 0)], dtype=torch.long, device=dev)
+        pn = torch.tensor([Bt if split == "poison" else 0], dtype=torch.long, device=dev)
+        idx, labels = bufs["idx"], bufs["labels"]
+        for s in range(0, n, Bt):
+            ids = ids_all[s:s + Bt]
+            idx.fill_(-1)
+            idx[0, :ids.numel()] = ids
+            self._forward_eval(M, Bt, idx, trow, pn, pack, scale, shift, bufs, labels)
+            a = bufs["out"]
+            native.check(lib.dba_head(native.ptr(a), native.ptr(models), models.stride(0), self.head_w_off,
+                                      self.head_b_off, None, 0, None, native.ptr(labels), 1, None, None,
+                                      native.ptr(mf), native.ptr(mi), 1, None, M, Bt, 256, 4, 4, self.ncls,
+                                      Geom(Bt, 4, 4).rows, native.stream()))
+        return mf[:, 0].double(), mi[:, 0, 0].long(), n
+
+    def _forward_eval(self, M, Bt, idx, trow, pn, pack, scale, shift, bufs, labels) -> None:
+        d, lib = self.data, self.lib
+        stem = self.layers[0]
+        xin = bufs["stem_in"]
+        native.check(lib.dba_input_stage_image(
+            native.ptr(d.test_x), native.ptr(d.test_y), native.ptr(idx), idx.stride(0), native.ptr(self.trig_u8),
+            native.ptr(trow), native.ptr(pn), None, native.ptr(xin), native.ptr(labels), 1, Bt, d.H, d.W, d.C,
+            3, 1, 1, 32, 32, stem.cin_p, self.label_swap, xin.shape[2], native.stream()))
+
+        def ss(l):
+            return scale[:, l.bn_off:l.bn_off + l.cout], shift[:, l.bn_off:l.bn_off + l.cout]
+
+        lv = bufs["lv"]
+        cur = lv[32][0]
+        sc_, sh_ = ss(stem)
+        self._conv(xin, pack, stem, M, Bt, cur, scale=sc_, shift=sh_, relu=True, x_shared=True)
+        res = 32
+        ci = 0
+        for (c1, c2, sc) in self.blocks:
+            r_out = res // c1.sub
+            pool = lv[r_out]
+            free = [b for b in pool if b is not cur]
+            mid, out, proj = free[0], free[1], free[2] if len(free) > 2 else None
+            s1, h1 = ss(c1)
+            self._conv(cur, pack, c1, M, Bt, mid, scale=s1, shift=h1, relu=True)
+            if sc is not None:
+                s3, h3 = ss(sc)
+                proj = free[2] if len(free) > 2 else pool[3]
+                self._conv(cur, pack, sc, M, Bt, proj, scale=s3, shift=h3, relu=False)
+                skip = proj
+            else:
+                skip = cur
+            s2, h2 = ss(c2)
+            self._conv(mid, pack, c2, M, Bt, out, res=skip, scale=s2, shift=h2, relu=True)
+            cur = out
+            res = r_out
+        bufs["out"] = cur
+
+    # -------------------------------------------------------------------------------------------- training
+    def _tbufs(self, K: int) -> dict:
+        if K in self._train_bufs:
+            return self._train_bufs[K]
+        dev, B = self.device, self.B
+
+        def z(c, r):
+            return torch.zeros(K, c // 8, Geom(B, r, r).rows, 8, dtype=torch.bfloat16, device=dev)
+
+        t = {"xin": z(32, 32), "labels": torch.zeros(K, B, dtype=torch.int32, device=dev)}
+        for l in self.layers:
+            ro = l.H // l.sub
+            t[("y", l.name)] = z(l.cout_p, ro)
+            t[("a", l.name)] = z(l.cout_p, ro)
+            if l.fold:
+                t[("dy", l.name)] = z(l.cout_p, ro)
+            else:
+                t[("dy", l.name)] = z(l.cout_p, l.H)          # on the input grid (zero-upsampled when sub == 2)
+        # gradient scratch per resolution level: g (block output grad), dz, da1, dx
+        for w, r in zip([32, 64, 128, 256], [32, 16, 8, 4]):
+            t[("g", r)] = [z(w, r) for _ in range(4)]
+        t["stats"] = torch.zeros(K, 2 * self.bn_total, device=dev)
+        t["saved"] = torch.zeros(K, 2 * self.bn_total, device=dev)
+        t["sums"] = torch.zeros(K, 2 * self.bn_total, device=dev)
+        t["Gr"] = torch.zeros(K, (self.spec.Dp + 3) // 4 * 4, device=dev)
+        t["V"] = torch.zeros_like(t["Gr"])
+        t["pack"] = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=dev)
+        self._train_bufs[K] = t
+        return t
+
+    def _bn_apply(self, l: ConvL, K, y, out, res, relu, W, t, nvalid, active):
+        e = self.spec.entries
+        r = l.H // l.sub
+        native.check(self.lib.dba_bn_apply(
+            native.ptr(y), native.ptr(res), native.ptr(out), native.ptr(t["stats"]), t["stats"].stride(0),
+            2 * l.bn_off, native.ptr(t["saved"]), t["saved"].stride(0), 2 * l.bn_off, native.ptr(W), W.stride(0),
+            e[l.bn + ".weight"].offset, e[l.bn + ".bias"].offset, e[l.bn + ".running_mean"].offset,
+            e[l.bn + ".running_var"].offset, native.ptr(nvalid), native.ptr(active), K, l.cout_p, self.B, r, r,
+            y.shape[2], int(relu), 0.1, BN_EPS, native.stream()))
+
+    def _bn_bwd(self, l: ConvL, K, g, y, act, dy, gmask, W, t, nvalid, up):
+        e = self.spec.entries
+        r = l.H // l.sub
+        Gr = t["Gr"]
+        native.check(self.lib.dba_bn_backward(
+            native.ptr(g), native.ptr(y), native.ptr(act), native.ptr(dy), native.ptr(gmask), native.ptr(t["sums"]),
+            t["sums"].stride(0), 2 * l.bn_off, native.ptr(t["saved"]), t["saved"].stride(0), 2 * l.bn_off,
+            native.ptr(W), W.stride(0), native.ptr(Gr), Gr.stride(0), e[l.bn + ".weight"].offset,
+            e[l.bn + ".bias"].offset, native.ptr(nvalid), K, l.cout_p, self.B, r, r, y.shape[2], int(up),
+            dy.shape[2], native.stream()))
+
+    def _wgrad(self, l: ConvL, K, dy, x, t):
+        Gr = t["Gr"]
+        e = self.spec.entries[l.name]
+        if l.fold:
+            cin, cin_real, ks, H = l.cin_p, l.ks * l.ks * l.cin, 1, l.H
+        else:
+            cin, cin_real, ks, H = l.cin_p, l.cin, l.ks, l.H
+        native.check(self.lib.dba_wgrad_tc(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0), e.offset, K,
+                                           self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks, native.stream()))
+
+    def _dgrad(self, l: ConvL, K, dy, pack, out, res=None):
+        wt = self._wt(pack, l, transposed=True)
+        native.check(self.lib.dba_conv_tc_strided(
+            native.ptr(dy), native.ptr(wt), pack.stride(0), native.ptr(out), native.ptr(res), None, None, 0, None, 0,
+            K, self.B, l.H, l.H, l.cout_p, l.cin_p, l.ks, 1, 0, 0, native.stream()))
+        return out
+
+    def train(self, sch, W: torch.Tensor, cnt: torch.Tensor, anchor: torch.Tensor, want_grad_sum: bool):
+        from .torch_backend import TrainResult
+        p, dev, lib, d = self.params, self.device, self.lib, self.data
+        K, Dp, B = W.shape[0], self.spec.Dp, self.B
+        if float(p["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any()):
+            raise NotImplementedError("alpha_loss != 1 is handled by the torch path")
+        E = max(sch.E_max, 1)
+        t = self._tbufs(K)
+        Gr, V = t["Gr"], t["V"]
+        V.zero_()
+        grad_sum = torch.zeros_like(Gr) if want_grad_sum else None
+        mf = torch.zeros(K, E, device=dev)
+        mi = torch.zeros(K, E, 2, dtype=torch.int32, device=dev)
+        nan = torch.zeros(K, dtype=torch.uint8, device=dev)
+        mask_all = sch.idx >= 0                                              # [K, T, B]
+        nvalid_all = mask_all.sum(2).to(torch.int32).contiguous()            # [K, T]
+        act_all = sch.active.to(torch.uint8).contiguous()
+        lr_all = sch.lr.contiguous()
+        ar = torch.arange(B, device=dev)
+        sel = (ar[None, None, :] < sch.poison_n[:, None, None]) & mask_all
+        pcount = torch.zeros(K, E, dtype=torch.long, device=dev)
+        pcount.scatter_add_(1, sch.epoch_of, sel.sum(2) * sch.active)
+        flip = sch.flip.to(torch.uint8).contiguous() if sch.flip is not None else None
+        idx = sch.idx.contiguous()
+        stem = self.layers[0]
+        lv_g = {r: t[("g", r)] for r in (32, 16, 8, 4)}
+        for step in range(sch.T):
+            idx_t = idx[:, step]
+            nvalid = nvalid_all[:, step].contiguous()
+            active = act_all[:, step].contiguous()
+            slot = sch.epoch_of[:, step].contiguous()
+            pack = self.pack_weights(W, t["pack"])
+            t["stats"].zero_(); t["sums"].zero_(); Gr.zero_()
+            native.check(lib.dba_input_stage_image(
+                native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(idx_t), idx.stride(0),
+                native.ptr(self.trig_u8), native.ptr(sch.trig_row), native.ptr(sch.poison_n),
+                native.ptr(flip[:, step]) if flip is not None else None, native.ptr(t["xin"]),
+                native.ptr(t["labels"]), K, B, d.H, d.W, d.C, 3, 1, 1, 32, 32, stem.cin_p, self.label_swap,
+                t["xin"].shape[2], native.stream()))
+            st = t["stats"]
+
+            def fconv(l, x, y):
+                self._conv(x, pack, l, K, B, y, stats=st[:, 2 * l.bn_off:], x_shared=False)
+
+            # ------------------------------------------------------------------ forward
+            y0, a0 = t[("y", stem.name)], t[("a", stem.name)]
+            fconv(stem, t["xin"], y0)
+            self._bn_apply(stem, K, y0, a0, None, True, W, t, nvalid, active)
+            x = a0
+            inputs = []
+            for (c1, c2, sc) in self.blocks:
+                inputs.append(x)
+                y1, a1 = t[("y", c1.name)], t[("a", c1.name)]
+                fconv(c1, x, y1)
+                self._bn_apply(c1, K, y1, a1, None, True, W, t, nvalid, active)
+                y2, out = t[("y", c2.name)], t[("a", c2.name)]
+                fconv(c2, a1, y2)
+                skip = x
+                if sc is not None:
+                    ys, as_ = t[("y", sc.name)], t[("a", sc.name)]
+                    fconv(sc, x, ys)
+                    self._bn_apply(sc, K, ys, as_, None, False, W, t, nvalid, active)
+                    skip = as_
+                self._bn_apply(c2, K, y2, out, skip, True, W, t, nvalid, active)
+                x = out
+            # ------------------------------------------------------------------ head (fwd + bwd)
+            g = lv_g[4][0]
+            native.check(lib.dba_head(native.ptr(x), native.ptr(W), W.stride(0), self.head_w_off, self.head_b_off,
+                                      native.ptr(Gr), Gr.stride(0), native.ptr(g), native.ptr(t["labels"]), 0,
+                                      native.ptr(nvalid), native.ptr(slot), native.ptr(mf), native.ptr(mi), E,
+                                      native.ptr(nan), K, B, 256, 4, 4, self.ncls, x.shape[2], native.stream()))
+            # ------------------------------------------------------------------ backward
+            for bi in range(len(self.blocks) - 1, -1, -1):
+                c1, c2, sc = self.blocks[bi]
+                xin_b = inputs[bi]
+                r_out, r_in = c2.H, c1.H
+                pool_o = [b for b in lv_g[r_out] if b is not g]
+                dz, da1 = pool_o[0], pool_o[1]
+                dy2, dy1 = t[("dy", c2.name)], t[("dy", c1.name)]
+                self._bn_bwd(c2, K, g, t[("y", c2.name)], t[("a", c2.name)], dy2, dz, W, t, nvalid, up=False)
+                self._wgrad(c2, K, dy2, t[("a", c1.name)], t)
+                self._dgrad(c2, K, dy2, pack, da1)
+                self._bn_bwd(c1, K, da1, t[("y", c1.name)], t[("a", c1.name)], dy1, None, W, t, nvalid,
+                             up=(c1.sub == 2))
+                self._wgrad(c1, K, dy1, xin_b, t)
+                pool_i = [b for b in lv_g[r_in] if b is not g and b is not dz and b is not da1]
+                dx = pool_i[0]
+                if sc is None:
+                    self._dgrad(c1, K, dy1, pack, dx, res=dz)
+                else:
+                    dx2 = pool_i[1]
+                    self._dgrad(c1, K, dy1, pack, dx2)
+                    dys = t[("dy", sc.name)]
+                    self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
+                    self._wgrad(sc, K, dys, xin_b, t)
+                    self._dgrad(sc, K, dys, pack, dx, res=dx2)
+                g = dx
+            dy0 = t[("dy", stem.name)]
+            self._bn_bwd(stem, K, g, y0, a0, dy0, None, W, t, nvalid, up=False)
+            self._wgrad(stem, K, dy0, t["xin"], t)
+            # ------------------------------------------------------------------ optimiser
+            from ..ops import flat
+            flat.sgd_step_(W, V, Gr, lr_all[:, step].contiguous(), active, Dp, self.mu, self.wd, grad_sum)
+            if cnt.numel():
+                cnt += active[:, None].long()
+        res = TrainResult(grad_sum[:, :Dp] if grad_sum is not None else None, mf, mi[:, :, 0].long(),
+                          mi[:, :, 1].long(), pcount, nan.bool())
+        return res

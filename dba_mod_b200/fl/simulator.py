@@ -227,12 +227,15 @@ class Simulator:
         pinned host memory every round, like the reference's DataLoader -> .to(device) path."""
         d = self.data
         if self._pinned is None:
-            self._pinned = {"train": d.train_x_host.pin_memory(), "test": d.test_x_host.pin_memory()}
+            pin = (lambda t: t.pin_memory()) if self.device.type == "cuda" else (lambda t: t)
+            self._pinned = {"train": pin(d.train_x_host), "test": pin(d.test_x_host)}
         idx = torch.cat([d.client_index_tensor(n) for n in names]) if names else None
         nbytes = 0
         if idx is not None and idx.numel():
             host_idx = idx.cpu()
-            rows = self._pinned["train"][host_idx].pin_memory()
+            rows = self._pinned["train"][host_idx]
+            if self.device.type == "cuda":
+                rows = rows.pin_memory()
             dev_rows = rows.to(self.device, non_blocking=True)
             d.train_x.index_copy_(0, idx, dev_rows)
             nbytes += rows.numel() * rows.element_size()
@@ -468,21 +471,25 @@ class Simulator:
         all_ns = self._gather_num_samples(num_samples, counts, order, len(names))
         names_in_order = [names[s] for s in order]
         if method == C.AGGR_MEAN:
+            fused = getattr(be, "fedavg_from_states_", None)
+            if fused is not None and fused(self.G, self.G_cnt, W, cnt if cnt.numel() else None, float(p["eta"]),
+                                           int(p["no_models"]), comm, sigma, int(p["seed"]) * 1000003 + epoch):
+                return
             delta = W - self.G[None, :]
             dcnt = (cnt - self.G_cnt[None, :]) if cnt.numel() else None
-            if hasattr(be, "fedavg_update_"):
-                be.fedavg_update_(self.G, self.G_cnt, delta, dcnt, float(p["eta"]), int(p["no_models"]), comm, sigma,
-                                  self.noise_gen)
-            else:
-                agg.fedavg_update_(self.G, self.G_cnt, delta, dcnt, float(p["eta"]), int(p["no_models"]), comm,
-                                   sigma, self.noise_gen)
+            agg.fedavg_update_(self.G, self.G_cnt, delta, dcnt, float(p["eta"]), int(p["no_models"]), comm, sigma,
+                               self.noise_gen)
             return
         self._log_poison_ratio("rfa" if method == C.AGGR_GEO_MED else "foolsgold", names, all_ns)
         if method == C.AGGR_GEO_MED:
-            delta = W - self.G[None, :]
-            ns = torch.tensor(num_samples, dtype=torch.float64, device=self.device)
-            fn = getattr(be, "geometric_median", None) or agg.geometric_median
-            res = fn(delta, ns, [all_ns[s] for s in order], counts, maxiter=int(p["geom_median_maxiter"]), comm=comm)
+            fused = getattr(be, "geometric_median_states", None)
+            if fused is not None and comm.world == 1:
+                res = fused(W, self.G, [all_ns[s] for s in order], int(p["geom_median_maxiter"]))
+            else:
+                delta = W - self.G[None, :]
+                ns = torch.tensor(num_samples, dtype=torch.float64, device=self.device)
+                res = agg.geometric_median(delta, ns, [all_ns[s] for s in order], counts,
+                                           maxiter=int(p["geom_median_maxiter"]), comm=comm)
             agg.rfa_update_(self.G, res, float(p["eta"]), sigma, comm, self.noise_gen)
             logger.info(f"[rfa agg] iters: {res.iters}, objective: {res.objective}, weight: {res.wv}")
             wv, alphas = res.wv, res.distances

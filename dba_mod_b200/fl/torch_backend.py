@@ -120,24 +120,31 @@ class TorchBackend:
             if use_dist:
                 dist = (Pg - anchor[:, :Dp]).norm(dim=1)
                 loss_k = torch.where(poisoning, alpha * loss_k + (1 - alpha) * dist, loss_k)
-            (loss_k * act).sum().backward()
+            torch.where(act, loss_k, torch.zeros_like(loss_k)).sum().backward()
             g = Pg.grad
             with torch.no_grad():
-                a = act[:, None].to(g.dtype)
-                if want_grad_sum:
-                    res.grad_sum += g * a
-                g = g + wd * P
-                V.mul_(1 - a + a * mu).add_(g * a)      # v = mu*v + g  (active rows only)
-                P.sub_(V * (sch.lr[:, t, None] * a))
+                self._sgd_update(W, V, g, sch.lr[:, t], act, res.grad_sum, mu, wd)
                 e = sch.epoch_of[:, t]
                 pred = logits.argmax(-1)
-                res.loss_sum[kk, e] += loss_k.detach() * act
+                res.loss_sum[kk, e] += torch.where(act, loss_k.detach(), torch.zeros_like(loss_k))
                 res.correct[kk, e] += (((pred == y) & mask).sum(1)) * act
                 res.count[kk, e] += n_k * act
                 res.poison_count[kk, e] += sel.sum(1) * act
                 res.nan_flag |= ~torch.isfinite(logits).reshape(K, -1).all(1) & act
         self.W_last = W
         return res
+
+    def _sgd_update(self, W, V, g, lr_t, act, grad_sum, mu, wd) -> None:
+        """v = mu*v + (g + wd*w); w -= lr*v on the rows with act[k]; grad_sum += g (raw gradient, Q10)."""
+        Dp = self.spec.Dp
+        P = W[:, :Dp]
+        a = act[:, None].to(g.dtype)
+        g = torch.where(act[:, None], g, torch.zeros_like(g))
+        if grad_sum is not None:
+            grad_sum += g
+        g = g + wd * P
+        V.mul_(1 - a + a * mu).add_(g * a)
+        P.sub_(V * (lr_t[:, None] * a))
 
     # ---------------------------------------------------------------------------------------- evaluation
     @torch.no_grad()

@@ -117,6 +117,13 @@ class _Ctx:
         w = self.w(wname)
         K, Cout = w.shape[:2]
         b = self.w(bname).reshape(-1) if bname else None
+        if x.is_cuda and K > 1:
+            # library grouped convolutions are pathologically slow for some shapes (stride 2); this torch path is
+            # only the oracle / fallback on GPUs, so K plain convolutions are fine
+            Cin = w.shape[2]
+            outs = [F.conv2d(x[:, k * Cin:(k + 1) * Cin], w[k], None if b is None else b[k * Cout:(k + 1) * Cout],
+                             stride, pad) for k in range(K)]
+            return torch.cat(outs, 1)
         return F.conv2d(x, w.reshape(K * Cout, *w.shape[2:]), b, stride, pad, groups=K)
 
     def bn(self, x, prefix):
@@ -139,7 +146,10 @@ class _Ctx:
             mk = m.reshape(B, K, 1, 1, 1)
             xv = x.reshape(B, K, Cn, H, W)
             mean = ((xv * mk).sum(dim=(0, 3, 4)) / n[:, None]).reshape(KC)
-            var = ((((xv - mean.reshape(1, K, Cn, 1, 1)) ** 2) * mk).sum(dim=(0, 3, 4)) / n[:, None]).reshape(KC)
+            var = ((((xv - mean.reshape(1, K, Cn, 1, 1)) ** 2) * mk).sum(dim=(0, 3, 4)) / n[:, None])
+            # a client with no valid sample in this step (idle slot of the lock-step schedule) must not blow its
+            # activations up by 1/sqrt(eps) per layer: normalise it with unit variance (its output is unused)
+            var = torch.where((m.sum(0) > 0)[:, None], var, torch.ones_like(var)).reshape(KC)
         with torch.no_grad():
             act = self.active if self.active is not None else torch.ones(K, dtype=torch.bool, device=x.device)
             a = act[:, None].to(x.dtype)

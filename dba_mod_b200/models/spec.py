@@ -6,6 +6,12 @@ model state is ``flat[Df] = [ all parameters (Dp) | all float buffers (Db: BN ru
 int64 side vector for the ``num_batches_tracked`` counters, so each of those steps is a single kernel over
 ``[K, Df]`` slabs.  The ``state_dict`` form (reference key names, order, shapes and dtypes) exists only at the
 checkpoint / oracle boundary: :meth:`flatten` and :meth:`unflatten`.
+
+Internal storage order of 4-D convolution weights is ``[Cout, kh, kw, Cin]`` (channels-last), not PyTorch's
+``[Cout, Cin, kh, kw]``: that is the order in which the tensor-core weight-gradient kernel produces its tiles
+(contiguous runs of Cin per (Cout, tap)) and from which the packed bf16 operand layouts are cut.  All flat-slab
+maths (SGD, deltas, aggregation, norms) is element-wise and therefore indifferent to the order; ``state_dict``s
+going in or out are permuted here, and :meth:`view` hands out ``[Cout, Cin, kh, kw]``-shaped (strided) views.
 """
 from __future__ import annotations
 
@@ -23,6 +29,7 @@ class Entry:
     kind: str          # 'param' | 'buffer' | 'counter'
     offset: int        # into flat (param / buffer) or into the counter vector
     numel: int
+    ohwi: bool = False  # 4-D conv weights are STORED [Cout, kh, kw, Cin] in the flat vector (see ParamSpec)
 
 
 class ParamSpec:
@@ -35,7 +42,7 @@ class ParamSpec:
         off = 0
         for n in pnames:
             t = sd[n]
-            self.entries[n] = Entry(n, tuple(t.shape), "param", off, t.numel())
+            self.entries[n] = Entry(n, tuple(t.shape), "param", off, t.numel(), ohwi=(t.dim() == 4))
             off += t.numel()
         self.Dp = off
         nc = 0
@@ -76,6 +83,8 @@ class ParamSpec:
             if e.kind == "counter":
                 cnt[e.offset:e.offset + e.numel] = t.reshape(-1).long()
             else:
+                if e.ohwi:
+                    t = t.permute(0, 2, 3, 1)
                 flat[e.offset:e.offset + e.numel] = t.reshape(-1).float()
         if device is not None:
             flat, cnt = flat.to(device), cnt.to(device)
@@ -89,6 +98,9 @@ class ParamSpec:
                 v = counters[e.offset:e.offset + e.numel] if counters is not None else torch.zeros(e.numel,
                                                                                                     dtype=torch.int64)
                 out[n] = v.reshape(e.shape).clone().long()
+            elif e.ohwi:
+                o, i, kh, kw = e.shape
+                out[n] = flat[e.offset:e.offset + e.numel].reshape(o, kh, kw, i).permute(0, 3, 1, 2).contiguous()
             else:
                 out[n] = flat[e.offset:e.offset + e.numel].reshape(e.shape).clone()
         return out
@@ -96,7 +108,13 @@ class ParamSpec:
     def view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
         """flat [..., Df] (or [..., Dp]) -> [..., *shape] view of one float entry (no copy)."""
         e = self.entries[name]
-        return flat[..., e.offset:e.offset + e.numel].reshape(*flat.shape[:-1], *e.shape)
+        v = flat[..., e.offset:e.offset + e.numel]
+        if e.ohwi:
+            o, i, kh, kw = e.shape
+            nd = flat.dim() - 1
+            v = v.reshape(*flat.shape[:-1], o, kh, kw, i)
+            return v.permute(*range(nd), nd, nd + 3, nd + 1, nd + 2)
+        return v.reshape(*flat.shape[:-1], *e.shape)
 
     def counter_index(self, name: str) -> int:
         return self.entries[name].offset

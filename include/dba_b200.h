@@ -1,0 +1,105 @@
+/* C ABI of libdba_b200.so - the hand-written sm_100a kernels of the dba_mod_b200 framework.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure (dba_last_error() has the text).  All device
+ * pointers are plain CUDA device addresses; `stream` is a cudaStream_t passed as void*.  Nothing here allocates device
+ * memory: callers own every buffer (sizes are stated per function).  "Reference" = ehsan886/DBA_mod, file:line.
+ */
+#ifndef DBA_B200_H
+#define DBA_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dba_last_error(void);
+unsigned long long dba_launch_count(void);       /* kernels launched by this library since the last reset */
+void dba_reset_launch_count(void);
+
+/* ---- flat-slab kernels (csrc/flat_ops.cu) ------------------------------------------------------------------- */
+
+/* SGD with momentum + weight decay for K client rows at once, optional FoolsGold raw-gradient accumulation.
+ * Reference: torch.optim.SGD use in image_train.py:33-35,102 and the grad-sum loop image_train.py:94-100. */
+int dba_sgd_step(float* W, long long ldw, float* V, const float* Gr, float* S, long long ldv, const float* lr,
+                 const unsigned char* active, int K, long long Dp, float mu, float wd, void* stream);
+
+/* Poison scaling W[k] = A[k] + (W[k]-A[k])*s[k].  Reference: image_train.py:166-171, loan_train.py:154-160. */
+int dba_scale_rows(float* W, long long ldw, const float* A, long long lda, const float* s, int K, long long D,
+                   void* stream);
+
+/* out[k] = ||X[k] - Y[k] - Z|| (or its square), fp64, deterministic two-stage reduction through `scratch`
+ * (dba_rows_sqdist_scratch_elems(K) doubles).  Reference: helper.py:60-71 (norms), 376-381 (l2dist). */
+long long dba_rows_sqdist_scratch_elems(int K);
+int dba_rows_sqdist(const float* X, long long ldx, const float* Y, long long ldy, const float* Z, int K, long long n,
+                    double* out, int take_sqrt, double* scratch, long long scratch_elems, void* stream);
+
+/* FedAvg: G += coef * sum_k (W[k]-G) (+ sigma*N(0,1)), optionally writes the new G back into every row of W.
+ * Reference: helper.py:193-257 (accumulate_weight + average_shrink_models), dp_noise helper.py:187-191. */
+int dba_fedavg_update(float* G, float* W, long long ldw, int K, long long D, float coef, float sigma,
+                      unsigned long long seed, int bcast, void* stream);
+
+/* RFA / Weiszfeld loop run entirely on the device.  Reference: helper.py:295-418. */
+int dba_weiszfeld(const float* W, long long ldw, const float* G, int n, long long D, const float* alphas, int maxiter,
+                  float eps, double ftol, float* median, double* dist, float* wts, float* wv, double* obj, int* state,
+                  double* scratch, long long scratch_elems, void* stream);
+
+/* FoolsGold: history update + fp64 Gram + cosine / pardoning / logit weights; then the weighted gradient reduce fused
+ * with the server SGD step.  Reference: helper.py:527-607 and 259-293. */
+int dba_foolsgold_weights(double* history, long long ldh, const int* ids, const float* feat, long long ldf, int n,
+                          long long L, int use_memory, double* work_rows, double* gram, double* cs, double* wv,
+                          double* alpha, void* stream);
+int dba_foolsgold_apply(float* G, const float* S, long long lds, const double* wv, int K, long long Dp,
+                        float eta_over_n, float lr, float decay, void* stream);
+
+/* ---- tensor-core convolution (csrc/conv_tc.cu, csrc/wgrad_tc.cu) ----------------------------------------------- */
+
+/* Rows of one planar-8 / shared-halo activation plane for B images of H x W. */
+long long dba_conv_rows(int B, int H, int W);
+
+/* Batched-client implicit-GEMM convolution (3x3 pad 1 or 1x1; stride via sub = 2) on tcgen05 / TMEM with fused
+ * scale-shift (folded BatchNorm) + residual + ReLU epilogue, or raw output + BatchNorm statistics.
+ * Reference: nn.Conv2d / BatchNorm2d / relu / residual in models/resnet_cifar.py:20-35,89. */
+int dba_conv_tc(const void* X, const void* Wt, void* Y, const void* Res, const float* scale, const float* shift,
+                float* stats, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub, int relu,
+                int x_shared, int reserved, void* stream);
+int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                        const float* scale, const float* shift, long long ss_stride, float* stats,
+                        long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                        int relu, int x_shared, void* stream);
+
+/* Convolution weight gradient (autograd of nn.Conv2d; image_train.py:91,209) added into the fp32 gradient slab. */
+int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
+                 int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream);
+
+/* ---- network plumbing (csrc/net_ops.cu, csrc/bn_ops.cu) -------------------------------------------------------- */
+
+/* fp32 master weights ([Cout][taps][Cin]) -> packed bf16 operand layouts (forward + transposed). */
+int dba_pack_weights(const float* W, long long ldw, const int* table, int n_layers, int K, void* dst,
+                     long long dst_client_stride, void* stream);
+/* Evaluation-mode BatchNorm folded to per-channel scale / shift. */
+int dba_bn_fold(const float* W, long long ldw, const int* table, int n_layers, int K, float* scale, float* shift,
+                long long ld_out, float eps, void* stream);
+/* uint8 gather + /255 + trigger stamping + flip + stem im2col.  Reference: image_helper.py:289-350. */
+int dba_input_stage_image(const void* data, const long long* labels, const long long* idx, long long ld_idx,
+                          const void* trig, const long long* trig_row, const long long* poison_n, const void* flip,
+                          void* out, int* labels_out, int K, int B, int Hi, int Wi, int C, int ks, int stride, int pad,
+                          int Ho, int Wo, int KP, int label_swap, long long R, void* stream);
+/* avg-pool + linear + cross-entropy + accuracy counters (+ backward).  Reference: resnet_cifar.py:94-96,
+ * image_train.py:85,104-105, test.py:20-24. */
+int dba_head(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat, long long ldg,
+             void* dact, const int* labels, int shared_labels, const int* nvalid, const long long* slot,
+             float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag, int K, int B, int C, int H, int W,
+             int ncls, long long R, void* stream);
+/* Training-mode BatchNorm forward (apply) and backward.  Reference: nn.BatchNorm2d in resnet_cifar.py:20-35. */
+int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long long ld_stats, int stats_off,
+                 float* saved, long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off,
+                 int rm_off, int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H,
+                 int W, long long R, int relu, float momentum, float eps, void* stream);
+int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, void* gmask, float* sums,
+                    long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
+                    long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
+                    int B, int H, int W, long long R, int up, long long Rup, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DBA_B200_H */

@@ -1,0 +1,124 @@
+"""Native ResNet executor (tcgen05 conv chain, bf16) vs the batched torch formulation (fp32) on a B200."""
+import pytest
+import torch
+import yaml
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(train=1500, test=700, **over):
+    from dba_mod_b200.config import Params
+    from dba_mod_b200.data import ImageData
+    from dba_mod_b200.models import initial_state
+    raw = yaml.safe_load(open("utils/cifar_params.yaml"))
+    raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=train, synthetic_test_size=test,
+               number_of_total_participants=20, **over)
+    p = Params(raw)
+    dev = torch.device("cuda", 0)
+    data = ImageData(p, dev)
+    spec, flat, cnt = initial_state("cifar", 1)
+    return p, dev, data, spec, flat.to(dev)
+
+
+def test_native_eval_matches_torch(native_lib):
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    from dba_mod_b200.fl.torch_backend import TorchBackend
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    p, dev, data, spec, flat = _setup()
+    torch.manual_seed(0)
+    M = 3
+    models = flat[None].repeat(M, 1)
+    models[:, :spec.Dp] += 0.02 * torch.randn(M, spec.Dp, device=dev)
+    models[:, spec.Dp:] = torch.rand(M, spec.Db, device=dev) * 0.5 + 0.25     # running mean / var
+    tb = TorchBackend(p, spec, data, dev)
+    nx = NativeResNet(p, spec, data, dev)
+    nx.eval_chunk = 256
+    for split, trig in [("clean", 0), ("poison", 0), ("poison", 2)]:
+        l0, c0, n0 = tb.evaluate(models, split, trig)
+        l1, c1, n1 = nx.evaluate(models, split, trig)
+        torch.cuda.synchronize()
+        assert n0 == n1
+        rel = ((l1 - l0).abs() / l0.abs()).max().item()
+        assert rel < 0.03, (split, trig, l0.tolist(), l1.tolist())
+        assert (c1 - c0).abs().max().item() <= max(3, 0.03 * n0), (c0.tolist(), c1.tolist())
+
+
+def _one_step_schedule(p, data, names, dev, T=1):
+    from dba_mod_b200.fl.schedule import build_schedule, plan_clients
+    plans = plan_clients(p, data, names, epoch=1)
+    g = torch.Generator(device=dev).manual_seed(5)
+    return build_schedule(p, data, plans, 1, dev, g)
+
+
+def test_native_train_gradients_match_autograd(native_lib):
+    """One SGD step of K=3 clients (one of them poisoning): per-tensor gradients of the native bf16 pipeline vs fp32
+    autograd of the batched torch formulation.
+
+    Tolerance calibration (tools/gpu_calib_bf16.py, profiles/calib_bf16_vs_fp32.txt): torch's own bf16 autocast of this
+    network at random init agrees with its fp32 gradients to cosine 0.918 (stem) ... 0.985 (layer4.1.conv2), 1.000
+    (linear) with norm ratios within 1.5 %; batch-statistics BatchNorm + ReLU make early-layer gradients that
+    sensitive to activation rounding.  The native pipeline measures 0.93 ... 0.99, 1.000 on the same scale."""
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    from dba_mod_b200.fl.torch_backend import TorchBackend
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    p, dev, data, spec, flat = _setup(train=1280, test=200, sampling_dirichlet=False,
+                                      **{"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 1,
+                                         "lr": 0.0, "poison_lr": 0.0})
+    names = [17, 3, 5]
+    sch = _one_step_schedule(p, data, names, dev)
+    assert sch.T == 1 and bool((sch.idx >= 0).all())
+    K = len(names)
+    torch.manual_seed(0)
+    W0 = flat[None].repeat(K, 1)
+    W0[:, :spec.Dp] += 0.01 * torch.randn(K, spec.Dp, device=dev)
+    cnt = torch.zeros(K, spec.n_counters, dtype=torch.long, device=dev)
+    # reference: grad_sum with lr = 0 is exactly the sum of raw gradients over the T steps
+    tb = TorchBackend(p, spec, data, dev)
+    Wt = W0.clone()
+    rt = tb.train(sch, Wt, cnt.clone(), W0.clone(), True)
+    nx = NativeResNet(p, spec, data, dev)
+    Wn = W0.clone()
+    rn = nx.train(sch, Wn, cnt.clone(), W0.clone(), True)
+    torch.cuda.synchronize()
+    bad = []
+    for name in spec.param_names:
+        e = spec.entries[name]
+        a = rt.grad_sum[:, e.offset:e.offset + e.numel]
+        b = rn.grad_sum[:, e.offset:e.offset + e.numel]
+        cos = torch.nn.functional.cosine_similarity(a, b, dim=1).min().item()
+        ratio = (b.norm(dim=1) / a.norm(dim=1).clamp(min=1e-12))
+        if not (cos >= 0.90) or not ((ratio - 1).abs().max().item() <= 0.1):
+            bad.append((name, round(cos, 4), [round(float(v), 3) for v in ratio]))
+    assert not bad, bad
+    # metrics of the step and BatchNorm running statistics
+    torch.testing.assert_close(rn.count, rt.count)
+    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, rtol=3e-2, atol=3e-2)
+    torch.testing.assert_close(Wn[:, spec.Dp:], Wt[:, spec.Dp:], rtol=5e-2, atol=5e-3)
+
+
+def test_native_train_multi_step_tracks_torch(native_lib):
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    from dba_mod_b200.fl.torch_backend import TorchBackend
+    torch.backends.cudnn.allow_tf32 = False
+    p, dev, data, spec, flat = _setup(train=1500, test=200, **{"0_poison_epochs": [1], "internal_epochs": 2,
+                                                               "internal_poison_epochs": 3, "lr": 0.05})
+    names = [17, 3]
+    sch = _one_step_schedule(p, data, names, dev)
+    K = len(names)
+    W0 = flat[None].repeat(K, 1)
+    cnt = torch.zeros(K, spec.n_counters, dtype=torch.long, device=dev)
+    tb = TorchBackend(p, spec, data, dev)
+    nx = NativeResNet(p, spec, data, dev)
+    Wt, Wn, ct, cn = W0.clone(), W0.clone(), cnt.clone(), cnt.clone()
+    rt = tb.train(sch, Wt, ct, W0.clone(), False)
+    rn = nx.train(sch, Wn, cn, W0.clone(), False)
+    torch.cuda.synchronize()
+    assert torch.equal(ct, cn)
+    dt, dn = (Wt - W0)[:, :spec.Dp], (Wn - W0)[:, :spec.Dp]
+    cos = torch.nn.functional.cosine_similarity(dt, dn, dim=1)
+    assert bool(torch.isfinite(dn).all()) and cos.min().item() > 0.8, cos.tolist()
+    assert ((dn.norm(dim=1) / dt.norm(dim=1)) - 1).abs().max().item() < 0.15
+    torch.testing.assert_close(rn.count, rt.count)
+    torch.testing.assert_close(rn.poison_count, rt.poison_count)
