@@ -161,6 +161,55 @@ extern "C" int dba_rows_sqdist(const float* X, long long ldx, const float* Y, lo
   return DBA_OK;
 }
 
+// --------------------------------------------------------------------------- row distances without a scratch argument
+// Same computation as dba_rows_sqdist, for callers that have no buffer to hand in as scratch and must not create
+// one: a process that has given all device memory to its own pool (so cudaMalloc fails or fragments it), or a side
+// thread - say a monitor sampling update norms next to a running training stream - for which cudaMalloc / cudaFree
+// are off limits because they synchronise the whole device.  The partial sums live in a fixed array inside the
+// library image instead; every GPU that loads the library carries these 64 KiB until the process exits.
+//
+// Limits and rules for the caller:
+//   * at most DBA_NOALLOC_MAX_ROWS (= 64) rows per call; more is refused with an error, nothing is launched;
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress with that device
+//     current) and remembers it - make that first call during start-up, before any stream capture begins;
+//   * all calls share the one array, which still holds the previous call's partial sums.  Nothing has to start at
+//     zero: stage 1 overwrites every slot stage 2 reads.  But two calls whose kernels can overlap on the GPU
+//     (different streams, no ordering between them) race on it - order them yourself;
+//   * no cudaMalloc, cudaFree or other allocating routine is called, here or in anything this function calls.
+#define DBA_NOALLOC_MAX_ROWS 64
+static __device__ __align__(256) double g_noalloc_sqdist_scratch[DBA_NOALLOC_MAX_ROWS * DBA_SQDIST_BLOCKS];
+#define DBA_NOALLOC_MAX_DEVICES 64
+static double* g_noalloc_scratch_addr[DBA_NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern "C" int dba_rows_sqdist_noalloc_max_rows() { return DBA_NOALLOC_MAX_ROWS; }
+
+extern "C" int dba_rows_sqdist_noalloc(const float* X, long long ldx, const float* Y, long long ldy, const float* Z,
+                                       int K, long long n, double* out, int take_sqrt, void* stream) {
+  DBA_REQUIRE(K > 0 && n > 0, "dba_rows_sqdist_noalloc: K=%d n=%lld", K, n);
+  if (K > DBA_NOALLOC_MAX_ROWS) {
+    dba_set_error("dba_rows_sqdist_noalloc: %d rows exceed the built-in scratch (max %d rows per call); split the "
+                  "call or use dba_rows_sqdist with your own scratch buffer", K, DBA_NOALLOC_MAX_ROWS);
+    return DBA_ERR_LIMIT;
+  }
+  int dev = -1;
+  DBA_CHECK_CUDA(cudaGetDevice(&dev));
+  DBA_REQUIRE(dev >= 0 && dev < DBA_NOALLOC_MAX_DEVICES, "dba_rows_sqdist_noalloc: device index %d not supported", dev);
+  if (g_noalloc_scratch_addr[dev] == nullptr) {
+    // In host code the array's name is only a handle; the device address of this device's copy has to be asked for.
+    double* p = nullptr;
+    DBA_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_sqdist_scratch));
+    DBA_REQUIRE(p != nullptr, "dba_rows_sqdist_noalloc: no device address for the built-in scratch");
+    g_noalloc_scratch_addr[dev] = p;
+  }
+  double* scratch = g_noalloc_scratch_addr[dev];
+  dim3 g(DBA_SQDIST_BLOCKS, K);
+  sqdist_stage1<<<g, 256, 0, (cudaStream_t)stream>>>(X, ldx, Y, ldy, Z, n, scratch);
+  sqdist_stage2<<<K, 32, 0, (cudaStream_t)stream>>>(scratch, DBA_SQDIST_BLOCKS, out, take_sqrt);
+  DBA_COUNT_LAUNCH(2);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
 // --------------------------------------------------------------------------------------------------- FedAvg
 // Single-GPU fused form of  delta extraction (K13) + accumulate (R2) + apply (K15) + DP noise (K18) + next round's
 // global->client broadcast (R1):   G[i] += coef * sum_k (W[k,i] - G[i]) + sigma * N(0,1);   W[k,i] = G[i] if bcast.

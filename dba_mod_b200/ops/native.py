@@ -51,6 +51,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_scale_rows", [P, L, P, L, P, I, L, P])
     _sig(lib, "dba_rows_sqdist_scratch_elems", [I], c_longlong)
     _sig(lib, "dba_rows_sqdist", [P, L, P, L, P, I, L, P, I, P, L, P])
+    _sig(lib, "dba_rows_sqdist_noalloc_max_rows", [], c_int)
+    _sig(lib, "dba_rows_sqdist_noalloc", [P, L, P, L, P, I, L, P, I, P])
     _sig(lib, "dba_fedavg_update", [P, P, L, I, L, F, F, U, I, P])
     _sig(lib, "dba_weiszfeld", [P, L, P, I, L, P, I, F, D, P, P, P, P, P, P, P, L, P])
     _sig(lib, "dba_foolsgold_weights", [P, L, P, P, L, I, L, I, P, P, P, P, P, P])

@@ -32,6 +32,16 @@ long long dba_rows_sqdist_scratch_elems(int K);
 int dba_rows_sqdist(const float* X, long long ldx, const float* Y, long long ldy, const float* Z, int K, long long n,
                     double* out, int take_sqrt, double* scratch, long long scratch_elems, void* stream);
 
+/* dba_rows_sqdist without the scratch argument, for callers that cannot allocate device memory (all of it is in
+ * their own pool, or cudaMalloc's device-wide synchronisation is not acceptable where they run).  The partial sums
+ * go to a 64 KiB array built into the library, so: at most dba_rows_sqdist_noalloc_max_rows() (64) rows per call,
+ * larger calls are refused; the first call on a device resolves the array's address and should happen before any
+ * stream capture; calls that may overlap on the GPU race on the shared array.  No counterpart in the reference
+ * (it has no native code and no scratch buffers). */
+int dba_rows_sqdist_noalloc_max_rows(void);
+int dba_rows_sqdist_noalloc(const float* X, long long ldx, const float* Y, long long ldy, const float* Z, int K,
+                            long long n, double* out, int take_sqrt, void* stream);
+
 /* FedAvg: G += coef * sum_k (W[k]-G) (+ sigma*N(0,1)), optionally writes the new G back into every row of W.
  * Reference: helper.py:193-257 (accumulate_weight + average_shrink_models), dp_noise helper.py:187-191. */
 int dba_fedavg_update(float* G, float* W, long long ldw, int K, long long D, float coef, float sigma,
