@@ -83,9 +83,19 @@ def plan_clients(params, data, names: List, epoch: int, poison_lr_override: Opti
     return plans
 
 
+def _stable_id(name) -> int:
+    import zlib
+    return int(name) if isinstance(name, int) else zlib.crc32(str(name).encode())
+
+
 def build_schedule(params, data, plans: List[ClientPlan], epoch: int, device: torch.device,
                    generator: Optional[torch.Generator] = None) -> RoundSchedule:
+    """Sample orders are drawn from a stream keyed by (seed, global epoch, client name), so a client sees the same
+    batches no matter which rank / slot it lands on (world-size invariance of the whole simulation)."""
     K = len(plans)
+    if generator is None:
+        generator = torch.Generator(device=device)
+    base_seed = (int(params["seed"]) * 1000003 + int(epoch)) * 1000003
     B = int(params["batch_size"])
     steps = [p.n_epochs * p.nb for p in plans]
     T = max(steps) if steps else 0
@@ -98,6 +108,7 @@ def build_schedule(params, data, plans: List[ClientPlan], epoch: int, device: to
         if p.n_samples == 0 or p.n_epochs == 0:
             continue
         table = data.client_index_tensor(p.name)
+        generator.manual_seed((base_seed + _stable_id(p.name)) % (2 ** 63 - 1))
         keys = torch.rand(p.n_epochs, p.n_samples, device=device, generator=generator)
         order = table[keys.argsort(dim=1)]                                    # [E, n] fresh order per epoch
         pad = p.nb * B - p.n_samples
@@ -114,5 +125,8 @@ def build_schedule(params, data, plans: List[ClientPlan], epoch: int, device: to
     trig_row = torch.tensor([max(p.trig_row, 0) for p in plans], dtype=torch.long, device=device)
     flip = None
     if getattr(data, "train_flip", False):
-        flip = torch.rand(K, max(T, 1), B, device=device, generator=generator) < 0.5
+        flip = torch.zeros(K, max(T, 1), B, dtype=torch.bool, device=device)
+        for k, p in enumerate(plans):
+            generator.manual_seed((base_seed + 7 + _stable_id(p.name)) % (2 ** 63 - 1))
+            flip[k] = torch.rand(max(T, 1), B, device=device, generator=generator) < 0.5
     return RoundSchedule(epoch, plans, idx, lr, active, epoch_of, poison_n, trig_row, flip, T, E_max, steps)

@@ -83,6 +83,7 @@ class Simulator:
         self.np_rng = np.random.RandomState(seed)
         self.torch_gen = torch.Generator(device=self.device).manual_seed(seed + 7919 * self.rank)
         self.noise_gen = torch.Generator(device=self.device).manual_seed(seed + 104729)
+        self.sched_gen = torch.Generator(device=self.device)
 
         name = params.get("name") or C.DEFAULT_NAME[params["type"]]
         self.name = name
@@ -272,7 +273,7 @@ class Simulator:
                 anchor, anchor_cnt = W.clone(), cnt.clone()
                 lr_override = self._loan_adaptive_lr(my_names, seg_epoch, W)
                 plans = plan_clients(p, self.data, my_names, seg_epoch, lr_override)
-                sch = build_schedule(p, self.data, plans, seg_epoch, dev, self.torch_gen)
+                sch = build_schedule(p, self.data, plans, seg_epoch, dev, self.sched_gen)
                 res = be.train(sch, W, cnt, anchor, use_fg, generator=self.torch_gen)
                 rep.steps += sch.T
                 if use_fg:
