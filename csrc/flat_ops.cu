@@ -19,6 +19,8 @@ void dba_set_error(const char* fmt, ...) {
 }
 extern "C" unsigned long long dba_launch_count() { return g_dba_launches; }
 extern "C" void dba_reset_launch_count() { g_dba_launches = 0; }
+// Kernels launched by replaying a captured CUDA graph are accounted for by the caller (n per replay).
+extern "C" void dba_add_launch_count(unsigned long long n) { g_dba_launches += n; }
 
 using namespace dba;
 

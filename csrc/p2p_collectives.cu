@@ -1,0 +1,192 @@
+// Fused compute + collective kernels over NVLink peer memory (one process per GPU, buffers exchanged through
+// torch.distributed._symmetric_memory; no NCCL call on these paths).
+//
+// Reference: the reduction / broadcast points R1-R4 of SURVEY §2.3 - helper.py:193-257 (FedAvg accumulate + apply),
+// helper.py:295-418 (Weiszfeld weighted averages), helper.py:534-572 (FoolsGold gather + weighted reduce), and the
+// global->client copy image_train.py:26-32.  The reference does them with Python loops on one device.
+//
+// Protocol.  Every rank launches the same kernel on its own GPU.  `peers[q]` are the device addresses of rank q's
+// symmetric staging buffer, global-model replica and signal pad, mapped into this process.  A kernel has up to three
+// phases separated by a cross-GPU barrier:
+//   phase 1  local K-way reduce of the client rows into this rank's staging vector (plain HBM traffic);
+//   barrier  (grid-wide arrival counter -> last block publishes this rank's ticket in every peer's signal pad with
+//            st.release.sys; every block then spins with ld.acquire.sys until all peers' tickets arrived);
+//   phase 2  rank r owns slice r of the vector: it loads that slice from every peer's staging buffer (P2P loads),
+//            applies the update (FedAvg scale + DP noise / plain sum) and stores the result into EVERY peer's replica
+//            (P2P stores) - reduce-scatter + update + all-gather in one launch, tile by tile;
+//   barrier  so that nobody reads a replica before all slices landed.
+// Tickets grow monotonically per call, so signal pads never need to be cleared.  All blocks of a launch must be
+// co-resident (grid <= 148): they wait on one another.
+#include "common.cuh"
+#include <curand_kernel.h>
+
+using namespace dba;
+
+namespace {
+
+constexpr int kMaxRanks = 8;
+
+struct PeerSet {
+  float* stage[kMaxRanks];        // [D] partial sums of each rank
+  float* replica[kMaxRanks];      // [D] global model (or any broadcast target) of each rank
+  unsigned int* signal[kMaxRanks];  // [2 * kMaxRanks] tickets: slot phase*kMaxRanks + sender
+  int rank, world;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Cross-GPU barrier usable inside a kernel whose blocks are all resident.  `counter` is a per-GPU arrival counter
+// (monotonic), `ticket` identifies (call, phase).
+__device__ void grid_and_peer_barrier(const PeerSet& ps, unsigned int* counter, unsigned int arrivals_target,
+                                      int phase, unsigned int ticket) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned int prev = atomicAdd(counter, 1u);
+    if (prev + 1 == arrivals_target) {        // last block of this GPU: publish to every peer (incl. self)
+      for (int q = 0; q < ps.world; ++q) st_release_sys(ps.signal[q] + phase * kMaxRanks + ps.rank, ticket);
+    }
+    for (int q = 0; q < ps.world; ++q) {
+      const unsigned int* flag = ps.signal[ps.rank] + phase * kMaxRanks + q;
+      while ((int)(ld_acquire_sys(flag) - ticket) < 0) { __nanosleep(64); }
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+}
+
+// F1: FedAvg fused with delta extraction, cross-GPU reduce, global update (+DP noise) and broadcast of the new model
+// into every replica (and, optionally, into this rank's client rows for the next round = R1).
+__global__ void __launch_bounds__(256) fedavg_p2p_kernel(const float* __restrict__ W, long long ldw, int K, long long D,
+                                                         float coef, float sigma, unsigned long long seed,
+                                                         PeerSet ps, unsigned int* counter, unsigned int call_id,
+                                                         int total_clients) {
+  const float* G = ps.replica[ps.rank];
+  float* stage = ps.stage[ps.rank];
+  // phase 1: local sum of client states (the -K*G term is applied once, in phase 2, with the global client count)
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < D; i += (long long)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int k = 0; k < K; ++k) acc += W[k * ldw + i];
+    stage[i] = acc;
+  }
+  grid_and_peer_barrier(ps, counter, (2 * call_id + 1) * gridDim.x, 0, 2 * call_id + 1);
+  // phase 2: this rank reduces + updates its slice and scatters it to all replicas
+  const long long per = (D + ps.world - 1) / ps.world;
+  const long long lo = per * ps.rank, hi = min(D, lo + per);
+  for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int q = 0; q < ps.world; ++q) acc += ps.stage[q][i];
+    const float g = G[i];
+    float out = g + coef * (acc - (float)total_clients * g);
+    if (sigma > 0.f) {
+      curandStatePhilox4_32_10_t st;
+      curand_init(seed, (unsigned long long)i, 0, &st);
+      out += sigma * curand_normal(&st);
+    }
+    for (int q = 0; q < ps.world; ++q) ps.replica[q][i] = out;
+  }
+  grid_and_peer_barrier(ps, counter, (2 * call_id + 2) * gridDim.x, 1, 2 * call_id + 2);
+}
+
+// Generic fused all-reduce (sum) of the ranks' staging vectors into every replica:  replica[q][i] = beta*replica[q][i]
+// + alpha * sum_r stage[r][i].  Used per Weiszfeld iteration (median) and for FoolsGold's weighted gradient reduce
+// fused with the server SGD step (alpha = -lr*eta/n, beta = 1 - lr*decay).
+__global__ void __launch_bounds__(256) allreduce_axpby_p2p_kernel(long long D, float alpha, float beta, PeerSet ps,
+                                                                  unsigned int* counter, unsigned int call_id) {
+  grid_and_peer_barrier(ps, counter, (2 * call_id + 1) * gridDim.x, 0, 2 * call_id + 1);
+  const long long per = (D + ps.world - 1) / ps.world;
+  const long long lo = per * ps.rank, hi = min(D, lo + per);
+  const float* mine = ps.replica[ps.rank];
+  for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int q = 0; q < ps.world; ++q) acc += ps.stage[q][i];
+    const float out = (beta != 0.f ? beta * mine[i] : 0.f) + alpha * acc;
+    for (int q = 0; q < ps.world; ++q) ps.replica[q][i] = out;
+  }
+  grid_and_peer_barrier(ps, counter, (2 * call_id + 2) * gridDim.x, 1, 2 * call_id + 2);
+}
+
+// F3 (gather part): Gram matrix over feature rows that live on DIFFERENT GPUs - rows are read through peer pointers
+// inside the dot-product kernel, so the all-gather is never materialised.
+__global__ void __launch_bounds__(256) gram_ptrs_kernel(const double* const* __restrict__ rows, int n, long long L,
+                                                        double* __restrict__ gram) {
+  __shared__ double red[32];
+  const int i = blockIdx.x, j = blockIdx.y;
+  if (j < i) return;
+  const double* a = rows[i];
+  const double* b = rows[j];
+  double acc = 0.0;
+  for (long long t = threadIdx.x; t < L; t += blockDim.x) acc += a[t] * b[t];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) {
+    gram[(long long)i * n + j] = acc;
+    gram[(long long)j * n + i] = acc;
+  }
+}
+
+static int fill_peers(PeerSet& ps, const void* const* stage, const void* const* replica, const void* const* signal,
+                      int rank, int world) {
+  if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world) return 1;
+  ps.rank = rank;
+  ps.world = world;
+  for (int q = 0; q < world; ++q) {
+    ps.stage[q] = (float*)stage[q];
+    ps.replica[q] = (float*)replica[q];
+    ps.signal[q] = (unsigned int*)signal[q];
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// stage / replica / signal: host arrays of `world` device pointers (peer-mapped symmetric memory).  signal pads need
+// 2*8 uint32 each, zero-initialised once.  counter: one zero-initialised uint32 in local device memory per GPU.
+// call_id: 0, 1, 2, ... identical on all ranks, strictly increasing per (signal pad, counter) pair.
+int dba_fedavg_p2p(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
+                   const void* const* stage, const void* const* replica, const void* const* signal, int rank,
+                   int world, int total_clients, unsigned int* counter, unsigned int call_id, void* stream) {
+  PeerSet ps;
+  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_fedavg_p2p: bad rank/world %d/%d", rank,
+              world);
+  DBA_REQUIRE(K >= 0 && D > 0, "dba_fedavg_p2p: K=%d D=%lld", K, D);
+  fedavg_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(W, ldw, K, D, coef, sigma, seed, ps, counter, call_id,
+                                                              total_clients);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+int dba_allreduce_axpby_p2p(long long D, float alpha, float beta, const void* const* stage,
+                            const void* const* replica, const void* const* signal, int rank, int world,
+                            unsigned int* counter, unsigned int call_id, void* stream) {
+  PeerSet ps;
+  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_allreduce_axpby_p2p: bad rank/world");
+  DBA_REQUIRE(D > 0, "dba_allreduce_axpby_p2p: D=%lld", D);
+  allreduce_axpby_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(D, alpha, beta, ps, counter, call_id);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// rows: DEVICE array of n pointers to fp64 feature rows (local or peer-mapped).
+int dba_gram_ptrs(const double* const* rows, int n, long long L, double* gram, void* stream) {
+  DBA_REQUIRE(n > 0 && n <= 1024 && L > 0, "dba_gram_ptrs: n=%d L=%lld", n, L);
+  dim3 g(n, n);
+  gram_ptrs_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(rows, n, L, gram);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+}  // extern "C"

@@ -97,6 +97,10 @@ _DEFAULTS: Dict[str, Any] = {
     "n_gpus": 0,                  # 0 = all visible
     "fused_collectives": True,    # False = NCCL baseline path for the aggregation collectives
     "multistep_lr_compat": "torch2",  # Q4: 'torch2' (decay only at integral milestones) | 'bisect'
+    "native_net": True,           # cuda backend: use the native tensor-core executor where it covers the model
+    "native_train": True,
+    "native_eval_chunk": 500,     # test images per evaluation pass (per model / input set)
+    "cuda_graphs": True,          # replay the captured training step instead of ~125 launches per step
 }
 
 # Keys that exist in the shipped YAML files but are never read by the reference (App. A).

@@ -86,7 +86,17 @@ class CudaBackend(TorchBackend):
             return self.exec.train(sch, W, cnt, anchor, want_grad_sum)
         return super().train(sch, W, cnt, anchor, want_grad_sum, generator)
 
-    def evaluate(self, models, split, trig_row):
+    def evaluate(self, models, split, trig_row, shard=None):
         if self.native_eval:
-            return self.exec.evaluate(models, split, trig_row)
-        return super().evaluate(models, split, trig_row)
+            return self.exec.evaluate(models, split, trig_row, shard=shard)
+        return super().evaluate(models, split, trig_row, shard=shard)
+
+    def evaluate_pairs(self, models, jobs, shard=None):
+        if self.native_eval:
+            return self.exec.evaluate_pairs(models, jobs, shard=shard)
+        return None
+
+    def evaluate_jobs(self, model, jobs, shard=None):
+        if self.native_eval:
+            return self.exec.evaluate_jobs(model, jobs, shard=shard)
+        return super().evaluate_jobs(model, jobs, shard=shard)

@@ -137,39 +137,102 @@ class NativeResNet:
         return pack[:, l.w_off:l.w_off + n].unflatten(1, (taps, l.cin_p // 8, l.cout_p, 8))
 
     def _conv(self, x, pack, l: ConvL, K, B, out, res=None, scale=None, shift=None, relu=False, stats=None,
-              x_shared=False):
-        """Forward convolution of layer l.  pack rows are strided views -> pass raw pointers."""
+              x_shared=False, w_shared=False):
+        """Forward convolution of layer l.  pack rows are strided views -> pass raw pointers.
+        w_shared: all K input sets are convolved with the SAME model (row 0 of pack / scale / shift)."""
         wt = self._wt(pack, l)
         ks = 1 if l.fold else l.ks
         cin = l.cin_p
         native.check(self.lib.dba_conv_tc_strided(
-            native.ptr(x), native.ptr(wt), pack.stride(0), native.ptr(out), native.ptr(res),
-            native.ptr(scale), native.ptr(shift), scale.stride(0) if scale is not None else 0, native.ptr(stats),
+            native.ptr(x), native.ptr(wt), 0 if w_shared else pack.stride(0), native.ptr(out), native.ptr(res),
+            native.ptr(scale), native.ptr(shift),
+            (0 if w_shared else scale.stride(0)) if scale is not None else 0, native.ptr(stats),
             stats.stride(0) if stats is not None else 0, K, B, l.H, l.H, cin, l.cout_p, ks, l.sub, int(relu),
             int(x_shared), native.stream()))
         return out
 
     # ------------------------------------------------------------------------------------------ evaluation
-    def _ebufs(self, M: int, Bt: int) -> dict:
-        key = (M, Bt)
+    def _ebufs(self, M: int, Bt: int, per_job_input: bool = False) -> dict:
+        key = (M, Bt, per_job_input)
         if key in self._eval_bufs:
             return self._eval_bufs[key]
         dev = self.device
         z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
-        bufs = {"stem_in": z(1, 32, 32), "lv": {}}
+        kin = M if per_job_input else 1
+        bufs = {"stem_in": z(kin, 32, 32), "lv": {}}
         for w, r in zip([32, 64, 128, 256], [32, 16, 8, 4]):
             bufs["lv"][r] = [z(M, w, r) for _ in range(4)]
-        bufs["labels"] = torch.zeros(1, Bt, dtype=torch.int32, device=dev)
+        bufs["labels"] = torch.zeros(kin, Bt, dtype=torch.int32, device=dev)
         bufs["idx"] = torch.full((1, Bt), -1, dtype=torch.long, device=dev)
         self._eval_bufs[key] = bufs
         return bufs
 
+    @staticmethod
+    def _shard(ids: torch.Tensor, shard) -> torch.Tensor:
+        if shard is None:
+            return ids
+        r, w = shard
+        n = ids.numel()
+        per = (n + w - 1) // w
+        return ids[r * per:min(n, (r + 1) * per)]
+
     @torch.no_grad()
-    def evaluate(self, models: torch.Tensor, split: str, trig_row: int):
+    def evaluate_jobs(self, model: torch.Tensor, jobs, shard=None):
+        """ONE model on several input sets at once: jobs = [(split, trig_row), ...] (e.g. the round's global clean /
+        combined-trigger / per-trigger evaluations, main.py:198-231).  The J input sets take the place of the client
+        dimension and all of them are convolved with the same packed weights (client stride 0).
+        Returns [(loss_sum, correct, n)] per job (sums over this rank's shard of each split)."""
+        return self._eval_general(model.reshape(1, -1), jobs, True, shard)
+
+    @torch.no_grad()
+    def evaluate_pairs(self, models: torch.Tensor, jobs, shard=None):
+        """P (model, input set) pairs in one batched pass: models [P, Df], jobs = [(split, trig_row)] * P.  This is
+        how all per-client evaluations that follow local training (image_train.py:148-164,268-295: clean test of
+        every client, the attackers' pre-/post-scaling backdoor tests and local-trigger tests) run together."""
+        return self._eval_general(models, jobs, False, shard)
+
+    def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None):
+        d, dev, lib = self.data, self.device, self.lib
+        J = len(jobs)
+        Bt = self.eval_chunk
+        models = models.contiguous()
+        Mw = models.shape[0]
+        pack = self.pack_weights(models)
+        scale = torch.empty(Mw, self.bn_total, device=dev)
+        shift = torch.empty(Mw, self.bn_total, device=dev)
+        native.check(lib.dba_bn_fold(native.ptr(models), models.stride(0), native.ptr(self.fold_table),
+                                     len(self.layers), Mw, native.ptr(scale), native.ptr(shift), scale.stride(0),
+                                     BN_EPS, native.stream()))
+        id_sets = [self._shard(d.all_test_idx if sp == "clean" else d.poison_test_idx, shard) for sp, _ in jobs]
+        ns = [int(t.numel()) for t in id_sets]
+        nmax = max(ns) if ns else 0
+        bufs = self._ebufs(J, Bt, per_job_input=True)
+        mf = torch.zeros(J, 1, device=dev)
+        mi = torch.zeros(J, 1, 2, dtype=torch.int32, device=dev)
+        trow = torch.tensor([max(tr, 0) for _, tr in jobs], dtype=torch.long, device=dev)
+        pn = torch.tensor([Bt if sp == "poison" else 0 for sp, _ in jobs], dtype=torch.long, device=dev)
+        idx_all = torch.full((J, (nmax + Bt - 1) // Bt * Bt if nmax else Bt), -1, dtype=torch.long, device=dev)
+        for j, t in enumerate(id_sets):
+            idx_all[j, :t.numel()] = t
+        labels = bufs["labels"]
+        for s in range(0, nmax, Bt):
+            idx = idx_all[:, s:s + Bt]
+            self._forward_eval(J, Bt, idx, trow, pn, pack, scale, shift, bufs, labels, per_job=True,
+                               ld_idx=idx_all.stride(0), w_shared=w_shared)
+            a = bufs["out"]
+            native.check(lib.dba_head(native.ptr(a), native.ptr(models), 0 if w_shared else models.stride(0),
+                                      self.head_w_off, self.head_b_off, None, 0, None, native.ptr(labels), 0, None,
+                                      None, native.ptr(mf), native.ptr(mi), 1, None, J, Bt, 256, 4, 4, self.ncls,
+                                      Geom(Bt, 4, 4).rows, native.stream()))
+        mf_c, mi_c = mf.cpu(), mi.cpu()
+        return [(float(mf_c[j, 0]), int(mi_c[j, 0, 0]), ns[j]) for j in range(J)]
+
+    @torch.no_grad()
+    def evaluate(self, models: torch.Tensor, split: str, trig_row: int, shard=None):
         d, dev, lib = self.data, self.device, self.lib
         M = models.shape[0]
         Bt = self.eval_chunk
-        ids_all = d.all_test_idx if split == "clean" else d.poison_test_idx
+        ids_all = self._shard(d.all_test_idx if split == "clean" else d.poison_test_idx, shard)
         n = int(ids_all.numel())
         models = models.contiguous()
         pack = self.pack_weights(models)
@@ -196,14 +259,17 @@ class NativeResNet:
                                       Geom(Bt, 4, 4).rows, native.stream()))
         return mf[:, 0].double(), mi[:, 0, 0].long(), n
 
-    def _forward_eval(self, M, Bt, idx, trow, pn, pack, scale, shift, bufs, labels) -> None:
+    def _forward_eval(self, M, Bt, idx, trow, pn, pack, scale, shift, bufs, labels, per_job=False,
+                      ld_idx=None, w_shared=None) -> None:
         d, lib = self.data, self.lib
         stem = self.layers[0]
         xin = bufs["stem_in"]
         native.check(lib.dba_input_stage_image(
-            native.ptr(d.test_x), native.ptr(d.test_y), native.ptr(idx), idx.stride(0), native.ptr(self.trig_u8),
-            native.ptr(trow), native.ptr(pn), None, native.ptr(xin), native.ptr(labels), 1, Bt, d.H, d.W, d.C,
-            3, 1, 1, 32, 32, stem.cin_p, self.label_swap, xin.shape[2], native.stream()))
+            native.ptr(d.test_x), native.ptr(d.test_y), native.ptr(idx), ld_idx if ld_idx is not None else idx.stride(0),
+            native.ptr(self.trig_u8), native.ptr(trow), native.ptr(pn), None, native.ptr(xin), native.ptr(labels),
+            M if per_job else 1, Bt, d.H, d.W, d.C, 3, 1, 1, 32, 32, stem.cin_p, self.label_swap, xin.shape[2],
+            native.stream()))
+        ws = per_job if w_shared is None else w_shared
 
         def ss(l):
             return scale[:, l.bn_off:l.bn_off + l.cout], shift[:, l.bn_off:l.bn_off + l.cout]
@@ -211,7 +277,7 @@ class NativeResNet:
         lv = bufs["lv"]
         cur = lv[32][0]
         sc_, sh_ = ss(stem)
-        self._conv(xin, pack, stem, M, Bt, cur, scale=sc_, shift=sh_, relu=True, x_shared=True)
+        self._conv(xin, pack, stem, M, Bt, cur, scale=sc_, shift=sh_, relu=True, x_shared=not per_job, w_shared=ws)
         res = 32
         ci = 0
         for (c1, c2, sc) in self.blocks:
@@ -220,16 +286,16 @@ class NativeResNet:
             free = [b for b in pool if b is not cur]
             mid, out, proj = free[0], free[1], free[2] if len(free) > 2 else None
             s1, h1 = ss(c1)
-            self._conv(cur, pack, c1, M, Bt, mid, scale=s1, shift=h1, relu=True)
+            self._conv(cur, pack, c1, M, Bt, mid, scale=s1, shift=h1, relu=True, w_shared=ws)
             if sc is not None:
                 s3, h3 = ss(sc)
                 proj = free[2] if len(free) > 2 else pool[3]
-                self._conv(cur, pack, sc, M, Bt, proj, scale=s3, shift=h3, relu=False)
+                self._conv(cur, pack, sc, M, Bt, proj, scale=s3, shift=h3, relu=False, w_shared=ws)
                 skip = proj
             else:
                 skip = cur
             s2, h2 = ss(c2)
-            self._conv(mid, pack, c2, M, Bt, out, res=skip, scale=s2, shift=h2, relu=True)
+            self._conv(mid, pack, c2, M, Bt, out, res=skip, scale=s2, shift=h2, relu=True, w_shared=ws)
             cur = out
             res = r_out
         bufs["out"] = cur
@@ -260,6 +326,21 @@ class NativeResNet:
         t["sums"] = torch.zeros(K, 2 * self.bn_total, device=dev)
         t["Gr"] = torch.zeros(K, (self.spec.Dp + 3) // 4 * 4, device=dev)
         t["V"] = torch.zeros_like(t["Gr"])
+        t["gs"] = torch.zeros_like(t["Gr"])
+        t["W"] = torch.zeros(K, (self.spec.Df + 3) // 4 * 4, device=dev)
+        t["cnt"] = torch.zeros(K, self.spec.n_counters, dtype=torch.long, device=dev)
+        t["mf"] = torch.zeros(K, 16, device=dev)
+        t["mi"] = torch.zeros(K, 16, 2, dtype=torch.int32, device=dev)
+        t["nan"] = torch.zeros(K, dtype=torch.uint8, device=dev)
+        t["st_idx"] = torch.full((K, B), -1, dtype=torch.long, device=dev)
+        t["st_flip"] = torch.zeros(K, B, dtype=torch.uint8, device=dev)
+        t["st_nvalid"] = torch.zeros(K, dtype=torch.int32, device=dev)
+        t["st_active"] = torch.zeros(K, dtype=torch.uint8, device=dev)
+        t["st_active_l"] = torch.zeros(K, dtype=torch.long, device=dev)
+        t["st_slot"] = torch.zeros(K, dtype=torch.long, device=dev)
+        t["st_lr"] = torch.zeros(K, dtype=torch.float32, device=dev)
+        t["trig_row"] = torch.zeros(K, dtype=torch.long, device=dev)
+        t["poison_n"] = torch.zeros(K, dtype=torch.long, device=dev)
         t["pack"] = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=dev)
         self._train_bufs[K] = t
         return t
@@ -304,109 +385,147 @@ class NativeResNet:
 
     def train(self, sch, W: torch.Tensor, cnt: torch.Tensor, anchor: torch.Tensor, want_grad_sum: bool):
         from .torch_backend import TrainResult
-        p, dev, lib, d = self.params, self.device, self.lib, self.data
-        K, Dp, B = W.shape[0], self.spec.Dp, self.B
+        p, dev = self.params, self.device
+        K, Dp, B, Df = W.shape[0], self.spec.Dp, self.B, self.spec.Df
         if float(p["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any()):
             raise NotImplementedError("alpha_loss != 1 is handled by the torch path")
         E = max(sch.E_max, 1)
         t = self._tbufs(K)
-        Gr, V = t["Gr"], t["V"]
-        V.zero_()
-        grad_sum = torch.zeros_like(Gr) if want_grad_sum else None
-        mf = torch.zeros(K, E, device=dev)
-        mi = torch.zeros(K, E, 2, dtype=torch.int32, device=dev)
-        nan = torch.zeros(K, dtype=torch.uint8, device=dev)
+        if E > t["mf"].shape[1]:
+            raise NotImplementedError(f"more than {t['mf'].shape[1]} internal epochs")
+        # persistent slabs (their addresses are baked into the captured step graph)
+        t["W"][:, :Df].copy_(W[:, :Df])
+        if cnt.numel():
+            t["cnt"].copy_(cnt)
+        for key in ("V", "mf", "mi", "nan", "gs"):
+            t[key].zero_()
+        t["trig_row"].copy_(sch.trig_row)
+        t["poison_n"].copy_(sch.poison_n)
         mask_all = sch.idx >= 0                                              # [K, T, B]
-        nvalid_all = mask_all.sum(2).to(torch.int32).contiguous()            # [K, T]
-        act_all = sch.active.to(torch.uint8).contiguous()
-        lr_all = sch.lr.contiguous()
+        nvalid_all = mask_all.sum(2).to(torch.int32)                         # [K, T]
+        act_all = sch.active.to(torch.uint8)
         ar = torch.arange(B, device=dev)
         sel = (ar[None, None, :] < sch.poison_n[:, None, None]) & mask_all
         pcount = torch.zeros(K, E, dtype=torch.long, device=dev)
         pcount.scatter_add_(1, sch.epoch_of, sel.sum(2) * sch.active)
-        flip = sch.flip.to(torch.uint8).contiguous() if sch.flip is not None else None
-        idx = sch.idx.contiguous()
+        flip = sch.flip.to(torch.uint8) if sch.flip is not None else None
+        use_graph = bool(p.get("cuda_graphs", True))
+        gkey = ("graph", bool(want_grad_sum), flip is not None)
+        for step in range(sch.T):
+            t["st_idx"].copy_(sch.idx[:, step])
+            t["st_nvalid"].copy_(nvalid_all[:, step])
+            t["st_active"].copy_(act_all[:, step])
+            t["st_slot"].copy_(sch.epoch_of[:, step])
+            t["st_lr"].copy_(sch.lr[:, step])
+            if flip is not None:
+                t["st_flip"].copy_(flip[:, step])
+            g = t.get(gkey)
+            if not use_graph:
+                self._step_body(K, t, want_grad_sum, flip is not None)
+            elif g is None:
+                if not t.get(("warm", gkey)):
+                    # first ever step for this K: run eagerly (lazy kernel attributes), then record the graph
+                    self._step_body(K, t, want_grad_sum, flip is not None)
+                    t[("warm", gkey)] = True
+                    continue
+                l0 = native.launch_count()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    self._step_body(K, t, want_grad_sum, flip is not None)
+                t[gkey] = graph
+                t[("nl", gkey)] = native.launch_count() - l0
+                graph.replay()
+            else:
+                g.replay()
+                self.lib.dba_add_launch_count(t[("nl", gkey)])
+        W[:, :Df].copy_(t["W"][:, :Df])
+        if cnt.numel():
+            cnt.copy_(t["cnt"])
+        mf, mi = t["mf"][:, :E].clone(), t["mi"][:, :E].clone()
+        res = TrainResult(t["gs"][:, :Dp].clone() if want_grad_sum else None, mf, mi[:, :, 0].long(),
+                          mi[:, :, 1].long(), pcount, t["nan"].bool().clone())
+        return res
+
+    def _step_body(self, K: int, t: dict, want_grad_sum: bool, with_flip: bool) -> None:
+        """One lock-step SGD step of K clients: ~125 kernel launches, no host decisions (CUDA-graph capturable).
+        All inputs come from the persistent staging tensors st_* filled by train()."""
+        from ..ops import flat
+        lib, d, B, Dp = self.lib, self.data, self.B, self.spec.Dp
+        W, Gr, V = t["W"], t["Gr"], t["V"]
+        nvalid, active, slot = t["st_nvalid"], t["st_active"], t["st_slot"]
+        mf, mi, nan = t["mf"], t["mi"], t["nan"]
         stem = self.layers[0]
         lv_g = {r: t[("g", r)] for r in (32, 16, 8, 4)}
-        for step in range(sch.T):
-            idx_t = idx[:, step]
-            nvalid = nvalid_all[:, step].contiguous()
-            active = act_all[:, step].contiguous()
-            slot = sch.epoch_of[:, step].contiguous()
-            pack = self.pack_weights(W, t["pack"])
-            t["stats"].zero_(); t["sums"].zero_(); Gr.zero_()
-            native.check(lib.dba_input_stage_image(
-                native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(idx_t), idx.stride(0),
-                native.ptr(self.trig_u8), native.ptr(sch.trig_row), native.ptr(sch.poison_n),
-                native.ptr(flip[:, step]) if flip is not None else None, native.ptr(t["xin"]),
-                native.ptr(t["labels"]), K, B, d.H, d.W, d.C, 3, 1, 1, 32, 32, stem.cin_p, self.label_swap,
-                t["xin"].shape[2], native.stream()))
-            st = t["stats"]
+        pack = self.pack_weights(W, t["pack"])
+        t["stats"].zero_(); t["sums"].zero_(); Gr.zero_()
+        native.check(lib.dba_input_stage_image(
+            native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(t["st_idx"]), t["st_idx"].stride(0),
+            native.ptr(self.trig_u8), native.ptr(t["trig_row"]), native.ptr(t["poison_n"]),
+            native.ptr(t["st_flip"]) if with_flip else None, native.ptr(t["xin"]),
+            native.ptr(t["labels"]), K, B, d.H, d.W, d.C, 3, 1, 1, 32, 32, stem.cin_p, self.label_swap,
+            t["xin"].shape[2], native.stream()))
+        st = t["stats"]
 
-            def fconv(l, x, y):
-                self._conv(x, pack, l, K, B, y, stats=st[:, 2 * l.bn_off:], x_shared=False)
+        def fconv(l, x, y):
+            self._conv(x, pack, l, K, B, y, stats=st[:, 2 * l.bn_off:], x_shared=False)
 
-            # ------------------------------------------------------------------ forward
-            y0, a0 = t[("y", stem.name)], t[("a", stem.name)]
-            fconv(stem, t["xin"], y0)
-            self._bn_apply(stem, K, y0, a0, None, True, W, t, nvalid, active)
-            x = a0
-            inputs = []
-            for (c1, c2, sc) in self.blocks:
-                inputs.append(x)
-                y1, a1 = t[("y", c1.name)], t[("a", c1.name)]
-                fconv(c1, x, y1)
-                self._bn_apply(c1, K, y1, a1, None, True, W, t, nvalid, active)
-                y2, out = t[("y", c2.name)], t[("a", c2.name)]
-                fconv(c2, a1, y2)
-                skip = x
-                if sc is not None:
-                    ys, as_ = t[("y", sc.name)], t[("a", sc.name)]
-                    fconv(sc, x, ys)
-                    self._bn_apply(sc, K, ys, as_, None, False, W, t, nvalid, active)
-                    skip = as_
-                self._bn_apply(c2, K, y2, out, skip, True, W, t, nvalid, active)
-                x = out
-            # ------------------------------------------------------------------ head (fwd + bwd)
-            g = lv_g[4][0]
-            native.check(lib.dba_head(native.ptr(x), native.ptr(W), W.stride(0), self.head_w_off, self.head_b_off,
-                                      native.ptr(Gr), Gr.stride(0), native.ptr(g), native.ptr(t["labels"]), 0,
-                                      native.ptr(nvalid), native.ptr(slot), native.ptr(mf), native.ptr(mi), E,
-                                      native.ptr(nan), K, B, 256, 4, 4, self.ncls, x.shape[2], native.stream()))
-            # ------------------------------------------------------------------ backward
-            for bi in range(len(self.blocks) - 1, -1, -1):
-                c1, c2, sc = self.blocks[bi]
-                xin_b = inputs[bi]
-                r_out, r_in = c2.H, c1.H
-                pool_o = [b for b in lv_g[r_out] if b is not g]
-                dz, da1 = pool_o[0], pool_o[1]
-                dy2, dy1 = t[("dy", c2.name)], t[("dy", c1.name)]
-                self._bn_bwd(c2, K, g, t[("y", c2.name)], t[("a", c2.name)], dy2, dz, W, t, nvalid, up=False)
-                self._wgrad(c2, K, dy2, t[("a", c1.name)], t)
-                self._dgrad(c2, K, dy2, pack, da1)
-                self._bn_bwd(c1, K, da1, t[("y", c1.name)], t[("a", c1.name)], dy1, None, W, t, nvalid,
-                             up=(c1.sub == 2))
-                self._wgrad(c1, K, dy1, xin_b, t)
-                pool_i = [b for b in lv_g[r_in] if b is not g and b is not dz and b is not da1]
-                dx = pool_i[0]
-                if sc is None:
-                    self._dgrad(c1, K, dy1, pack, dx, res=dz)
-                else:
-                    dx2 = pool_i[1]
-                    self._dgrad(c1, K, dy1, pack, dx2)
-                    dys = t[("dy", sc.name)]
-                    self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
-                    self._wgrad(sc, K, dys, xin_b, t)
-                    self._dgrad(sc, K, dys, pack, dx, res=dx2)
-                g = dx
-            dy0 = t[("dy", stem.name)]
-            self._bn_bwd(stem, K, g, y0, a0, dy0, None, W, t, nvalid, up=False)
-            self._wgrad(stem, K, dy0, t["xin"], t)
-            # ------------------------------------------------------------------ optimiser
-            from ..ops import flat
-            flat.sgd_step_(W, V, Gr, lr_all[:, step].contiguous(), active, Dp, self.mu, self.wd, grad_sum)
-            if cnt.numel():
-                cnt += active[:, None].long()
-        res = TrainResult(grad_sum[:, :Dp] if grad_sum is not None else None, mf, mi[:, :, 0].long(),
-                          mi[:, :, 1].long(), pcount, nan.bool())
-        return res
+        # ---------------------------------------------------------------------- forward
+        y0, a0 = t[("y", stem.name)], t[("a", stem.name)]
+        fconv(stem, t["xin"], y0)
+        self._bn_apply(stem, K, y0, a0, None, True, W, t, nvalid, active)
+        x = a0
+        inputs = []
+        for (c1, c2, sc) in self.blocks:
+            inputs.append(x)
+            y1, a1 = t[("y", c1.name)], t[("a", c1.name)]
+            fconv(c1, x, y1)
+            self._bn_apply(c1, K, y1, a1, None, True, W, t, nvalid, active)
+            y2, out = t[("y", c2.name)], t[("a", c2.name)]
+            fconv(c2, a1, y2)
+            skip = x
+            if sc is not None:
+                ys, as_ = t[("y", sc.name)], t[("a", sc.name)]
+                fconv(sc, x, ys)
+                self._bn_apply(sc, K, ys, as_, None, False, W, t, nvalid, active)
+                skip = as_
+            self._bn_apply(c2, K, y2, out, skip, True, W, t, nvalid, active)
+            x = out
+        # ---------------------------------------------------------------------- head (fwd + bwd)
+        g = lv_g[4][0]
+        native.check(lib.dba_head(native.ptr(x), native.ptr(W), W.stride(0), self.head_w_off, self.head_b_off,
+                                  native.ptr(Gr), Gr.stride(0), native.ptr(g), native.ptr(t["labels"]), 0,
+                                  native.ptr(nvalid), native.ptr(slot), native.ptr(mf), native.ptr(mi), mf.shape[1],
+                                  native.ptr(nan), K, B, 256, 4, 4, self.ncls, x.shape[2], native.stream()))
+        # ---------------------------------------------------------------------- backward
+        for bi in range(len(self.blocks) - 1, -1, -1):
+            c1, c2, sc = self.blocks[bi]
+            xin_b = inputs[bi]
+            r_out, r_in = c2.H, c1.H
+            pool_o = [b for b in lv_g[r_out] if b is not g]
+            dz, da1 = pool_o[0], pool_o[1]
+            dy2, dy1 = t[("dy", c2.name)], t[("dy", c1.name)]
+            self._bn_bwd(c2, K, g, t[("y", c2.name)], t[("a", c2.name)], dy2, dz, W, t, nvalid, up=False)
+            self._wgrad(c2, K, dy2, t[("a", c1.name)], t)
+            self._dgrad(c2, K, dy2, pack, da1)
+            self._bn_bwd(c1, K, da1, t[("y", c1.name)], t[("a", c1.name)], dy1, None, W, t, nvalid,
+                         up=(c1.sub == 2))
+            self._wgrad(c1, K, dy1, xin_b, t)
+            pool_i = [b for b in lv_g[r_in] if b is not g and b is not dz and b is not da1]
+            dx = pool_i[0]
+            if sc is None:
+                self._dgrad(c1, K, dy1, pack, dx, res=dz)
+            else:
+                dx2 = pool_i[1]
+                self._dgrad(c1, K, dy1, pack, dx2)
+                dys = t[("dy", sc.name)]
+                self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
+                self._wgrad(sc, K, dys, xin_b, t)
+                self._dgrad(sc, K, dys, pack, dx, res=dx2)
+            g = dx
+        dy0 = t[("dy", stem.name)]
+        self._bn_bwd(stem, K, g, y0, a0, dy0, None, W, t, nvalid, up=False)
+        self._wgrad(stem, K, dy0, t["xin"], t)
+        # ---------------------------------------------------------------------- optimiser
+        flat.sgd_step_(W, V, Gr, t["st_lr"], active, Dp, self.mu, self.wd, t["gs"] if want_grad_sum else None)
+        if t["cnt"].numel():
+            t["cnt"].add_(t["st_active_l"].copy_(active)[:, None])

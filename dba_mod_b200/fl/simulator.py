@@ -135,6 +135,11 @@ class Simulator:
         self.target_name = display_name(params["type"], "Target")
 
         self.backend = self._make_backend()
+        if (self.world > 1 and self.device.type == "cuda" and params["fused_collectives"]
+                and not hasattr(self.comm, "fedavg_")):
+            from ..parallel.symm import PeerComm
+            self.comm = PeerComm(self.comm, self.spec.Df, self.device)
+            self.G = self.comm.set_global(self.G)
         self.fg = agg.FoolsGoldState(use_memory=bool(params["fg_use_memory"]))
         self._loan_local_epoch = self.start_epoch - 1
         self.stream_inputs = False          # bench end-to-end mode: re-upload the round's inputs from pinned host
@@ -427,6 +432,14 @@ class Simulator:
                         self.metrics.trigger_agent_test_vis(epoch, acc, f"{pl.name}_trigger")
 
     def _run_eval_jobs(self, jobs) -> Dict[Tuple[int, str], Tuple[float, float, int, int]]:
+        pairs = getattr(self.backend, "evaluate_pairs", None)
+        if pairs is not None and jobs:
+            res = pairs(torch.stack([j[2] for j in jobs]), [(j[0], max(j[1], 0)) for j in jobs])
+            if res is not None:
+                out = {}
+                for (split, trig, _, k, tag), (loss, corr, n) in zip(jobs, res):
+                    out[(k, tag)] = (loss / n if n else 0, 100.0 * corr / n if n else 0, corr, n)
+                return out
         groups: Dict[Tuple[str, int], list] = {}
         for split, trig, row, k, tag in jobs:
             groups.setdefault((split, trig), []).append((row, k, tag))
@@ -475,6 +488,14 @@ class Simulator:
             fused = getattr(be, "fedavg_from_states_", None)
             if fused is not None and fused(self.G, self.G_cnt, W, cnt if cnt.numel() else None, float(p["eta"]),
                                            int(p["no_models"]), comm, sigma, int(p["seed"]) * 1000003 + epoch):
+                return
+            if hasattr(comm, "fedavg_"):      # fused peer-memory kernel: reduce + update + broadcast, no NCCL
+                comm.fedavg_(W, float(p["eta"]) / int(p["no_models"]), len(names), sigma or 0.0,
+                             int(p["seed"]) * 1000003 + epoch)
+                if cnt.numel():
+                    c = (cnt - self.G_cnt[None, :]).sum(0).double()
+                    comm.all_reduce_sum_(c)
+                    self.G_cnt.add_((c * (float(p["eta"]) / int(p["no_models"]))).trunc().long())
                 return
             delta = W - self.G[None, :]
             dcnt = (cnt - self.G_cnt[None, :]) if cnt.numel() else None
@@ -529,15 +550,35 @@ class Simulator:
                     f"{adv * p['poisoning_per_batch'] / p['batch_size']}")
 
     # ---------------------------------------------------------------------------------------- global eval
-    def _eval_global(self, split: str, trig: int) -> Tuple[float, float, int, int]:
-        loss, correct, n = self.backend.evaluate(self.G[None, :], split, trig)
-        c = int(correct[0])
-        return (float(loss[0]) / n if n else 0, 100.0 * c / n if n else 0, c, n)
+    def _eval_global_jobs(self, jobs) -> List[Tuple[float, float, int, int]]:
+        """All global evaluations of a round in one batched pass; with several ranks every rank evaluates its shard
+        of the test split and the three sums are all-reduced (R5)."""
+        shard = (self.rank, self.world) if self.world > 1 else None
+        res = self.backend.evaluate_jobs(self.G, jobs, shard=shard)
+        t = torch.tensor([[r[0], float(r[1]), float(r[2])] for r in res], dtype=torch.float64, device=self.device)
+        if self.world > 1:
+            self.comm.all_reduce_sum_(t)
+        out = []
+        for row in t.cpu().tolist():
+            loss, c, n = row[0], int(round(row[1])), int(round(row[2]))
+            out.append((loss / n if n else 0, 100.0 * c / n if n else 0, c, n))
+        return out
 
     def _global_eval(self, epoch: int, rep: RoundReport) -> None:
         p, rec = self.params, self.recorder
         tge = epoch + p["aggr_epoch_interval"] - 1
-        loss, acc, corr, n = self._eval_global("clean", 0)
+        jobs = [("clean", 0)]
+        tests = []
+        if p["is_poison"]:
+            jobs.append(("poison", 0))
+            if p.is_centralized_attack:
+                if p["centralized_test_trigger"]:
+                    tests = [(f"global_in_index_{j}_trigger", j + 1) for j in range(int(p["trigger_num"]))]
+            else:
+                tests = [(f"global_in_{a}_trigger", p.adversary_index(a) + 1) for a in p["adversary_list"]]
+            jobs += [("poison", row) for _, row in tests]
+        results = self._eval_global_jobs(jobs)
+        loss, acc, corr, n = results[0]
         logger.info("___Test {} poisoned: {}, epoch: {}: Average loss: {:.4f}, Accuracy: {}/{} ({:.4f}%)".format(
             self.target_name, False, tge, loss, corr, n, acc))
         rep.global_loss, rep.global_acc = loss, acc
@@ -547,7 +588,7 @@ class Simulator:
             self.metrics.test_vis(tge, acc, None, "global")
         if not p["is_poison"]:
             return
-        loss, acc_p, corr, n = self._eval_global("poison", 0)
+        loss, acc_p, corr, n = results[1]
         logger.info("___Test {} poisoned: {}, epoch: {}: Average loss: {:.4f}, Accuracy: {}/{} ({:.4f}%)".format(
             self.target_name, True, tge, loss, corr, n, acc_p))
         rep.poison_loss, rep.poison_acc = loss, acc_p
@@ -556,14 +597,7 @@ class Simulator:
             rec.add_trigger_test("global", "combine", "", tge, loss, acc_p, corr, n)
             if p["vis_trigger_split_test"]:
                 self.metrics.trigger_agent_test_vis(epoch, acc_p, "global_combine")
-        tests = []
-        if p.is_centralized_attack:
-            if p["centralized_test_trigger"]:
-                tests = [(f"global_in_index_{j}_trigger", j + 1) for j in range(int(p["trigger_num"]))]
-        else:
-            tests = [(f"global_in_{a}_trigger", p.adversary_index(a) + 1) for a in p["adversary_list"]]
-        for tname, row in tests:
-            l_, a_, c_, n_ = self._eval_global("poison", row)
+        for (tname, _), (l_, a_, c_, n_) in zip(tests, results[2:]):
             rep.trigger_acc[tname] = a_
             if self.is_main:
                 rec.add_trigger_test("global", tname, "", epoch, l_, a_, c_, n_)

@@ -148,13 +148,27 @@ class TorchBackend:
 
     # ---------------------------------------------------------------------------------------- evaluation
     @torch.no_grad()
-    def evaluate(self, models: torch.Tensor, split: str, trig_row: int) -> Tuple[torch.Tensor, torch.Tensor, int]:
+    def evaluate_jobs(self, model: torch.Tensor, jobs, shard=None):
+        """One model on several (split, trigger) input sets; returns [(loss_sum, correct, n)] for this rank's shard."""
+        out = []
+        for split, trig in jobs:
+            l, c, n = self.evaluate(model.reshape(1, -1), split, trig, shard=shard)
+            out.append((float(l[0]), int(c[0]), n))
+        return out
+
+    @torch.no_grad()
+    def evaluate(self, models: torch.Tensor, split: str, trig_row: int, shard=None
+                 ) -> Tuple[torch.Tensor, torch.Tensor, int]:
         """models [M, Df].  split 'clean' (whole test set, true labels) or 'poison' (poison test subset, every
         sample stamped with trigger ``trig_row`` and relabelled; test.py:54-239).  Returns per-model
         (sum of CE, number correct) and the sample count."""
         d, spec, dev = self.data, self.spec, self.device
         M = models.shape[0]
         ids_all = d.all_test_idx if split == "clean" else d.poison_test_idx
+        if shard is not None:
+            r, w = shard
+            per = (int(ids_all.numel()) + w - 1) // w
+            ids_all = ids_all[r * per:(r + 1) * per]
         loss = torch.zeros(M, dtype=torch.float64, device=dev)
         correct = torch.zeros(M, dtype=torch.long, device=dev)
         P, S = models[:, :spec.Dp], models[:, spec.Dp:]

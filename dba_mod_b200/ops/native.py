@@ -47,6 +47,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_last_error", [], ctypes.c_char_p)
     _sig(lib, "dba_launch_count", [], c_ulonglong)
     _sig(lib, "dba_reset_launch_count", [], None)
+    _sig(lib, "dba_add_launch_count", [c_ulonglong], None)
     _sig(lib, "dba_sgd_step", [P, L, P, P, P, L, P, P, I, L, F, F, P])
     _sig(lib, "dba_scale_rows", [P, L, P, L, P, I, L, P])
     _sig(lib, "dba_rows_sqdist_scratch_elems", [I], c_longlong)
@@ -67,6 +68,9 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_bn_apply", [P, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
     _sig(lib, "dba_bn_backward", [P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
     _sig(lib, "dba_wgrad_tc", [P, P, P, L, I, I, I, I, I, I, I, I, I, I, P])
+    _sig(lib, "dba_fedavg_p2p", [P, L, I, L, F, F, U, P, P, P, I, I, I, P, ctypes.c_uint, P])
+    _sig(lib, "dba_allreduce_axpby_p2p", [L, F, F, P, P, P, I, I, P, ctypes.c_uint, P])
+    _sig(lib, "dba_gram_ptrs", [P, I, L, P, P])
     _LIB = lib
     return lib
 

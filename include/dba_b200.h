@@ -14,6 +14,7 @@ extern "C" {
 const char* dba_last_error(void);
 unsigned long long dba_launch_count(void);       /* kernels launched by this library since the last reset */
 void dba_reset_launch_count(void);
+void dba_add_launch_count(unsigned long long n); /* kernels launched through a replayed CUDA graph */
 
 /* ---- flat-slab kernels (csrc/flat_ops.cu) ------------------------------------------------------------------- */
 

@@ -125,3 +125,32 @@ def test_native_train_multi_step_tracks_torch(native_lib):
     assert ((dn.norm(dim=1) / dt.norm(dim=1)) - 1).abs().max().item() < 0.15
     torch.testing.assert_close(rn.count, rt.count)
     torch.testing.assert_close(rn.poison_count, rt.poison_count)
+
+
+def test_native_eval_pairs_and_jobs_match_plain_eval(native_lib):
+    """Batched (model, input-set) pairs and one-model-many-input-sets give the same sums as one evaluate() per job."""
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    p, dev, data, spec, flat = _setup()
+    torch.manual_seed(1)
+    M = 3
+    models = flat[None].repeat(M, 1)
+    models[:, :spec.Dp] += 0.02 * torch.randn(M, spec.Dp, device=dev)
+    models[:, spec.Dp:] = torch.rand(M, spec.Db, device=dev) * 0.5 + 0.25
+    nx = NativeResNet(p, spec, data, dev)
+    nx.eval_chunk = 256
+    jobs = [("clean", 0), ("poison", 0), ("poison", 3)]
+    plain = []
+    for m, (sp, tr) in zip(range(M), jobs):
+        l, c, n = nx.evaluate(models[m:m + 1], sp, tr)
+        plain.append((float(l[0]), int(c[0]), n))
+    pairs = nx.evaluate_pairs(models, jobs)
+    for a, b in zip(plain, pairs):
+        assert a[2] == b[2] and abs(a[1] - b[1]) <= 1 and abs(a[0] - b[0]) / abs(a[0]) < 2e-3, (plain, pairs)
+    one = nx.evaluate_jobs(models[1], jobs)
+    for (sp, tr), b in zip(jobs, one):
+        l, c, n = nx.evaluate(models[1:2], sp, tr)
+        assert n == b[2] and abs(int(c[0]) - b[1]) <= 1 and abs(float(l[0]) - b[0]) / abs(b[0]) < 2e-3
+    # rank sharding partitions the split
+    parts = [nx.evaluate_jobs(models[0], [("poison", 1)], shard=(r, 3))[0] for r in range(3)]
+    whole = nx.evaluate_jobs(models[0], [("poison", 1)])[0]
+    assert sum(x[2] for x in parts) == whole[2] and abs(sum(x[1] for x in parts) - whole[1]) <= 1
