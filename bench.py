@@ -169,7 +169,8 @@ def run_own(args) -> dict:
                    "parallelism": f"client-sharded x{comm.world}", "timed_l2": "inputs larger than L2 (no flush)",
                    "per_client_eval": True, "backend": be.name,
                    "native_train": bool(getattr(be, "native_train", False)),
-                   "native_eval": bool(getattr(be, "native_eval", False))},
+                   "native_eval": bool(getattr(be, "native_eval", False)),
+                   "collectives": sim.collective_path},
         "e2e": {"value": K / (ms_e2e / 1e3), "unit": "rounds/s", "h2d_bytes_per_step": sim.h2d_bytes_last,
                 "d2h_bytes_per_step": sim.d2h_bytes_last, "ms_per_step": ms_e2e / K,
                 "wall_ms_per_step": wall_e2e / K},

@@ -27,14 +27,20 @@
 //              per-channel sum / sum-of-squares for training-mode BatchNorm -> bf16 planar store (coalesced 16 B
 //              per lane), optional stride-2 subsampling of the output grid.
 // Accumulator sets in TMEM are double-buffered when 2*T*N <= 512 columns so the epilogue overlaps the next pass.
+// Work items (client, n-block, pass) are dealt to CTAs in contiguous ranges, so a CTA stays with one weight set for
+// as long as possible: when all taps of that weight set fit in shared memory ("resident" mode, every layer with
+// Cin*Cout <= 64*64) they are fetched ONCE per (client, n-block) with a single bulk copy and the per-tap
+// producer/consumer round trips disappear; larger layers stream one weight block per (tap, k-block).
 #include "common.cuh"
 
 using namespace dba;
 
+
 namespace {
 
 constexpr int kTileM = 128;
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;                  // two warps per TMEM lane quadrant
+constexpr int kThreads = 64 + 32 * kEpiWarps;
 
 struct ConvArgs {
   const __nv_bfloat16* X;      // [Kx][Cin/8][R][8]
@@ -47,14 +53,14 @@ struct ConvArgs {
   long long x_client_stride;   // elements; 0 = all clients read the same input (shared evaluation batch)
   long long x_plane_stride;    // elements between channel-chunk planes (= R*8)
   long long y_client_stride, y_plane_stride;
-  long long w_client_stride;   // elements between the clients' packed weight sets
+  long long w_client_stride;   // elements between the clients' packed weight sets (0 = one model for all)
   long long ss_stride;         // floats between the clients' scale / shift rows
   long long stats_stride;      // floats between the clients' statistics rows
   int K, Cin, Cout, taps;      // taps = 1 (1x1) or 9 (3x3, pad 1)
   int H, W, Wp, S, lead, B;    // input (= compute) geometry
   int T;                       // row tiles per pass
   int NB;                      // output channels per n-block (<= 256), Cout % NB == 0
-  int KB;                      // input channels per k-block (multiple of 16, <= 64)
+  int KB;                      // input channels per k-block (16, 32 or 64)
   int relu;
   int sub;                     // 1 = same grid, 2 = keep even (h, w) only (stride-2 convolution)
   int Ho, Wo, Wpo, So, leado;  // output geometry (equals input geometry when sub == 1)
@@ -62,7 +68,10 @@ struct ConvArgs {
   int rowsA;                   // T*128 + halo rows
   int halo;                    // Wp + 1 for 3x3, 0 for 1x1
   int num_pass;                // ceil(B*S / (T*128))
-  int lbo_sbo_swap;            // debug: swap descriptor LBO/SBO meaning
+  int resident;                // 1 = whole weight set of a (client, n-block) kept in shared memory
+  unsigned int wbytes;         // bytes of that weight set
+  unsigned long long magicS, magicWp;   // ceil(2^40 / S), ceil(2^40 / Wp): exact division of row indices < 2^26
+  long long* dbg;              // optional [grid][8] cycle counters (profiling aid), null in production
 };
 
 struct Pipe {
@@ -85,33 +94,40 @@ __device__ __forceinline__ void warp_transpose_reduce32(float (&v)[32], int lane
   }
 }
 
+#define DBG_T0() long long t0__ = a.dbg ? clock64() : 0
+#define DBG_ADD(slot) do { if (a.dbg) { long long t1__ = clock64(); dbgacc[slot] += t1__ - t0__; t0__ = t1__; } } while (0)
+
+template <int KC2>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) {
+  long long dbgacc[4] = {0, 0, 0, 0};
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kc = a.KB >> 3;                      // 16-byte channel chunks per k-block
   const int nkb = a.Cin / a.KB;
   const int nnb = a.Cout / a.NB;
+  const int planes = a.Cin >> 3;
   const uint32_t pitchA = (uint32_t)a.rowsA * 16u;
   const uint32_t bytesA = (uint32_t)kc * pitchA;
   const uint32_t pitchB = (uint32_t)a.NB * 16u;
   const uint32_t bytesB = (uint32_t)kc * pitchB;
+  const size_t bRegion = a.resident ? (size_t)a.wbytes : (size_t)a.SB * bytesB;
 
   uint8_t* smA = smem;
   uint8_t* smB = smA + (size_t)a.SA * bytesA;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smB + (size_t)a.SB * bytesB);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smB + bRegion);
   uint64_t* a_full = bars;
   uint64_t* a_empty = a_full + a.SA;
-  uint64_t* b_full = a_empty + a.SA;
-  uint64_t* b_empty = b_full + a.SB;
-  uint64_t* acc_full = b_empty + a.SB;
-  uint64_t* acc_empty = acc_full + a.NS;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + a.NS);
-  float* stat_s = reinterpret_cast<float*>(tmem_slot + 4);   // [NB][2] when stats requested
+  uint64_t* b_full = a_empty + a.SA;            // streaming: SB stages; resident: [0] = weights landed
+  uint64_t* b_empty = b_full + 4;               //                        resident: [0] = weights no longer needed
+  uint64_t* acc_full = b_empty + 4;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* ss_s = reinterpret_cast<float*>(tmem_slot + 4);     // [2][NB] scale / shift of the current weight group
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.SA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < a.SB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < a.NS; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+    for (int i = 0; i < 4; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], kEpiWarps); }
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -123,38 +139,60 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int items = a.K * a.num_pass * nnb;
+  // contiguous range of work items for this CTA; item = (k * nnb + nb) * num_pass + pass
+  const long long items = (long long)a.K * nnb * a.num_pass;
+  const int item_lo = (int)(items * blockIdx.x / gridDim.x);
+  const int item_hi = (int)(items * (blockIdx.x + 1) / gridDim.x);
   const int accCols = a.T * a.NB;               // columns of one accumulator set
 
   if (warp == 0) {
     // ================================================================= producer
     if (elect_one()) {
       Pipe pa, pb;
-      for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        const int nb = item % nnb;
-        const int pass = (item / nnb) % a.num_pass;
-        const int k = item / (nnb * a.num_pass);
-        const long long row0 = (long long)a.lead + (long long)pass * a.T * kTileM - a.halo;
+      int cur_group = -1, wloads = 0;
+      for (int item = item_lo; item < item_hi; ++item) {
+        const int group = item / a.num_pass;
+        const int pass = item - group * a.num_pass;
+        const int nb = group % nnb, k = group / nnb;
         const __nv_bfloat16* xk = a.X + (long long)k * a.x_client_stride;
         const __nv_bfloat16* wk = a.Wt + (long long)k * a.w_client_stride;
+        if (a.resident && group != cur_group) {
+          cur_group = group;
+          mbar_wait(&b_empty[0], (uint32_t)(wloads & 1) ^ 1u);
+          mbar_arrive_expect_tx(&b_full[0], a.wbytes);
+          if (nnb == 1) {
+            bulk_g2s(smB, wk, a.wbytes, &b_full[0]);            // [tap][plane][Cout][8] is contiguous
+          } else {
+            for (int tp = 0; tp < a.taps * planes; ++tp)
+              bulk_g2s(smB + (size_t)tp * pitchB, wk + ((long long)tp * a.Cout + (long long)nb * a.NB) * 8, pitchB,
+                       &b_full[0]);
+          }
+          ++wloads;
+        }
+        const long long row0 = (long long)a.lead + (long long)pass * a.T * kTileM - a.halo;
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = pa.stage(a.SA);
+          DBG_T0();
           mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
+          DBG_ADD(0);
           mbar_arrive_expect_tx(&a_full[sa], bytesA);
           for (int c = 0; c < kc; ++c) {
             const __nv_bfloat16* src = xk + (long long)(kb * kc + c) * a.x_plane_stride + row0 * 8;
             bulk_g2s(smA + (size_t)sa * bytesA + (size_t)c * pitchA, src, pitchA, &a_full[sa]);
           }
           ++pa.it;
+          if (a.resident) continue;
           for (int tap = 0; tap < a.taps; ++tap) {
             const int sb = pb.stage(a.SB);
             mbar_wait(&b_empty[sb], pb.phase(a.SB) ^ 1u);
             mbar_arrive_expect_tx(&b_full[sb], bytesB);
-            // weights [tap][Cin/8][Cout][8]: rows nb*NB .. +NB of chunks kb*kc .. +kc
-            for (int c = 0; c < kc; ++c) {
-              const __nv_bfloat16* src =
-                  wk + (((long long)tap * (a.Cin >> 3) + (kb * kc + c)) * a.Cout + (long long)nb * a.NB) * 8;
-              bulk_g2s(smB + (size_t)sb * bytesB + (size_t)c * pitchB, src, pitchB, &b_full[sb]);
+            const __nv_bfloat16* wsrc = wk + (((long long)tap * planes + kb * kc) * a.Cout + (long long)nb * a.NB) * 8;
+            if (nnb == 1) {
+              bulk_g2s(smB + (size_t)sb * bytesB, wsrc, bytesB, &b_full[sb]);   // kc planes are contiguous
+            } else {
+              for (int c = 0; c < kc; ++c)
+                bulk_g2s(smB + (size_t)sb * bytesB + (size_t)c * pitchB, wsrc + (long long)c * a.Cout * 8, pitchB,
+                         &b_full[sb]);
             }
             ++pb.it;
           }
@@ -165,144 +203,198 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     // =============================================================== MMA issuer
     if (elect_one()) {
       Pipe pa, pb, pacc;
+      int cur_group = -1, wuses = 0;
       const uint32_t idesc = umma_idesc_bf16(kTileM, a.NB, 0, 0);
-      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+      const uint32_t kstepA = (2u * pitchA) >> 4, kstepB = (2u * pitchB) >> 4;
+      for (int item = item_lo; item < item_hi; ++item) {
+        const int group = item / a.num_pass;
+        if (a.resident && group != cur_group) {
+          cur_group = group;
+          mbar_wait(&b_full[0], (uint32_t)(wuses & 1));
+          tc_fence_after();
+          ++wuses;
+        }
         const int as = pacc.stage(a.NS);
+        DBG_T0();
         mbar_wait(&acc_empty[as], pacc.phase(a.NS) ^ 1u);
+        DBG_ADD(0);
         tc_fence_after();
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = pa.stage(a.SA);
           mbar_wait(&a_full[sa], pa.phase(a.SA));
+          DBG_ADD(1);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(smA + (size_t)sa * bytesA);
+          // Descriptors differ from one MMA to the next only in their 14-bit start-address field: build the stage's
+          // base descriptors once and add row / k-step offsets (in 16-byte units) - the single issuing thread must
+          // spend only a handful of instructions per tcgen05.mma, or small-N layers become issue-bound.
+          const uint64_t dA0 = umma_desc_noswz(smem_u32(smA + (size_t)sa * bytesA), pitchA, 128) + (uint64_t)a.halo;
           for (int tap = 0; tap < a.taps; ++tap) {
-            const int sb = pb.stage(a.SB);
-            mbar_wait(&b_full[sb], pb.phase(a.SB));
-            tc_fence_after();
-            const uint32_t b_base = smem_u32(smB + (size_t)sb * bytesB);
+            uint64_t dB0;
+            int sb = 0;
+            if (a.resident) {
+              dB0 = umma_desc_noswz(smem_u32(smB + (size_t)(tap * planes + kb * kc) * pitchB), pitchB, 128);
+            } else {
+              sb = pb.stage(a.SB);
+              mbar_wait(&b_full[sb], pb.phase(a.SB));
+              tc_fence_after();
+              dB0 = umma_desc_noswz(smem_u32(smB + (size_t)sb * bytesB), pitchB, 128);
+            }
             int shift = 0;
             if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
-            for (int t = 0; t < a.T; ++t) {
-              const uint32_t d_tmem = tmem_base + (uint32_t)(as * accCols + t * a.NB);
-              const uint32_t a_row = (uint32_t)(t * kTileM + a.halo + shift) * 16u;
-              for (int kk = 0; kk < (kc >> 1); ++kk) {
-                const uint32_t a_addr = a_base + (uint32_t)(2 * kk) * pitchA + a_row;
-                const uint32_t b_addr = b_base + (uint32_t)(2 * kk) * pitchB;
-                uint64_t da, db;
-                if (!a.lbo_sbo_swap) {
-                  da = umma_desc_noswz(a_addr, pitchA, 128);
-                  db = umma_desc_noswz(b_addr, pitchB, 128);
-                } else {
-                  da = umma_desc_noswz(a_addr, 128, pitchA);
-                  db = umma_desc_noswz(b_addr, 128, pitchB);
-                }
-                umma_f16(d_tmem, da, db, idesc, (kb | tap | kk) != 0 ? 1u : 0u);
+            const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
+            uint32_t d_tmem = tmem_base + (uint32_t)(as * accCols);
+            uint64_t da = dA0 + (uint64_t)(int64_t)shift;       // halo + shift >= 0: no borrow out of the field
+            for (int t = 0; t < a.T; ++t, d_tmem += (uint32_t)a.NB, da += (uint64_t)kTileM) {
+              umma_f16(d_tmem, da, dB0, idesc, first);
+              if (KC2 >= 2) umma_f16(d_tmem, da + kstepA, dB0 + kstepB, idesc, 1u);
+              if (KC2 >= 4) {
+                umma_f16(d_tmem, da + 2 * kstepA, dB0 + 2 * kstepB, idesc, 1u);
+                umma_f16(d_tmem, da + 3 * kstepA, dB0 + 3 * kstepB, idesc, 1u);
               }
             }
-            umma_commit(&b_empty[sb]);
-            ++pb.it;
+            if (!a.resident) {
+              umma_commit(&b_empty[sb]);
+              ++pb.it;
+            }
           }
           umma_commit(&a_empty[sa]);
           ++pa.it;
+          DBG_ADD(2);
         }
         umma_commit(&acc_full[as]);
         ++pacc.it;
+        if (a.resident && (item + 1 == item_hi || (item + 1) / a.num_pass != group)) umma_commit(&b_empty[0]);
       }
     }
   } else {
     // ================================================================= epilogue
+    // 8 warps: warps e and e+4 share TMEM lane quadrant (e & 3) and split the pass' tiles (or, for single-tile
+    // passes, its 32-channel groups) between them - with one warp per scheduler the epilogue is latency-bound.
+    const int ew = warp - 2;
     const int q = warp & 3;                       // TMEM lane quadrant this warp may access
+    const int half = ew >> 2;                     // 0 / 1
     Pipe pacc;
     const int totalRows = a.B * a.S;
-    for (int item = blockIdx.x; item < items; item += gridDim.x) {
-      const int nb = item % nnb;
-      const int pass = (item / nnb) % a.num_pass;
-      const int k = item / (nnb * a.num_pass);
+    int cur_group = -1;
+    const bool affine = a.scale != nullptr;
+    const int t_step = a.T >= 2 ? 2 : 1, t_first = a.T >= 2 ? half : 0;
+    const int c_step = a.T >= 2 ? 32 : 64, c_first = a.T >= 2 ? 0 : 32 * half;
+    for (int item = item_lo; item < item_hi; ++item) {
+      const int group = item / a.num_pass;
+      const int pass = item - group * a.num_pass;
+      const int nb = group % nnb, k = group / nnb;
       const int as = pacc.stage(a.NS);
-      if (a.stats) {
-        for (int i = threadIdx.x - 64; i < 2 * a.NB; i += 128) stat_s[i] = 0.f;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (group != cur_group) {
+        cur_group = group;
+        if (affine) {     // per-channel scale / shift of this (client, n-block) -> shared memory
+          const float* gsc = a.scale + (long long)k * a.ss_stride + nb * a.NB;
+          const float* gsh = a.shift + (long long)k * a.ss_stride + nb * a.NB;
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          for (int i = threadIdx.x - 64; i < a.NB; i += 32 * kEpiWarps) { ss_s[i] = gsc[i]; ss_s[a.NB + i] = gsh[i]; }
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
       }
+      // which of this thread's rows (one per tile) are real output pixels, and where they go
+      bool store[2];
+      long long orow[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int t = t_first + i * t_step;
+        store[i] = false;
+        orow[i] = 0;
+        if (t < a.T) {
+          const unsigned int qrow = (unsigned int)(pass * a.T * kTileM + t * kTileM + q * 32 + lane);
+          const unsigned int b = (unsigned int)(((unsigned long long)qrow * a.magicS) >> 40);
+          const unsigned int rem = qrow - b * (unsigned int)a.S;
+          const unsigned int h = (unsigned int)(((unsigned long long)rem * a.magicWp) >> 40);
+          const unsigned int w = rem - h * (unsigned int)a.Wp;
+          bool st = (int)qrow < totalRows && (int)h < a.H && (int)w < a.W;
+          if (a.sub == 2) {
+            st = st && !((h | w) & 1u);
+            orow[i] = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
+          } else {
+            orow[i] = (long long)a.lead + qrow;
+          }
+          store[i] = st;
+        }
+      }
+      DBG_T0();
       mbar_wait(&acc_full[as], pacc.phase(a.NS));
+      DBG_ADD(0);
       tc_fence_after();
-      const float* sc = a.scale ? a.scale + (long long)k * a.ss_stride + nb * a.NB : nullptr;
-      const float* sh = a.shift ? a.shift + (long long)k * a.ss_stride + nb * a.NB : nullptr;
       __nv_bfloat16* yk = a.Y + (long long)k * a.y_client_stride;
       const __nv_bfloat16* rk = a.Res ? a.Res + (long long)k * a.y_client_stride : nullptr;
-      for (int t = 0; t < a.T; ++t) {
-        const int qrow = pass * a.T * kTileM + t * kTileM + q * 32 + lane;   // row index relative to `lead`
-        bool store = qrow < totalRows;
-        long long orow = 0;
-        {
-          const int b = qrow / a.S;
-          const int rem = qrow - b * a.S;
-          const int h = rem / a.Wp, w = rem - h * a.Wp;
-          store = store && h < a.H && w < a.W;
-          if (a.sub == 2) {
-            store = store && !((h | w) & 1);
-            orow = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
-          } else {
-            orow = (long long)a.lead + qrow;
-          }
-        }
-        const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * accCols + t * a.NB);
-        for (int c0 = 0; c0 < a.NB; c0 += 32) {
-          float sv[32];
+      float* gs = a.stats ? a.stats + (long long)k * a.stats_stride + (long long)nb * a.NB * 2 : nullptr;
+      for (int c0 = c_first; c0 < a.NB; c0 += c_step) {
+        // u1/u2 hold scale/shift (evaluation epilogue) or the running sum / sum of squares (training epilogue);
+        // the two modes are mutually exclusive (checked on the host), sharing the registers avoids spills
+        float u1[32], u2[32];
+        if (affine) {
 #pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-            uint32_t v[16];
-            tmem_ld_32x32b_x16(t_addr + (uint32_t)(c0 + 16 * h2), v);
+          for (int j = 0; j < 32; ++j) { u1[j] = ss_s[c0 + j]; u2[j] = ss_s[a.NB + c0 + j]; }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) u1[j] = u2[j] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int t = t_first + i * t_step;
+          if (t >= a.T) break;
+          const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * accCols + t * a.NB + c0);
+          float sv[32];
+          {
+            uint32_t v[16], v2[16];
+            tmem_ld_32x32b_x16(t_addr, v);
+            tmem_ld_32x32b_x16(t_addr + 16u, v2);
             tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 16; ++j) sv[16 * h2 + j] = __uint_as_float(v[j]);
+            for (int j = 0; j < 16; ++j) { sv[j] = __uint_as_float(v[j]); sv[16 + j] = __uint_as_float(v2[j]); }
           }
-          // NB is a multiple of 16; a trailing half-group of 16 columns is handled by masking below
-          const int ncol = min(32, a.NB - c0);
+          if (affine) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {            // 4 chunks of 8 channels
-            if (g * 8 >= ncol) break;
-            const int ch = c0 + g * 8;
-            float o[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float x = sv[g * 8 + j];
-              if (sc) x = x * __ldg(sc + ch + j) + __ldg(sh + ch + j);
-              o[j] = x;
-            }
-            const long long off = (long long)((nb * a.NB + ch) >> 3) * a.y_plane_stride + orow * 8;
-            if (store) {
-              if (rk) {
-                const uint4 r = *reinterpret_cast<const uint4*>(rk + off);
-                o[0] += bf16lo(r.x); o[1] += bf16hi(r.x); o[2] += bf16lo(r.y); o[3] += bf16hi(r.y);
-                o[4] += bf16lo(r.z); o[5] += bf16hi(r.z); o[6] += bf16lo(r.w); o[7] += bf16hi(r.w);
-              }
-              if (a.relu) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
-              }
-              uint4 pk;
-              pk.x = pack_bf16x2(o[0], o[1]); pk.y = pack_bf16x2(o[2], o[3]);
-              pk.z = pack_bf16x2(o[4], o[5]); pk.w = pack_bf16x2(o[6], o[7]);
-              *reinterpret_cast<uint4*>(yk + off) = pk;
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) sv[g * 8 + j] = store ? o[j] : 0.f;
+            for (int j = 0; j < 32; ++j) sv[j] = fmaf(sv[j], u1[j], u2[j]);
           }
-          if (a.stats) {
-            float s1[32], s2[32];
+          if (!store[i]) continue;
+          const long long obase = (long long)((nb * a.NB + c0) >> 3) * a.y_plane_stride + orow[i] * 8;
+          if (rk) {
+            uint4 r[4];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int g = 0; g < 4; ++g) r[g] = *reinterpret_cast<const uint4*>(rk + obase + g * a.y_plane_stride);
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              sv[g * 8 + 0] += bf16lo(r[g].x); sv[g * 8 + 1] += bf16hi(r[g].x);
+              sv[g * 8 + 2] += bf16lo(r[g].y); sv[g * 8 + 3] += bf16hi(r[g].y);
+              sv[g * 8 + 4] += bf16lo(r[g].z); sv[g * 8 + 5] += bf16hi(r[g].z);
+              sv[g * 8 + 6] += bf16lo(r[g].w); sv[g * 8 + 7] += bf16hi(r[g].w);
+            }
+          }
+          if (a.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) sv[j] = fmaxf(sv[j], 0.f);
+          }
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {            // 4 chunks of 8 channels -> 4 coalesced 16-byte stores
+            uint4 pk;
+            pk.x = pack_bf16x2(sv[g * 8 + 0], sv[g * 8 + 1]); pk.y = pack_bf16x2(sv[g * 8 + 2], sv[g * 8 + 3]);
+            pk.z = pack_bf16x2(sv[g * 8 + 4], sv[g * 8 + 5]); pk.w = pack_bf16x2(sv[g * 8 + 6], sv[g * 8 + 7]);
+            *reinterpret_cast<uint4*>(yk + obase + g * a.y_plane_stride) = pk;
+            if (gs) {
               // statistics of the value as stored (bf16-rounded), so BatchNorm normalises exactly what it reads
-              const float r = (j < ncol) ? __bfloat162float(__float2bfloat16(sv[j])) : 0.f;
-              s1[j] = r;
-              s2[j] = r * r;
+              const float r0 = bf16lo(pk.x), r1 = bf16hi(pk.x), r2 = bf16lo(pk.y), r3 = bf16hi(pk.y);
+              const float r4 = bf16lo(pk.z), r5 = bf16hi(pk.z), r6 = bf16lo(pk.w), r7 = bf16hi(pk.w);
+              u1[g * 8 + 0] += r0; u2[g * 8 + 0] += r0 * r0; u1[g * 8 + 1] += r1; u2[g * 8 + 1] += r1 * r1;
+              u1[g * 8 + 2] += r2; u2[g * 8 + 2] += r2 * r2; u1[g * 8 + 3] += r3; u2[g * 8 + 3] += r3 * r3;
+              u1[g * 8 + 4] += r4; u2[g * 8 + 4] += r4 * r4; u1[g * 8 + 5] += r5; u2[g * 8 + 5] += r5 * r5;
+              u1[g * 8 + 6] += r6; u2[g * 8 + 6] += r6 * r6; u1[g * 8 + 7] += r7; u2[g * 8 + 7] += r7 * r7;
             }
-            warp_transpose_reduce32(s1, lane);
-            warp_transpose_reduce32(s2, lane);
-            if (lane < ncol) {
-              atomicAdd(&stat_s[2 * (c0 + lane)], s1[0]);
-              atomicAdd(&stat_s[2 * (c0 + lane) + 1], s2[0]);
-            }
+          }
+        }
+        if (gs) {       // one cross-lane reduction per 32 channels per pass, then one atomic per channel per warp
+          warp_transpose_reduce32(u1, lane);
+          warp_transpose_reduce32(u2, lane);
+          if (u1[0] != 0.f || u2[0] != 0.f) {
+            atomicAdd(gs + 2 * (c0 + lane), u1[0]);
+            atomicAdd(gs + 2 * (c0 + lane) + 1, u2[0]);
           }
         }
       }
@@ -310,16 +402,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);
       ++pacc.it;
-      if (a.stats) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        float* gs = a.stats + (long long)k * a.stats_stride + (long long)nb * a.NB * 2;
-        for (int i = threadIdx.x - 64; i < 2 * a.NB; i += 128) {
-          const float v = stat_s[i];
-          if (v != 0.f) atomicAdd(gs + i, v);
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-      }
+      DBG_ADD(1);
     }
+  }
+  if (a.dbg && lane == 0 && warp <= 2) {      // [cta][role 0..2][4]
+    for (int i = 0; i < 4; ++i) a.dbg[((long long)blockIdx.x * 3 + warp) * 4 + i] = dbgacc[i];
   }
 
   tc_fence_before();
@@ -332,7 +419,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
 
 }  // namespace
 
+static long long* g_conv_dbg = nullptr;
+
 extern "C" {
+
+// Profiling aid: when set, every conv launch writes per-CTA cycle counters [grid][3 roles][4] (producer: wait a_empty;
+// MMA: wait acc_empty, wait a_full, issue; epilogue: wait acc_full, work).  Pass null to switch it off.
+void dba_conv_set_debug(long long* buf) { g_conv_dbg = buf; }
 
 // Geometry helpers shared with the Python side (dba_mod_b200/ops/layout.py mirrors these).
 long long dba_conv_rows(int B, int H, int W) {
@@ -343,19 +436,20 @@ long long dba_conv_rows(int B, int H, int W) {
 }
 
 // Y = epilogue(conv(X, Wt)).  See ConvArgs for layouts.  X: [Kx][Cin/8][R][8] with R = dba_conv_rows(B,H,W);
-// Wt: [K][taps][Cin/8][Cout][8]; Y (and Res): [K][Cout/8][Ro][8], Ro = dba_conv_rows(B,Ho,Wo), Ho = H/sub.
-// scale/shift (nullable together): per (client, out-channel) affine = folded BatchNorm.  stats (nullable): [K][Cout][2]
-// accumulated (+=) with sum / sum-of-squares of the stored outputs.  x_shared != 0: every client reads client 0's X.
+// Wt: per client [taps][Cin/8][Cout][8] (client stride w_client_stride elements, 0 = shared model); Y (and Res):
+// [K][Cout/8][Ro][8], Ro = dba_conv_rows(B,Ho,Wo), Ho = H/sub.  scale/shift (nullable together): per (client,
+// out-channel) affine = folded BatchNorm (row stride ss_stride).  stats (nullable): rows of (sum, sumsq) pairs,
+// accumulated (+=).  x_shared != 0: every client reads client 0's X.
 int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
                         const float* scale, const float* shift, long long ss_stride, float* stats,
                         long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
                         int relu, int x_shared, void* stream) {
-  const int debug_swap = 0;
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
   DBA_REQUIRE(ksize == 1 || ksize == 3, "dba_conv_tc: ksize must be 1 or 3, got %d", ksize);
-  DBA_REQUIRE(Cin % 16 == 0 && Cout % 16 == 0, "dba_conv_tc: Cin (%d) and Cout (%d) must be multiples of 16", Cin, Cout);
+  DBA_REQUIRE(Cin % 16 == 0 && Cout % 32 == 0, "dba_conv_tc: Cin (%d) %% 16 and Cout (%d) %% 32 must be 0", Cin, Cout);
   DBA_REQUIRE(sub == 1 || (sub == 2 && H % 2 == 0 && W % 2 == 0), "dba_conv_tc: sub=%d needs even H, W", sub);
   DBA_REQUIRE((scale == nullptr) == (shift == nullptr), "dba_conv_tc: scale and shift go together");
+  DBA_REQUIRE(!(scale && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
   ConvArgs a{};
   a.X = (const __nv_bfloat16*)X; a.Wt = (const __nv_bfloat16*)Wt; a.Y = (__nv_bfloat16*)Y;
   a.Res = (const __nv_bfloat16*)Res; a.scale = scale; a.shift = shift; a.stats = stats;
@@ -371,45 +465,71 @@ int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride
   a.w_client_stride = w_client_stride;
   a.ss_stride = ss_stride;
   a.stats_stride = stats_stride;
-  a.NB = Cout <= 256 ? Cout : 256;
-  DBA_REQUIRE(Cout % a.NB == 0, "dba_conv_tc: Cout=%d not a multiple of the n-block %d", Cout, a.NB);
   a.KB = Cin >= 64 ? 64 : Cin;
-  DBA_REQUIRE(Cin % a.KB == 0, "dba_conv_tc: Cin=%d not a multiple of the k-block %d", Cin, a.KB);
+  DBA_REQUIRE(Cin % a.KB == 0 && (a.KB == 16 || a.KB == 32 || a.KB == 64), "dba_conv_tc: unsupported Cin=%d", Cin);
   a.halo = ksize == 3 ? a.Wp + 1 : 0;
-  a.lbo_sbo_swap = debug_swap;
-  // rows per pass: as many 128-row tiles as fit in TMEM (512 columns) and in shared memory
   const int kc = a.KB / 8;
   const long long body = (long long)B * a.S;
-  DBA_REQUIRE(a.NB % 32 == 0, "dba_conv_tc: output channels per block (%d) must be a multiple of 32", a.NB);
-  int T = 512 / a.NB;                          // T stays a power of two so that T*128 divides the 512-row tail slack
+  // n-block and rows per pass: as many 128-row tiles as fit in TMEM (512 columns); when that leaves SMs idle, first
+  // split wide output-channel blocks (halves the weight traffic per CTA), then shorten the passes.
+  int NB = Cout <= 256 ? Cout : 256;
+  DBA_REQUIRE(Cout % NB == 0, "dba_conv_tc: Cout=%d not a multiple of the n-block %d", Cout, NB);
+  // T stays a power of two so that T*128 divides the 512-row tail slack; two accumulator sets (epilogue of pass p
+  // overlaps the MMAs of pass p+1) are preferred over longer passes except for NB = 256, where the weight traffic
+  // per row would double.
+  int T = NB >= 256 ? 2 : 256 / NB;
   if (T > 4) T = 4;
   while (T > 1 && (long long)(T / 2) * kTileM >= body) T /= 2;
+  auto n_items = [&](int T_, int NB_) {
+    return (long long)K * (Cout / NB_) * ((body + (long long)T_ * kTileM - 1) / ((long long)T_ * kTileM));
+  };
+  while (n_items(T, NB) < kNumSMs) {
+    if (NB >= 128) NB /= 2;
+    else if (T > 1) T /= 2;
+    else break;
+  }
   const size_t budget = 220 * 1024;
   size_t need = 0;
   for (;; T /= 2) {
-    a.T = T;
+    a.T = T; a.NB = NB;
     a.rowsA = T * kTileM + 2 * a.halo;
-    const size_t bytesA = (size_t)kc * a.rowsA * 16, bytesB = (size_t)kc * a.NB * 16;
+    const size_t bytesA = (size_t)kc * a.rowsA * 16, bytesB = (size_t)kc * NB * 16;
+    const size_t misc = 1024 + 2 * NB * sizeof(float);
     a.SA = 2;
-    a.SB = 4;
-    a.NS = (2 * T * a.NB <= 512) ? 2 : 1;
-    need = a.SA * bytesA + a.SB * bytesB + 1024 + (stats ? 2 * a.NB * sizeof(float) : 0);
-    if (need > budget) { a.SB = 2; need = a.SA * bytesA + a.SB * bytesB + 1024 + (stats ? 2 * a.NB * sizeof(float) : 0); }
+    a.NS = (2 * T * NB <= 512) ? 2 : 1;
+    a.wbytes = (unsigned int)((size_t)a.taps * Cin * NB * 2);
+    a.resident = a.wbytes <= 100 * 1024 && a.SA * bytesA + a.wbytes + misc <= budget;
+    if (a.resident) {
+      a.SB = 1;
+      need = a.SA * bytesA + a.wbytes + misc;
+    } else {
+      a.SB = 4;
+      need = a.SA * bytesA + a.SB * bytesB + misc;
+      if (need > budget) { a.SB = 2; need = a.SA * bytesA + a.SB * bytesB + misc; }
+    }
     if (need <= budget || T == 1) break;
   }
   DBA_REQUIRE(need <= budget, "dba_conv_tc: shared memory need %zu exceeds budget", need);
+  a.dbg = g_conv_dbg;
+  a.magicS = ((1ULL << 40) + (unsigned long long)a.S - 1) / (unsigned long long)a.S;
+  a.magicWp = ((1ULL << 40) + (unsigned long long)a.Wp - 1) / (unsigned long long)a.Wp;
   a.num_pass = (int)((body + (long long)a.T * kTileM - 1) / ((long long)a.T * kTileM));
-  const int items = K * a.num_pass * (Cout / a.NB);
+  const long long items = (long long)K * a.num_pass * (Cout / a.NB);
   static bool attr_set[64] = {false};
   int dev = 0;
   DBA_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
-    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
     attr_set[dev] = true;
   }
   if (need < 120 * 1024) need = 120 * 1024;    // one CTA per SM: each CTA allocates all 512 TMEM columns
-  const int grid = items < kNumSMs ? items : kNumSMs;
-  conv_tc_kernel<<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
+  const int grid = items < kNumSMs ? (int)items : kNumSMs;
+  const int kc2 = a.KB / 16;
+  if (kc2 == 4) conv_tc_kernel<4><<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
+  else if (kc2 == 2) conv_tc_kernel<2><<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
+  else conv_tc_kernel<1><<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;

@@ -117,18 +117,19 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
           const int s = it % a.stages;
           mbar_wait(&full[s], (it / a.stages) & 1);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(smA + (size_t)s * bytesA);
-          const uint32_t b_base = smem_u32(smB + (size_t)s * bytesB);
+          // base descriptors once per stage; per MMA only the 14-bit start-address field moves (16-byte units)
+          const uint64_t dA0 = umma_desc_noswz(smem_u32(smA + (size_t)s * bytesA), 128, pitchA);
+          const uint64_t dB0 = umma_desc_noswz(smem_u32(smB + (size_t)s * bytesB), 128, pitchB) + (uint64_t)a.halo;
+          const uint32_t acc0 = ch != c0 ? 1u : 0u;
           for (int tap = t0; tap < t1; ++tap) {
             int shift = 0;
             if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
             const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.Cin);
-#pragma unroll 1
-            for (int ks = 0; ks < kRowsK / 16; ++ks) {
-              const uint64_t da = umma_desc_noswz(a_base + (uint32_t)ks * 256u, 128, pitchA);
-              const uint64_t db = umma_desc_noswz(b_base + (uint32_t)(ks * 16 + a.halo + shift) * 16u, 128, pitchB);
-              umma_f16(d_tmem, da, db, idesc, (ch != c0 || ks != 0) ? 1u : 0u);
-            }
+            const uint64_t dB1 = dB0 + (uint64_t)(int64_t)shift;
+            umma_f16(d_tmem, dA0, dB1, idesc, acc0);
+#pragma unroll
+            for (int ks = 1; ks < kRowsK / 16; ++ks)
+              umma_f16(d_tmem, dA0 + (uint64_t)(ks * 16), dB1 + (uint64_t)(ks * 16), idesc, 1u);
           }
           umma_commit(&empty[s]);
         }

@@ -43,6 +43,10 @@ class CudaBackend(TorchBackend):
                 self.native_train = self.exec.can_train
             except ImportError:
                 self.exec = None
+        if params["type"] == C.TYPE_LOAN and params.get("native_net", True):
+            from .native_loan import NativeLoan
+            self.exec = NativeLoan(params, spec, data, device)
+            self.native_eval = self.native_train = True
 
     # ---------------------------------------------------------------------------------------- flat ops
     def _sgd_update(self, W, V, g, lr_t, act, grad_sum, mu, wd) -> None:
@@ -82,7 +86,8 @@ class CudaBackend(TorchBackend):
 
     # -------------------------------------------------------------------------------- train / evaluate
     def train(self, sch, W, cnt, anchor, want_grad_sum, generator=None):
-        if self.native_train:
+        needs_dist = float(self.params["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any())
+        if self.native_train and not needs_dist:     # the distance-regularised poison loss runs on the torch path
             return self.exec.train(sch, W, cnt, anchor, want_grad_sum)
         return super().train(sch, W, cnt, anchor, want_grad_sum, generator)
 
@@ -92,11 +97,11 @@ class CudaBackend(TorchBackend):
         return super().evaluate(models, split, trig_row, shard=shard)
 
     def evaluate_pairs(self, models, jobs, shard=None):
-        if self.native_eval:
+        if self.native_eval and hasattr(self.exec, "evaluate_pairs"):
             return self.exec.evaluate_pairs(models, jobs, shard=shard)
         return None
 
     def evaluate_jobs(self, model, jobs, shard=None):
-        if self.native_eval:
+        if self.native_eval and hasattr(self.exec, "evaluate_jobs"):
             return self.exec.evaluate_jobs(model, jobs, shard=shard)
         return super().evaluate_jobs(model, jobs, shard=shard)

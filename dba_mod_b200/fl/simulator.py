@@ -135,11 +135,25 @@ class Simulator:
         self.target_name = display_name(params["type"], "Target")
 
         self.backend = self._make_backend()
+        self.collective_path = "single process" if self.world == 1 else "torch.distributed baseline"
         if (self.world > 1 and self.device.type == "cuda" and params["fused_collectives"]
                 and not hasattr(self.comm, "fedavg_")):
-            from ..parallel.symm import PeerComm
-            self.comm = PeerComm(self.comm, self.spec.Df, self.device)
-            self.G = self.comm.set_global(self.G)
+            # all ranks must agree on the path: try to set the peer-memory communicator up, then vote
+            peer, err = None, None
+            try:
+                from ..parallel.symm import PeerComm
+                peer = PeerComm(self.comm, self.spec.Df, self.device)
+            except Exception as e:  # noqa: BLE001
+                err = e
+            ok = torch.tensor([1.0 if peer is not None else 0.0], device=self.device)
+            self.comm.all_reduce_sum_(ok)
+            if int(ok.item()) == self.world:
+                self.comm = peer
+                self.G = self.comm.set_global(self.G)
+                self.collective_path = "fused peer-memory kernels (NVLink P2P)"
+            else:
+                logger.warning(f"peer-memory communicator unavailable ({err}); using the NCCL baseline collectives")
+                self.collective_path = "nccl baseline"
         self.fg = agg.FoolsGoldState(use_memory=bool(params["fg_use_memory"]))
         self._loan_local_epoch = self.start_epoch - 1
         self.stream_inputs = False          # bench end-to-end mode: re-upload the round's inputs from pinned host

@@ -32,6 +32,7 @@ class BatchedNet:
         self.spec = spec
         self.has_bn = spec.Db > 0
         self.has_dropout = kind == C.TYPE_LOAN
+        self.dropout_p = 0.5          # LoanNet's nn.Dropout(0.5); 0 disables it (deterministic tests)
 
     # -------------------------------------------------------------------------------------------- public
     def forward(self, P: torch.Tensor, S: Optional[torch.Tensor], cnt: Optional[torch.Tensor], x: torch.Tensor,
@@ -45,6 +46,7 @@ class BatchedNet:
         (inactive clients' BN statistics / counters are left untouched).
         """
         ctx = _Ctx(self.spec, P, S, cnt, training, mask, active, generator)
+        ctx.dropout_p = self.dropout_p
         if self.kind == C.TYPE_LOAN:
             return self._loan(ctx, x, shared_input)
         if self.kind == C.TYPE_MNIST:
@@ -172,8 +174,9 @@ class _Ctx:
         w, b = self.w(wname), self.w(bname)
         return torch.baddbmm(b.unsqueeze(1), x, w.transpose(1, 2))
 
-    def dropout(self, x, p: float = 0.5):
-        if not self.training:
+    def dropout(self, x, p: float = None):
+        p = getattr(self, "dropout_p", 0.5) if p is None else p
+        if not self.training or p <= 0.0:
             return x
         keep = torch.rand(x.shape, device=x.device, generator=self.gen) >= p
         return x * keep.to(x.dtype) / (1.0 - p)

@@ -59,6 +59,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_foolsgold_weights", [P, L, P, P, L, I, L, I, P, P, P, P, P, P])
     _sig(lib, "dba_foolsgold_apply", [P, P, L, P, I, L, F, F, F, P])
     _sig(lib, "dba_conv_rows", [I, I, I], c_longlong)
+    _sig(lib, "dba_conv_set_debug", [P], None)
     _sig(lib, "dba_conv_tc", [P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_conv_tc_strided", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_pack_weights", [P, L, P, I, I, P, L, P])
@@ -71,6 +72,9 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_fedavg_p2p", [P, L, I, L, F, F, U, P, P, P, I, I, I, P, ctypes.c_uint, P])
     _sig(lib, "dba_allreduce_axpby_p2p", [L, F, F, P, P, P, I, I, P, ctypes.c_uint, P])
     _sig(lib, "dba_gram_ptrs", [P, I, L, P, P])
+    _sig(lib, "dba_loan_train", [P, L, P, L, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, F, F,
+                                 ctypes.c_uint, I, P])
+    _sig(lib, "dba_loan_eval", [P, L, I, P, P, P, L, P, P, I, P, P, P])
     _LIB = lib
     return lib
 

@@ -110,6 +110,37 @@ int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, voi
                     long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
                     int B, int H, int W, long long R, int up, long long Rup, void* stream);
 
+/* ---- LOAN MLP (csrc/loan_mlp.cu) ------------------------------------------------------------------------------- */
+
+/* Whole local training of K LOAN clients, one persistent CTA per client (gather + feature trigger + forward with
+ * fused dropout + CE + backward + SGD for all T steps).  Reference: models/loan_model.py:10-27, loan_train.py:11-261. */
+int dba_loan_train(float* W, long long ldw, float* gsum, long long ldg, const float* X, const long long* Y,
+                   const long long* idx, const float* lr, const unsigned char* active, const long long* epoch_of,
+                   const long long* poison_n, const long long* trig_row, const unsigned char* trig_mask,
+                   const float* trig_val, float* loss_sum, int* correct, int* count, int* pcount,
+                   unsigned char* nan_flag, int K, int T, int B, int E, int label_swap, float mu, float wd,
+                   unsigned int seed, int dropout, void* stream);
+/* M LOAN models on the rows idx[0..n) (optionally with one feature trigger applied).  Reference: test.py:7-239. */
+int dba_loan_eval(const float* W, long long ldw, int M, const float* X, const long long* Y, const long long* idx,
+                  long long n, const unsigned char* trig_mask, const float* trig_val, int label_swap, double* loss,
+                  long long* correct, void* stream);
+
+/* ---- peer-memory fused collectives (csrc/p2p_collectives.cu) ---------------------------------------------------- */
+
+/* FedAvg over all ranks: local K-way reduce -> cross-GPU reduce of the owned slice over NVLink peer loads -> update
+ * (+DP noise) -> peer stores into every replica.  Reference: helper.py:193-257 + the copy image_train.py:26-32. */
+int dba_fedavg_p2p(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
+                   const void* const* stage, const void* const* replica, const void* const* signal, int rank,
+                   int world, int total_clients, unsigned int* counter, unsigned int call_id, void* stream);
+/* replica = beta*replica + alpha*sum_r stage_r on every rank (Weiszfeld averages helper.py:395-418, FoolsGold weighted
+ * gradient reduce + server step helper.py:561-570,280-290). */
+int dba_allreduce_axpby_p2p(long long D, float alpha, float beta, const void* const* stage,
+                            const void* const* replica, const void* const* signal, int rank, int world,
+                            unsigned int* counter, unsigned int call_id, void* stream);
+/* Gram matrix over feature rows given by (possibly peer-mapped) pointers: FoolsGold's gather fused into the cosine
+ * GEMM (helper.py:544-555,574-577). */
+int dba_gram_ptrs(const double* const* rows, int n, long long L, double* gram, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
