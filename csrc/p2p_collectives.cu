@@ -62,37 +62,103 @@ __device__ void grid_and_peer_barrier(const PeerSet& ps, unsigned int* counter, 
   __syncthreads();
 }
 
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(float* p, const float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ float4 add4(float4 a, const float4 b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; return a; }
+
+// Slice [lo, hi) of the vector owned by `rank` (4-element aligned so the slices can be moved with 16-byte accesses).
+__device__ __forceinline__ void owned_slice(long long D, int rank, int world, long long& lo, long long& hi) {
+  long long per = (D + world - 1) / world;
+  per = (per + 3) & ~3LL;
+  lo = per * rank;
+  hi = lo + per;
+  if (lo > D) lo = D;
+  if (hi > D) hi = D;
+}
+
+// Phase 2 worker shared by both kernels: out = f(own value, sum over all peers' staging vectors) for the owned slice,
+// written to every peer's replica.  Remote loads have ~2-3 us latency, so every thread keeps world x 2 independent
+// 16-byte loads in flight before it touches the data.
+template <typename F>
+__device__ __forceinline__ void reduce_scatter_update_gather(const PeerSet& ps, long long D, F f) {
+  long long lo, hi;
+  owned_slice(D, ps.rank, ps.world, lo, hi);
+  const float* mine = ps.replica[ps.rank];
+  const long long nvec = (hi - lo) >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  for (; v + stride < nvec; v += 2 * stride) {
+    const long long i0 = lo + (v << 2), i1 = lo + ((v + stride) << 2);
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    float4 t0[kMaxRanks], t1[kMaxRanks];
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < ps.world) { t0[q] = ld4(ps.stage[q] + i0); t1[q] = ld4(ps.stage[q] + i1); }
+    const float4 g0 = ld4(mine + i0), g1 = ld4(mine + i1);
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < ps.world) { a0 = add4(a0, t0[q]); a1 = add4(a1, t1[q]); }
+    float4 o0, o1;
+    o0.x = f(g0.x, a0.x, i0); o0.y = f(g0.y, a0.y, i0 + 1); o0.z = f(g0.z, a0.z, i0 + 2); o0.w = f(g0.w, a0.w, i0 + 3);
+    o1.x = f(g1.x, a1.x, i1); o1.y = f(g1.y, a1.y, i1 + 1); o1.z = f(g1.z, a1.z, i1 + 2); o1.w = f(g1.w, a1.w, i1 + 3);
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < ps.world) { st4(ps.replica[q] + i0, o0); st4(ps.replica[q] + i1, o1); }
+  }
+  for (; v < nvec; v += stride) {
+    const long long i0 = lo + (v << 2);
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < ps.world; ++q) a0 = add4(a0, ld4(ps.stage[q] + i0));
+    const float4 g0 = ld4(mine + i0);
+    float4 o0;
+    o0.x = f(g0.x, a0.x, i0); o0.y = f(g0.y, a0.y, i0 + 1); o0.z = f(g0.z, a0.z, i0 + 2); o0.w = f(g0.w, a0.w, i0 + 3);
+    for (int q = 0; q < ps.world; ++q) st4(ps.replica[q] + i0, o0);
+  }
+  // scalar tail of the slice (only the last rank's slice can have one)
+  const long long t0s = lo + (nvec << 2);
+  for (long long i = t0s + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi; i += stride) {
+    float acc = 0.f;
+    for (int q = 0; q < ps.world; ++q) acc += ps.stage[q][i];
+    const float out = f(mine[i], acc, i);
+    for (int q = 0; q < ps.world; ++q) ps.replica[q][i] = out;
+  }
+}
+
 // F1: FedAvg fused with delta extraction, cross-GPU reduce, global update (+DP noise) and broadcast of the new model
-// into every replica (and, optionally, into this rank's client rows for the next round = R1).
+// into every replica.
 __global__ void __launch_bounds__(256) fedavg_p2p_kernel(const float* __restrict__ W, long long ldw, int K, long long D,
                                                          float coef, float sigma, unsigned long long seed,
                                                          PeerSet ps, unsigned int* counter, unsigned int call_id,
                                                          int total_clients) {
-  const float* G = ps.replica[ps.rank];
   float* stage = ps.stage[ps.rank];
-  // phase 1: local sum of client states (the -K*G term is applied once, in phase 2, with the global client count)
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < D; i += (long long)gridDim.x * blockDim.x) {
+  // phase 1: local sum of client states (the -n*G term is applied once, in phase 2, with the global client count)
+  const long long nvec = D >> 2;
+  const bool vec_ok = (ldw & 3) == 0 && (((uintptr_t)W & 15) == 0);
+  if (vec_ok) {
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < K; ++k) acc = add4(acc, ld4(W + k * ldw + (v << 2)));
+      st4(stage + (v << 2), acc);
+    }
+  }
+  for (long long i = (vec_ok ? (nvec << 2) : 0) + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < D;
+       i += (long long)gridDim.x * blockDim.x) {
     float acc = 0.f;
     for (int k = 0; k < K; ++k) acc += W[k * ldw + i];
     stage[i] = acc;
   }
   grid_and_peer_barrier(ps, counter, (2 * call_id + 1) * gridDim.x, 0, 2 * call_id + 1);
   // phase 2: this rank reduces + updates its slice and scatters it to all replicas
-  const long long per = (D + ps.world - 1) / ps.world;
-  const long long lo = per * ps.rank, hi = min(D, lo + per);
-  for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
-       i += (long long)gridDim.x * blockDim.x) {
-    float acc = 0.f;
-    for (int q = 0; q < ps.world; ++q) acc += ps.stage[q][i];
-    const float g = G[i];
-    float out = g + coef * (acc - (float)total_clients * g);
+  const float n = (float)total_clients;
+  reduce_scatter_update_gather(ps, D, [=](float g, float acc, long long i) {
+    float out = g + coef * (acc - n * g);
     if (sigma > 0.f) {
       curandStatePhilox4_32_10_t st;
       curand_init(seed, (unsigned long long)i, 0, &st);
       out += sigma * curand_normal(&st);
     }
-    for (int q = 0; q < ps.world; ++q) ps.replica[q][i] = out;
-  }
+    return out;
+  });
   grid_and_peer_barrier(ps, counter, (2 * call_id + 2) * gridDim.x, 1, 2 * call_id + 2);
 }
 
@@ -102,16 +168,9 @@ __global__ void __launch_bounds__(256) fedavg_p2p_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) allreduce_axpby_p2p_kernel(long long D, float alpha, float beta, PeerSet ps,
                                                                   unsigned int* counter, unsigned int call_id) {
   grid_and_peer_barrier(ps, counter, (2 * call_id + 1) * gridDim.x, 0, 2 * call_id + 1);
-  const long long per = (D + ps.world - 1) / ps.world;
-  const long long lo = per * ps.rank, hi = min(D, lo + per);
-  const float* mine = ps.replica[ps.rank];
-  for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
-       i += (long long)gridDim.x * blockDim.x) {
-    float acc = 0.f;
-    for (int q = 0; q < ps.world; ++q) acc += ps.stage[q][i];
-    const float out = (beta != 0.f ? beta * mine[i] : 0.f) + alpha * acc;
-    for (int q = 0; q < ps.world; ++q) ps.replica[q][i] = out;
-  }
+  reduce_scatter_update_gather(ps, D, [=](float g, float acc, long long) {
+    return (beta != 0.f ? beta * g : 0.f) + alpha * acc;
+  });
   grid_and_peer_barrier(ps, counter, (2 * call_id + 2) * gridDim.x, 1, 2 * call_id + 2);
 }
 

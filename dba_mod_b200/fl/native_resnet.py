@@ -195,7 +195,7 @@ class NativeResNet:
         d, dev, lib = self.data, self.device, self.lib
         J = len(jobs)
         Bt = self.eval_chunk
-        models = models.contiguous()
+        models = models if models.stride(-1) == 1 else models.contiguous()
         Mw = models.shape[0]
         pack = self.pack_weights(models)
         scale = torch.empty(Mw, self.bn_total, device=dev)
@@ -234,7 +234,7 @@ class NativeResNet:
         Bt = self.eval_chunk
         ids_all = self._shard(d.all_test_idx if split == "clean" else d.poison_test_idx, shard)
         n = int(ids_all.numel())
-        models = models.contiguous()
+        models = models if models.stride(-1) == 1 else models.contiguous()
         pack = self.pack_weights(models)
         scale = torch.empty(M, self.bn_total, device=dev)
         shift = torch.empty(M, self.bn_total, device=dev)

@@ -253,9 +253,16 @@ class Simulator:
         nbytes = 0
         if idx is not None and idx.numel():
             host_idx = idx.cpu()
-            rows = self._pinned["train"][host_idx]
-            if self.device.type == "cuda":
-                rows = rows.pin_memory()
+            n = int(host_idx.numel())
+            stage = self._pinned.get("stage")
+            if stage is None or stage.shape[0] < n:
+                stage = torch.empty((max(n, 8192),) + tuple(self._pinned["train"].shape[1:]),
+                                    dtype=self._pinned["train"].dtype)
+                if self.device.type == "cuda":
+                    stage = stage.pin_memory()
+                self._pinned["stage"] = stage
+            rows = stage[:n]
+            torch.index_select(self._pinned["train"], 0, host_idx, out=rows)      # gather into pinned memory
             dev_rows = rows.to(self.device, non_blocking=True)
             d.train_x.index_copy_(0, idx, dev_rows)
             nbytes += rows.numel() * rows.element_size()
@@ -280,7 +287,9 @@ class Simulator:
         use_fg = p["aggregation_methods"] == C.AGGR_FOOLSGOLD
 
         # R1: global -> client broadcast (image_train.py:26-32)
-        W = self.G.unsqueeze(0).repeat(K, 1)
+        ld = (Df + 31) // 32 * 32               # 128-byte aligned rows: the flat kernels vectorise over them
+        W = torch.empty(K, ld, device=dev)[:, :Df]
+        W.copy_(self.G.unsqueeze(0).expand(K, Df))
         cnt = self.G_cnt.unsqueeze(0).repeat(K, 1) if self.spec.n_counters else torch.zeros(K, 0, dtype=torch.long,
                                                                                              device=dev)
         grad_sum = None
@@ -447,6 +456,10 @@ class Simulator:
 
     def _run_eval_jobs(self, jobs) -> Dict[Tuple[int, str], Tuple[float, float, int, int]]:
         pairs = getattr(self.backend, "evaluate_pairs", None)
+        if pairs is not None and self.world > 1:
+            out = self._run_eval_jobs_balanced(jobs, pairs)
+            if out is not None:
+                return out
         if pairs is not None and jobs:
             res = pairs(torch.stack([j[2] for j in jobs]), [(j[0], max(j[1], 0)) for j in jobs])
             if res is not None:
@@ -465,6 +478,36 @@ class Simulator:
             for j, (_, k, tag) in enumerate(items):
                 acc = 100.0 * float(correct[j]) / n if n else 0
                 out[(k, tag)] = (float(loss[j]) / n if n else 0, acc, int(correct[j]), n)
+        return out
+
+    def _run_eval_jobs_balanced(self, jobs, pairs):
+        """Several ranks: the client -> rank placement is uneven (10 clients on 8 GPUs, attackers with extra tests),
+        so the models to evaluate are exchanged (~11 MB each over NVLink) and EVERY rank evaluates ALL
+        (model, input set) pairs on its own slice of the test split; the (loss, correct, count) sums are then
+        all-reduced and each rank keeps the rows of its own jobs."""
+        import torch.distributed as dist
+        meta_local = [(j[0], max(j[1], 0)) for j in jobs]
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, meta_local)
+        counts = [len(g) for g in gathered]
+        total = sum(counts)
+        if total == 0:
+            return {}
+        Df = self.spec.Df
+        mine = torch.stack([j[2][:Df] for j in jobs]) if jobs else torch.zeros(0, Df, device=self.device)
+        models_all = self.comm.all_gather_rows(mine.contiguous(), counts)
+        jobs_all = [m for g in gathered for m in g]
+        res = pairs(models_all, jobs_all, shard=(self.rank, self.world))
+        if res is None:
+            return None
+        t = torch.tensor([[r[0], float(r[1]), float(r[2])] for r in res], dtype=torch.float64, device=self.device)
+        self.comm.all_reduce_sum_(t)
+        lo = sum(counts[: self.rank])
+        rows = t[lo: lo + counts[self.rank]].cpu().tolist()
+        out = {}
+        for (split, trig, _, k, tag), (loss, corr, n) in zip(jobs, rows):
+            corr, n = int(round(corr)), int(round(n))
+            out[(k, tag)] = (loss / n if n else 0, 100.0 * corr / n if n else 0, corr, n)
         return out
 
     def _emit_rows(self, rows_local, counts) -> None:

@@ -31,10 +31,6 @@ class PeerComm:
         self.device = device
         self.lib = native.load()
         group = dist.group.WORLD
-        try:
-            symm.enable_symm_mem_for_group(group.group_name)
-        except Exception:  # noqa: BLE001  (newer torch enables it implicitly)
-            pass
         self.stage = symm.empty(self.D, dtype=torch.float32, device=device)
         self.replica = symm.empty(self.D, dtype=torch.float32, device=device)
         self.aux = symm.empty(self.D, dtype=torch.float32, device=device)
@@ -44,9 +40,10 @@ class PeerComm:
         self._h_replica = symm.rendezvous(self.replica, group)
         self._h_aux = symm.rendezvous(self.aux, group)
         self._h_signal = symm.rendezvous(self.signal, group)
-        self.has_multicast = bool(getattr(self._h_replica, "has_multicast_support", lambda *a: False)
-                                  (device.type, device.index)) if hasattr(self._h_replica, "has_multicast_support") \
-            else False
+        try:
+            self.has_multicast = int(self._h_replica.multicast_ptr) != 0
+        except Exception:  # noqa: BLE001
+            self.has_multicast = False
         PtrArr = ctypes.c_void_p * self.world
         self._p_stage = PtrArr(*[int(p) for p in self._h_stage.buffer_ptrs])
         self._p_replica = PtrArr(*[int(p) for p in self._h_replica.buffer_ptrs])

@@ -1,0 +1,38 @@
+"""Multi-GPU tests (need >= 2 GPUs on the box; skipped otherwise): fused peer-memory collectives and world-size
+invariance of a short CIFAR simulation on the native backend."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _need2():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+
+
+def _torchrun(n, script, *args, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+           "127.0.0.1", "--master-port", str(29600 + os.getpid() % 300), script, *args]
+    return subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+
+
+def test_p2p_collectives_two_ranks(native_lib):
+    _need2()
+    r = _torchrun(2, "tools/gpu_test_p2p.py")
+    assert r.returncode == 0 and "P2P_OK" in r.stdout, (r.stdout[-1500:], r.stderr[-1500:])
+
+
+def test_bench_two_ranks_runs(native_lib):
+    _need2()
+    r = _torchrun(2, "bench.py", "--gpus", "2", "--steps", "2", "--warmup", "3", timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    out = json.loads(line)
+    assert out["n_gpus"] == 2 and out["value"] > 0 and "peer-memory" in out["config"]["collectives"]
