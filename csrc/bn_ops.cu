@@ -219,6 +219,89 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------ max pooling
+// MaxPool2d(3, stride 2, pad 1) on planar-8 activations (Tiny-ImageNet stem, models/resnet_tinyimagenet.py:147).
+// Inputs are post-ReLU (>= 0) and the halo rows / columns of the layout are zero, so the window can be read without
+// bounds checks: a zero never beats a real maximum.  Backward is gather-style (no atomics): an input pixel receives
+// the gradient of every output window in which it is the first maximum in scan order (PyTorch's tie rule).
+struct PoolArgs {
+  const __nv_bfloat16* x;     // [K][C/8][Rin][8]   H x W grid
+  __nv_bfloat16* y;           // [K][C/8][Rout][8]  H/2 x W/2 grid (fwd out)
+  const __nv_bfloat16* gy;    // bwd: gradient wrt y
+  __nv_bfloat16* gx;          // bwd: gradient wrt x
+  long long Rin, Rout;
+  int K, C, B, H, W;
+};
+__device__ __forceinline__ uint4 max8(const uint4 a, const uint4 b) {
+  float x[8], y[8];
+  unpack8(a, x); unpack8(b, y);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) x[j] = fmaxf(x[j], y[j]);
+  return pack8(x);
+}
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const PoolArgs a) {
+  const int chunk = blockIdx.y, k = blockIdx.z;
+  const int Ho = a.H >> 1, Wo = a.W >> 1;
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const int Wpo = Wo + 1, So = (Ho + 1) * Wpo, leado = Wpo + 1;
+  const long long pin = ((long long)k * (a.C >> 3) + chunk) * a.Rin, pout = ((long long)k * (a.C >> 3) + chunk) * a.Rout;
+  const int total = a.B * Ho * Wo;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int wo = i % Wo, ho = (i / Wo) % Ho, b = i / (Wo * Ho);
+    const long long c = pin + lead + (long long)b * S + (2 * ho) * Wp + 2 * wo;      // window centre (h=2ho, w=2wo)
+    uint4 m = *reinterpret_cast<const uint4*>(a.x + (c - Wp - 1) * 8);
+#pragma unroll
+    for (int dh = -1; dh <= 1; ++dh)
+#pragma unroll
+      for (int dw = -1; dw <= 1; ++dw)
+        if (dh != -1 || dw != -1) m = max8(m, *reinterpret_cast<const uint4*>(a.x + (c + dh * Wp + dw) * 8));
+    *reinterpret_cast<uint4*>(a.y + (pout + leado + (long long)b * So + ho * Wpo + wo) * 8) = m;
+  }
+}
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const PoolArgs a) {
+  const int chunk = blockIdx.y, k = blockIdx.z;
+  const int Ho = a.H >> 1, Wo = a.W >> 1;
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const int Wpo = Wo + 1, So = (Ho + 1) * Wpo, leado = Wpo + 1;
+  const long long pin = ((long long)k * (a.C >> 3) + chunk) * a.Rin, pout = ((long long)k * (a.C >> 3) + chunk) * a.Rout;
+  const int total = a.B * a.H * a.W;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int w = i % a.W, h = (i / a.W) % a.H, b = i / (a.W * a.H);
+    const long long me = pin + lead + (long long)b * S + h * Wp + w;
+    float xv[8], acc[8];
+    unpack8(*reinterpret_cast<const uint4*>(a.x + me * 8), xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    // output windows (ho, wo) with |2ho - h| <= 1 and |2wo - w| <= 1
+    for (int ho = (h >> 1); ho <= ((h + 1) >> 1) && ho < Ho; ++ho)
+      for (int wo = (w >> 1); wo <= ((w + 1) >> 1) && wo < Wo; ++wo) {
+        const long long c = pin + lead + (long long)b * S + (2 * ho) * Wp + 2 * wo;
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(a.gy + (pout + leado + (long long)b * So + ho * Wpo + wo) * 8), g);
+        // first maximum in scan order per channel; positions before `me` in the scan must be strictly smaller,
+        // positions after it smaller or equal
+        bool first[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) first[j] = true;
+        const int my_dh = h - 2 * ho, my_dw = w - 2 * wo;
+        for (int dh = -1; dh <= 1; ++dh)
+          for (int dw = -1; dw <= 1; ++dw) {
+            if (dh == my_dh && dw == my_dw) continue;
+            const int hh = 2 * ho + dh, ww = 2 * wo + dw;
+            if (hh < 0 || hh >= a.H || ww < 0 || ww >= a.W) continue;       // padding never wins (-inf in PyTorch)
+            float o[8];
+            unpack8(*reinterpret_cast<const uint4*>(a.x + (c + dh * Wp + dw) * 8), o);
+            const bool before = dh < my_dh || (dh == my_dh && dw < my_dw);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) first[j] = first[j] && (before ? o[j] < xv[j] : o[j] <= xv[j]);
+          }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += first[j] ? g[j] : 0.f;
+      }
+    *reinterpret_cast<uint4*>(a.gx + me * 8) = pack8(acc);
+  }
+}
+
 inline dim3 bn_grid(int B, int H, int W, int C, int K) {
   const int total = B * (H + 1) * (W + 1);
   int rb = (total + 1023) / 1024;
@@ -270,6 +353,31 @@ int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, voi
   bn_bwd_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   bn_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(2);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// y = MaxPool2d(3, 2, 1)(x); x on the B x H x W grid, y on B x H/2 x W/2.  Rin / Rout = dba_conv_rows of the two grids.
+int dba_maxpool_fwd(const void* x, void* y, int K, int C, int B, int H, int W, long long Rin, long long Rout,
+                    void* stream) {
+  DBA_REQUIRE(K > 0 && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "dba_maxpool_fwd: K=%d C=%d H=%d W=%d", K, C, H, W);
+  PoolArgs a{(const __nv_bfloat16*)x, (__nv_bfloat16*)y, nullptr, nullptr, Rin, Rout, K, C, B, H, W};
+  int rb = (B * (H / 2) * (W / 2) + 1023) / 1024;
+  if (rb > 64) rb = 64;
+  maxpool_fwd_kernel<<<dim3(rb < 1 ? 1 : rb, C / 8, K), 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+// gx = d loss / d x given gy = d loss / d y (x is the forward input).
+int dba_maxpool_bwd(const void* x, const void* gy, void* gx, int K, int C, int B, int H, int W, long long Rin,
+                    long long Rout, void* stream) {
+  DBA_REQUIRE(K > 0 && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "dba_maxpool_bwd: K=%d C=%d H=%d W=%d", K, C, H, W);
+  PoolArgs a{(const __nv_bfloat16*)x, nullptr, (const __nv_bfloat16*)gy, (__nv_bfloat16*)gx, Rin, Rout, K, C, B, H, W};
+  int rb = (B * H * W + 1023) / 1024;
+  if (rb > 64) rb = 64;
+  maxpool_bwd_kernel<<<dim3(rb < 1 ? 1 : rb, C / 8, K), 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
 }

@@ -457,6 +457,37 @@ __global__ void fg_history_kernel(double* __restrict__ H, long long ldh, const i
     out[c * ldo + t] = use_memory ? nv : f;
   }
 }
+// Same, but every feature row is given by its own pointer: rows that live in another GPU's (peer-mapped) symmetric
+// buffer are pulled over NVLink by the loads of this kernel - the all-gather of FoolsGold's client features is fused
+// into the history update and never materialised (F3 of SURVEY §2.4).
+__global__ void fg_history_ptrs_kernel(double* __restrict__ H, long long ldh, const int* __restrict__ ids,
+                                       const float* const* __restrict__ feat_rows, int n, long long L, int use_memory,
+                                       double* __restrict__ out, long long ldo) {
+  const int c = blockIdx.y;
+  double* h = H + (long long)ids[c] * ldh;
+  const float* f_row = feat_rows[c];
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < L; t += (long long)gridDim.x * blockDim.x) {
+    double f = (double)f_row[t];
+    double nv = h[t] + f;
+    h[t] = nv;
+    out[c * ldo + t] = use_memory ? nv : f;
+  }
+}
+extern "C" int dba_foolsgold_weights_ptrs(double* history, long long ldh, const int* ids, const float* const* feat_rows,
+                                          int n, long long L, int use_memory, double* work_rows, double* gram,
+                                          double* cs, double* wv, double* alpha, void* stream) {
+  DBA_REQUIRE(n > 0 && n <= 1024 && L > 0, "dba_foolsgold_weights_ptrs: n=%d L=%lld", n, L);
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 gh(grid_for(L, 256, 2), n);
+  fg_history_ptrs_kernel<<<gh, 256, 0, st>>>(history, ldh, ids, feat_rows, n, L, use_memory, work_rows, L);
+  dim3 gg(n, n);
+  gram_kernel<<<gg, 256, 0, st>>>(work_rows, L, n, L, gram);
+  foolsgold_finish_kernel<<<1, 256, 2 * n * sizeof(double), st>>>(gram, n, cs, wv, alpha);
+  DBA_COUNT_LAUNCH(3);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
 // Client ids must be distinct within one call (they are: a client is selected at most once per round).
 extern "C" int dba_foolsgold_weights(double* history, long long ldh, const int* ids, const float* feat, long long ldf,
                                      int n, long long L, int use_memory, double* work_rows, double* gram, double* cs,

@@ -33,6 +33,8 @@ struct WgArgs {
   int tpg;                     // taps per group
   int ngroups;                 // tap groups
   int nmb;                     // Cout blocks of 128
+  int N;                       // input channels per accumulator block (<= 256)
+  int nnblk;                   // Cin / N
   int stages;
 };
 
@@ -44,7 +46,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mplanes = 16;                                   // M = 128 -> 16 planes of 8 output channels
-  const int nplanes = a.Cin >> 3;
+  const int nplanes = a.N >> 3;
   const uint32_t pitchA = kRowsK * 16u;
   const uint32_t bytesA = mplanes * pitchA;
   const uint32_t rowsB = kRowsK + 2 * a.halo;
@@ -73,7 +75,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int items = a.K * a.nmb * a.ngroups * a.nsplit;
+  const int items = a.K * a.nmb * a.ngroups * a.nnblk * a.nsplit;
   // real planes of dY available for this M block (the rest of the 16 planes stays unloaded: rows >= Cout of D are
   // never read back)
   if (warp == 0) {
@@ -81,8 +83,9 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       int it = 0;
       for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int sp = item % a.nsplit;
-        const int mb = (item / (a.nsplit * a.ngroups)) % a.nmb;
-        const int k = item / (a.nsplit * a.ngroups * a.nmb);
+        const int nbk = (item / a.nsplit) % a.nnblk;
+        const int mb = (item / (a.nsplit * a.nnblk * a.ngroups)) % a.nmb;
+        const int k = item / (a.nsplit * a.nnblk * a.ngroups * a.nmb);
         const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
         const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
         const int mreal = min(16, (a.Cout >> 3) - mb * 16);
@@ -97,17 +100,18 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
                      &full[s]);
           for (int p = 0; p < nplanes; ++p)
             bulk_g2s(smB + (size_t)s * bytesB + (size_t)p * pitchB,
-                     a.X + (long long)k * a.x_client + (long long)p * a.x_plane + (row - a.halo) * 8, pitchB, &full[s]);
+                     a.X + (long long)k * a.x_client + (long long)(nbk * nplanes + p) * a.x_plane + (row - a.halo) * 8,
+                     pitchB, &full[s]);
         }
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      const uint32_t idesc = umma_idesc_bf16(128, a.Cin, 1, 1);     // both operands MN-major
+      const uint32_t idesc = umma_idesc_bf16(128, a.N, 1, 1);       // both operands MN-major
       int it = 0, acc_it = 0;
       for (int item = blockIdx.x; item < items; item += gridDim.x, ++acc_it) {
         const int sp = item % a.nsplit;
-        const int grp = (item / a.nsplit) % a.ngroups;
+        const int grp = (item / (a.nsplit * a.nnblk)) % a.ngroups;
         const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
         const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
         const int t0 = grp * a.tpg, t1 = min(a.taps, t0 + a.tpg);
@@ -124,7 +128,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
           for (int tap = t0; tap < t1; ++tap) {
             int shift = 0;
             if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
-            const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.Cin);
+            const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.N);
             const uint64_t dB1 = dB0 + (uint64_t)(int64_t)shift;
             umma_f16(d_tmem, dA0, dB1, idesc, acc0);
 #pragma unroll
@@ -141,9 +145,10 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
     int acc_it = 0;
     for (int item = blockIdx.x; item < items; item += gridDim.x, ++acc_it) {
       const int sp = item % a.nsplit;
-      const int grp = (item / a.nsplit) % a.ngroups;
-      const int mb = (item / (a.nsplit * a.ngroups)) % a.nmb;
-      const int k = item / (a.nsplit * a.ngroups * a.nmb);
+      const int nbk = (item / a.nsplit) % a.nnblk;
+      const int grp = (item / (a.nsplit * a.nnblk)) % a.ngroups;
+      const int mb = (item / (a.nsplit * a.nnblk * a.ngroups)) % a.nmb;
+      const int k = item / (a.nsplit * a.nnblk * a.ngroups * a.nmb);
       const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
       const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
       const int t0 = grp * a.tpg, t1 = min(a.taps, t0 + a.tpg);
@@ -154,22 +159,23 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       const bool vec = ((a.cin_real | a.w_off) & 3) == 0 && (a.ldg & 3) == 0;
       if (c1 > c0) {
         for (int tap = t0; tap < t1; ++tap) {
-          float* dst = gk + ((long long)co * a.taps + tap) * a.cin_real;
-          for (int n0 = 0; n0 < a.Cin; n0 += 16) {
+          float* dst = gk + ((long long)co * a.taps + tap) * a.cin_real + nbk * a.N;
+          const int cin_left = a.cin_real - nbk * a.N;
+          for (int n0 = 0; n0 < a.N; n0 += 16) {
             uint32_t v[16];
-            tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tap - t0) * a.Cin + n0), v);
+            tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tap - t0) * a.N + n0), v);
             tmem_ld_wait();
             if (co < a.cout_real) {
               if (vec) {
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
-                  if (n0 + j < a.cin_real)
+                  if (n0 + j < cin_left)
                     red_add_v4(dst + n0 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
                                __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
               } else {
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
-                  if (n0 + j < a.cin_real) atomicAdd(dst + n0 + j, __uint_as_float(v[j]));
+                  if (n0 + j < cin_left) atomicAdd(dst + n0 + j, __uint_as_float(v[j]));
               }
             }
           }
@@ -199,7 +205,7 @@ extern "C" {
 int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
                  int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
-  DBA_REQUIRE(Cin % 16 == 0 && Cin <= 256 && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d (<=256, %%16) Cout=%d", Cin, Cout);
+  DBA_REQUIRE(Cin % 16 == 0 && (Cin <= 256 || Cin % 256 == 0) && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d Cout=%d", Cin, Cout);
   WgArgs a{};
   a.dY = (const __nv_bfloat16*)dY; a.X = (const __nv_bfloat16*)X; a.G = G; a.ldg = ldg; a.w_off = w_off;
   a.K = K; a.Cout = Cout; a.Cin = Cin; a.cin_real = cin_real; a.cout_real = cout_real; a.taps = ksize * ksize;
@@ -212,16 +218,18 @@ int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_o
   a.x_plane = R * 8; a.x_client = (long long)(Cin / 8) * R * 8;
   a.body_chunks = (int)(((long long)B * S + kRowsK - 1) / kRowsK);
   a.nmb = (Cout + 127) / 128;
-  a.tpg = 512 / Cin;
+  a.N = Cin <= 256 ? Cin : 256;
+  a.nnblk = Cin / a.N;
+  a.tpg = 512 / a.N;
   if (a.tpg > a.taps) a.tpg = a.taps;
   a.ngroups = (a.taps + a.tpg - 1) / a.tpg;
   a.tpg = (a.taps + a.ngroups - 1) / a.ngroups;            // balance the groups (e.g. 9 taps, 4 max -> 3+3+3)
-  const int base_items = K * a.nmb * a.ngroups;
+  const int base_items = K * a.nmb * a.ngroups * a.nnblk;
   int nsplit = (2 * kNumSMs + base_items - 1) / base_items;
   if (nsplit > a.body_chunks) nsplit = a.body_chunks;
   if (nsplit < 1) nsplit = 1;
   a.nsplit = nsplit;
-  const size_t bytesA = 16 * kRowsK * 16, bytesB = (size_t)(Cin / 8) * (kRowsK + 2 * a.halo) * 16;
+  const size_t bytesA = 16 * kRowsK * 16, bytesB = (size_t)(a.N / 8) * (kRowsK + 2 * a.halo) * 16;
   a.stages = 3;
   size_t need = a.stages * (bytesA + bytesB) + 1024;
   if (need > 220 * 1024) { a.stages = 2; need = a.stages * (bytesA + bytesB) + 1024; }

@@ -84,6 +84,56 @@ class CudaBackend(TorchBackend):
         return agg.RFAResult(int(st[2]), [float(v) for v in wv.cpu().tolist()],
                              [float(v) for v in dist.cpu().tolist()], med, float(obj.cpu()[0]), int(st[1]))
 
+    def foolsgold_native(self, names_in_order, feats_local, counts, comm, use_memory: bool):
+        """FoolsGold weights on the device (helper.py:527-607): per-client fp64 history, Gram, cosine, pardoning, logit.
+        With several ranks the clients' feature rows stay where they were produced: every rank's kernel pulls the
+        remote rows through peer-mapped pointers (NVLink loads inside the history/Gram kernels, no all-gather)."""
+        from ..ops import flat
+        dev = self.device
+        L = feats_local.shape[1]
+        n = len(names_in_order)
+        if not hasattr(self, "_fg_hist"):
+            cap = max(int(self.params["number_of_total_participants"]), n) + 64
+            self._fg_hist = torch.zeros(cap, L, dtype=torch.float64, device=dev)
+            self._fg_ids = {}
+        for nm in names_in_order:
+            if nm not in self._fg_ids:
+                if len(self._fg_ids) >= self._fg_hist.shape[0]:
+                    self._fg_hist = torch.cat([self._fg_hist, torch.zeros_like(self._fg_hist)], 0)
+                self._fg_ids[nm] = len(self._fg_ids)
+        ids = torch.tensor([self._fg_ids[nm] for nm in names_in_order], dtype=torch.int32, device=dev)
+        if comm.world == 1:
+            return flat.foolsgold_weights(self._fg_hist, ids, feats_local.float().contiguous(), use_memory)
+        if not hasattr(comm, "feature_row_ptrs"):
+            return None
+        ptrs = comm.feature_row_ptrs(feats_local.float().contiguous(), counts)      # device int64 [n]
+        work = torch.empty(n, L, dtype=torch.float64, device=dev)
+        gram = torch.empty(n, n, dtype=torch.float64, device=dev)
+        cs = torch.empty(n, n, dtype=torch.float64, device=dev)
+        wv = torch.empty(n, dtype=torch.float64, device=dev)
+        alpha = torch.empty(n, dtype=torch.float64, device=dev)
+        lib = native.load()
+        native.check(lib.dba_foolsgold_weights_ptrs(native.ptr(self._fg_hist), self._fg_hist.stride(0),
+                                                    native.ptr(ids), native.ptr(ptrs), n, L, int(use_memory),
+                                                    native.ptr(work), native.ptr(gram), native.ptr(cs),
+                                                    native.ptr(wv), native.ptr(alpha), native.stream()))
+        return wv, alpha
+
+    def foolsgold_apply_native(self, G, grad_sum, wv_local, n_clients, eta, lr, decay, comm) -> bool:
+        """G[:Dp] -= lr * (eta/n * sum_c wv_c * gradsum_c + decay * G[:Dp]); one fused launch (per rank)."""
+        from ..ops import flat
+        Dp = self.spec.Dp
+        if comm.world == 1:
+            S = grad_sum if grad_sum is not None else torch.zeros(0, Dp, device=self.device)
+            flat.foolsgold_apply_(G, S.contiguous(), wv_local.double().contiguous(), Dp, eta / n_clients, lr, decay)
+            return True
+        if hasattr(comm, "allreduce_axpby_"):
+            part = (wv_local.float()[:, None] * grad_sum[:, :Dp]).sum(0) if grad_sum is not None and grad_sum.shape[0] \
+                else torch.zeros(Dp, device=self.device)
+            comm.allreduce_axpby_(part.contiguous(), -lr * eta / n_clients, 1.0 - lr * decay, n=Dp, target="replica")
+            return True
+        return False
+
     # -------------------------------------------------------------------------------- train / evaluate
     def train(self, sch, W, cnt, anchor, want_grad_sum, generator=None):
         needs_dist = float(self.params["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any())

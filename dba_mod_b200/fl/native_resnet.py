@@ -49,11 +49,19 @@ class NativeResNet:
         self.params, self.spec, self.data, self.device = params, spec, data, device
         self.lib = native.load()
         self.kind = params["type"]
-        if self.kind != C.TYPE_CIFAR:
-            raise ImportError("native executor currently covers the CIFAR ResNet-18")
+        if self.kind == C.TYPE_CIFAR:       # models/resnet_cifar.py:67-104
+            self.widths, self.ress, self.ncls = [32, 64, 128, 256], [32, 16, 8, 4], 10
+            self.stem = dict(ks=3, stride=1, pad=1, res=32)
+            self.pool, self.head, self.skip = False, "linear", "shortcut"
+        elif self.kind == C.TYPE_TINYIMAGENET:   # models/resnet_tinyimagenet.py:122-238 (torchvision layout)
+            self.widths, self.ress, self.ncls = [64, 128, 256, 512], [16, 8, 4, 2], 200
+            self.stem = dict(ks=7, stride=2, pad=3, res=32)
+            self.pool, self.head, self.skip = True, "fc", "downsample"
+        else:
+            raise ImportError("the native tensor-core executor covers the ResNet-18 families (CIFAR, Tiny-ImageNet)")
         self.B = int(params["batch_size"])
         self.label_swap = int(params["poison_label_swap"])
-        self.ncls = 10
+        self.head_C, self.head_H = self.widths[-1], self.ress[-1]
         self._plan()
         self.can_eval = True
         self.can_train = bool(params.get("native_train", True))
@@ -67,10 +75,11 @@ class NativeResNet:
     # ----------------------------------------------------------------------------------------------- plan
     def _plan(self) -> None:
         sp = self.spec
-        L: List[ConvL] = [ConvL("conv1.weight", "bn1", 3, 32, 3, 32, 1, fold=True)]
-        widths = [32, 64, 128, 256]
-        res = 32
-        cin = 32
+        st = self.stem
+        L: List[ConvL] = [ConvL("conv1.weight", "bn1", 3, self.widths[0], st["ks"], st["res"], 1, fold=True)]
+        widths = self.widths
+        res = self.ress[0]
+        cin = widths[0]
         self.blocks = []
         for li, w in enumerate(widths, start=1):
             for bi in range(2):
@@ -79,8 +88,8 @@ class NativeResNet:
                 c1 = ConvL(f"{pre}.conv1.weight", f"{pre}.bn1", cin, w, 3, res, sub)
                 c2 = ConvL(f"{pre}.conv2.weight", f"{pre}.bn2", w, w, 3, res // sub, 1)
                 sc = None
-                if f"{pre}.shortcut.0.weight" in sp.entries:
-                    sc = ConvL(f"{pre}.shortcut.0.weight", f"{pre}.shortcut.1", cin, w, 1, res, sub)
+                if f"{pre}.{self.skip}.0.weight" in sp.entries:
+                    sc = ConvL(f"{pre}.{self.skip}.0.weight", f"{pre}.{self.skip}.1", cin, w, 1, res, sub)
                 L += [c1, c2] + ([sc] if sc else [])
                 self.blocks.append((c1, c2, sc))
                 res //= sub
@@ -92,7 +101,9 @@ class NativeResNet:
         for l in L:
             taps = l.ks * l.ks
             if l.fold:
-                l.cin_p, l.cout_p = (taps * l.cin + 15) // 16 * 16, (l.cout + 31) // 32 * 32
+                kk = taps * l.cin
+                l.cin_p = 32 if kk <= 32 else (kk + 63) // 64 * 64       # 27 -> 32 (CIFAR), 147 -> 192 (Tiny 7x7)
+                l.cout_p = (l.cout + 31) // 32 * 32
                 n_f = l.cin_p * l.cout_p
             else:
                 l.cin_p, l.cout_p = (l.cin + 15) // 16 * 16, (l.cout + 31) // 32 * 32
@@ -114,8 +125,8 @@ class NativeResNet:
         self.bn_total = bn_off
         self.pack_table = torch.tensor(rows, dtype=torch.int32, device=self.device).contiguous()
         self.fold_table = torch.tensor(fold_rows, dtype=torch.int32, device=self.device).contiguous()
-        self.head_w_off = sp.entries["linear.weight"].offset
-        self.head_b_off = sp.entries["linear.bias"].offset
+        self.head_w_off = sp.entries[self.head + ".weight"].offset
+        self.head_b_off = sp.entries[self.head + ".bias"].offset
 
     # ------------------------------------------------------------------------------------------ helpers
     def pack_weights(self, W: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -159,9 +170,12 @@ class NativeResNet:
         dev = self.device
         z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
         kin = M if per_job_input else 1
-        bufs = {"stem_in": z(kin, 32, 32), "lv": {}}
-        for w, r in zip([32, 64, 128, 256], [32, 16, 8, 4]):
+        stem = self.layers[0]
+        bufs = {"stem_in": z(kin, stem.cin_p, stem.H), "lv": {}}
+        for w, r in zip(self.widths, self.ress):
             bufs["lv"][r] = [z(M, w, r) for _ in range(4)]
+        if self.pool:
+            bufs["stem_out"] = z(M, self.widths[0], stem.H)
         bufs["labels"] = torch.zeros(kin, Bt, dtype=torch.int32, device=dev)
         bufs["idx"] = torch.full((1, Bt), -1, dtype=torch.long, device=dev)
         self._eval_bufs[key] = bufs
@@ -222,8 +236,9 @@ class NativeResNet:
             a = bufs["out"]
             native.check(lib.dba_head(native.ptr(a), native.ptr(models), 0 if w_shared else models.stride(0),
                                       self.head_w_off, self.head_b_off, None, 0, None, native.ptr(labels), 0, None,
-                                      None, native.ptr(mf), native.ptr(mi), 1, None, J, Bt, 256, 4, 4, self.ncls,
-                                      Geom(Bt, 4, 4).rows, native.stream()))
+                                      None, native.ptr(mf), native.ptr(mi), 1, None, J, Bt, self.head_C, self.head_H,
+                                      self.head_H, self.ncls, Geom(Bt, self.head_H, self.head_H).rows,
+                                      native.stream()))
         mf_c, mi_c = mf.cpu(), mi.cpu()
         return [(float(mf_c[j, 0]), int(mi_c[j, 0, 0]), ns[j]) for j in range(J)]
 
@@ -255,8 +270,9 @@ class NativeResNet:
             a = bufs["out"]
             native.check(lib.dba_head(native.ptr(a), native.ptr(models), models.stride(0), self.head_w_off,
                                       self.head_b_off, None, 0, None, native.ptr(labels), 1, None, None,
-                                      native.ptr(mf), native.ptr(mi), 1, None, M, Bt, 256, 4, 4, self.ncls,
-                                      Geom(Bt, 4, 4).rows, native.stream()))
+                                      native.ptr(mf), native.ptr(mi), 1, None, M, Bt, self.head_C, self.head_H,
+                                      self.head_H, self.ncls, Geom(Bt, self.head_H, self.head_H).rows,
+                                      native.stream()))
         return mf[:, 0].double(), mi[:, 0, 0].long(), n
 
     def _forward_eval(self, M, Bt, idx, trow, pn, pack, scale, shift, bufs, labels, per_job=False,
@@ -267,18 +283,26 @@ class NativeResNet:
         native.check(lib.dba_input_stage_image(
             native.ptr(d.test_x), native.ptr(d.test_y), native.ptr(idx), ld_idx if ld_idx is not None else idx.stride(0),
             native.ptr(self.trig_u8), native.ptr(trow), native.ptr(pn), None, native.ptr(xin), native.ptr(labels),
-            M if per_job else 1, Bt, d.H, d.W, d.C, 3, 1, 1, 32, 32, stem.cin_p, self.label_swap, xin.shape[2],
-            native.stream()))
+            M if per_job else 1, Bt, d.H, d.W, d.C, self.stem["ks"], self.stem["stride"], self.stem["pad"], stem.H,
+            stem.H, stem.cin_p, self.label_swap, xin.shape[2], native.stream()))
         ws = per_job if w_shared is None else w_shared
 
         def ss(l):
             return scale[:, l.bn_off:l.bn_off + l.cout], shift[:, l.bn_off:l.bn_off + l.cout]
 
         lv = bufs["lv"]
-        cur = lv[32][0]
         sc_, sh_ = ss(stem)
-        self._conv(xin, pack, stem, M, Bt, cur, scale=sc_, shift=sh_, relu=True, x_shared=not per_job, w_shared=ws)
-        res = 32
+        if self.pool:
+            so = bufs["stem_out"]
+            self._conv(xin, pack, stem, M, Bt, so, scale=sc_, shift=sh_, relu=True, x_shared=not per_job, w_shared=ws)
+            cur = lv[self.ress[0]][0]
+            native.check(lib.dba_maxpool_fwd(native.ptr(so), native.ptr(cur), M, self.widths[0], Bt, stem.H, stem.H,
+                                             so.shape[2], cur.shape[2], native.stream()))
+        else:
+            cur = lv[self.ress[0]][0]
+            self._conv(xin, pack, stem, M, Bt, cur, scale=sc_, shift=sh_, relu=True, x_shared=not per_job,
+                       w_shared=ws)
+        res = self.ress[0]
         ci = 0
         for (c1, c2, sc) in self.blocks:
             r_out = res // c1.sub
@@ -309,7 +333,8 @@ class NativeResNet:
         def z(c, r):
             return torch.zeros(K, c // 8, Geom(B, r, r).rows, 8, dtype=torch.bfloat16, device=dev)
 
-        t = {"xin": z(32, 32), "labels": torch.zeros(K, B, dtype=torch.int32, device=dev)}
+        stem = self.layers[0]
+        t = {"xin": z(stem.cin_p, stem.H), "labels": torch.zeros(K, B, dtype=torch.int32, device=dev)}
         for l in self.layers:
             ro = l.H // l.sub
             t[("y", l.name)] = z(l.cout_p, ro)
@@ -319,8 +344,11 @@ class NativeResNet:
             else:
                 t[("dy", l.name)] = z(l.cout_p, l.H)          # on the input grid (zero-upsampled when sub == 2)
         # gradient scratch per resolution level: g (block output grad), dz, da1, dx
-        for w, r in zip([32, 64, 128, 256], [32, 16, 8, 4]):
+        for w, r in zip(self.widths, self.ress):
             t[("g", r)] = [z(w, r) for _ in range(4)]
+        if self.pool:
+            t["pool_out"] = z(self.widths[0], self.ress[0])
+            t["pool_g"] = z(self.widths[0], stem.H)
         t["stats"] = torch.zeros(K, 2 * self.bn_total, device=dev)
         t["saved"] = torch.zeros(K, 2 * self.bn_total, device=dev)
         t["sums"] = torch.zeros(K, 2 * self.bn_total, device=dev)
@@ -455,15 +483,15 @@ class NativeResNet:
         nvalid, active, slot = t["st_nvalid"], t["st_active"], t["st_slot"]
         mf, mi, nan = t["mf"], t["mi"], t["nan"]
         stem = self.layers[0]
-        lv_g = {r: t[("g", r)] for r in (32, 16, 8, 4)}
+        lv_g = {r: t[("g", r)] for r in self.ress}
         pack = self.pack_weights(W, t["pack"])
         t["stats"].zero_(); t["sums"].zero_(); Gr.zero_()
         native.check(lib.dba_input_stage_image(
             native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(t["st_idx"]), t["st_idx"].stride(0),
             native.ptr(self.trig_u8), native.ptr(t["trig_row"]), native.ptr(t["poison_n"]),
             native.ptr(t["st_flip"]) if with_flip else None, native.ptr(t["xin"]),
-            native.ptr(t["labels"]), K, B, d.H, d.W, d.C, 3, 1, 1, 32, 32, stem.cin_p, self.label_swap,
-            t["xin"].shape[2], native.stream()))
+            native.ptr(t["labels"]), K, B, d.H, d.W, d.C, self.stem["ks"], self.stem["stride"], self.stem["pad"],
+            stem.H, stem.H, stem.cin_p, self.label_swap, t["xin"].shape[2], native.stream()))
         st = t["stats"]
 
         def fconv(l, x, y):
@@ -474,6 +502,10 @@ class NativeResNet:
         fconv(stem, t["xin"], y0)
         self._bn_apply(stem, K, y0, a0, None, True, W, t, nvalid, active)
         x = a0
+        if self.pool:
+            x = t["pool_out"]
+            native.check(lib.dba_maxpool_fwd(native.ptr(a0), native.ptr(x), K, self.widths[0], B, stem.H, stem.H,
+                                             a0.shape[2], x.shape[2], native.stream()))
         inputs = []
         for (c1, c2, sc) in self.blocks:
             inputs.append(x)
@@ -491,11 +523,12 @@ class NativeResNet:
             self._bn_apply(c2, K, y2, out, skip, True, W, t, nvalid, active)
             x = out
         # ---------------------------------------------------------------------- head (fwd + bwd)
-        g = lv_g[4][0]
+        g = lv_g[self.head_H][0]
         native.check(lib.dba_head(native.ptr(x), native.ptr(W), W.stride(0), self.head_w_off, self.head_b_off,
                                   native.ptr(Gr), Gr.stride(0), native.ptr(g), native.ptr(t["labels"]), 0,
                                   native.ptr(nvalid), native.ptr(slot), native.ptr(mf), native.ptr(mi), mf.shape[1],
-                                  native.ptr(nan), K, B, 256, 4, 4, self.ncls, x.shape[2], native.stream()))
+                                  native.ptr(nan), K, B, self.head_C, self.head_H, self.head_H, self.ncls, x.shape[2],
+                                  native.stream()))
         # ---------------------------------------------------------------------- backward
         for bi in range(len(self.blocks) - 1, -1, -1):
             c1, c2, sc = self.blocks[bi]
@@ -522,6 +555,10 @@ class NativeResNet:
                 self._wgrad(sc, K, dys, xin_b, t)
                 self._dgrad(sc, K, dys, pack, dx, res=dx2)
             g = dx
+        if self.pool:
+            native.check(lib.dba_maxpool_bwd(native.ptr(a0), native.ptr(g), native.ptr(t["pool_g"]), K, self.widths[0], B,
+                                             stem.H, stem.H, a0.shape[2], g.shape[2], native.stream()))
+            g = t["pool_g"]
         dy0 = t[("dy", stem.name)]
         self._bn_bwd(stem, K, g, y0, a0, dy0, None, W, t, nvalid, up=False)
         self._wgrad(stem, K, dy0, t["xin"], t)

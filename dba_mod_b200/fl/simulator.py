@@ -575,16 +575,25 @@ class Simulator:
         else:
             feats_local = grad_sum[:, self.spec.fg_slice] if grad_sum is not None and grad_sum.shape[0] else \
                 torch.zeros(0, self.spec.fg_len, device=self.device)
-            feats = comm.all_gather_rows(feats_local.contiguous(), counts)
-            fmat = self.fg.features(names_in_order, feats)
-            wv_t, alpha_t = agg.foolsgold_weights(fmat)
+            res = None
+            if hasattr(be, "foolsgold_native"):
+                res = be.foolsgold_native(names_in_order, feats_local.contiguous(), counts, comm,
+                                          bool(p["fg_use_memory"]))
+            if res is None:       # torch / NCCL path (CPU, or peer memory unavailable)
+                feats = comm.all_gather_rows(feats_local.contiguous(), counts)
+                fmat = self.fg.features(names_in_order, feats)
+                res = agg.foolsgold_weights(fmat)
+            wv_t, alpha_t = res
             logger.info(f"[foolsgold agg] wv: {wv_t.tolist()}")
             self.fg.wv_history.append(wv_t.tolist())
             lo = sum(counts[: self.rank])
             wv_local = wv_t[lo: lo + counts[self.rank]].to(self.device)
             gs = grad_sum if grad_sum is not None else torch.zeros(0, self.spec.Dp, device=self.device)
-            agg.foolsgold_update_(self.G, self.spec.Dp, gs, wv_local, len(names), float(p["eta"]), float(p["lr"]),
-                                  float(p["decay"]), comm)
+            done = hasattr(be, "foolsgold_apply_native") and be.foolsgold_apply_native(
+                self.G, gs, wv_local, len(names), float(p["eta"]), float(p["lr"]), float(p["decay"]), comm)
+            if not done:
+                agg.foolsgold_update_(self.G, self.spec.Dp, gs, wv_local, len(names), float(p["eta"]),
+                                      float(p["lr"]), float(p["decay"]), comm)
             wv, alphas = [float(v) for v in wv_t.tolist()], [float(v) for v in alpha_t.tolist()]
         rep.agg_weights, rep.agg_alphas = wv, alphas
         if self.is_main:

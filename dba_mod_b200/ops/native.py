@@ -57,6 +57,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_fedavg_update", [P, P, L, I, L, F, F, U, I, P])
     _sig(lib, "dba_weiszfeld", [P, L, P, I, L, P, I, F, D, P, P, P, P, P, P, P, L, P])
     _sig(lib, "dba_foolsgold_weights", [P, L, P, P, L, I, L, I, P, P, P, P, P, P])
+    _sig(lib, "dba_foolsgold_weights_ptrs", [P, L, P, P, I, L, I, P, P, P, P, P, P])
     _sig(lib, "dba_foolsgold_apply", [P, P, L, P, I, L, F, F, F, P])
     _sig(lib, "dba_conv_rows", [I, I, I], c_longlong)
     _sig(lib, "dba_conv_set_debug", [P], None)
@@ -68,6 +69,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_head", [P, P, L, I, I, P, L, P, P, I, P, P, P, P, I, P, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_bn_apply", [P, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
     _sig(lib, "dba_bn_backward", [P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
+    _sig(lib, "dba_maxpool_fwd", [P, P, I, I, I, I, I, L, L, P])
+    _sig(lib, "dba_maxpool_bwd", [P, P, P, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_wgrad_tc", [P, P, P, L, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_fedavg_p2p", [P, L, I, L, F, F, U, P, P, P, I, I, I, P, ctypes.c_uint, P])
     _sig(lib, "dba_allreduce_axpby_p2p", [L, F, F, P, P, P, I, I, P, ctypes.c_uint, P])

@@ -100,3 +100,27 @@ class PeerComm:
                                                       native.stream()))
         self.call_id += 1
         return tgt[:n]
+
+    def feature_row_ptrs(self, feats_local: torch.Tensor, counts) -> torch.Tensor:
+        """Publishes this rank's FoolsGold feature rows in a symmetric buffer and returns, for the concatenated
+        global row order, a device array of pointers to where each row lives (own memory or a peer's, mapped over
+        NVLink).  Kernels that walk these pointers perform the gather themselves."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        n, L = sum(counts), feats_local.shape[1]
+        need = n * L
+        if getattr(self, "_feat", None) is None or self._feat.numel() < need:
+            self._feat = symm.empty(max(need, 1), dtype=torch.float32, device=self.device)
+            self._h_feat = symm.rendezvous(self._feat, dist.group.WORLD)
+        lo = sum(counts[: self.rank])
+        if feats_local.shape[0]:
+            self._feat[lo * L:(lo + feats_local.shape[0]) * L].copy_(feats_local.reshape(-1))
+        torch.cuda.synchronize(self.device)      # rows must be in memory before any peer starts reading them
+        self.base.barrier()
+        ptrs, row = [], 0
+        for r, c in enumerate(counts):
+            base = int(self._h_feat.buffer_ptrs[r])
+            for _ in range(c):
+                ptrs.append(base + row * L * 4)
+                row += 1
+        return torch.tensor(ptrs, dtype=torch.int64, device=self.device)

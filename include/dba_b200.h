@@ -58,6 +58,11 @@ int dba_weiszfeld(const float* W, long long ldw, const float* G, int n, long lon
 int dba_foolsgold_weights(double* history, long long ldh, const int* ids, const float* feat, long long ldf, int n,
                           long long L, int use_memory, double* work_rows, double* gram, double* cs, double* wv,
                           double* alpha, void* stream);
+/* Variant whose feature rows are given by (possibly peer-mapped) pointers: the gather of the clients' features from the
+ * other GPUs happens inside the kernel's loads. */
+int dba_foolsgold_weights_ptrs(double* history, long long ldh, const int* ids, const float* const* feat_rows, int n,
+                               long long L, int use_memory, double* work_rows, double* gram, double* cs, double* wv,
+                               double* alpha, void* stream);
 int dba_foolsgold_apply(float* G, const float* S, long long lds, const double* wv, int K, long long Dp,
                         float eta_over_n, float lr, float decay, void* stream);
 
@@ -109,6 +114,12 @@ int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, voi
                     long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
                     long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
                     int B, int H, int W, long long R, int up, long long Rup, void* stream);
+
+/* MaxPool2d(3, 2, 1) forward / backward on planar-8 activations (Tiny-ImageNet stem, resnet_tinyimagenet.py:147). */
+int dba_maxpool_fwd(const void* x, void* y, int K, int C, int B, int H, int W, long long Rin, long long Rout,
+                    void* stream);
+int dba_maxpool_bwd(const void* x, const void* gy, void* gx, int K, int C, int B, int H, int W, long long Rin,
+                    long long Rout, void* stream);
 
 /* ---- LOAN MLP (csrc/loan_mlp.cu) ------------------------------------------------------------------------------- */
 

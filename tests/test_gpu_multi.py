@@ -36,3 +36,22 @@ def test_bench_two_ranks_runs(native_lib):
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     out = json.loads(line)
     assert out["n_gpus"] == 2 and out["value"] > 0 and "peer-memory" in out["config"]["collectives"]
+
+
+@pytest.mark.parametrize("method", ["mean", "geom_median", "foolsgold"])
+def test_world_size_invariance_native(native_lib, method):
+    """1 rank vs 2 ranks (clients sharded, fused peer-memory collectives): same global model up to bf16 / reduction
+    order noise, same aggregation weights."""
+    _need2()
+    one = subprocess.run([sys.executable, "tools/gpu_sim_worker.py", method, "2"], cwd=ROOT, capture_output=True,
+                         text=True, timeout=600, env=dict(os.environ, WORLD_SIZE="1"))
+    assert one.returncode == 0, one.stderr[-1500:]
+    two = _torchrun(2, "tools/gpu_sim_worker.py", method, "2")
+    assert two.returncode == 0, two.stderr[-1500:]
+    a = json.loads([l for l in one.stdout.splitlines() if l.startswith("RESULT ")][0][7:])
+    b = json.loads([l for l in two.stdout.splitlines() if l.startswith("RESULT ")][0][7:])
+    assert "peer-memory" in b["path"]
+    assert abs(a["norm"] - b["norm"]) / a["norm"] < 2e-2, (a, b)
+    if a["w"] is not None:
+        # weights are reported in rank-concatenated client order, which depends on the placement -> compare sorted
+        assert max(abs(x - y) for x, y in zip(sorted(a["w"]), sorted(b["w"]))) < 0.05, (a["w"], b["w"])

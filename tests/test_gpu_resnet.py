@@ -154,3 +154,64 @@ def test_native_eval_pairs_and_jobs_match_plain_eval(native_lib):
     parts = [nx.evaluate_jobs(models[0], [("poison", 1)], shard=(r, 3))[0] for r in range(3)]
     whole = nx.evaluate_jobs(models[0], [("poison", 1)])[0]
     assert sum(x[2] for x in parts) == whole[2] and abs(sum(x[1] for x in parts) - whole[1]) <= 1
+
+
+def _setup_tiny(train=640, test=200, **over):
+    from dba_mod_b200.config import Params
+    from dba_mod_b200.data import ImageData
+    from dba_mod_b200.models import initial_state
+    raw = yaml.safe_load(open("utils/tiny_params.yaml"))
+    raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=train, synthetic_test_size=test,
+               number_of_total_participants=10, sampling_dirichlet=False, batch_size=32, **over)
+    p = Params(raw)
+    dev = torch.device("cuda", 0)
+    data = ImageData(p, dev)
+    spec, flat, cnt = initial_state("tiny-imagenet-200", 1)
+    return p, dev, data, spec, flat.to(dev)
+
+
+def test_tiny_native_eval_and_train(native_lib):
+    """Tiny-ImageNet ResNet-18 (7x7 stride-2 stem as a tensor-core GEMM over im2col'd patches, max-pool, 64..512
+    channels, 200-way head) on the native executor vs the batched torch formulation."""
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    from dba_mod_b200.fl.torch_backend import TorchBackend
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    p, dev, data, spec, flat = _setup_tiny(**{"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 1,
+                                              "lr": 0.0, "poison_lr": 0.0})
+    torch.manual_seed(0)
+    M = 2
+    models = flat[None].repeat(M, 1)
+    models[:, :spec.Dp] += 0.01 * torch.randn(M, spec.Dp, device=dev)
+    models[:, spec.Dp:] = torch.rand(M, spec.Db, device=dev) * 0.5 + 0.25
+    tb = TorchBackend(p, spec, data, dev)
+    nx = NativeResNet(p, spec, data, dev)
+    nx.eval_chunk = 100
+    for split, trig in [("clean", 0), ("poison", 1)]:
+        l0, c0, n0 = tb.evaluate(models, split, trig)
+        l1, c1, n1 = nx.evaluate(models, split, trig)
+        assert n0 == n1 and ((l1 - l0).abs() / l0.abs()).max().item() < 0.03, (l0.tolist(), l1.tolist())
+    names = [0, 3]
+    sch = _one_step_schedule(p, data, names, dev)
+    K = len(names)
+    W0 = flat[None].repeat(K, 1)
+    W0[:, :spec.Dp] += 0.01 * torch.randn(K, spec.Dp, device=dev)
+    cnt = torch.zeros(K, spec.n_counters, dtype=torch.long, device=dev)
+    Wt, Wn = W0.clone(), W0.clone()
+    rt = tb.train(sch, Wt, cnt.clone(), W0.clone(), True)
+    rn = nx.train(sch, Wn, cnt.clone(), W0.clone(), True)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(rn.count, rt.count)
+    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, rtol=3e-2, atol=3e-2)
+    bad = []
+    for name in spec.param_names:
+        e = spec.entries[name]
+        if len(e.shape) == 1 and name != "fc.bias":
+            continue
+        a = rt.grad_sum[:, e.offset:e.offset + e.numel]
+        b = rn.grad_sum[:, e.offset:e.offset + e.numel]
+        cos = torch.nn.functional.cosine_similarity(a, b, dim=1).min().item()
+        ratio = (b.norm(dim=1) / a.norm(dim=1).clamp(min=1e-12))
+        if not (cos >= 0.85) or not ((ratio - 1).abs().max().item() <= 0.15):
+            bad.append((name, round(cos, 4), [round(float(v), 3) for v in ratio]))
+    assert not bad, bad

@@ -1,0 +1,44 @@
+"""End-to-end rounds on the native CUDA backend (single GPU): the three aggregators on a CIFAR-shaped task and LOAN."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(method, rounds=2):
+    r = subprocess.run([sys.executable, "tools/gpu_sim_worker.py", method, str(rounds)], cwd=ROOT,
+                       capture_output=True, text=True, timeout=600, env=dict(os.environ, WORLD_SIZE="1"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    return json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][0][7:])
+
+
+@pytest.mark.parametrize("method", ["mean", "geom_median", "foolsgold"])
+def test_cifar_rounds_native_backend(native_lib, method):
+    out = _run(method)
+    assert out["backend"] == "cuda" and out["native"] == [True, True]
+    assert out["norm"] == out["norm"] and out["norm"] > 0
+    if method == "geom_median":
+        assert len(out["w"]) == 6 and out["w"][0] < 0.05        # scaled attacker (slot 0) is down-weighted
+    if method == "foolsgold":
+        assert len(out["w"]) == 6 and all(0.0 <= w <= 1.0 for w in out["w"])
+
+
+def test_loan_rounds_native_backend(native_lib):
+    import yaml
+    from dba_mod_b200.config import Params
+    from dba_mod_b200.fl.simulator import Simulator
+    raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "loan_params.yaml")))
+    raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=20000, epochs=3,
+               internal_poison_epochs=3, **{"0_poison_epochs": [2], "1_poison_epochs": [9], "2_poison_epochs": [9]})
+    sim = Simulator(Params(raw), device=torch.device("cuda", 0), quiet=True, write_files=False)
+    reps = sim.run()
+    assert sim.backend.name == "cuda" and sim.backend.native_train and sim.backend.native_eval
+    assert reps[1].adversaries == ["CT"] and reps[1].poison_acc is not None
+    assert reps[2].global_acc >= reps[0].global_acc - 5.0 and reps[-1].global_loss == reps[-1].global_loss
+    sim.close()
