@@ -168,6 +168,10 @@ def run_reference(params: dict, warmup: int, steps: int, train_size=None, test_s
     with open(os.path.join(work, "utils", "bench_params.yaml"), "w") as f:
         yaml.safe_dump(params, f)
 
+    if params.get("type") == "loan":      # the reference reads ./data/loan/loan_XX.csv (loan_helper.py:117-140)
+        sys.path.insert(0, ROOT)
+        from dba_mod_b200.data import synthetic
+        synthetic.write_loan_csvs(os.path.join(work, "data", "loan"), int(train_size or 60000))
     _install_stubs()
     _install_synthetic_datasets(train_size, test_size)
     sys.path.insert(0, REF)

@@ -135,9 +135,20 @@ class CudaBackend(TorchBackend):
         return False
 
     # -------------------------------------------------------------------------------- train / evaluate
+    def _empty_result(self, sch, want_grad_sum):
+        from .torch_backend import TrainResult
+        dev, E = self.device, max(sch.E_max, 1)
+        z = lambda dt: torch.zeros(0, E, dtype=dt, device=dev)  # noqa: E731
+        return TrainResult(torch.zeros(0, self.spec.Dp, device=dev) if want_grad_sum else None, z(torch.float32),
+                           z(torch.long), z(torch.long), z(torch.long), torch.zeros(0, dtype=torch.bool, device=dev))
+
     def train(self, sch, W, cnt, anchor, want_grad_sum, generator=None):
+        if W.shape[0] == 0:               # a rank without clients this round (more ranks than selected clients)
+            return self._empty_result(sch, want_grad_sum)
         needs_dist = float(self.params["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any())
-        if self.native_train and not needs_dist:     # the distance-regularised poison loss runs on the torch path
+        per_batch = bool(self.params["vis_train_batch_loss"] or self.params["batch_track_distance"])
+        if self.native_train and not needs_dist and not per_batch:
+            # (the distance-regularised poison loss and the per-batch loss / distance traces run on the torch path)
             return self.exec.train(sch, W, cnt, anchor, want_grad_sum)
         return super().train(sch, W, cnt, anchor, want_grad_sum, generator)
 

@@ -242,6 +242,15 @@ class Simulator:
         logger.info(f"This run has a label: {p['current_time']}. Metrics stream: {self.metrics.path}")
         return reports
 
+    def prepare_streaming(self) -> None:
+        """Pins the host copies of the data set once (end-to-end mode); afterwards every round only gathers and
+        uploads that round's inputs."""
+        d = self.data
+        if self._pinned is None:
+            pin = (lambda t: t.pin_memory()) if self.device.type == "cuda" else (lambda t: t)
+            self._pinned = {"train": pin(d.train_x_host), "test": pin(d.test_x_host)}
+        self.stream_inputs = True
+
     def _stage_inputs(self, names: List) -> None:
         """End-to-end mode: the round's inputs (selected clients' training samples + the test split) come from
         pinned host memory every round, like the reference's DataLoader -> .to(device) path."""
@@ -391,6 +400,21 @@ class Simulator:
                     self.metrics.train_vis(tle, acc, tl, str(pl.name), pl.poisoning)
             if pl.n_epochs:
                 num_samples[k] = int(count[k, pl.n_epochs - 1])
+
+        # ---- per-batch traces (vis_train_batch_loss / batch_track_distance windows of the reference)
+        for trace, fn in ((getattr(res, "step_loss", None), "loss"), (getattr(res, "step_dist", None), "dist")):
+            if trace is None:
+                continue
+            tr = trace.cpu()
+            for k, pl in enumerate(plans):
+                for step in range(pl.n_epochs * pl.nb):
+                    e, b = divmod(step, pl.nb)
+                    tle = (epoch - 1) * pl.n_epochs + e + 1
+                    if fn == "loss":
+                        self.metrics.train_batch_vis(tle, pl.nb, b, float(tr[k, step]), str(pl.name), pl.poisoning)
+                    else:
+                        self.metrics.track_distance_batch_vis(tle, pl.nb, b, float(tr[k, step]), str(pl.name),
+                                                              pl.poisoning)
 
         # ---- evaluations + scaling; jobs are batched over models that share the same inputs
         scaling = [k for k, pl in enumerate(plans) if pl.poisoning and not p["baseline"]]

@@ -38,6 +38,9 @@ class TrainResult:
     count: torch.Tensor                # [K, E_max] samples seen
     poison_count: torch.Tensor         # [K, E_max] poisoned samples seen
     nan_flag: torch.Tensor             # [K] bool: non-finite logits seen (replaces LoanNet's per-forward host sync)
+    step_loss: Optional[torch.Tensor] = None   # [K, T] per-batch loss   (only when vis_train_batch_loss)
+    step_dist: Optional[torch.Tensor] = None   # [K, T] distance to the round's start model after each batch
+                                               # (only when batch_track_distance; image_train.py:107-117,225-236)
 
 
 class TorchBackend:
@@ -94,6 +97,10 @@ class TorchBackend:
             torch.zeros(K, dtype=torch.bool, device=dev))
         if sch.T == 0:
             return res
+        if p["vis_train_batch_loss"]:
+            res.step_loss = torch.zeros(K, sch.T, device=dev)
+        if p["batch_track_distance"]:
+            res.step_dist = torch.zeros(K, sch.T, device=dev)
         V = torch.zeros(K, Dp, device=dev)
         P = W[:, :Dp]                      # view: updated in place
         S = W[:, Dp:]
@@ -131,6 +138,10 @@ class TorchBackend:
                 res.count[kk, e] += n_k * act
                 res.poison_count[kk, e] += sel.sum(1) * act
                 res.nan_flag |= ~torch.isfinite(logits).reshape(K, -1).all(1) & act
+                if res.step_loss is not None:
+                    res.step_loss[:, t] = torch.where(act, loss_k.detach(), torch.zeros_like(loss_k))
+                if res.step_dist is not None:
+                    res.step_dist[:, t] = (P - anchor[:, :Dp]).norm(dim=1) * act
         self.W_last = W
         return res
 

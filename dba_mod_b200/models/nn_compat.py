@@ -127,3 +127,93 @@ def display_name(kind: str, role: str) -> str:
     if kind in (C.TYPE_CIFAR, C.TYPE_TINYIMAGENET):
         return f"{role}_ResNet_18"
     return f"{role}_Simple"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Models the reference defines but never instantiates from main.py (ResNet34/50/101/152 + Bottleneck in
+# models/resnet_cifar.py:39-64,106-116, SimpleMnist in models/simple.py:223-240).  Provided as plain modules with the
+# same state_dict layout so user code written against them keeps working; they can be trained through
+# ``ParamSpec`` + the torch backend's generic autograd path but have no native executor.
+class _Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, cin: int, planes: int, stride: int) -> None:
+        super().__init__()
+        self.conv1 = nn.Conv2d(cin, planes, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(planes)
+        self.conv2 = nn.Conv2d(planes, planes, 3, stride, 1, bias=False)
+        self.bn2 = nn.BatchNorm2d(planes)
+        self.conv3 = nn.Conv2d(planes, planes * 4, 1, bias=False)
+        self.bn3 = nn.BatchNorm2d(planes * 4)
+        self.shortcut = nn.Sequential()
+        if stride != 1 or cin != planes * 4:
+            self.shortcut = nn.Sequential(nn.Conv2d(cin, planes * 4, 1, stride, bias=False), nn.BatchNorm2d(planes * 4))
+
+    def forward(self, x):
+        y = F.relu(self.bn1(self.conv1(x)))
+        y = F.relu(self.bn2(self.conv2(y)))
+        y = self.bn3(self.conv3(y))
+        return F.relu(y + self.shortcut(x))
+
+
+class _BasicCifar(_ResBlock):
+    expansion = 1
+
+    def __init__(self, cin: int, planes: int, stride: int) -> None:
+        super().__init__(cin, planes, stride, "shortcut")
+
+
+class CifarResNetCompat(nn.Module):
+    """Narrow (32/64/128/256) CIFAR ResNet of arbitrary depth."""
+
+    def __init__(self, block, num_blocks, num_classes: int = 10) -> None:
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, 32, 3, 1, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(32)
+        cin = 32
+        for li, (planes, n) in enumerate(zip((32, 64, 128, 256), num_blocks), start=1):
+            layers = []
+            for bi in range(n):
+                layers.append(block(cin, planes, (1 if li == 1 else 2) if bi == 0 else 1))
+                cin = planes * block.expansion
+            setattr(self, f"layer{li}", nn.Sequential(*layers))
+        self.linear = nn.Linear(256 * block.expansion, num_classes)
+
+    def forward(self, x):
+        x = F.relu(self.bn1(self.conv1(x)))
+        for li in range(1, 5):
+            x = getattr(self, f"layer{li}")(x)
+        return self.linear(F.avg_pool2d(x, 4).flatten(1))
+
+
+def ResNet34():
+    return CifarResNetCompat(_BasicCifar, [3, 4, 6, 3])
+
+
+def ResNet50():
+    return CifarResNetCompat(_Bottleneck, [3, 4, 6, 3])
+
+
+def ResNet101():
+    return CifarResNetCompat(_Bottleneck, [3, 4, 23, 3])
+
+
+def ResNet152():
+    return CifarResNetCompat(_Bottleneck, [3, 8, 36, 3])
+
+
+class SimpleMnistCompat(nn.Module):
+    def __init__(self) -> None:
+        super().__init__()
+        self.conv1 = nn.Conv2d(1, 10, kernel_size=5)
+        self.conv2 = nn.Conv2d(10, 20, kernel_size=5)
+        self.conv2_drop = nn.Dropout2d()
+        self.fc1 = nn.Linear(320, 50)
+        self.fc2 = nn.Linear(50, 10)
+
+    def forward(self, x):
+        x = F.relu(F.max_pool2d(self.conv1(x), 2))
+        x = F.relu(F.max_pool2d(self.conv2_drop(self.conv2(x)), 2))
+        x = F.relu(self.fc1(x.flatten(1)))
+        x = F.dropout(x, training=self.training)
+        return F.log_softmax(self.fc2(x), dim=1)

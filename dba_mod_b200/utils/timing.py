@@ -24,11 +24,13 @@ class PhaseTimer:
             return
         if self.cuda:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.nvtx.range_push(f"dba/{name}")       # visible in Nsight timelines
             a.record()
             try:
                 yield
             finally:
                 b.record()
+                torch.cuda.nvtx.range_pop()
                 self._pending.setdefault(name, []).append((a, b))
         else:
             t0 = time.perf_counter()

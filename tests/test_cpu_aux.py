@@ -90,3 +90,30 @@ def test_metrics_stream(tmp_path):
     assert [r["win"] for r in recs] == ["train_acc", "train_loss", "aggregation_weight"]
     assert "<td>lr</td><td>0.1</td>" in dict_html({"lr": 0.1, "folder_path": "x"}, "t") and "folder_path" not in \
         dict_html({"lr": 0.1, "folder_path": "x"}, "t")
+
+
+def test_extra_model_definitions_match_reference_layout():
+    """ResNet34/50 and SimpleMnist (defined but unused by the reference) keep its state_dict keys and shapes."""
+    import sys
+    from dba_mod_b200.models import nn_compat as nc
+    REF = "/root/reference"
+    if not os.path.isdir(REF):
+        pytest.skip("reference tree not mounted")
+    sys.path.insert(0, REF)
+    try:
+        for k in [k for k in sys.modules if k == "models" or k.startswith("models.")]:
+            del sys.modules[k]
+        from models.resnet_cifar import ResNet34 as R34, ResNet50 as R50
+        from models.simple import SimpleMnist
+        pairs = [(nc.ResNet34(), R34(name="x", created_time="t")), (nc.ResNet50(), R50(name="x", created_time="t")),
+                 (nc.SimpleMnistCompat(), SimpleMnist(name="x", created_time="t"))]
+    finally:
+        sys.path.remove(REF)
+        for k in [k for k in sys.modules if k == "models" or k.startswith("models.")]:
+            del sys.modules[k]
+    for ours, theirs in pairs:
+        a, b = ours.state_dict(), theirs.state_dict()
+        assert list(a.keys()) == list(b.keys())
+        assert all(a[k].shape == b[k].shape for k in a)
+    y = nc.ResNet50()(torch.randn(2, 3, 32, 32))
+    assert y.shape == (2, 10)
