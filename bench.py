@@ -29,6 +29,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly ONE JSON line: NCCL's version banner / debug output goes to a file instead
+os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/dba_nccl_%h_%p.log")
 
 METRIC = "fl_rounds_per_sec_cifar10_resnet18"
 

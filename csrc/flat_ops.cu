@@ -93,6 +93,43 @@ extern "C" int dba_sgd_step(float* W, long long ldw, float* V, const float* Gr, 
   return DBA_OK;
 }
 
+// ------------------------------------------------------------------- distance-regularised poison loss (K11, W14)
+// Reference: loss = alpha*CE + (1-alpha)*||w - w_anchor||_2 for poisoning clients (image_train.py:85-90,
+// helper.py:111-123).  After the backward pass produced the CE gradient in Gr, this turns it into the gradient of
+// the combined loss,  Gr = alpha*Gr + (1-alpha)*(w - a)/||w - a||  (0 at w == a, torch.norm's subgradient), and adds
+// the distance to the per-(client, internal epoch) trace so the logged loss can be rebuilt as alpha*CE + (1-alpha)*dist.
+__global__ void __launch_bounds__(256) dist_grad_kernel(float* __restrict__ Gr, long long ldv,
+                                                        const float* __restrict__ W, long long ldw,
+                                                        const float* __restrict__ A, long long lda,
+                                                        const double* __restrict__ dist,
+                                                        const long long* __restrict__ poison_n,
+                                                        const unsigned char* __restrict__ active,
+                                                        const long long* __restrict__ slot, float* __restrict__ mf_dist,
+                                                        int ld_m, float alpha, int K, long long Dp) {
+  const long long total = (long long)K * Dp;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / Dp);
+    if (poison_n[k] <= 0 || (active && !active[k])) continue;
+    const long long j = i - (long long)k * Dp;
+    const float d = (float)dist[k];
+    const float inv = d > 0.f ? 1.f / d : 0.f;
+    Gr[k * ldv + j] = alpha * Gr[k * ldv + j] + (1.f - alpha) * (W[k * ldw + j] - A[k * lda + j]) * inv;
+    if (j == 0) mf_dist[k * ld_m + (int)slot[k]] += (float)dist[k];
+  }
+}
+extern "C" int dba_dist_grad(float* Gr, long long ldv, const float* W, long long ldw, const float* A, long long lda,
+                             const double* dist, const long long* poison_n, const unsigned char* active,
+                             const long long* slot, float* mf_dist, int ld_m, float alpha, int K, long long Dp,
+                             void* stream) {
+  DBA_REQUIRE(K > 0 && Dp > 0, "dba_dist_grad: K=%d Dp=%lld", K, Dp);
+  dist_grad_kernel<<<grid_for((long long)K * Dp, 256), 256, 0, (cudaStream_t)stream>>>(
+      Gr, ldv, W, ldw, A, lda, dist, poison_n, active, slot, mf_dist, ld_m, alpha, K, Dp);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
 // ------------------------------------------------------------------------------------------- poison scaling
 // W[k] = A[k] + (W[k] - A[k]) * s[k]   over the whole state row (params + BN buffers).
 __global__ void __launch_bounds__(256) scale_rows_kernel(float* __restrict__ W, long long ldw,

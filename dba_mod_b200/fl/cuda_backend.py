@@ -147,7 +147,7 @@ class CudaBackend(TorchBackend):
             return self._empty_result(sch, want_grad_sum)
         needs_dist = float(self.params["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any())
         per_batch = bool(self.params["vis_train_batch_loss"] or self.params["batch_track_distance"])
-        if self.native_train and not needs_dist and not per_batch:
+        if self.native_train and not per_batch and (not needs_dist or getattr(self.exec, "supports_dist_loss", False)):
             # (the distance-regularised poison loss and the per-batch loss / distance traces run on the torch path)
             return self.exec.train(sch, W, cnt, anchor, want_grad_sum)
         return super().train(sch, W, cnt, anchor, want_grad_sum, generator)

@@ -64,6 +64,7 @@ class NativeResNet:
         self.head_C, self.head_H = self.widths[-1], self.ress[-1]
         self._plan()
         self.can_eval = True
+        self.supports_dist_loss = True
         self.can_train = bool(params.get("native_train", True))
         self._train_bufs: Dict[int, dict] = {}
         self.mu, self.wd = float(params["momentum"]), float(params["decay"])
@@ -358,6 +359,11 @@ class NativeResNet:
         t["W"] = torch.zeros(K, (self.spec.Df + 3) // 4 * 4, device=dev)
         t["cnt"] = torch.zeros(K, self.spec.n_counters, dtype=torch.long, device=dev)
         t["mf"] = torch.zeros(K, 16, device=dev)
+        t["mf_dist"] = torch.zeros(K, 16, device=dev)
+        t["anchor"] = torch.zeros(K, (self.spec.Dp + 3) // 4 * 4, device=dev)
+        t["dist"] = torch.zeros(K, dtype=torch.float64, device=dev)
+        t["dist_scratch"] = torch.zeros(int(self.lib.dba_rows_sqdist_scratch_elems(max(K, 1))), dtype=torch.float64,
+                                        device=dev)
         t["mi"] = torch.zeros(K, 16, 2, dtype=torch.int32, device=dev)
         t["nan"] = torch.zeros(K, dtype=torch.uint8, device=dev)
         t["st_idx"] = torch.full((K, B), -1, dtype=torch.long, device=dev)
@@ -415,8 +421,8 @@ class NativeResNet:
         from .torch_backend import TrainResult
         p, dev = self.params, self.device
         K, Dp, B, Df = W.shape[0], self.spec.Dp, self.B, self.spec.Df
-        if float(p["alpha_loss"]) != 1.0 and bool((sch.poison_n > 0).any()):
-            raise NotImplementedError("alpha_loss != 1 is handled by the torch path")
+        alpha = float(p["alpha_loss"])
+        use_dist = alpha != 1.0 and bool((sch.poison_n > 0).any())
         E = max(sch.E_max, 1)
         t = self._tbufs(K)
         if E > t["mf"].shape[1]:
@@ -425,8 +431,10 @@ class NativeResNet:
         t["W"][:, :Df].copy_(W[:, :Df])
         if cnt.numel():
             t["cnt"].copy_(cnt)
-        for key in ("V", "mf", "mi", "nan", "gs"):
+        for key in ("V", "mf", "mi", "nan", "gs", "mf_dist"):
             t[key].zero_()
+        if use_dist:
+            t["anchor"][:, :Dp].copy_(anchor[:, :Dp])
         t["trig_row"].copy_(sch.trig_row)
         t["poison_n"].copy_(sch.poison_n)
         mask_all = sch.idx >= 0                                              # [K, T, B]
@@ -438,7 +446,7 @@ class NativeResNet:
         pcount.scatter_add_(1, sch.epoch_of, sel.sum(2) * sch.active)
         flip = sch.flip.to(torch.uint8) if sch.flip is not None else None
         use_graph = bool(p.get("cuda_graphs", True))
-        gkey = ("graph", bool(want_grad_sum), flip is not None)
+        gkey = ("graph", bool(want_grad_sum), flip is not None, use_dist)
         for step in range(sch.T):
             t["st_idx"].copy_(sch.idx[:, step])
             t["st_nvalid"].copy_(nvalid_all[:, step])
@@ -449,17 +457,17 @@ class NativeResNet:
                 t["st_flip"].copy_(flip[:, step])
             g = t.get(gkey)
             if not use_graph:
-                self._step_body(K, t, want_grad_sum, flip is not None)
+                self._step_body(K, t, want_grad_sum, flip is not None, use_dist)
             elif g is None:
                 if not t.get(("warm", gkey)):
                     # first ever step for this K: run eagerly (lazy kernel attributes), then record the graph
-                    self._step_body(K, t, want_grad_sum, flip is not None)
+                    self._step_body(K, t, want_grad_sum, flip is not None, use_dist)
                     t[("warm", gkey)] = True
                     continue
                 l0 = native.launch_count()
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
-                    self._step_body(K, t, want_grad_sum, flip is not None)
+                    self._step_body(K, t, want_grad_sum, flip is not None, use_dist)
                 t[gkey] = graph
                 t[("nl", gkey)] = native.launch_count() - l0
                 graph.replay()
@@ -470,11 +478,14 @@ class NativeResNet:
         if cnt.numel():
             cnt.copy_(t["cnt"])
         mf, mi = t["mf"][:, :E].clone(), t["mi"][:, :E].clone()
+        if use_dist:       # logged loss of poisoning clients = alpha*CE + (1-alpha)*distance (image_train.py:88-89,103)
+            pz = (sch.poison_n > 0)[:, None]
+            mf = torch.where(pz, alpha * mf + (1.0 - alpha) * t["mf_dist"][:, :E], mf)
         res = TrainResult(t["gs"][:, :Dp].clone() if want_grad_sum else None, mf, mi[:, :, 0].long(),
                           mi[:, :, 1].long(), pcount, t["nan"].bool().clone())
         return res
 
-    def _step_body(self, K: int, t: dict, want_grad_sum: bool, with_flip: bool) -> None:
+    def _step_body(self, K: int, t: dict, want_grad_sum: bool, with_flip: bool, use_dist: bool = False) -> None:
         """One lock-step SGD step of K clients: ~125 kernel launches, no host decisions (CUDA-graph capturable).
         All inputs come from the persistent staging tensors st_* filled by train()."""
         from ..ops import flat
@@ -562,6 +573,16 @@ class NativeResNet:
         dy0 = t[("dy", stem.name)]
         self._bn_bwd(stem, K, g, y0, a0, dy0, None, W, t, nvalid, up=False)
         self._wgrad(stem, K, dy0, t["xin"], t)
+        if use_dist:   # K11: distance-regularised poison loss, gradient term added before the optimiser step
+            sc = t["dist_scratch"]
+            native.check(lib.dba_rows_sqdist(native.ptr(W), W.stride(0), native.ptr(t["anchor"]), t["anchor"].stride(0),
+                                             None, K, Dp, native.ptr(t["dist"]), 1, native.ptr(sc), sc.numel(),
+                                             native.stream()))
+            native.check(lib.dba_dist_grad(native.ptr(Gr), Gr.stride(0), native.ptr(W), W.stride(0),
+                                           native.ptr(t["anchor"]), t["anchor"].stride(0), native.ptr(t["dist"]),
+                                           native.ptr(t["poison_n"]), native.ptr(active), native.ptr(slot),
+                                           native.ptr(t["mf_dist"]), t["mf_dist"].shape[1],
+                                           float(self.params["alpha_loss"]), K, Dp, native.stream()))
         # ---------------------------------------------------------------------- optimiser
         flat.sgd_step_(W, V, Gr, t["st_lr"], active, Dp, self.mu, self.wd, t["gs"] if want_grad_sum else None)
         if t["cnt"].numel():

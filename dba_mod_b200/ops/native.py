@@ -50,6 +50,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_add_launch_count", [c_ulonglong], None)
     _sig(lib, "dba_sgd_step", [P, L, P, P, P, L, P, P, I, L, F, F, P])
     _sig(lib, "dba_scale_rows", [P, L, P, L, P, I, L, P])
+    _sig(lib, "dba_dist_grad", [P, L, P, L, P, L, P, P, P, P, P, I, F, I, L, P])
     _sig(lib, "dba_rows_sqdist_scratch_elems", [I], c_longlong)
     _sig(lib, "dba_rows_sqdist", [P, L, P, L, P, I, L, P, I, P, L, P])
     _sig(lib, "dba_rows_sqdist_noalloc_max_rows", [], c_int)

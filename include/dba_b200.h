@@ -23,6 +23,12 @@ void dba_add_launch_count(unsigned long long n); /* kernels launched through a r
 int dba_sgd_step(float* W, long long ldw, float* V, const float* Gr, float* S, long long ldv, const float* lr,
                  const unsigned char* active, int K, long long Dp, float mu, float wd, void* stream);
 
+/* Gradient of the distance-regularised poison loss alpha*CE + (1-alpha)*||w - w_anchor|| on top of the CE gradient.
+ * Reference: image_train.py:85-90, helper.py:111-123. */
+int dba_dist_grad(float* Gr, long long ldv, const float* W, long long ldw, const float* A, long long lda,
+                  const double* dist, const long long* poison_n, const unsigned char* active, const long long* slot,
+                  float* mf_dist, int ld_m, float alpha, int K, long long Dp, void* stream);
+
 /* Poison scaling W[k] = A[k] + (W[k]-A[k])*s[k].  Reference: image_train.py:166-171, loan_train.py:154-160. */
 int dba_scale_rows(float* W, long long ldw, const float* A, long long lda, const float* s, int K, long long D,
                    void* stream);

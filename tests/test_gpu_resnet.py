@@ -215,3 +215,28 @@ def test_tiny_native_eval_and_train(native_lib):
         if not (cos >= 0.85) or not ((ratio - 1).abs().max().item() <= 0.15):
             bad.append((name, round(cos, 4), [round(float(v), 3) for v in ratio]))
     assert not bad, bad
+
+
+def test_native_distance_regularised_poison_loss(native_lib):
+    """alpha_loss = 0.5: gradient of alpha*CE + (1-alpha)*||w - w_anchor|| on the native path vs autograd."""
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    from dba_mod_b200.fl.torch_backend import TorchBackend
+    torch.backends.cudnn.allow_tf32 = False
+    p, dev, data, spec, flat = _setup(train=1280, test=200, sampling_dirichlet=False, alpha_loss=0.5,
+                                      **{"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 2,
+                                         "lr": 0.01, "poison_lr": 0.01})
+    names = [17, 3]
+    sch = _one_step_schedule(p, data, names, dev)
+    assert sch.T == 2
+    K = len(names)
+    W0 = flat[None].repeat(K, 1)
+    cnt = torch.zeros(K, spec.n_counters, dtype=torch.long, device=dev)
+    tb, nx = TorchBackend(p, spec, data, dev), NativeResNet(p, spec, data, dev)
+    Wt, Wn = W0.clone(), W0.clone()
+    rt = tb.train(sch, Wt, cnt.clone(), W0.clone(), True)
+    rn = nx.train(sch, Wn, cnt.clone(), W0.clone(), True)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, rtol=3e-2, atol=3e-2)
+    dt, dn = (Wt - W0)[:, :spec.Dp], (Wn - W0)[:, :spec.Dp]
+    cos = torch.nn.functional.cosine_similarity(dt, dn, dim=1)
+    assert cos.min().item() > 0.9 and ((dn.norm(dim=1) / dt.norm(dim=1)) - 1).abs().max().item() < 0.1, cos.tolist()
