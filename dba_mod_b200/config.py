@@ -101,6 +101,7 @@ _DEFAULTS: Dict[str, Any] = {
     "native_train": True,
     "native_eval_chunk": 500,     # test images per evaluation pass (per model / input set)
     "cuda_graphs": True,          # replay the captured training step instead of ~125 launches per step
+    "compact_tail": True,         # clients that finished their local steps stop being computed (native trainer)
 }
 
 # Keys that exist in the shipped YAML files but are never read by the reference (App. A).

@@ -417,6 +417,32 @@ class NativeResNet:
             K, self.B, l.H, l.H, l.cout_p, l.cin_p, l.ks, 1, 0, 0, native.stream()))
         return out
 
+    # modelled cost of one lock-step step over k clients (ms): fixed launch floor + per-client work (measured, B200)
+    _STEP_COST = (1.0, 0.32)
+
+    @classmethod
+    def _segments(cls, steps: List[int], max_cuts: int = 2) -> List[tuple]:
+        """Split the lock-step schedule into [(rows, lo, hi)] so that clients that finished early stop being
+        computed: a lone attacker training ``internal_poison_epochs`` x longer than the benign clients runs its tail
+        on a 1-client slab instead of dragging K-1 idle clients through every kernel."""
+        a, b = cls._STEP_COST
+        rows = list(range(len(steps)))
+        T = max(steps) if steps else 0
+        segs, lo = [], 0
+        for _ in range(max_cuts):
+            best = None
+            for c in sorted({steps[r] for r in rows if lo < steps[r] < T}):
+                tail = [r for r in rows if steps[r] > c]
+                cost = (c - lo) * (a + b * len(rows)) + (T - c) * (a + b * len(tail))
+                if best is None or cost < best[0]:
+                    best = (cost, c, tail)
+            if best is None or best[0] > 0.93 * (T - lo) * (a + b * len(rows)):
+                break
+            segs.append((rows, lo, best[1]))
+            rows, lo = best[2], best[1]
+        segs.append((rows, lo, T))
+        return segs
+
     def train(self, sch, W: torch.Tensor, cnt: torch.Tensor, anchor: torch.Tensor, want_grad_sum: bool):
         from .torch_backend import TrainResult
         p, dev = self.params, self.device
@@ -438,42 +464,33 @@ class NativeResNet:
         t["trig_row"].copy_(sch.trig_row)
         t["poison_n"].copy_(sch.poison_n)
         mask_all = sch.idx >= 0                                              # [K, T, B]
-        nvalid_all = mask_all.sum(2).to(torch.int32)                         # [K, T]
-        act_all = sch.active.to(torch.uint8)
         ar = torch.arange(B, device=dev)
         sel = (ar[None, None, :] < sch.poison_n[:, None, None]) & mask_all
         pcount = torch.zeros(K, E, dtype=torch.long, device=dev)
         pcount.scatter_add_(1, sch.epoch_of, sel.sum(2) * sch.active)
-        flip = sch.flip.to(torch.uint8) if sch.flip is not None else None
-        use_graph = bool(p.get("cuda_graphs", True))
-        gkey = ("graph", bool(want_grad_sum), flip is not None, use_dist)
-        for step in range(sch.T):
-            t["st_idx"].copy_(sch.idx[:, step])
-            t["st_nvalid"].copy_(nvalid_all[:, step])
-            t["st_active"].copy_(act_all[:, step])
-            t["st_slot"].copy_(sch.epoch_of[:, step])
-            t["st_lr"].copy_(sch.lr[:, step])
-            if flip is not None:
-                t["st_flip"].copy_(flip[:, step])
-            g = t.get(gkey)
-            if not use_graph:
-                self._step_body(K, t, want_grad_sum, flip is not None, use_dist)
-            elif g is None:
-                if not t.get(("warm", gkey)):
-                    # first ever step for this K: run eagerly (lazy kernel attributes), then record the graph
-                    self._step_body(K, t, want_grad_sum, flip is not None, use_dist)
-                    t[("warm", gkey)] = True
-                    continue
-                l0 = native.launch_count()
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
-                    self._step_body(K, t, want_grad_sum, flip is not None, use_dist)
-                t[gkey] = graph
-                t[("nl", gkey)] = native.launch_count() - l0
-                graph.replay()
-            else:
-                g.replay()
-                self.lib.dba_add_launch_count(t[("nl", gkey)])
+        per_step = {"idx": sch.idx, "nvalid": mask_all.sum(2).to(torch.int32), "active": sch.active.to(torch.uint8),
+                    "slot": sch.epoch_of, "lr": sch.lr,
+                    "flip": sch.flip.to(torch.uint8) if sch.flip is not None else None}
+        flags = (bool(want_grad_sum), sch.flip is not None, use_dist)
+        steps = list(sch.steps_host) if len(sch.steps_host) == K else [sch.T] * K
+        segs = self._segments(steps) if bool(p.get("compact_tail", True)) else [(list(range(K)), 0, sch.T)]
+        carry = ("V", "gs", "anchor") if use_dist else ("V", "gs")
+        for rows, lo, hi in segs:
+            if len(rows) == K:
+                self._run_steps(K, t, per_step, None, lo, hi, flags)
+                continue
+            r = torch.tensor(rows, dtype=torch.long, device=dev)
+            t2 = self._tbufs(len(rows))
+            for key in carry + ("W", "cnt", "trig_row", "poison_n"):
+                t2[key].copy_(t[key][r])
+            for key in ("mf", "mi", "nan", "mf_dist"):
+                t2[key].zero_()
+            self._run_steps(len(rows), t2, per_step, r, lo, hi, flags)
+            for key in ("V", "gs", "W", "cnt"):
+                t[key][r] = t2[key]
+            for key in ("mf", "mi", "mf_dist"):
+                t[key][r] += t2[key]
+            t["nan"][r] |= t2["nan"]
         W[:, :Df].copy_(t["W"][:, :Df])
         if cnt.numel():
             cnt.copy_(t["cnt"])
@@ -484,6 +501,44 @@ class NativeResNet:
         res = TrainResult(t["gs"][:, :Dp].clone() if want_grad_sum else None, mf, mi[:, :, 0].long(),
                           mi[:, :, 1].long(), pcount, t["nan"].bool().clone())
         return res
+
+    def _run_steps(self, K: int, t: dict, per_step: dict, rows, lo: int, hi: int, flags: tuple) -> None:
+        """Steps [lo, hi) of the clients ``rows`` (None = all) on the K-client slab ``t``: stage the step's index /
+        lr / mask rows, then replay the captured step graph (first use of a slab: one eager step, then capture)."""
+        want_grad_sum, with_flip, use_dist = flags
+        use_graph = bool(self.params.get("cuda_graphs", True))
+        gkey = ("graph",) + flags
+
+        def pick(x, step):
+            return x[:, step] if rows is None else x[rows, step]
+
+        for step in range(lo, hi):
+            t["st_idx"].copy_(pick(per_step["idx"], step))
+            t["st_nvalid"].copy_(pick(per_step["nvalid"], step))
+            t["st_active"].copy_(pick(per_step["active"], step))
+            t["st_slot"].copy_(pick(per_step["slot"], step))
+            t["st_lr"].copy_(pick(per_step["lr"], step))
+            if with_flip:
+                t["st_flip"].copy_(pick(per_step["flip"], step))
+            g = t.get(gkey)
+            if not use_graph:
+                self._step_body(K, t, want_grad_sum, with_flip, use_dist)
+            elif g is None:
+                if not t.get(("warm", gkey)):
+                    # first ever step for this K: run eagerly (lazy kernel attributes), then record the graph
+                    self._step_body(K, t, want_grad_sum, with_flip, use_dist)
+                    t[("warm", gkey)] = True
+                    continue
+                l0 = native.launch_count()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    self._step_body(K, t, want_grad_sum, with_flip, use_dist)
+                t[gkey] = graph
+                t[("nl", gkey)] = native.launch_count() - l0
+                graph.replay()
+            else:
+                g.replay()
+                self.lib.dba_add_launch_count(t[("nl", gkey)])
 
     def _step_body(self, K: int, t: dict, want_grad_sum: bool, with_flip: bool, use_dist: bool = False) -> None:
         """One lock-step SGD step of K clients: ~125 kernel launches, no host decisions (CUDA-graph capturable).

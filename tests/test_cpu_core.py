@@ -334,3 +334,22 @@ def test_checkpoint_roundtrip_with_reference_state_dict(kind, tmp_path):
         assert back[k].dtype == sd[k].dtype and torch.equal(back[k], sd[k]), k
     # and the reference model accepts what we write
     m.load_state_dict(back)
+
+
+def test_schedule_segments_drop_finished_clients():
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    seg = NativeResNet._segments
+    # ten clients, one attacker training 3x longer: the tail runs on the attacker alone
+    s = seg([16] * 4 + [48] + [14] * 5)
+    assert s[0] == (list(range(10)), 0, 16) and s[-1] == ([4], 16, 48)
+    # nothing to gain: one segment
+    assert seg([16] * 10) == [(list(range(10)), 0, 16)]
+    assert seg([16, 15, 16]) == [([0, 1, 2], 0, 16)]
+    # every step of every client is covered exactly once
+    steps = [5, 40, 12, 40, 9]
+    cover = [0] * len(steps)
+    for rows, lo, hi in seg(steps):
+        for r in rows:
+            cover[r] += min(hi, steps[r]) - min(lo, steps[r])
+    assert cover == steps
+    assert seg([]) == [([], 0, 0)]

@@ -127,6 +127,58 @@ def test_native_train_multi_step_tracks_torch(native_lib):
     torch.testing.assert_close(rn.poison_count, rt.poison_count)
 
 
+def test_tail_compaction_matches_full_width_run(native_lib):
+    """An attacker that trains 3x longer than its benign neighbours finishes on a narrower slab.
+
+    (a) bookkeeping: with a deterministic stand-in for the step body, the segmented run equals the full-width run
+    bit for bit (state rows, momentum, counters and metrics are carried across slabs);  (b) real kernels: the
+    segmented run is as close to a full-width run as two full-width runs are to each other (fp32 atomics in the
+    BatchNorm statistics make a random-init bf16 ResNet visibly non-reproducible run to run)."""
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    over = {"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 3, "lr": 0.02}
+    p, dev, data, spec, flat = _setup(train=1500, test=200, **over)
+    names = [17, 3, 5]
+    sch = _one_step_schedule(p, data, names, dev)
+    assert len(NativeResNet._segments(list(sch.steps_host))) > 1
+    K = len(names)
+    W0 = flat[None].repeat(K, 1)
+
+    def fake_step(K_, t, want_gs, with_flip, use_dist=False):
+        act = t["st_active"].float()[:, None]
+        t["V"][:, :8] += act * (1.0 + t["st_lr"][:, None])
+        t["W"][:, :8] += act * (t["st_idx"].clamp(min=0).sum(1, keepdim=True).float() * 1e-6 + t["V"][:, :8])
+        t["gs"][:, :4] += act * t["st_nvalid"].float()[:, None]
+        t["mf"][:, 0] += act[:, 0]
+        t["mi"][:, 0, 0] += t["st_nvalid"] * t["st_active"].int()
+        t["cnt"] += t["st_active"].long()[:, None]
+
+    def run(compact, fake):
+        p["compact_tail"], p["cuda_graphs"] = compact, not fake
+        nx = NativeResNet(p, spec, data, dev)
+        if fake:
+            nx._step_body = fake_step
+        W, c = W0.clone(), torch.zeros(K, spec.n_counters, dtype=torch.long, device=dev)
+        r = nx.train(sch, W, c, W0.clone(), True)
+        torch.cuda.synchronize()
+        return W, c, r
+
+    (Wa, ca, ra), (Wb, cb, rb) = run(False, True), run(True, True)
+    assert torch.equal(Wa, Wb) and torch.equal(ca, cb) and torch.equal(ra.grad_sum, rb.grad_sum)
+    assert torch.equal(ra.loss_sum, rb.loss_sum) and torch.equal(ra.count, rb.count)
+    assert ca[:, 0].tolist() == list(sch.steps_host)
+
+    (W1, c1, r1), (W2, c2, r2), (W3, c3, r3) = run(False, False), run(False, False), run(True, False)
+    assert torch.equal(c1, c3)
+    torch.testing.assert_close(r1.count, r3.count)
+    torch.testing.assert_close(r1.poison_count, r3.poison_count)
+    d1, d2, d3 = ((w - W0)[:, :spec.Dp] for w in (W1, W2, W3))
+    cos = torch.nn.functional.cosine_similarity
+    floor, got = cos(d1, d2, dim=1), cos(d1, d3, dim=1)
+    assert bool((got > floor - 0.1).all()) and got.min().item() > 0.7, (floor.tolist(), got.tolist())
+    torch.testing.assert_close(r1.loss_sum, r3.loss_sum, rtol=5e-2, atol=5e-2)
+    assert ((d3.norm(dim=1) / d1.norm(dim=1)) - 1).abs().max().item() < 0.1
+
+
 def test_native_eval_pairs_and_jobs_match_plain_eval(native_lib):
     """Batched (model, input-set) pairs and one-model-many-input-sets give the same sums as one evaluate() per job."""
     from dba_mod_b200.fl.native_resnet import NativeResNet
