@@ -72,6 +72,14 @@ struct ConvArgs {
   unsigned int wbytes;         // bytes of that weight set
   unsigned long long magicS, magicWp;   // ceil(2^40 / S), ceil(2^40 / Wp): exact division of row indices < 2^26
   long long* dbg;              // optional [grid][8] cycle counters (profiling aid), null in production
+  int dbg_shift;               // profiling aid: 0 = real tap shifts, 1 = all zero, 2 = multiples of 8 rows (wrong results)
+  // Stride-2 convolutions without the 4x full-grid waste: X is the space-to-depth form of the real input (parity
+  // planes p = 2*(h&1) + (w&1), each Cin channels, on the OUTPUT grid); tap (dh, dw) of the 3x3 kernel reads parity
+  // plane (dh != 1, dw != 1) shifted by (dh == 0 ? -1 : 0, dw == 0 ? -1 : 0); the 1x1 kernel reads plane 0 unshifted.
+  int in_s2d;
+  // Store Y (and only Y - Res stays in the plain layout) as the space-to-depth form of the (H, W) output.
+  int out_s2d;
+  long long res_client_stride, res_plane_stride;
 };
 
 struct Pipe {
@@ -100,6 +108,7 @@ __device__ __forceinline__ void warp_transpose_reduce32(float (&v)[32], int lane
 template <int KC2>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) {
   long long dbgacc[4] = {0, 0, 0, 0};
+  const long long dbg_start = a.dbg ? clock64() : 0;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kc = a.KB >> 3;                      // 16-byte channel chunks per k-block
@@ -107,7 +116,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   const int nnb = a.Cout / a.NB;
   const int planes = a.Cin >> 3;
   const uint32_t pitchA = (uint32_t)a.rowsA * 16u;
-  const uint32_t bytesA = (uint32_t)kc * pitchA;
+  const int npar = (a.in_s2d && a.taps == 9) ? 4 : 1;      // parity planes staged per k-block
+  const uint32_t bytesA = (uint32_t)(npar * kc) * pitchA;
   const uint32_t pitchB = (uint32_t)a.NB * 16u;
   const uint32_t bytesB = (uint32_t)kc * pitchB;
   const size_t bRegion = a.resident ? (size_t)a.wbytes : (size_t)a.SB * bytesB;
@@ -176,10 +186,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
           DBG_ADD(0);
           mbar_arrive_expect_tx(&a_full[sa], bytesA);
-          for (int c = 0; c < kc; ++c) {
-            const __nv_bfloat16* src = xk + (long long)(kb * kc + c) * a.x_plane_stride + row0 * 8;
-            bulk_g2s(smA + (size_t)sa * bytesA + (size_t)c * pitchA, src, pitchA, &a_full[sa]);
-          }
+          for (int pp = 0; pp < npar; ++pp)
+            for (int c = 0; c < kc; ++c) {
+              const __nv_bfloat16* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0 * 8;
+              bulk_g2s(smA + (size_t)sa * bytesA + (size_t)(pp * kc + c) * pitchA, src, pitchA, &a_full[sa]);
+            }
           ++pa.it;
           if (a.resident) continue;
           for (int tap = 0; tap < a.taps; ++tap) {
@@ -241,6 +252,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             }
             int shift = 0;
             if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
+            if (npar == 4) {
+              const int dh = tap / 3, dw = tap - dh * 3;
+              shift = (dh == 0 ? -a.Wp : 0) + (dw == 0 ? -1 : 0)
+                      + (int)((uint32_t)((dh != 1) * 2 + (dw != 1)) * (uint32_t)kc * (pitchA >> 4));
+            }
+            if (a.dbg_shift == 1) shift = 0;
+            if (a.dbg_shift == 2) shift = (tap / 3 - 1) * 24 + (tap % 3 - 1) * 8;
             const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
             uint32_t d_tmem = tmem_base + (uint32_t)(as * accCols);
             uint64_t da = dA0 + (uint64_t)(int64_t)shift;       // halo + shift >= 0: no borrow out of the field
@@ -296,12 +314,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       }
       // which of this thread's rows (one per tile) are real output pixels, and where they go
       bool store[2];
-      long long orow[2];
+      long long orow[2], rrow[2];                 // output row / residual row (differ only for out_s2d)
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int t = t_first + i * t_step;
         store[i] = false;
-        orow[i] = 0;
+        orow[i] = rrow[i] = 0;
         if (t < a.T) {
           const unsigned int qrow = (unsigned int)(pass * a.T * kTileM + t * kTileM + q * 32 + lane);
           const unsigned int b = (unsigned int)(((unsigned long long)qrow * a.magicS) >> 40);
@@ -311,9 +329,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           bool st = (int)qrow < totalRows && (int)h < a.H && (int)w < a.W;
           if (a.sub == 2) {
             st = st && !((h | w) & 1u);
-            orow[i] = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
+            orow[i] = rrow[i] = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
+          } else if (a.out_s2d) {
+            rrow[i] = (long long)a.lead + qrow;
+            orow[i] = (long long)(((h & 1u) << 1) | (w & 1u)) * (a.y_plane_stride >> 3) * (a.Cout >> 3)
+                      + (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
           } else {
-            orow[i] = (long long)a.lead + qrow;
+            orow[i] = rrow[i] = (long long)a.lead + qrow;
           }
           store[i] = st;
         }
@@ -323,7 +345,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       DBG_ADD(0);
       tc_fence_after();
       __nv_bfloat16* yk = a.Y + (long long)k * a.y_client_stride;
-      const __nv_bfloat16* rk = a.Res ? a.Res + (long long)k * a.y_client_stride : nullptr;
+      const __nv_bfloat16* rk = a.Res ? a.Res + (long long)k * a.res_client_stride : nullptr;
       float* gs = a.stats ? a.stats + (long long)k * a.stats_stride + (long long)nb * a.NB * 2 : nullptr;
       for (int c0 = c_first; c0 < a.NB; c0 += c_step) {
         // u1/u2 hold scale/shift (evaluation epilogue) or the running sum / sum of squares (training epilogue);
@@ -358,8 +380,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           const long long obase = (long long)((nb * a.NB + c0) >> 3) * a.y_plane_stride + orow[i] * 8;
           if (rk) {
             uint4 r[4];
+            const long long rbase = (long long)((nb * a.NB + c0) >> 3) * a.res_plane_stride + rrow[i] * 8;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) r[g] = *reinterpret_cast<const uint4*>(rk + obase + g * a.y_plane_stride);
+            for (int g = 0; g < 4; ++g) r[g] = *reinterpret_cast<const uint4*>(rk + rbase + g * a.res_plane_stride);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               sv[g * 8 + 0] += bf16lo(r[g].x); sv[g * 8 + 1] += bf16hi(r[g].x);
@@ -405,7 +428,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       DBG_ADD(1);
     }
   }
-  if (a.dbg && lane == 0 && warp <= 2) {      // [cta][role 0..2][4]
+  if (a.dbg && lane == 0 && warp <= 2) {      // [cta][role 0..2][4]; slot 3 = the role's whole lifetime
+    dbgacc[3] = clock64() - dbg_start;
     for (int i = 0; i < 4; ++i) a.dbg[((long long)blockIdx.x * 3 + warp) * 4 + i] = dbgacc[i];
   }
 
@@ -420,12 +444,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
 }  // namespace
 
 static long long* g_conv_dbg = nullptr;
+static int g_conv_dbg_shift = 0;
 
 extern "C" {
 
 // Profiling aid: when set, every conv launch writes per-CTA cycle counters [grid][3 roles][4] (producer: wait a_empty;
 // MMA: wait acc_empty, wait a_full, issue; epilogue: wait acc_full, work).  Pass null to switch it off.
 void dba_conv_set_debug(long long* buf) { g_conv_dbg = buf; }
+void dba_conv_set_debug_shift(int mode) { g_conv_dbg_shift = mode; }
 
 // Geometry helpers shared with the Python side (dba_mod_b200/ops/layout.py mirrors these).
 long long dba_conv_rows(int B, int H, int W) {
@@ -440,32 +466,42 @@ long long dba_conv_rows(int B, int H, int W) {
 // [K][Cout/8][Ro][8], Ro = dba_conv_rows(B,Ho,Wo), Ho = H/sub.  scale/shift (nullable together): per (client,
 // out-channel) affine = folded BatchNorm (row stride ss_stride).  stats (nullable): rows of (sum, sumsq) pairs,
 // accumulated (+=).  x_shared != 0: every client reads client 0's X.
-int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
-                        const float* scale, const float* shift, long long ss_stride, float* stats,
-                        long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
-                        int relu, int x_shared, void* stream) {
+// in_s2d / out_s2d: space-to-depth forms for stride-2 convolutions (see ConvArgs).  With in_s2d, (H, W) is the
+// OUTPUT grid of the stride-2 convolution (the grid X' lives on), X' has 4*Cin channels and sub must be 1.  With
+// out_s2d, Y gets 4*Cout channels on the (H/2, W/2) grid; Res (if any) stays a plain (H, W) tensor.
+int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                   const float* scale, const float* shift, long long ss_stride, float* stats,
+                   long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                   int relu, int x_shared, int in_s2d, int out_s2d, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
   DBA_REQUIRE(ksize == 1 || ksize == 3, "dba_conv_tc: ksize must be 1 or 3, got %d", ksize);
   DBA_REQUIRE(Cin % 16 == 0 && Cout % 32 == 0, "dba_conv_tc: Cin (%d) %% 16 and Cout (%d) %% 32 must be 0", Cin, Cout);
   DBA_REQUIRE(sub == 1 || (sub == 2 && H % 2 == 0 && W % 2 == 0), "dba_conv_tc: sub=%d needs even H, W", sub);
   DBA_REQUIRE((scale == nullptr) == (shift == nullptr), "dba_conv_tc: scale and shift go together");
   DBA_REQUIRE(!(scale && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
+  DBA_REQUIRE(!(in_s2d || out_s2d) || sub == 1, "dba_conv_tc: space-to-depth forms replace sub=2, pass sub=1");
+  DBA_REQUIRE(!out_s2d || (H % 2 == 0 && W % 2 == 0), "dba_conv_tc: out_s2d needs even H, W");
   ConvArgs a{};
+  a.in_s2d = in_s2d ? 1 : 0; a.out_s2d = out_s2d ? 1 : 0;
   a.X = (const __nv_bfloat16*)X; a.Wt = (const __nv_bfloat16*)Wt; a.Y = (__nv_bfloat16*)Y;
   a.Res = (const __nv_bfloat16*)Res; a.scale = scale; a.shift = shift; a.stats = stats;
   a.K = K; a.Cin = Cin; a.Cout = Cout; a.taps = ksize * ksize;
   a.H = H; a.W = W; a.Wp = W + 1; a.S = (H + 1) * a.Wp; a.lead = a.Wp + 1; a.B = B;
   a.relu = relu; a.sub = sub;
-  a.Ho = H / sub; a.Wo = W / sub; a.Wpo = a.Wo + 1; a.So = (a.Ho + 1) * a.Wpo; a.leado = a.Wpo + 1;
+  const int osub = out_s2d ? 2 : sub;
+  a.Ho = H / osub; a.Wo = W / osub; a.Wpo = a.Wo + 1; a.So = (a.Ho + 1) * a.Wpo; a.leado = a.Wpo + 1;
   const long long R = dba_conv_rows(B, H, W), Ro = dba_conv_rows(B, a.Ho, a.Wo);
   a.x_plane_stride = R * 8;
-  a.x_client_stride = x_shared ? 0 : (long long)(Cin / 8) * R * 8;
+  a.x_client_stride = x_shared ? 0 : (long long)(in_s2d ? 4 : 1) * (Cin / 8) * R * 8;
   a.y_plane_stride = Ro * 8;
-  a.y_client_stride = (long long)(Cout / 8) * Ro * 8;
+  a.y_client_stride = (long long)(out_s2d ? 4 : 1) * (Cout / 8) * Ro * 8;
+  a.res_plane_stride = out_s2d ? R * 8 : a.y_plane_stride;
+  a.res_client_stride = out_s2d ? (long long)(Cout / 8) * R * 8 : a.y_client_stride;
   a.w_client_stride = w_client_stride;
   a.ss_stride = ss_stride;
   a.stats_stride = stats_stride;
   a.KB = Cin >= 64 ? 64 : Cin;
+  if (in_s2d && ksize == 3 && a.KB > 32) a.KB = 32;      // four parity planes per k-block share the stage
   DBA_REQUIRE(Cin % a.KB == 0 && (a.KB == 16 || a.KB == 32 || a.KB == 64), "dba_conv_tc: unsupported Cin=%d", Cin);
   a.halo = ksize == 3 ? a.Wp + 1 : 0;
   const int kc = a.KB / 8;
@@ -490,27 +526,34 @@ int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride
   }
   const size_t budget = 220 * 1024;
   size_t need = 0;
+  const int npar = (in_s2d && ksize == 3) ? 4 : 1;
   for (;; T /= 2) {
     a.T = T; a.NB = NB;
-    a.rowsA = T * kTileM + 2 * a.halo;
-    const size_t bytesA = (size_t)kc * a.rowsA * 16, bytesB = (size_t)kc * NB * 16;
+    a.rowsA = T * kTileM + (npar == 4 ? 1 : 2) * a.halo;      // parity-plane taps only reach up / left
+    const size_t bytesA = (size_t)npar * kc * a.rowsA * 16, bytesB = (size_t)kc * NB * 16;
     const size_t misc = 1024 + 2 * NB * sizeof(float);
-    a.SA = 2;
     a.NS = (2 * T * NB <= 512) ? 2 : 1;
     a.wbytes = (unsigned int)((size_t)a.taps * Cin * NB * 2);
-    a.resident = a.wbytes <= 100 * 1024 && a.SA * bytesA + a.wbytes + misc <= budget;
+    a.resident = a.wbytes <= 100 * 1024 && 2 * bytesA + a.wbytes + misc <= budget;
+    size_t breg;
     if (a.resident) {
       a.SB = 1;
-      need = a.SA * bytesA + a.wbytes + misc;
+      breg = a.wbytes;
     } else {
       a.SB = 4;
-      need = a.SA * bytesA + a.SB * bytesB + misc;
-      if (need > budget) { a.SB = 2; need = a.SA * bytesA + a.SB * bytesB + misc; }
+      if (2 * bytesA + a.SB * bytesB + misc > budget) a.SB = 2;
+      breg = a.SB * bytesB;
     }
+    // Two A stages.  Measured on B200: a third / fourth stage does not help even the bandwidth-hungry
+    // space-to-depth layers (26.97 vs 26.92 ms per 40k evaluations) and costs the MMA-bound layers 8% (more bulk-copy
+    // writes under the tensor core's operand reads); shortening the pass to make room for them costs 6% (halo rows).
+    a.SA = 2;
+    need = a.SA * bytesA + breg + misc;
     if (need <= budget || T == 1) break;
   }
   DBA_REQUIRE(need <= budget, "dba_conv_tc: shared memory need %zu exceeds budget", need);
   a.dbg = g_conv_dbg;
+  a.dbg_shift = g_conv_dbg_shift;
   a.magicS = ((1ULL << 40) + (unsigned long long)a.S - 1) / (unsigned long long)a.S;
   a.magicWp = ((1ULL << 40) + (unsigned long long)a.Wp - 1) / (unsigned long long)a.Wp;
   a.num_pass = (int)((body + (long long)a.T * kTileM - 1) / ((long long)a.T * kTileM));
@@ -533,6 +576,14 @@ int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
+}
+
+int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                        const float* scale, const float* shift, long long ss_stride, float* stats,
+                        long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                        int relu, int x_shared, void* stream) {
+  return dba_conv_tc_ex(X, Wt, w_client_stride, Y, Res, scale, shift, ss_stride, stats, stats_stride, K, B, H, W, Cin,
+                        Cout, ksize, sub, relu, x_shared, 0, 0, stream);
 }
 
 // Dense-stride convenience form: Wt [K][taps][Cin/8][Cout][8], scale/shift [K][Cout], stats [K][Cout][2].

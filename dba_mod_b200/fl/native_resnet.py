@@ -69,6 +69,7 @@ class NativeResNet:
         self._train_bufs: Dict[int, dict] = {}
         self.mu, self.wd = float(params["momentum"]), float(params["decay"])
         self.eval_chunk = int(params.get("native_eval_chunk", 500))
+        self.use_s2d = bool(params.get("native_s2d", True))
         self._eval_bufs: Dict[Tuple[int, int], dict] = {}
         d = data
         self.trig_u8 = d.trigger_masks.to(torch.uint8).contiguous()
@@ -149,21 +150,32 @@ class NativeResNet:
         return pack[:, l.w_off:l.w_off + n].unflatten(1, (taps, l.cin_p // 8, l.cout_p, 8))
 
     def _conv(self, x, pack, l: ConvL, K, B, out, res=None, scale=None, shift=None, relu=False, stats=None,
-              x_shared=False, w_shared=False):
+              x_shared=False, w_shared=False, in_s2d=False, out_s2d=False):
         """Forward convolution of layer l.  pack rows are strided views -> pass raw pointers.
-        w_shared: all K input sets are convolved with the SAME model (row 0 of pack / scale / shift)."""
+        w_shared: all K input sets are convolved with the SAME model (row 0 of pack / scale / shift).
+        in_s2d: x is the space-to-depth form of the stride-2 layer's input (computed on the output grid only);
+        out_s2d: write the output in that form for the next stage's stride-2 consumers."""
         wt = self._wt(pack, l)
         ks = 1 if l.fold else l.ks
         cin = l.cin_p
-        native.check(self.lib.dba_conv_tc_strided(
+        H, sub = (l.H // l.sub, 1) if in_s2d else (l.H, l.sub)
+        native.check(self.lib.dba_conv_tc_ex(
             native.ptr(x), native.ptr(wt), 0 if w_shared else pack.stride(0), native.ptr(out), native.ptr(res),
             native.ptr(scale), native.ptr(shift),
             (0 if w_shared else scale.stride(0)) if scale is not None else 0, native.ptr(stats),
-            stats.stride(0) if stats is not None else 0, K, B, l.H, l.H, cin, l.cout_p, ks, l.sub, int(relu),
-            int(x_shared), native.stream()))
+            stats.stride(0) if stats is not None else 0, K, B, H, H, cin, l.cout_p, ks, sub, int(relu),
+            int(x_shared), int(in_s2d), int(out_s2d), native.stream()))
         return out
 
     # ------------------------------------------------------------------------------------------ evaluation
+    def _s2d_block(self, bi: int) -> bool:
+        """Block bi opens with stride-2 convolutions whose input is written by the previous block's last
+        convolution: that producer stores the space-to-depth form and the stride-2 layers compute output pixels only."""
+        if not self.use_s2d or bi <= 0 or bi >= len(self.blocks):
+            return False
+        c1, _, sc = self.blocks[bi]
+        return c1.sub == 2 and c1.ks == 3 and sc is not None and sc.sub == 2 and c1.H % 2 == 0
+
     def _ebufs(self, M: int, Bt: int, per_job_input: bool = False) -> dict:
         key = (M, Bt, per_job_input)
         if key in self._eval_bufs:
@@ -175,6 +187,11 @@ class NativeResNet:
         bufs = {"stem_in": z(kin, stem.cin_p, stem.H), "lv": {}}
         for w, r in zip(self.widths, self.ress):
             bufs["lv"][r] = [z(M, w, r) for _ in range(4)]
+        # space-to-depth form of a stage's output when the next stage opens with stride-2 convolutions
+        bufs["s2d"] = {}
+        for bi, (c1, _, _) in enumerate(self.blocks):
+            if self._s2d_block(bi):
+                bufs["s2d"][bi] = z(M, 4 * c1.cin_p, c1.H // 2)
         if self.pool:
             bufs["stem_out"] = z(M, self.widths[0], stem.H)
         bufs["labels"] = torch.zeros(kin, Bt, dtype=torch.int32, device=dev)
@@ -304,24 +321,28 @@ class NativeResNet:
             self._conv(xin, pack, stem, M, Bt, cur, scale=sc_, shift=sh_, relu=True, x_shared=not per_job,
                        w_shared=ws)
         res = self.ress[0]
-        ci = 0
-        for (c1, c2, sc) in self.blocks:
+        cur_s2d = False                           # cur holds the space-to-depth form (feeds stride-2 convolutions only)
+        for bi, (c1, c2, sc) in enumerate(self.blocks):
             r_out = res // c1.sub
             pool = lv[r_out]
             free = [b for b in pool if b is not cur]
             mid, out, proj = free[0], free[1], free[2] if len(free) > 2 else None
             s1, h1 = ss(c1)
-            self._conv(cur, pack, c1, M, Bt, mid, scale=s1, shift=h1, relu=True, w_shared=ws)
+            self._conv(cur, pack, c1, M, Bt, mid, scale=s1, shift=h1, relu=True, w_shared=ws, in_s2d=cur_s2d)
             if sc is not None:
                 s3, h3 = ss(sc)
                 proj = free[2] if len(free) > 2 else pool[3]
-                self._conv(cur, pack, sc, M, Bt, proj, scale=s3, shift=h3, relu=False, w_shared=ws)
+                self._conv(cur, pack, sc, M, Bt, proj, scale=s3, shift=h3, relu=False, w_shared=ws, in_s2d=cur_s2d)
                 skip = proj
             else:
                 skip = cur
             s2, h2 = ss(c2)
-            self._conv(mid, pack, c2, M, Bt, out, res=skip, scale=s2, shift=h2, relu=True, w_shared=ws)
-            cur = out
+            nxt_s2d = self._s2d_block(bi + 1)
+            if nxt_s2d:
+                out = bufs["s2d"][bi + 1]
+            self._conv(mid, pack, c2, M, Bt, out, res=skip, scale=s2, shift=h2, relu=True, w_shared=ws,
+                       out_s2d=nxt_s2d)
+            cur, cur_s2d = out, nxt_s2d
             res = r_out
         bufs["out"] = cur
 

@@ -29,3 +29,27 @@ def conv_tc(x: torch.Tensor, wt: torch.Tensor, K: int, B: int, H: int, W: int, k
                                  native.ptr(shift), native.ptr(stats), K, B, H, W, Cin, Cout, ksize, sub, int(relu),
                                  int(x_shared), int(debug_swap), native.stream()))
     return out
+
+
+def conv_tc_s2d(x: torch.Tensor, wt: torch.Tensor, K: int, B: int, H: int, W: int, ksize: int,
+                in_s2d: bool = False, out_s2d: bool = False, relu: bool = False,
+                res: Optional[torch.Tensor] = None, scale: Optional[torch.Tensor] = None,
+                shift: Optional[torch.Tensor] = None, stats: Optional[torch.Tensor] = None,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Space-to-depth variants (``dba_conv_tc_ex``).  (H, W) is the grid the convolution is COMPUTED on: with
+    ``in_s2d`` that is the stride-2 layer's output grid and x is ``layout.to_planar(layout.space_to_depth(input))``
+    with 4*Cin channels; with ``out_s2d`` the result has 4*Cout channels on the (H/2, W/2) grid."""
+    lib = native.load()
+    Cin, Cout = wt.shape[2] * 8, wt.shape[3]
+    assert x.dtype == torch.bfloat16 and wt.dtype == torch.bfloat16 and x.is_contiguous() and wt.is_contiguous()
+    assert x.shape[1] * 8 == (4 if in_s2d else 1) * Cin and x.shape[2] == Geom(B, H, W).rows
+    go = Geom(B, H // 2, W // 2) if out_s2d else Geom(B, H, W)
+    oshape = (K, (4 if out_s2d else 1) * Cout // 8, go.rows, 8)
+    if out is None:
+        out = torch.zeros(oshape, dtype=torch.bfloat16, device=x.device)
+    assert tuple(out.shape) == oshape and out.is_contiguous()
+    native.check(lib.dba_conv_tc_ex(
+        native.ptr(x), native.ptr(wt), wt[0].numel(), native.ptr(out), native.ptr(res), native.ptr(scale),
+        native.ptr(shift), Cout, native.ptr(stats), 2 * Cout, K, B, H, W, Cin, Cout, ksize, 1, int(relu), 0,
+        int(in_s2d), int(out_s2d), native.stream()))
+    return out

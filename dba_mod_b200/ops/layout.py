@@ -58,6 +58,22 @@ def from_planar(y: torch.Tensor, B: int, H: int, W: int, C: int = None) -> torch
     return out[:, :, :C] if C is not None else out
 
 
+def space_to_depth(x: torch.Tensor) -> torch.Tensor:
+    """[K, B, C, H, W] -> [K, B, 4C, H/2, W/2], channel p*C + c with parity plane p = 2*(h & 1) + (w & 1): the operand
+    form of stride-2 convolutions (csrc/conv_tc.cu ``in_s2d``)."""
+    K, B, C, H, W = x.shape
+    v = x.reshape(K, B, C, H // 2, 2, W // 2, 2).permute(0, 1, 4, 6, 2, 3, 5)       # [K, B, ph, pw, C, H/2, W/2]
+    return v.reshape(K, B, 4 * C, H // 2, W // 2)
+
+
+def depth_to_space(x: torch.Tensor) -> torch.Tensor:
+    """Inverse of :func:`space_to_depth`."""
+    K, B, C4, H2, W2 = x.shape
+    C = C4 // 4
+    v = x.reshape(K, B, 2, 2, C, H2, W2).permute(0, 1, 4, 5, 2, 6, 3)               # [K, B, C, H/2, ph, W/2, pw]
+    return v.reshape(K, B, C, 2 * H2, 2 * W2)
+
+
 def halo_is_zero(y: torch.Tensor, B: int, H: int, W: int) -> bool:
     K, C8 = y.shape[:2]
     g = Geom(B, H, W)

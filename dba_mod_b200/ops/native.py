@@ -62,8 +62,10 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_foolsgold_apply", [P, P, L, P, I, L, F, F, F, P])
     _sig(lib, "dba_conv_rows", [I, I, I], c_longlong)
     _sig(lib, "dba_conv_set_debug", [P], None)
+    _sig(lib, "dba_conv_set_debug_shift", [c_int], None)
     _sig(lib, "dba_conv_tc", [P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_conv_tc_strided", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, P])
+    _sig(lib, "dba_conv_tc_ex", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_pack_weights", [P, L, P, I, I, P, L, P])
     _sig(lib, "dba_bn_fold", [P, L, P, I, I, P, P, L, F, P])
     _sig(lib, "dba_input_stage_image", [P, P, P, L, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, L, P])

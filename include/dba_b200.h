@@ -87,6 +87,14 @@ int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride
                         const float* scale, const float* shift, long long ss_stride, float* stats,
                         long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
                         int relu, int x_shared, void* stream);
+/* Same, with space-to-depth operands for stride-2 convolutions (models/resnet_cifar.py:20,27: stride=2 conv1 and
+ * shortcut): in_s2d - X is [K][4*Cin/8][R'][8], parity plane p = 2*(h&1)+(w&1) of the real input on the (H, W) OUTPUT
+ * grid, pass sub = 1; out_s2d - Y is written in that form ((H/2, W/2) grid, 4*Cout channels) for the next stage's
+ * stride-2 consumers while Res stays plain.  Only computed positions are real outputs: no 4x full-grid waste. */
+int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                   const float* scale, const float* shift, long long ss_stride, float* stats,
+                   long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                   int relu, int x_shared, int in_s2d, int out_s2d, void* stream);
 
 /* Convolution weight gradient (autograd of nn.Conv2d; image_train.py:91,209) added into the fp32 gradient slab. */
 int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,

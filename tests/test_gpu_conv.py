@@ -71,3 +71,57 @@ def test_conv_stats(native_lib):
     s2 = (got * got).sum(dim=(1, 3, 4))
     torch.testing.assert_close(stats[..., 0], s1, rtol=1e-3, atol=1e-2)
     torch.testing.assert_close(stats[..., 1], s2, rtol=1e-3, atol=1e-2)
+
+
+S2D_SHAPES = [  # K, B, H, W (input grid), Cin, Cout, ksize
+    (2, 3, 32, 32, 32, 64, 3),
+    (1, 5, 16, 16, 64, 128, 3),
+    (2, 4, 8, 8, 128, 256, 3),
+    (2, 3, 16, 16, 64, 128, 1),
+    (1, 70, 32, 32, 32, 64, 3),
+]
+
+
+@pytest.mark.parametrize("K,B,H,W,Cin,Cout,ksize", S2D_SHAPES)
+def test_conv_stride2_from_space_to_depth_input(native_lib, K, B, H, W, Cin, Cout, ksize):
+    """Stride-2 convolutions computed on the output grid only, from the parity-plane form of their input."""
+    from dba_mod_b200.ops import conv, layout
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(2)
+    d = torch.device("cuda", 0)
+    x = torch.randn(K, B, Cin, H, W, device=d)
+    w = torch.randn(K, Cout, Cin, ksize, ksize, device=d) / (Cin * ksize * ksize) ** 0.5
+    xs = layout.to_planar(layout.space_to_depth(x))
+    stats = torch.zeros(K, Cout, 2, device=d)
+    y = conv.conv_tc_s2d(xs, layout.pack_conv_weight(w), K, B, H // 2, W // 2, ksize, in_s2d=True, stats=stats)
+    torch.cuda.synchronize()
+    got = layout.from_planar(y, B, H // 2, W // 2)
+    ref = _ref(x, w, ksize, 2)
+    torch.testing.assert_close(got, ref, rtol=2e-2, atol=2e-2)
+    assert layout.halo_is_zero(y, B, H // 2, W // 2)
+    torch.testing.assert_close(stats[..., 0], got.sum((1, 3, 4)), rtol=1e-3, atol=2e-2)
+
+
+def test_conv_space_to_depth_output_with_residual(native_lib):
+    """The producer side: folded-BN + residual + ReLU epilogue storing the parity-plane form, then a stride-2
+    convolution consuming it equals the plain two-layer computation."""
+    from dba_mod_b200.ops import conv, layout
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(3)
+    d = torch.device("cuda", 0)
+    K, B, H, W, C, C2 = 2, 5, 16, 16, 64, 128
+    x = torch.randn(K, B, C, H, W, device=d)
+    w1 = torch.randn(K, C, C, 3, 3, device=d) / (C * 9) ** 0.5
+    w2 = torch.randn(K, C2, C, 3, 3, device=d) / (C * 9) ** 0.5
+    res = torch.randn(K, B, C, H, W, device=d)
+    scale, shift = torch.rand(K, C, device=d) + 0.5, torch.randn(K, C, device=d)
+    y1 = conv.conv_tc_s2d(layout.to_planar(x), layout.pack_conv_weight(w1), K, B, H, W, 3, out_s2d=True, relu=True,
+                          res=layout.to_planar(res), scale=scale, shift=shift)
+    ref1 = F.relu(_ref(x, w1, 3, 1) * scale[:, None, :, None, None] + shift[:, None, :, None, None]
+                  + res.bfloat16().float())
+    got1 = layout.depth_to_space(layout.from_planar(y1, B, H // 2, W // 2))
+    torch.testing.assert_close(got1, ref1, rtol=2e-2, atol=3e-2)
+    assert layout.halo_is_zero(y1, B, H // 2, W // 2)
+    y2 = conv.conv_tc_s2d(y1, layout.pack_conv_weight(w2), K, B, H // 2, W // 2, 3, in_s2d=True)
+    ref2 = _ref(got1, w2, 3, 2)
+    torch.testing.assert_close(layout.from_planar(y2, B, H // 2, W // 2), ref2, rtol=2e-2, atol=3e-2)

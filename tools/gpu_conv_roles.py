@@ -33,4 +33,5 @@ for (K, B, shared, stats) in [(10, 64, False, True), (10, 500, True, False)]:
         m = v[:used].mean(0) / 1e3
         print(f"K={K} B={B} {'stats' if stats else 'eval '} layer {(H, W, Cin, Cout, ks, sub)}: {us:7.1f} us  ctas {used} | kcyc/CTA  "
               f"prod wait_a_empty {m[0,0]:.1f} | mma wait_acc_empty {m[1,0]:.1f} wait_a_full {m[1,1]:.1f} issue {m[1,2]:.1f} | "
-              f"epi wait_acc_full {m[2,0]:.1f} work {m[2,1]:.1f}", flush=True)
+              f"epi wait_acc_full {m[2,0]:.1f} work {m[2,1]:.1f} | lifetime prod {m[0,3]:.1f} mma {m[1,3]:.1f} epi {m[2,3]:.1f} "
+              f"max {v[:used, :, 3].max().item() / 1e3:.1f}", flush=True)
