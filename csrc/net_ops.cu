@@ -117,36 +117,48 @@ struct InputArgs {
   int K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo, KP, label_swap;
   long long R;
 };
+// grid: x = 256-pixel blocks of one image, y = sample, z = client * chunks + chunk.  Everything that depends on
+// (client, sample, chunk) - the sample id, poison / flip flags, the (kh, kw, c) of the chunk's 8 im2col columns - is
+// block-uniform, so the per-thread work is one 32-bit division, 8 byte loads and one 16-byte store (the first version
+// decomposed a flat 64-bit index per thread and spent its time in integer division: 0.5 TB/s of stores).
 __global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
   const int Wp = a.Wo + 1, S = (a.Ho + 1) * Wp, lead = Wp + 1;
   const int nchunk = a.KP >> 3;
-  const long long total = (long long)a.K * a.B * a.Ho * a.Wo * nchunk;
-  const int kreal = a.ks * a.ks * a.C;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    // pixel index fastest -> 16-byte stores of consecutive threads are contiguous inside one chunk plane
-    const int wo = (int)(i % a.Wo);
-    const int ho = (int)((i / a.Wo) % a.Ho);
-    const int b = (int)((i / ((long long)a.Wo * a.Ho)) % a.B);
-    const int chunk = (int)((i / ((long long)a.Wo * a.Ho * a.B)) % nchunk);
-    const int k = (int)(i / ((long long)a.Wo * a.Ho * a.B * nchunk));
-    const long long id = a.idx[(long long)k * a.ld_idx + b];
-    const bool poisoned = id >= 0 && b < a.poison_n[k];
-    const bool flip = a.flip && a.flip[(long long)k * a.ld_idx + b];
-    const unsigned char* img = a.data + (id < 0 ? 0 : id) * (long long)a.Hi * a.Wi * a.C;
-    const unsigned char* tm = a.trig + a.trig_row[k] * (long long)a.Hi * a.Wi;
+  const int b = blockIdx.y;
+  const int k = blockIdx.z / nchunk, chunk = blockIdx.z - k * nchunk;
+  __shared__ int s_dh[8], s_dw[8], s_c[8];
+  if (threadIdx.x < 8) {
+    const int e = chunk * 8 + threadIdx.x;
+    int c = -1, dh = 0, dw = 0;
+    if (e < a.ks * a.ks * a.C) {
+      const int tap = e / a.C;
+      c = e - tap * a.C;
+      const int kh = tap / a.ks;
+      dh = kh - a.pad;
+      dw = tap - kh * a.ks - a.pad;
+    }
+    s_dh[threadIdx.x] = dh; s_dw[threadIdx.x] = dw; s_c[threadIdx.x] = c;
+  }
+  __syncthreads();
+  const long long id = a.idx[(long long)k * a.ld_idx + b];
+  const bool poisoned = id >= 0 && b < a.poison_n[k];
+  const bool flip = a.flip && a.flip[(long long)k * a.ld_idx + b];
+  const unsigned char* img = a.data + (id < 0 ? 0 : id) * (long long)a.Hi * a.Wi * a.C;
+  const unsigned char* tm = a.trig + a.trig_row[k] * (long long)a.Hi * a.Wi;
+  __nv_bfloat16* dst = a.out + (((long long)k * nchunk + chunk) * a.R + lead + (long long)b * S) * 8;
+  const int npix = a.Ho * a.Wo;
+  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
+    const int ho = pix / a.Wo, wo = pix - ho * a.Wo;
     float v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int e = chunk * 8 + j;
       float x = 0.f;
-      if (id >= 0 && e < kreal) {
-        const int tap = e / a.C, c = e - tap * a.C;
-        const int kh = tap / a.ks, kw = tap - kh * a.ks;
-        const int hi = ho * a.stride + kh - a.pad, wi = wo * a.stride + kw - a.pad;
+      const int c = s_c[j];
+      if (id >= 0 && c >= 0) {
+        const int hi = ho * a.stride + s_dh[j], wi = wo * a.stride + s_dw[j];
         if (hi >= 0 && hi < a.Hi && wi >= 0 && wi < a.Wi) {
           if (poisoned && tm[hi * a.Wi + wi]) x = 1.f;
-          else x = (float)img[((long long)hi * a.Wi + (flip ? a.Wi - 1 - wi : wi)) * a.C + c] * (1.f / 255.f);
+          else x = (float)img[(hi * a.Wi + (flip ? a.Wi - 1 - wi : wi)) * a.C + c] * (1.f / 255.f);
         }
       }
       v[j] = x;
@@ -154,11 +166,10 @@ __global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
     uint4 pk;
     pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
     pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-    const long long row = lead + (long long)b * S + ho * Wp + wo;
-    *reinterpret_cast<uint4*>(a.out + (((long long)k * nchunk + chunk) * a.R + row) * 8) = pk;
-    if (a.labels_out && chunk == 0 && ho == 0 && wo == 0)
-      a.labels_out[k * a.B + b] = id < 0 ? -1 : (poisoned ? a.label_swap : (int)a.labels[id]);
+    *reinterpret_cast<uint4*>(dst + (long long)(ho * Wp + wo) * 8) = pk;
   }
+  if (a.labels_out && chunk == 0 && blockIdx.x == 0 && threadIdx.x == 0)
+    a.labels_out[k * a.B + b] = id < 0 ? -1 : (poisoned ? a.label_swap : (int)a.labels[id]);
 }
 extern "C" int dba_input_stage_image(const void* data, const long long* labels, const long long* idx, long long ld_idx,
                                      const void* trig, const long long* trig_row, const long long* poison_n,
@@ -169,10 +180,10 @@ extern "C" int dba_input_stage_image(const void* data, const long long* labels, 
   InputArgs a{(const unsigned char*)data, labels, idx, ld_idx, (const unsigned char*)trig, trig_row, poison_n,
               (const unsigned char*)flip, (__nv_bfloat16*)out, labels_out, K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo,
               KP, label_swap, R};
-  const long long total = (long long)K * B * Ho * Wo * (KP / 8);
-  long long g = (total + 255) / 256;
-  if (g > kNumSMs * 16) g = kNumSMs * 16;
-  input_stage_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(a);
+  DBA_REQUIRE(B <= 65535 && (long long)K * (KP / 8) <= 65535, "dba_input_stage_image: grid too large (B=%d K=%d)", B, K);
+  int gx = (Ho * Wo + 255) / 256;
+  if (gx > 64) gx = 64;
+  input_stage_kernel<<<dim3(gx, B, K * (KP / 8)), 256, 0, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
