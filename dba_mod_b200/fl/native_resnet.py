@@ -438,30 +438,52 @@ class NativeResNet:
             K, self.B, l.H, l.H, l.cout_p, l.cin_p, l.ks, 1, 0, 0, native.stream()))
         return out
 
-    # modelled cost of one lock-step step over k clients (ms): fixed launch floor + per-client work (measured, B200)
-    _STEP_COST = (1.0, 0.32)
+    # cost of one lock-step step over k clients (ms), measured on B200 with tools/gpu_step_cost.py (CIFAR ResNet-18,
+    # B = 64, graph replay): 1.52 ms at k = 1 ... 4.11 ms at k = 10; and of moving the carried state to another slab
+    _STEP_COST = (1.23, 0.285)
+    _CUT_COST = 0.25
 
     @classmethod
-    def _segments(cls, steps: List[int], max_cuts: int = 2) -> List[tuple]:
-        """Split the lock-step schedule into [(rows, lo, hi)] so that clients that finished early stop being
-        computed: a lone attacker training ``internal_poison_epochs`` x longer than the benign clients runs its tail
-        on a 1-client slab instead of dragging K-1 idle clients through every kernel."""
+    def _segments(cls, steps: List[int], max_cuts: int = 4) -> List[tuple]:
+        """Split the lock-step schedule into [(rows, lo, hi)] so that clients that finished stop being computed.
+
+        Clients hold different numbers of samples (Dirichlet partition) and attackers train
+        ``internal_poison_epochs`` x longer, so T = max steps while the average client is done much earlier: without
+        this a round of 10 clients runs at ~57% utilisation.  Cut points are chosen by dynamic programming over the
+        distinct step counts (cost model above); each segment runs on a slab sized for the clients still active."""
         a, b = cls._STEP_COST
-        rows = list(range(len(steps)))
+        K = len(steps)
         T = max(steps) if steps else 0
-        segs, lo = [], 0
-        for _ in range(max_cuts):
-            best = None
-            for c in sorted({steps[r] for r in rows if lo < steps[r] < T}):
-                tail = [r for r in rows if steps[r] > c]
-                cost = (c - lo) * (a + b * len(rows)) + (T - c) * (a + b * len(tail))
-                if best is None or cost < best[0]:
-                    best = (cost, c, tail)
-            if best is None or best[0] > 0.93 * (T - lo) * (a + b * len(rows)):
-                break
-            segs.append((rows, lo, best[1]))
-            rows, lo = best[2], best[1]
-        segs.append((rows, lo, T))
+        if K == 0 or T == 0:
+            return [(list(range(K)), 0, T)]
+        cuts = sorted({s for s in steps if 0 < s < T})          # candidate boundaries
+        pts = [0] + cuts + [T]
+
+        def active(lo):
+            return [r for r in range(K) if steps[r] > lo]
+
+        n = len(pts)
+        INF = float("inf")
+        # best[j][c] = minimal cost of covering [pts[j], T) with at most c further cuts
+        best = [[INF] * (max_cuts + 1) for _ in range(n)]
+        nxt = [[-1] * (max_cuts + 1) for _ in range(n)]
+        for c in range(max_cuts + 1):
+            best[n - 1][c] = 0.0
+        for j in range(n - 2, -1, -1):
+            k = len(active(pts[j]))
+            for c in range(max_cuts + 1):
+                for m in range(j + 1, n):
+                    if m < n - 1 and c == 0:
+                        continue
+                    tail = best[m][c - 1] + cls._CUT_COST if m < n - 1 else 0.0
+                    cost = (pts[m] - pts[j]) * (a + b * k) + tail
+                    if cost < best[j][c] - 1e-12:
+                        best[j][c], nxt[j][c] = cost, m
+        segs, j, c = [], 0, max_cuts
+        while j < n - 1:
+            m = nxt[j][c]
+            segs.append((active(pts[j]), pts[j], pts[m]))
+            j, c = m, c - 1
         return segs
 
     def train(self, sch, W: torch.Tensor, cnt: torch.Tensor, anchor: torch.Tensor, want_grad_sum: bool):
@@ -526,9 +548,8 @@ class NativeResNet:
     def _run_steps(self, K: int, t: dict, per_step: dict, rows, lo: int, hi: int, flags: tuple) -> None:
         """Steps [lo, hi) of the clients ``rows`` (None = all) on the K-client slab ``t``: stage the step's index /
         lr / mask rows, then replay the captured step graph (first use of a slab: one eager step, then capture)."""
-        want_grad_sum, with_flip, use_dist = flags
+        with_flip = flags[1]
         use_graph = bool(self.params.get("cuda_graphs", True))
-        gkey = ("graph",) + flags
 
         def pick(x, step):
             return x[:, step] if rows is None else x[rows, step]
@@ -541,25 +562,50 @@ class NativeResNet:
             t["st_lr"].copy_(pick(per_step["lr"], step))
             if with_flip:
                 t["st_flip"].copy_(pick(per_step["flip"], step))
-            g = t.get(gkey)
-            if not use_graph:
+            self._replay(K, t, flags, use_graph)
+
+    def _replay(self, K: int, t: dict, flags: tuple, use_graph: bool = True) -> None:
+        """One step on slab t: eager the first time (lazy kernel attributes), then capture, then graph replays."""
+        want_grad_sum, with_flip, use_dist = flags
+        gkey = ("graph",) + flags
+        g = t.get(gkey)
+        if not use_graph:
+            self._step_body(K, t, want_grad_sum, with_flip, use_dist)
+        elif g is None:
+            if not t.get(("warm", gkey)):
                 self._step_body(K, t, want_grad_sum, with_flip, use_dist)
-            elif g is None:
-                if not t.get(("warm", gkey)):
-                    # first ever step for this K: run eagerly (lazy kernel attributes), then record the graph
-                    self._step_body(K, t, want_grad_sum, with_flip, use_dist)
-                    t[("warm", gkey)] = True
-                    continue
-                l0 = native.launch_count()
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
-                    self._step_body(K, t, want_grad_sum, with_flip, use_dist)
-                t[gkey] = graph
-                t[("nl", gkey)] = native.launch_count() - l0
-                graph.replay()
-            else:
-                g.replay()
-                self.lib.dba_add_launch_count(t[("nl", gkey)])
+                t[("warm", gkey)] = True
+                return
+            l0 = native.launch_count()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._step_body(K, t, want_grad_sum, with_flip, use_dist)
+            t[gkey] = graph
+            t[("nl", gkey)] = native.launch_count() - l0
+            graph.replay()
+        else:
+            g.replay()
+            self.lib.dba_add_launch_count(t[("nl", gkey)])
+
+    def prewarm(self, Kmax: int, want_grad_sum: bool) -> None:
+        """Allocate the slabs and capture the step graphs of every batch width 1..Kmax up front (all-idle dummy steps:
+        no client is active, nothing is updated), so that no round pays for a capture in its critical path."""
+        if not bool(self.params.get("cuda_graphs", True)):
+            return
+        p = self.params
+        with_flip = bool(getattr(self.data, "train_flip", False))
+        dists = [False] + ([True] if (p["is_poison"] and float(p["alpha_loss"]) != 1.0) else [])
+        for K in range(1, Kmax + 1):
+            t = self._tbufs(K)
+            t["st_idx"].fill_(-1); t["st_nvalid"].zero_(); t["st_active"].zero_(); t["st_lr"].zero_()
+            for use_dist in dists:
+                flags = (bool(want_grad_sum), with_flip, use_dist)
+                for _ in range(2):
+                    self._replay(K, t, flags)
+            for key in ("V", "mf", "mi", "nan", "gs", "mf_dist", "W"):
+                t[key].zero_()
+            if t["cnt"].numel():
+                t["cnt"].zero_()
 
     def _step_body(self, K: int, t: dict, want_grad_sum: bool, with_flip: bool, use_dist: bool = False) -> None:
         """One lock-step SGD step of K clients: ~125 kernel launches, no host decisions (CUDA-graph capturable).

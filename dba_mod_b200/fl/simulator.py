@@ -135,6 +135,12 @@ class Simulator:
         self.target_name = display_name(params["type"], "Target")
 
         self.backend = self._make_backend()
+        ex = getattr(self.backend, "exec", None)
+        if (ex is not None and hasattr(ex, "prewarm") and getattr(self.backend, "native_train", False)
+                and params.get("compact_tail", True) and params.get("prewarm", True)):
+            # every batch width a round can shrink to gets its slab and captured step graph now, not mid-round
+            kmax = min(int(params["no_models"]), (int(params["no_models"]) + self.world - 1) // self.world + 1)
+            ex.prewarm(kmax, params["aggregation_methods"] == C.AGGR_FOOLSGOLD)
         self.collective_path = "single process" if self.world == 1 else "torch.distributed baseline"
         if (self.world > 1 and self.device.type == "cuda" and params["fused_collectives"]
                 and not hasattr(self.comm, "fedavg_")):
@@ -309,14 +315,17 @@ class Simulator:
             for seg_epoch in range(epoch, epoch + p["aggr_epoch_interval"]):
                 anchor, anchor_cnt = W.clone(), cnt.clone()
                 lr_override = self._loan_adaptive_lr(my_names, seg_epoch, W)
-                plans = plan_clients(p, self.data, my_names, seg_epoch, lr_override)
-                sch = build_schedule(p, self.data, plans, seg_epoch, dev, self.sched_gen)
-                res = be.train(sch, W, cnt, anchor, use_fg, generator=self.torch_gen)
+                with self.timer.phase("train/schedule"):
+                    plans = plan_clients(p, self.data, my_names, seg_epoch, lr_override)
+                    sch = build_schedule(p, self.data, plans, seg_epoch, dev, self.sched_gen)
+                with self.timer.phase("train/local_steps"):
+                    res = be.train(sch, W, cnt, anchor, use_fg, generator=self.torch_gen)
                 rep.steps += sch.T
                 if use_fg:
                     grad_sum = res.grad_sum     # "only works for aggr_epoch_interval=1" (image_train.py:24)
-                self._after_training(seg_epoch, plans, my_slots, sch, res, W, cnt, anchor, anchor_cnt, rows_local,
-                                     num_samples, rep)
+                with self.timer.phase("train/client_eval"):
+                    self._after_training(seg_epoch, plans, my_slots, sch, res, W, cnt, anchor, anchor_cnt,
+                                         rows_local, num_samples, rep)
         # emit per-client rows in the reference's order (client by client)
         self._emit_rows(rows_local, counts)
 

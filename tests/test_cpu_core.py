@@ -341,15 +341,20 @@ def test_schedule_segments_drop_finished_clients():
     seg = NativeResNet._segments
     # ten clients, one attacker training 3x longer: the tail runs on the attacker alone
     s = seg([16] * 4 + [48] + [14] * 5)
-    assert s[0] == (list(range(10)), 0, 16) and s[-1] == ([4], 16, 48)
+    assert s[0] == (list(range(10)), 0, 14) and s[-1] == ([4], 16, 48)
     # nothing to gain: one segment
     assert seg([16] * 10) == [(list(range(10)), 0, 16)]
-    assert seg([16, 15, 16]) == [([0, 1, 2], 0, 16)]
-    # every step of every client is covered exactly once
-    steps = [5, 40, 12, 40, 9]
-    cover = [0] * len(steps)
-    for rows, lo, hi in seg(steps):
-        for r in rows:
-            cover[r] += min(hi, steps[r]) - min(lo, steps[r])
-    assert cover == steps
+    # every step of every client is covered exactly once, segments are contiguous, rows only ever shrink
+    for steps in ([5, 40, 12, 40, 9], [6, 10, 12, 14, 16, 18, 20, 24, 28, 32], [3, 1, 2], [7], [0, 4]):
+        cover = [0] * len(steps)
+        segs = seg(steps)
+        assert segs[0][1] == 0 and segs[-1][2] == max(steps)
+        for (rows, lo, hi), nxt in zip(segs, segs[1:] + [None]):
+            assert rows == [r for r in range(len(steps)) if steps[r] > lo]
+            if nxt is not None:
+                assert nxt[1] == hi and set(nxt[0]) <= set(rows)
+            for r in rows:
+                cover[r] += min(hi, steps[r]) - min(lo, steps[r])
+        assert cover == steps
+    assert len(seg([6, 10, 12, 14, 16, 18, 20, 24, 28, 32], max_cuts=2)) <= 3
     assert seg([]) == [([], 0, 0)]
