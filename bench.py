@@ -239,9 +239,19 @@ def main() -> int:
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--small", action="store_true", help="5000/1000 images (CPU smoke test only; not a valid number)")
     args = ap.parse_args()
-    out = run_reference(args) if args.impl == "reference" else run_own(args)
+    # stdout carries exactly ONE JSON line: whatever libraries print while the benchmark runs (NCCL's version banner,
+    # the reference's progress prints) is diverted to stderr at the file-descriptor level
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        out = run_reference(args) if args.impl == "reference" else run_own(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if int(os.environ.get("RANK", "0")) == 0 and out:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     return 0
 
 
