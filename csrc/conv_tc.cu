@@ -76,6 +76,9 @@ struct ConvArgs {
   // Stride-2 convolutions without the 4x full-grid waste: X is the space-to-depth form of the real input (parity
   // planes p = 2*(h&1) + (w&1), each Cin channels, on the OUTPUT grid); tap (dh, dw) of the 3x3 kernel reads parity
   // plane (dh != 1, dw != 1) shifted by (dh == 0 ? -1 : 0, dw == 0 ? -1 : 0); the 1x1 kernel reads plane 0 unshifted.
+  int ksz;                     // 1, 3 or 5: taps = ksz*ksz, centred (pad = ksz/2)
+  int vlo, vhi;                // outputs are stored for vlo <= h, w < vhi only (a 'valid' convolution is the centre
+                               // crop of the 'same' one: 5x5 pad 0 on 12x12 -> vlo = 2, vhi = 10)
   int in_s2d;
   // Store Y (and only Y - Res stays in the plain layout) as the space-to-depth form of the (H, W) output.
   int out_s2d;
@@ -251,7 +254,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
               dB0 = umma_desc_noswz(smem_u32(smB + (size_t)sb * bytesB), pitchB, 128);
             }
             int shift = 0;
-            if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
+            if (a.taps > 1) {
+              const int th = tap / a.ksz;
+              shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
+            }
             if (npar == 4) {
               const int dh = tap / 3, dw = tap - dh * 3;
               shift = (dh == 0 ? -a.Wp : 0) + (dw == 0 ? -1 : 0)
@@ -294,7 +300,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     Pipe pacc;
     const int totalRows = a.B * a.S;
     int cur_group = -1;
-    const bool affine = a.scale != nullptr;
+    const bool affine = a.shift != nullptr;       // scale may be null: bias-only epilogue (networks without BatchNorm)
     const int t_step = a.T >= 2 ? 2 : 1, t_first = a.T >= 2 ? half : 0;
     const int c_step = a.T >= 2 ? 32 : 64, c_first = a.T >= 2 ? 0 : 32 * half;
     for (int item = item_lo; item < item_hi; ++item) {
@@ -305,10 +311,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       if (group != cur_group) {
         cur_group = group;
         if (affine) {     // per-channel scale / shift of this (client, n-block) -> shared memory
-          const float* gsc = a.scale + (long long)k * a.ss_stride + nb * a.NB;
+          const float* gsc = a.scale ? a.scale + (long long)k * a.ss_stride + nb * a.NB : nullptr;
           const float* gsh = a.shift + (long long)k * a.ss_stride + nb * a.NB;
           asm volatile("bar.sync 1, 256;" ::: "memory");
-          for (int i = threadIdx.x - 64; i < a.NB; i += 32 * kEpiWarps) { ss_s[i] = gsc[i]; ss_s[a.NB + i] = gsh[i]; }
+          for (int i = threadIdx.x - 64; i < a.NB; i += 32 * kEpiWarps) {
+            ss_s[i] = gsc ? gsc[i] : 1.f;
+            ss_s[a.NB + i] = gsh[i];
+          }
           asm volatile("bar.sync 1, 256;" ::: "memory");
         }
       }
@@ -326,7 +335,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           const unsigned int rem = qrow - b * (unsigned int)a.S;
           const unsigned int h = (unsigned int)(((unsigned long long)rem * a.magicWp) >> 40);
           const unsigned int w = rem - h * (unsigned int)a.Wp;
-          bool st = (int)qrow < totalRows && (int)h < a.H && (int)w < a.W;
+          bool st = (int)qrow < totalRows && (int)h < a.vhi && (int)w < a.vhi && (int)h >= a.vlo && (int)w >= a.vlo &&
+                    (int)h < a.H && (int)w < a.W;
           if (a.sub == 2) {
             st = st && !((h | w) & 1u);
             orow[i] = rrow[i] = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
@@ -444,6 +454,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
 }  // namespace
 
 static long long* g_conv_dbg = nullptr;
+static thread_local int g_conv_vlo = 0, g_conv_vhi = 0;     // set by dba_conv_tc_valid around one launch
 static int g_conv_dbg_shift = 0;
 
 extern "C" {
@@ -474,11 +485,11 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
                    long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
                    int relu, int x_shared, int in_s2d, int out_s2d, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
-  DBA_REQUIRE(ksize == 1 || ksize == 3, "dba_conv_tc: ksize must be 1 or 3, got %d", ksize);
+  DBA_REQUIRE(ksize == 1 || ksize == 3 || ksize == 5, "dba_conv_tc: ksize must be 1, 3 or 5, got %d", ksize);
   DBA_REQUIRE(Cin % 16 == 0 && Cout % 32 == 0, "dba_conv_tc: Cin (%d) %% 16 and Cout (%d) %% 32 must be 0", Cin, Cout);
   DBA_REQUIRE(sub == 1 || (sub == 2 && H % 2 == 0 && W % 2 == 0), "dba_conv_tc: sub=%d needs even H, W", sub);
-  DBA_REQUIRE((scale == nullptr) == (shift == nullptr), "dba_conv_tc: scale and shift go together");
-  DBA_REQUIRE(!(scale && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
+  DBA_REQUIRE(scale == nullptr || shift != nullptr, "dba_conv_tc: scale needs shift (shift alone = bias epilogue)");
+  DBA_REQUIRE(!(shift && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
   DBA_REQUIRE(!(in_s2d || out_s2d) || sub == 1, "dba_conv_tc: space-to-depth forms replace sub=2, pass sub=1");
   DBA_REQUIRE(!out_s2d || (H % 2 == 0 && W % 2 == 0), "dba_conv_tc: out_s2d needs even H, W");
   ConvArgs a{};
@@ -503,7 +514,9 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   a.KB = Cin >= 64 ? 64 : Cin;
   if (in_s2d && ksize == 3 && a.KB > 32) a.KB = 32;      // four parity planes per k-block share the stage
   DBA_REQUIRE(Cin % a.KB == 0 && (a.KB == 16 || a.KB == 32 || a.KB == 64), "dba_conv_tc: unsupported Cin=%d", Cin);
-  a.halo = ksize == 3 ? a.Wp + 1 : 0;
+  a.halo = (ksize / 2) * (a.Wp + 1);
+  a.ksz = ksize;
+  a.vlo = g_conv_vlo; a.vhi = g_conv_vhi > 0 ? g_conv_vhi : (H > W ? H : W);
   const int kc = a.KB / 8;
   const long long body = (long long)B * a.S;
   // n-block and rows per pass: as many 128-row tiles as fit in TMEM (512 columns); when that leaves SMs idle, first
@@ -576,6 +589,21 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
+}
+
+// 'Valid' (unpadded) convolution as the centre crop of the padded one: only outputs with vlo <= h, w < vhi are stored
+// (at their position on the input grid); everything else as dba_conv_tc_ex.  With ksize = 5 the operand block reaches
+// 2*(W+1)+2 rows beyond a pass on either side: X needs (W+2) zero rows of slack before its first and after its last
+// plane (see NativeMnist._zbuf).
+int dba_conv_tc_valid(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                      const float* scale, const float* shift, long long ss_stride, float* stats,
+                      long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int relu,
+                      int x_shared, int vlo, int vhi, void* stream) {
+  g_conv_vlo = vlo; g_conv_vhi = vhi;
+  const int rc = dba_conv_tc_ex(X, Wt, w_client_stride, Y, Res, scale, shift, ss_stride, stats, stats_stride, K, B, H, W,
+                                Cin, Cout, ksize, 1, relu, x_shared, 0, 0, stream);
+  g_conv_vlo = 0; g_conv_vhi = 0;
+  return rc;
 }
 
 int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,

@@ -12,14 +12,17 @@ using namespace dba;
 // Table entry per convolution (all ints): [0] src offset in the flat parameter vector (weights stored
 // [Cout][taps][Cin]), [1] Cout, [2] Cin, [3] taps, [4] dst offset (elements) of the forward pack
 // [taps'][CinP/8][CoutP][8], [5] dst offset of the transposed pack [taps][CoutP/8][CinP][8] with flipped taps (-1 =
-// none), [6] CinP, [7] CoutP, [8] fold: 1 = treat (taps, Cin) as one K axis of length taps*Cin padded to CinP (stem).
+// none), [6] CinP, [7] CoutP, [8] mode: 1 = fold, treat (taps, Cin) as one K axis of length taps*Cin padded to CinP
+// (stem); 2 = linear layer over a flattened [Cin][taps] feature map (torch's x.view(-1, C*h*w): source index
+// co*(Cin*taps) + ci*taps + tap), packed as a 1x1 convolution over channels n = tap*CinP + ci - forward
+// [1][taps*CinP/8][CoutP][8] (which IS the [taps][CinP/8][CoutP][8] layout), transposed [1][CoutP/8][taps*CinP][8].
 #define PACK_FIELDS 9
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ W, long long ldw,
                                                            const int* __restrict__ table,
                                                            __nv_bfloat16* __restrict__ dst, long long dst_client_stride) {
   const int* e = table + blockIdx.y * PACK_FIELDS;
   const int k = blockIdx.z;
-  const int Cout = e[1], Cin = e[2], taps = e[3], CinP = e[6], CoutP = e[7], fold = e[8];
+  const int Cout = e[1], Cin = e[2], taps = e[3], CinP = e[6], CoutP = e[7], fold = e[8] == 1, chw = e[8] == 2;
   const float* src = W + (long long)k * ldw + e[0];
   __nv_bfloat16* d = dst + (long long)k * dst_client_stride;
   const int ptaps = fold ? 1 : taps;             // taps as seen by the kernel
@@ -34,7 +37,9 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int ci = c8 * 8 + j;
-      v[j] = (co < Cout && ci < kreal) ? src[((long long)co * ptaps + tap) * kreal + ci] : 0.f;
+      v[j] = (co < Cout && ci < kreal)
+                 ? (chw ? src[(long long)co * (Cin * taps) + ci * taps + tap] : src[((long long)co * ptaps + tap) * kreal + ci])
+                 : 0.f;
     }
     uint4 pk;
     pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
@@ -52,13 +57,19 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int co = o8 * 8 + j;
-      v[j] = (co < Cout && ci < Cin) ? src[((long long)co * taps + tap) * Cin + ci] : 0.f;
+      v[j] = (co < Cout && ci < Cin)
+                 ? (chw ? src[(long long)co * (Cin * taps) + ci * taps + tap] : src[((long long)co * taps + tap) * Cin + ci])
+                 : 0.f;
     }
     uint4 pk;
     pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
     pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-    const int ftap = taps - 1 - tap;
-    *reinterpret_cast<uint4*>(d + e[5] + (((long long)ftap * (CoutP >> 3) + o8) * CinP + ci) * 8) = pk;
+    if (chw) {
+      *reinterpret_cast<uint4*>(d + e[5] + (((long long)o8 * taps + tap) * CinP + ci) * 8) = pk;
+    } else {
+      const int ftap = taps - 1 - tap;
+      *reinterpret_cast<uint4*>(d + e[5] + (((long long)ftap * (CoutP >> 3) + o8) * CinP + ci) * 8) = pk;
+    }
   }
 }
 extern "C" int dba_pack_weights(const float* W, long long ldw, const int* table, int n_layers, int K, void* dst,
@@ -208,6 +219,7 @@ struct HeadArgs {
   unsigned char* nan_flag;   // [K] or null
   long long ldw, ldg, R;
   int w_off, b_off, K, B, C, H, W, ncls, ld_m, shared_labels;
+  int Cp;                    // channels of the activation buffers (C rounded up to the planar layout's padding)
 };
 // Block = kHeadWarps samples of ONE client (grid.x = blocks per client, grid.y = client), so the gradient of the
 // linear layer is first summed in shared memory and leaves the block as one atomic per weight (the first version
@@ -226,11 +238,11 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
   const int label = b < a.B ? a.labels[(a.shared_labels ? 0 : k) * a.B + b] : -1;
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
   const long long plane = a.R * 8;
-  const __nv_bfloat16* act = a.act + (long long)k * (a.C >> 3) * plane;
+  const __nv_bfloat16* act = a.act + (long long)k * (a.Cp >> 3) * plane;
   constexpr int PER = MAXC / 32;
   const float inv_hw = 1.f / (float)(a.H * a.W);
   if (b < a.B && label < 0 && a.dact) {        // padding sample: contributes nothing, its gradient rows must be zero
-    __nv_bfloat16* d = a.dact + (long long)k * (a.C >> 3) * plane;
+    __nv_bfloat16* d = a.dact + (long long)k * (a.Cp >> 3) * plane;
     for (int i = 0; i < PER; ++i) {
       const int c = lane + 32 * i;
       if (c < a.C)
@@ -308,7 +320,7 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
         }
       }
       if (a.dact) {
-        __nv_bfloat16* d = a.dact + (long long)k * (a.C >> 3) * plane;
+        __nv_bfloat16* d = a.dact + (long long)k * (a.Cp >> 3) * plane;
 #pragma unroll
         for (int i = 0; i < PER; ++i) {
           const int c = lane + 32 * i;
@@ -332,13 +344,26 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
       if (s_gw[a.ncls * a.C + i] != 0.f) atomicAdd(&Gb[i], s_gw[a.ncls * a.C + i]);
   }
 }
+extern "C" int dba_head_ex(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat,
+                           long long ldg, void* dact, const int* labels, int shared_labels, const int* nvalid,
+                           const long long* slot, float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag,
+                           int K, int B, int C, int c_pad, int H, int W, int ncls, long long R, void* stream);
 extern "C" int dba_head(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat,
                         long long ldg, void* dact, const int* labels, int shared_labels, const int* nvalid,
                         const long long* slot, float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag,
                         int K, int B, int C, int H, int W, int ncls, long long R, void* stream) {
+  return dba_head_ex(act, Wflat, ldw, w_off, b_off, Gflat, ldg, dact, labels, shared_labels, nvalid, slot, metrics_f,
+                     metrics_i, ld_m, nan_flag, K, B, C, (C + 7) / 8 * 8, H, W, ncls, R, stream);
+}
+// c_pad: channel count of the planar act / dact buffers (>= C, multiple of 8) when the layer is padded (500 -> 512).
+extern "C" int dba_head_ex(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat,
+                           long long ldg, void* dact, const int* labels, int shared_labels, const int* nvalid,
+                           const long long* slot, float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag,
+                           int K, int B, int C, int c_pad, int H, int W, int ncls, long long R, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && C <= 512 && ncls <= 200, "dba_head: K=%d B=%d C=%d ncls=%d", K, B, C, ncls);
   HeadArgs a{(const __nv_bfloat16*)act, Wflat, Gflat, (__nv_bfloat16*)dact, labels, nvalid, slot, metrics_f, metrics_i,
-             nan_flag, ldw, ldg, R, w_off, b_off, K, B, C, H, W, ncls, ld_m, shared_labels};
+             nan_flag, ldw, ldg, R, w_off, b_off, K, B, C, H, W, ncls, ld_m, shared_labels, c_pad};
+  DBA_REQUIRE(c_pad >= C && c_pad % 8 == 0, "dba_head: c_pad=%d for C=%d", c_pad, C);
   DBA_REQUIRE(K <= 65535, "dba_head: K=%d too large for grid.y", K);
   const dim3 grid((B + kHeadWarps - 1) / kHeadWarps, K);
   const size_t gsm = (size_t)(ncls * C + ncls) * sizeof(float);

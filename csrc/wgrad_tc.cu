@@ -36,6 +36,11 @@ struct WgArgs {
   int N;                       // input channels per accumulator block (<= 256)
   int nnblk;                   // Cin / N
   int stages;
+  int ksz;                     // 1, 3 or 5 (taps = ksz*ksz, centred)
+  // Destination index of (co, tap, ci): co*g_co + tap*g_tap + ci*g_ci.  Convolutions: [Cout][taps][Cin] ->
+  // (taps*cin_real, cin_real, 1).  A linear layer over a flattened C x h x w map, run as a 1x1 convolution over
+  // channels n = pos*cpad + c: ci -> (pos, c) with c < cgrp_real, destination (in_features, 1 per pos, npos per c).
+  int cgrp_pad, cgrp_real, npos;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -127,7 +132,10 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
           const uint32_t acc0 = ch != c0 ? 1u : 0u;
           for (int tap = t0; tap < t1; ++tap) {
             int shift = 0;
-            if (a.taps == 9) shift = (tap / 3 - 1) * a.Wp + (tap % 3 - 1);
+            if (a.taps > 1) {
+              const int th = tap / a.ksz;
+              shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
+            }
             const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.N);
             const uint64_t dB1 = dB0 + (uint64_t)(int64_t)shift;
             umma_f16(d_tmem, dA0, dB1, idesc, acc0);
@@ -156,7 +164,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       tc_fence_after();
       const int co = mb * 128 + q * 32 + lane;
       float* gk = a.G + (long long)k * a.ldg + a.w_off;
-      const bool vec = ((a.cin_real | a.w_off) & 3) == 0 && (a.ldg & 3) == 0;
+      const bool vec = ((a.cin_real | a.w_off) & 3) == 0 && (a.ldg & 3) == 0 && a.npos == 0;
       if (c1 > c0) {
         for (int tap = t0; tap < t1; ++tap) {
           float* dst = gk + ((long long)co * a.taps + tap) * a.cin_real + nbk * a.N;
@@ -172,10 +180,18 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
                   if (n0 + j < cin_left)
                     red_add_v4(dst + n0 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
                                __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-              } else {
+              } else if (a.npos == 0) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
                   if (n0 + j < cin_left) atomicAdd(dst + n0 + j, __uint_as_float(v[j]));
+              } else {          // flattened-map linear layer: channel n = pos*cgrp_pad + c -> [co][c*npos + pos]
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const int n = nbk * a.N + n0 + j;
+                  const int pos = n / a.cgrp_pad, c = n - pos * a.cgrp_pad;
+                  if (c < a.cgrp_real && pos < a.npos)
+                    atomicAdd(gk + (long long)co * (a.cgrp_real * a.npos) + c * a.npos + pos, __uint_as_float(v[j]));
+                }
               }
             }
           }
@@ -202,14 +218,16 @@ extern "C" {
 // (R = dba_conv_rows(B,H,W)).  Adds the weight gradient of a ksize x ksize convolution (ksize 1 or 3, pad ksize/2) into
 // G[k*ldg + w_off + (co*taps + tap)*cin_real + ci] for co < cout_real, ci < cin_real (the gradient slab is zeroed by
 // the caller once per step).  Cin / Cout are the padded channel counts of the planar buffers.
-int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
-                 int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
-  DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
+static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
+                        int Cin, int Cout, int cin_real, int cout_real, int ksize, int cgrp_pad, int cgrp_real,
+                        int npos, void* stream) {
+  DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3 || ksize == 5), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
   DBA_REQUIRE(Cin % 16 == 0 && (Cin <= 256 || Cin % 256 == 0) && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d Cout=%d", Cin, Cout);
   WgArgs a{};
   a.dY = (const __nv_bfloat16*)dY; a.X = (const __nv_bfloat16*)X; a.G = G; a.ldg = ldg; a.w_off = w_off;
   a.K = K; a.Cout = Cout; a.Cin = Cin; a.cin_real = cin_real; a.cout_real = cout_real; a.taps = ksize * ksize;
-  a.Wp = W + 1; a.lead = a.Wp + 1; a.halo = ksize == 3 ? a.Wp + 1 : 0;
+  a.Wp = W + 1; a.lead = a.Wp + 1; a.halo = (ksize / 2) * (a.Wp + 1);
+  a.ksz = ksize; a.cgrp_pad = cgrp_pad; a.cgrp_real = cgrp_real; a.npos = npos;
   const long long S = (long long)(H + 1) * a.Wp;
   long long body = (long long)B * S;
   body = (body + 511) / 512 * 512;
@@ -248,6 +266,19 @@ int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_o
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
+}
+
+int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
+                 int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
+  return wgrad_launch(dY, X, G, ldg, w_off, K, B, H, W, Cin, Cout, cin_real, cout_real, ksize, 0, 0, 0, stream);
+}
+
+// Weight gradient of a linear layer applied to a flattened [c_real][npos] feature map (torch's x.view(-1, C*h*w)) that
+// the native path keeps as channels n = pos*c_pad + c of a 1x1 grid: G[w_off + co*(c_real*npos) + c*npos + pos].
+int dba_wgrad_linear_chw(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int Cout,
+                         int cout_real, int c_pad, int c_real, int npos, void* stream) {
+  return wgrad_launch(dY, X, G, ldg, w_off, K, B, 1, 1, c_pad * npos, Cout, c_pad * npos, cout_real, 1, c_pad, c_real,
+                      npos, stream);
 }
 
 }  // extern "C"

@@ -43,6 +43,10 @@ class CudaBackend(TorchBackend):
                 self.native_train = self.exec.can_train
             except ImportError:
                 self.exec = None
+        if params["type"] == C.TYPE_MNIST and params.get("native_net", True):
+            from .native_mnist import NativeMnist
+            self.exec = NativeMnist(params, spec, data, device)
+            self.native_eval, self.native_train = self.exec.can_eval, self.exec.can_train
         if params["type"] == C.TYPE_LOAN and params.get("native_net", True):
             from .native_loan import NativeLoan
             self.exec = NativeLoan(params, spec, data, device)

@@ -66,10 +66,16 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_conv_tc", [P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_conv_tc_strided", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_conv_tc_ex", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, I, I, P])
+    _sig(lib, "dba_conv_tc_valid", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, I, P])
+    _sig(lib, "dba_wgrad_linear_chw", [P, P, P, L, I, I, I, I, I, I, I, I, P])
+    _sig(lib, "dba_maxpool2_fwd", [P, P, I, I, I, I, I, I, I, I, I, L, L, P])
+    _sig(lib, "dba_maxpool2_bwd_relu_bias", [P, P, P, P, L, I, I, I, I, I, I, I, I, I, I, I, L, L, P])
+    _sig(lib, "dba_relu_bwd_bias", [P, P, P, P, L, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_pack_weights", [P, L, P, I, I, P, L, P])
     _sig(lib, "dba_bn_fold", [P, L, P, I, I, P, P, L, F, P])
     _sig(lib, "dba_input_stage_image", [P, P, P, L, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_head", [P, P, L, I, I, P, L, P, P, I, P, P, P, P, I, P, I, I, I, I, I, I, L, P])
+    _sig(lib, "dba_head_ex", [P, P, L, I, I, P, L, P, P, I, P, P, P, P, I, P, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_bn_apply", [P, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
     _sig(lib, "dba_bn_backward", [P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
     _sig(lib, "dba_maxpool_fwd", [P, P, I, I, I, I, I, L, L, P])

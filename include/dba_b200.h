@@ -96,9 +96,31 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
                    long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
                    int relu, int x_shared, int in_s2d, int out_s2d, void* stream);
 
+/* 'Valid' (unpadded) convolution as the centre crop of the padded one (MnistNet's 5x5 convolutions,
+ * models/MnistNet.py:11-12): outputs are stored only for vlo <= h, w < vhi, at their position on the input grid.
+ * shift without scale = bias epilogue.  ksize 5 needs (W+2) zero rows of slack before / after X. */
+int dba_conv_tc_valid(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                      const float* scale, const float* shift, long long ss_stride, float* stats,
+                      long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int relu,
+                      int x_shared, int vlo, int vhi, void* stream);
+
 /* Convolution weight gradient (autograd of nn.Conv2d; image_train.py:91,209) added into the fp32 gradient slab. */
 int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
                  int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream);
+
+/* Weight gradient of a linear layer over a flattened [c_real][npos] map kept as channels n = pos*c_pad + c of a 1x1
+ * grid (MnistNet fc1 after x.view(-1, 4*4*50), models/MnistNet.py:22-23). */
+int dba_wgrad_linear_chw(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int Cout,
+                         int cout_real, int c_pad, int c_real, int npos, void* stream);
+
+/* ---- BatchNorm-free MnistNet path (csrc/mnist_ops.cu; models/MnistNet.py:17-30) ------------------------------- */
+int dba_maxpool2_fwd(const void* x, void* y, int K, int C, int B, int Hi, int Wi, int off, int Ho, int Wo, int flatten,
+                     long long Ri, long long Ro, void* stream);
+int dba_maxpool2_bwd_relu_bias(const void* g, const void* x, void* dz, float* G, long long ldg, int b_off, int c_real,
+                               int K, int C, int B, int Hi, int Wi, int off, int Ho, int Wo, int flatten, long long Ri,
+                               long long Ro, void* stream);
+int dba_relu_bwd_bias(const void* g, const void* act, void* dz, float* G, long long ldg, int b_off, int c_real, int K,
+                      int C, int B, int H, int W, long long R, void* stream);
 
 /* ---- network plumbing (csrc/net_ops.cu, csrc/bn_ops.cu) -------------------------------------------------------- */
 
@@ -118,6 +140,11 @@ int dba_input_stage_image(const void* data, const long long* labels, const long 
 int dba_head(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat, long long ldg,
              void* dact, const int* labels, int shared_labels, const int* nvalid, const long long* slot,
              float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag, int K, int B, int C, int H, int W,
+             int ncls, long long R, void* stream);
+/* c_pad: channel count of the planar act / dact buffers when the layer is padded (MnistNet fc1: 500 -> 512). */
+int dba_head_ex(const void* act, const float* Wflat, long long ldw, int w_off, int b_off, float* Gflat, long long ldg,
+             void* dact, const int* labels, int shared_labels, const int* nvalid, const long long* slot,
+             float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag, int K, int B, int C, int c_pad, int H, int W,
              int ncls, long long R, void* stream);
 /* Training-mode BatchNorm forward (apply) and backward.  Reference: nn.BatchNorm2d in resnet_cifar.py:20-35. */
 int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long long ld_stats, int stats_off,

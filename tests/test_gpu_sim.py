@@ -42,3 +42,22 @@ def test_loan_rounds_native_backend(native_lib):
     assert reps[1].adversaries == ["CT"] and reps[1].poison_acc is not None
     assert reps[2].global_acc >= reps[0].global_acc - 5.0 and reps[-1].global_loss == reps[-1].global_loss
     sim.close()
+
+
+def test_mnist_rounds_native_backend(native_lib):
+    """MNIST DBA with the native MnistNet executor: the main task's loss falls over the benign rounds and the
+    single-shot attack drives the backdoor accuracy up (eta = 1: the shipped eta = 0.1 assumes a resumed model)."""
+    import yaml
+    from dba_mod_b200.config import Params
+    from dba_mod_b200.fl.simulator import Simulator
+    raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "mnist_params.yaml")))
+    raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=6000, synthetic_test_size=1000,
+               number_of_total_participants=20, adversary_list=[3, 7, 11, 15], internal_epochs=2, epochs=5, eta=1.0,
+               **{"0_poison_epochs": [5], "1_poison_epochs": [5], "2_poison_epochs": [99], "3_poison_epochs": [99]})
+    sim = Simulator(Params(raw), device=torch.device("cuda", 0), quiet=True, write_files=False)
+    assert sim.backend.name == "cuda" and sim.backend.native_train and sim.backend.native_eval
+    reps = sim.run()
+    sim.close()
+    assert len(reps) == 5 and all(r.global_loss == r.global_loss for r in reps)
+    assert reps[3].global_loss < reps[0].global_loss - 0.02, [r.global_loss for r in reps]
+    assert reps[4].poison_acc > reps[3].poison_acc + 30.0, [r.poison_acc for r in reps]

@@ -1,6 +1,6 @@
 """Times the other BASELINE.json configurations through the public API (own arm only), device-timed rounds:
 
-    python tools/bench_configs.py loan|rfa1000|tiny_fg|cifar_fg|cifar_rfa [--rounds K] [--warmup W]
+    python tools/bench_configs.py loan|rfa1000|tiny_fg|cifar_fg|cifar_rfa|mnist [--rounds K] [--warmup W]
 
 Prints one JSON line per config.  Multi-GPU: launch under torchrun like bench.py.
 """
@@ -51,6 +51,10 @@ def cfg(name, W, K):
         raw.update(aggregation_methods="foolsgold", native_eval_chunk=250, dirichlet_alpha=0.5)
         for i in range(4):
             raw[f"{i}_poison_epochs"] = [W + 2 + i]
+    elif name == "mnist":       # config 1: MNIST MnistNet, 100 clients / 10 per round, DBA, FedAvg
+        raw = load("mnist_params.yaml")
+        for i in range(4):
+            raw[f"{i}_poison_epochs"] = [W + 2 + (i % 2)]
     else:
         raise SystemExit(f"unknown config {name}")
     return raw
