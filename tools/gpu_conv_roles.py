@@ -7,6 +7,9 @@ d = torch.device("cuda", 0)
 dbg = torch.zeros(148 * 12, dtype=torch.int64, device=d)
 layers = [(32, 32, 32, 32, 3, 1), (32, 32, 32, 64, 3, 2), (16, 16, 64, 64, 3, 1), (8, 8, 128, 128, 3, 1),
           (4, 4, 256, 256, 3, 1), (32, 32, 32, 64, 1, 2)]
+if len(sys.argv) > 1 and sys.argv[1] == "nprobe":      # per-MMA cost vs N
+    layers = [(32, 32, 32, 32, 3, 1), (32, 32, 32, 64, 3, 1), (32, 32, 32, 96, 3, 1), (32, 32, 32, 128, 3, 1),
+              (16, 16, 64, 64, 3, 1), (16, 16, 64, 192, 3, 1)]
 for (K, B, shared, stats) in [(10, 64, False, True), (10, 500, True, False)]:
     for (H, W, Cin, Cout, ks, sub) in layers:
         x = layout.to_planar(torch.randn(1 if shared else K, B, Cin, H, W, device=d))
