@@ -358,3 +358,17 @@ def test_schedule_segments_drop_finished_clients():
         assert cover == steps
     assert len(seg([6, 10, 12, 14, 16, 18, 20, 24, 28, 32], max_cuts=2)) <= 3
     assert seg([]) == [([], 0, 0)]
+
+
+def test_space_to_depth_layout_round_trip():
+    from dba_mod_b200.ops.layout import Geom, depth_to_space, from_planar, space_to_depth, to_planar
+    x = torch.randn(2, 3, 5, 8, 6)
+    y = space_to_depth(x)
+    assert y.shape == (2, 3, 20, 4, 3) and torch.equal(depth_to_space(y), x)
+    # channel p*C + c holds parity plane p = 2*(h & 1) + (w & 1)
+    assert torch.equal(y[:, :, 1 * 5 + 2], x[:, :, 2, 0::2, 1::2]) and torch.equal(y[:, :, 2 * 5 + 4], x[:, :, 4, 1::2, 0::2])
+    # planar-8 round trip (bf16 rounding only), halo rows stay zero
+    p = to_planar(x)
+    g = Geom(3, 8, 6)
+    assert p.shape == (2, 1, g.rows, 8)
+    torch.testing.assert_close(from_planar(p, 3, 8, 6, 5), x.bfloat16().float())
