@@ -31,6 +31,7 @@
 // as long as possible: when all taps of that weight set fit in shared memory ("resident" mode, every layer with
 // Cin*Cout <= 64*64) they are fetched ONCE per (client, n-block) with a single bulk copy and the per-tap
 // producer/consumer round trips disappear; larger layers stream one weight block per (tap, k-block).
+#include <cstdlib>
 #include "common.cuh"
 
 using namespace dba;
@@ -40,6 +41,7 @@ namespace {
 
 constexpr int kTileM = 128;
 constexpr int kEpiWarps = 8;                  // two warps per TMEM lane quadrant
+constexpr int kMaxSB = 16;      // weight-stream pipeline depth limit (barrier slots)
 constexpr int kThreads = 64 + 32 * kEpiWarps;
 
 struct ConvArgs {
@@ -86,9 +88,15 @@ struct ConvArgs {
 };
 
 struct Pipe {
-  int it = 0;
-  __device__ __forceinline__ int stage(int n) const { return it % n; }
-  __device__ __forceinline__ uint32_t phase(int n) const { return (uint32_t)((it / n) & 1); }
+  // ring position kept incrementally: `it % n` and `(it / n) & 1` with a run-time n are ~50 instructions each, which is
+  // what bounded the single MMA-issuing thread on layers with few MMAs per stage
+  int st = 0;
+  uint32_t ph = 0;
+  __device__ __forceinline__ int stage(int) const { return st; }
+  __device__ __forceinline__ uint32_t phase(int) const { return ph; }
+  __device__ __forceinline__ void advance(int n) {
+    if (++st == n) { st = 0; ph ^= 1u; }
+  }
 };
 
 __device__ __forceinline__ void warp_transpose_reduce32(float (&v)[32], int lane) {
@@ -131,15 +139,32 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   uint64_t* a_full = bars;
   uint64_t* a_empty = a_full + a.SA;
   uint64_t* b_full = a_empty + a.SA;            // streaming: SB stages; resident: [0] = weights landed
-  uint64_t* b_empty = b_full + 4;               //                        resident: [0] = weights no longer needed
-  uint64_t* acc_full = b_empty + 4;
+  uint64_t* b_empty = b_full + kMaxSB;             //                        resident: [0] = weights no longer needed
+  uint64_t* acc_full = b_empty + kMaxSB;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   float* ss_s = reinterpret_cast<float*>(tmem_slot + 4);     // [2][NB] scale / shift of the current weight group
+  int* tap_shift = reinterpret_cast<int*>(ss_s + 2 * a.NB);  // [taps] A-view offset of every tap (16-byte units)
 
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + a.taps) {      // per-tap view offsets, computed once
+    const int tap = threadIdx.x - 64;
+    int shift = 0;
+    if (a.taps > 1) {
+      const int th = tap / a.ksz;
+      shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
+    }
+    if (npar == 4) {
+      const int dh = tap / 3, dw = tap - dh * 3;
+      shift = (dh == 0 ? -a.Wp : 0) + (dw == 0 ? -1 : 0)
+              + (int)((uint32_t)((dh != 1) * 2 + (dw != 1)) * (uint32_t)kc * (pitchA >> 4));
+    }
+    if (a.dbg_shift == 1) shift = 0;
+    if (a.dbg_shift == 2) shift = (tap / 3 - 1) * 24 + (tap % 3 - 1) * 8;
+    tap_shift[tap] = shift;
+  }
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.SA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < 4; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < kMaxSB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], kEpiWarps); }
     mbar_fence_init();
   }
@@ -157,10 +182,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   const int item_lo = (int)(items * blockIdx.x / gridDim.x);
   const int item_hi = (int)(items * (blockIdx.x + 1) / gridDim.x);
   const int accCols = a.T * a.NB;               // columns of one accumulator set
-
   if (warp == 0) {
     // ================================================================= producer
-    if (elect_one()) {
+    // The whole warp runs the loop: lane 0 waits for the free stage and posts the expected byte count, then the lanes
+    // issue the stage's bulk copies in parallel (one elected thread issuing 8 one-KB copies per stage was the limit
+    // of every layer whose output channels are split over CTAs: ~100 cycles per copy against 280 cycles of MMAs).
+    {
       Pipe pa, pb;
       int cur_group = -1, wloads = 0;
       for (int item = item_lo; item < item_hi; ++item) {
@@ -171,12 +198,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
         const __nv_bfloat16* wk = a.Wt + (long long)k * a.w_client_stride;
         if (a.resident && group != cur_group) {
           cur_group = group;
-          mbar_wait(&b_empty[0], (uint32_t)(wloads & 1) ^ 1u);
-          mbar_arrive_expect_tx(&b_full[0], a.wbytes);
+          if (lane == 0) {
+            mbar_wait(&b_empty[0], (uint32_t)(wloads & 1) ^ 1u);
+            mbar_arrive_expect_tx(&b_full[0], a.wbytes);
+          }
+          __syncwarp();
           if (nnb == 1) {
-            bulk_g2s(smB, wk, a.wbytes, &b_full[0]);            // [tap][plane][Cout][8] is contiguous
+            if (lane == 0) bulk_g2s(smB, wk, a.wbytes, &b_full[0]);            // [tap][plane][Cout][8] is contiguous
           } else {
-            for (int tp = 0; tp < a.taps * planes; ++tp)
+            for (int tp = lane; tp < a.taps * planes; tp += 32)
               bulk_g2s(smB + (size_t)tp * pitchB, wk + ((long long)tp * a.Cout + (long long)nb * a.NB) * 8, pitchB,
                        &b_full[0]);
           }
@@ -186,29 +216,34 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = pa.stage(a.SA);
           DBG_T0();
-          mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
+          if (lane == 0) {
+            mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
+            mbar_arrive_expect_tx(&a_full[sa], bytesA);
+          }
+          __syncwarp();
           DBG_ADD(0);
-          mbar_arrive_expect_tx(&a_full[sa], bytesA);
-          for (int pp = 0; pp < npar; ++pp)
-            for (int c = 0; c < kc; ++c) {
-              const __nv_bfloat16* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0 * 8;
-              bulk_g2s(smA + (size_t)sa * bytesA + (size_t)(pp * kc + c) * pitchA, src, pitchA, &a_full[sa]);
-            }
-          ++pa.it;
+          for (int i = lane; i < npar * kc; i += 32) {
+            const int pp = i / kc, c = i - pp * kc;
+            const __nv_bfloat16* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0 * 8;
+            bulk_g2s(smA + (size_t)sa * bytesA + (size_t)i * pitchA, src, pitchA, &a_full[sa]);
+          }
+          pa.advance(a.SA);
           if (a.resident) continue;
           for (int tap = 0; tap < a.taps; ++tap) {
             const int sb = pb.stage(a.SB);
-            mbar_wait(&b_empty[sb], pb.phase(a.SB) ^ 1u);
-            mbar_arrive_expect_tx(&b_full[sb], bytesB);
+            if (lane == 0) {
+              mbar_wait(&b_empty[sb], pb.phase(a.SB) ^ 1u);
+              mbar_arrive_expect_tx(&b_full[sb], bytesB);
+            }
+            __syncwarp();
             const __nv_bfloat16* wsrc = wk + (((long long)tap * planes + kb * kc) * a.Cout + (long long)nb * a.NB) * 8;
             if (nnb == 1) {
-              bulk_g2s(smB + (size_t)sb * bytesB, wsrc, bytesB, &b_full[sb]);   // kc planes are contiguous
-            } else {
-              for (int c = 0; c < kc; ++c)
-                bulk_g2s(smB + (size_t)sb * bytesB + (size_t)c * pitchB, wsrc + (long long)c * a.Cout * 8, pitchB,
-                         &b_full[sb]);
+              if (lane == 0) bulk_g2s(smB + (size_t)sb * bytesB, wsrc, bytesB, &b_full[sb]);   // kc planes contiguous
+            } else if (lane < kc) {
+              bulk_g2s(smB + (size_t)sb * bytesB + (size_t)lane * pitchB, wsrc + (long long)lane * a.Cout * 8, pitchB,
+                       &b_full[sb]);
             }
-            ++pb.it;
+            pb.advance(a.SB);
           }
         }
       }
@@ -220,6 +255,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       int cur_group = -1, wuses = 0;
       const uint32_t idesc = umma_idesc_bf16(kTileM, a.NB, 0, 0);
       const uint32_t kstepA = (2u * pitchA) >> 4, kstepB = (2u * pitchB) >> 4;
+      const uint64_t dBres = umma_desc_noswz(smem_u32(smB), pitchB, 128);      // + stage / tap offset in 16-byte units
       for (int item = item_lo; item < item_hi; ++item) {
         const int group = item / a.num_pass;
         if (a.resident && group != cur_group) {
@@ -246,28 +282,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             uint64_t dB0;
             int sb = 0;
             if (a.resident) {
-              dB0 = umma_desc_noswz(smem_u32(smB + (size_t)(tap * planes + kb * kc) * pitchB), pitchB, 128);
+              dB0 = dBres + (uint64_t)((uint32_t)(tap * planes + kb * kc) * (pitchB >> 4));
             } else {
               sb = pb.stage(a.SB);
               mbar_wait(&b_full[sb], pb.phase(a.SB));
               tc_fence_after();
-              dB0 = umma_desc_noswz(smem_u32(smB + (size_t)sb * bytesB), pitchB, 128);
+              dB0 = dBres + (uint64_t)((uint32_t)sb * (bytesB >> 4));
             }
-            int shift = 0;
-            if (a.taps > 1) {
-              const int th = tap / a.ksz;
-              shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
-            }
-            if (npar == 4) {
-              const int dh = tap / 3, dw = tap - dh * 3;
-              shift = (dh == 0 ? -a.Wp : 0) + (dw == 0 ? -1 : 0)
-                      + (int)((uint32_t)((dh != 1) * 2 + (dw != 1)) * (uint32_t)kc * (pitchA >> 4));
-            }
-            if (a.dbg_shift == 1) shift = 0;
-            if (a.dbg_shift == 2) shift = (tap / 3 - 1) * 24 + (tap % 3 - 1) * 8;
             const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
             uint32_t d_tmem = tmem_base + (uint32_t)(as * accCols);
-            uint64_t da = dA0 + (uint64_t)(int64_t)shift;       // halo + shift >= 0: no borrow out of the field
+            uint64_t da = dA0 + (uint64_t)(int64_t)tap_shift[tap];    // halo + shift >= 0: no borrow out of the field
             for (int t = 0; t < a.T; ++t, d_tmem += (uint32_t)a.NB, da += (uint64_t)kTileM) {
               umma_f16(d_tmem, da, dB0, idesc, first);
               if (KC2 >= 2) umma_f16(d_tmem, da + kstepA, dB0 + kstepB, idesc, 1u);
@@ -278,15 +302,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             }
             if (!a.resident) {
               umma_commit(&b_empty[sb]);
-              ++pb.it;
+              pb.advance(a.SB);
             }
           }
           umma_commit(&a_empty[sa]);
-          ++pa.it;
+          pa.advance(a.SA);
           DBG_ADD(2);
         }
         umma_commit(&acc_full[as]);
-        ++pacc.it;
+        pacc.advance(a.NS);
         if (a.resident && (item + 1 == item_hi || (item + 1) / a.num_pass != group)) umma_commit(&b_empty[0]);
       }
     }
@@ -434,7 +458,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);
-      ++pacc.it;
+      pacc.advance(a.NS);
       DBG_ADD(1);
     }
   }
@@ -544,7 +568,7 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
     a.T = T; a.NB = NB;
     a.rowsA = T * kTileM + (npar == 4 ? 1 : 2) * a.halo;      // parity-plane taps only reach up / left
     const size_t bytesA = (size_t)npar * kc * a.rowsA * 16, bytesB = (size_t)kc * NB * 16;
-    const size_t misc = 1024 + 2 * NB * sizeof(float);
+    const size_t misc = 1024 + 2 * NB * sizeof(float) + 128;
     a.NS = (2 * T * NB <= 512) ? 2 : 1;
     a.wbytes = (unsigned int)((size_t)a.taps * Cin * NB * 2);
     a.resident = a.wbytes <= 100 * 1024 && 2 * bytesA + a.wbytes + misc <= budget;
@@ -553,8 +577,12 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
       a.SB = 1;
       breg = a.wbytes;
     } else {
-      a.SB = 4;
-      if (2 * bytesA + a.SB * bytesB + misc > budget) a.SB = 2;
+      // Streamed weights: as many stages as fit (<= kMaxSB).  A CTA that owns few row tiles is bound by the latency of
+      // its own weight stream (K = 1, 256 channels: 295 KB per CTA at 32 KB in flight = 11 B/clk); deeper is faster.
+      static const int sb_cap = getenv("DBA_CONV_SB") ? atoi(getenv("DBA_CONV_SB")) : kMaxSB;
+      long long sb = budget > 2 * bytesA + misc ? (long long)((budget - 2 * bytesA - misc) / bytesB) : 0;
+      a.SB = sb > sb_cap ? sb_cap : (int)sb;
+      if (a.SB < 2) a.SB = 2;
       breg = a.SB * bytesB;
     }
     // Two A stages.  Measured on B200: a third / fourth stage does not help even the bandwidth-hungry

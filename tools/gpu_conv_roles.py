@@ -10,7 +10,10 @@ layers = [(32, 32, 32, 32, 3, 1), (32, 32, 32, 64, 3, 2), (16, 16, 64, 64, 3, 1)
 if len(sys.argv) > 1 and sys.argv[1] == "nprobe":      # per-MMA cost vs N
     layers = [(32, 32, 32, 32, 3, 1), (32, 32, 32, 64, 3, 1), (32, 32, 32, 96, 3, 1), (32, 32, 32, 128, 3, 1),
               (16, 16, 64, 64, 3, 1), (16, 16, 64, 192, 3, 1)]
-for (K, B, shared, stats) in [(10, 64, False, True), (10, 500, True, False)]:
+cases = [(10, 64, False, True), (10, 500, True, False)]
+if len(sys.argv) > 1 and sys.argv[1] == "k1":
+    cases = [(1, 64, False, True), (2, 64, False, True)]
+for (K, B, shared, stats) in cases:
     for (H, W, Cin, Cout, ks, sub) in layers:
         x = layout.to_planar(torch.randn(1 if shared else K, B, Cin, H, W, device=d))
         wt = layout.pack_conv_weight(torch.randn(K, Cout, Cin, ks, ks, device=d) * 0.05)
