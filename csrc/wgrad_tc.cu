@@ -64,6 +64,16 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   uint64_t* acc_full = empty + a.stages;
   uint64_t* acc_empty = acc_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
+  int* tap_shift = reinterpret_cast<int*>(tmem_slot + 4);    // [taps] row shift of every tap, computed once
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + a.taps) {
+    const int tap = threadIdx.x - 64;
+    int shift = 0;
+    if (a.taps > 1) {
+      const int th = tap / a.ksz;
+      shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
+    }
+    tap_shift[tap] = shift;
+  }
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -84,36 +94,42 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   // real planes of dY available for this M block (the rest of the 16 planes stays unloaded: rows >= Cout of D are
   // never read back)
   if (warp == 0) {
-    if (elect_one()) {
-      int it = 0;
-      for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        const int sp = item % a.nsplit;
-        const int nbk = (item / a.nsplit) % a.nnblk;
-        const int mb = (item / (a.nsplit * a.nnblk * a.ngroups)) % a.nmb;
-        const int k = item / (a.nsplit * a.nnblk * a.ngroups * a.nmb);
-        const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
-        const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
-        const int mreal = min(16, (a.Cout >> 3) - mb * 16);
-        for (int ch = c0; ch < c1; ++ch, ++it) {
-          const int s = it % a.stages;
-          mbar_wait(&empty[s], ((it / a.stages) & 1) ^ 1u);
-          mbar_arrive_expect_tx(&full[s], (uint32_t)mreal * pitchA + bytesB);
-          const long long row = (long long)a.lead + (long long)ch * kRowsK;
-          for (int p = 0; p < mreal; ++p)
-            bulk_g2s(smA + (size_t)s * bytesA + (size_t)p * pitchA,
-                     a.dY + (long long)k * a.dy_client + (long long)(mb * 16 + p) * a.dy_plane + row * 8, pitchA,
-                     &full[s]);
-          for (int p = 0; p < nplanes; ++p)
-            bulk_g2s(smB + (size_t)s * bytesB + (size_t)p * pitchB,
-                     a.X + (long long)k * a.x_client + (long long)(nbk * nplanes + p) * a.x_plane + (row - a.halo) * 8,
-                     pitchB, &full[s]);
+    // whole warp: lane 0 waits for the free stage and posts the byte count, all lanes issue the plane copies
+    int st = 0;
+    uint32_t ph = 0;
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+      const int sp = item % a.nsplit;
+      const int nbk = (item / a.nsplit) % a.nnblk;
+      const int mb = (item / (a.nsplit * a.nnblk * a.ngroups)) % a.nmb;
+      const int k = item / (a.nsplit * a.nnblk * a.ngroups * a.nmb);
+      const int c0 = (int)((long long)a.body_chunks * sp / a.nsplit);
+      const int c1 = (int)((long long)a.body_chunks * (sp + 1) / a.nsplit);
+      const int mreal = min(16, (a.Cout >> 3) - mb * 16);
+      const __nv_bfloat16* dyk = a.dY + (long long)k * a.dy_client + (long long)(mb * 16) * a.dy_plane;
+      const __nv_bfloat16* xk = a.X + (long long)k * a.x_client + (long long)(nbk * nplanes) * a.x_plane;
+      for (int ch = c0; ch < c1; ++ch) {
+        if (lane == 0) {
+          mbar_wait(&empty[st], ph ^ 1u);
+          mbar_arrive_expect_tx(&full[st], (uint32_t)mreal * pitchA + bytesB);
         }
+        __syncwarp();
+        const long long row = (long long)a.lead + (long long)ch * kRowsK;
+        for (int p = lane; p < mreal + nplanes; p += 32) {
+          if (p < mreal)
+            bulk_g2s(smA + (size_t)st * bytesA + (size_t)p * pitchA, dyk + (long long)p * a.dy_plane + row * 8, pitchA,
+                     &full[st]);
+          else
+            bulk_g2s(smB + (size_t)st * bytesB + (size_t)(p - mreal) * pitchB,
+                     xk + (long long)(p - mreal) * a.x_plane + (row - a.halo) * 8, pitchB, &full[st]);
+        }
+        if (++st == a.stages) { st = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(128, a.N, 1, 1);       // both operands MN-major
-      int it = 0, acc_it = 0;
+      int st = 0, acc_it = 0;
+      uint32_t ph = 0;
       for (int item = blockIdx.x; item < items; item += gridDim.x, ++acc_it) {
         const int sp = item % a.nsplit;
         const int grp = (item / (a.nsplit * a.nnblk)) % a.ngroups;
@@ -122,20 +138,17 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
         const int t0 = grp * a.tpg, t1 = min(a.taps, t0 + a.tpg);
         mbar_wait(acc_empty, (acc_it & 1) ^ 1u);
         tc_fence_after();
-        for (int ch = c0; ch < c1; ++ch, ++it) {
-          const int s = it % a.stages;
-          mbar_wait(&full[s], (it / a.stages) & 1);
+        for (int ch = c0; ch < c1; ++ch) {
+          const int s = st;
+          mbar_wait(&full[s], ph);
+          if (++st == a.stages) { st = 0; ph ^= 1u; }
           tc_fence_after();
           // base descriptors once per stage; per MMA only the 14-bit start-address field moves (16-byte units)
           const uint64_t dA0 = umma_desc_noswz(smem_u32(smA + (size_t)s * bytesA), 128, pitchA);
           const uint64_t dB0 = umma_desc_noswz(smem_u32(smB + (size_t)s * bytesB), 128, pitchB) + (uint64_t)a.halo;
           const uint32_t acc0 = ch != c0 ? 1u : 0u;
           for (int tap = t0; tap < t1; ++tap) {
-            int shift = 0;
-            if (a.taps > 1) {
-              const int th = tap / a.ksz;
-              shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
-            }
+            const int shift = tap_shift[tap];
             const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.N);
             const uint64_t dB1 = dB0 + (uint64_t)(int64_t)shift;
             umma_f16(d_tmem, dA0, dB1, idesc, acc0);
