@@ -21,6 +21,18 @@ class LockStepTrainer:
     _STEP_COST = (1.23, 0.285)
     _CUT_COST = 0.25
 
+    # Slab widths: every distinct width owns a full set of activation buffers and a captured graph, so segments run on
+    # the next width of a geometric ladder (at most ~33 % idle rows) instead of on their exact client count; with 80
+    # clients per round that is 13 slab sets instead of up to 80.
+    _LADDER = (1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512)
+
+    @classmethod
+    def _width(cls, k: int, K: int) -> int:
+        for w in cls._LADDER:
+            if w >= k:
+                return min(w, K)
+        return K
+
     @classmethod
     def _segments(cls, steps: List[int], max_cuts: int = 4) -> List[tuple]:
         """Split the lock-step schedule into [(rows, lo, hi)] so that clients that finished stop being computed.
@@ -48,7 +60,7 @@ class LockStepTrainer:
         for c in range(max_cuts + 1):
             best[n - 1][c] = 0.0
         for j in range(n - 2, -1, -1):
-            k = len(active(pts[j]))
+            k = cls._width(len(active(pts[j])), K)
             for c in range(max_cuts + 1):
                 for m in range(j + 1, n):
                     if m < n - 1 and c == 0:
@@ -97,21 +109,27 @@ class LockStepTrainer:
         segs = self._segments(steps) if bool(p.get("compact_tail", True)) else [(list(range(K)), 0, sch.T)]
         carry = ("V", "gs", "anchor") if use_dist else ("V", "gs")
         for rows, lo, hi in segs:
-            if len(rows) == K:
+            if self._width(len(rows), K) == K:       # (nearly) everybody still active: stay on the home slab
                 self._run_steps(K, t, per_step, None, lo, hi, flags)
                 continue
             r = torch.tensor(rows, dtype=torch.long, device=dev)
-            t2 = self._tbufs(len(rows))
+            n = len(rows)
+            w = self._width(n, K)
+            t2 = self._tbufs(w)
             for key in carry + ("W", "cnt", "trig_row", "poison_n"):
-                t2[key].copy_(t[key][r])
+                t2[key][:n].copy_(t[key][r])
             for key in ("mf", "mi", "nan", "mf_dist"):
                 t2[key].zero_()
-            self._run_steps(len(rows), t2, per_step, r, lo, hi, flags)
+            if w > n:           # spare rows of the slab: idle clients (no samples, no update)
+                t2["st_idx"][n:].fill_(-1)
+                for key in ("st_nvalid", "st_active", "st_lr", "poison_n"):
+                    t2[key][n:].zero_()
+            self._run_steps(w, t2, per_step, r, lo, hi, flags)
             for key in ("V", "gs", "W", "cnt"):
-                t[key][r] = t2[key]
+                t[key][r] = t2[key][:n]
             for key in ("mf", "mi", "mf_dist"):
-                t[key][r] += t2[key]
-            t["nan"][r] |= t2["nan"]
+                t[key][r] += t2[key][:n]
+            t["nan"][r] |= t2["nan"][:n]
         W[:, :Df].copy_(t["W"][:, :Df])
         if cnt.numel():
             cnt.copy_(t["cnt"])
@@ -132,14 +150,15 @@ class LockStepTrainer:
         def pick(x, step):
             return x[:, step] if rows is None else x[rows, step]
 
+        n = K if rows is None else int(rows.numel())
         for step in range(lo, hi):
-            t["st_idx"].copy_(pick(per_step["idx"], step))
-            t["st_nvalid"].copy_(pick(per_step["nvalid"], step))
-            t["st_active"].copy_(pick(per_step["active"], step))
-            t["st_slot"].copy_(pick(per_step["slot"], step))
-            t["st_lr"].copy_(pick(per_step["lr"], step))
+            t["st_idx"][:n].copy_(pick(per_step["idx"], step))
+            t["st_nvalid"][:n].copy_(pick(per_step["nvalid"], step))
+            t["st_active"][:n].copy_(pick(per_step["active"], step))
+            t["st_slot"][:n].copy_(pick(per_step["slot"], step))
+            t["st_lr"][:n].copy_(pick(per_step["lr"], step))
             if with_flip:
-                t["st_flip"].copy_(pick(per_step["flip"], step))
+                t["st_flip"][:n].copy_(pick(per_step["flip"], step))
             self._replay(K, t, flags, use_graph)
 
     def _replay(self, K: int, t: dict, flags: tuple, use_graph: bool = True) -> None:
@@ -173,7 +192,9 @@ class LockStepTrainer:
         p = self.params
         with_flip = bool(getattr(self.data, "train_flip", False))
         dists = [False] + ([True] if (p["is_poison"] and float(p["alpha_loss"]) != 1.0) else [])
-        for K in range(1, Kmax + 1):
+        if Kmax > 16:            # many clients per GPU: slabs are created on first use instead
+            return
+        for K in sorted({self._width(k, Kmax) for k in range(1, Kmax + 1)} | {Kmax, max(Kmax - 1, 1)}):
             t = self._tbufs(K)
             t["st_idx"].fill_(-1); t["st_nvalid"].zero_(); t["st_active"].zero_(); t["st_lr"].zero_()
             for use_dist in dists:
