@@ -71,6 +71,8 @@ class NativeResNet(LockStepTrainer):
         self.mu, self.wd = float(params["momentum"]), float(params["decay"])
         self.eval_chunk = int(params.get("native_eval_chunk", 500))
         self.use_s2d = bool(params.get("native_s2d", True))
+        self.overlap_wgrad = bool(params.get("overlap_wgrad", True)) and device.type == "cuda"
+        self._side = torch.cuda.Stream(device=device) if self.overlap_wgrad else None
         self._eval_bufs: Dict[Tuple[int, int], dict] = {}
         d = data
         self.trig_u8 = d.trigger_masks.to(torch.uint8).contiguous()
@@ -429,8 +431,17 @@ class NativeResNet(LockStepTrainer):
             cin, cin_real, ks, H = l.cin_p, l.ks * l.ks * l.cin, 1, l.H
         else:
             cin, cin_real, ks, H = l.cin_p, l.cin, l.ks, l.H
-        native.check(self.lib.dba_wgrad_tc(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0), e.offset, K,
-                                           self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks, native.stream()))
+        if not self.overlap_wgrad:
+            native.check(self.lib.dba_wgrad_tc(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0), e.offset, K,
+                                               self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks, native.stream()))
+            return
+        # weight gradients are off the critical path (only the optimiser step needs them): they run on a side stream
+        # (a parallel branch of the captured graph) next to the input-gradient / BatchNorm-backward chain
+        main = torch.cuda.current_stream()
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            native.check(self.lib.dba_wgrad_tc(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0), e.offset, K,
+                                               self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks, native.stream()))
 
     def _dgrad(self, l: ConvL, K, dy, pack, out, res=None):
         wt = self._wt(pack, l, transposed=True)
@@ -537,6 +548,8 @@ class NativeResNet(LockStepTrainer):
                                            native.ptr(t["poison_n"]), native.ptr(active), native.ptr(slot),
                                            native.ptr(t["mf_dist"]), t["mf_dist"].shape[1],
                                            float(self.params["alpha_loss"]), K, Dp, native.stream()))
+        if self.overlap_wgrad:
+            torch.cuda.current_stream().wait_stream(self._side)
         # ---------------------------------------------------------------------- optimiser
         flat.sgd_step_(W, V, Gr, t["st_lr"], active, Dp, self.mu, self.wd, t["gs"] if want_grad_sum else None)
         if t["cnt"].numel():

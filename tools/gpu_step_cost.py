@@ -11,7 +11,8 @@ from dba_mod_b200.models import initial_state
 KIND = sys.argv[1] if len(sys.argv) > 1 else "cifar"
 raw = yaml.safe_load(open(f"utils/{KIND}_params.yaml"))
 raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=12800, synthetic_test_size=100,
-           sampling_dirichlet=False, number_of_total_participants=20, internal_epochs=2, compact_tail=False)
+           sampling_dirichlet=False, number_of_total_participants=20, internal_epochs=2, compact_tail=False,
+           overlap_wgrad=os.environ.get("DBA_OVERLAP", "1") == "1")
 p = Params(raw)
 dev = torch.device("cuda", 0)
 data = ImageData(p, dev)
