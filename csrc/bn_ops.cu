@@ -23,13 +23,15 @@ struct BnArgs {
   const __nv_bfloat16* g;      // bwd: upstream gradient
   const __nv_bfloat16* act;    // bwd: post-ReLU output of this BN (mask) or null
   __nv_bfloat16* gmask;        // bwd: optional copy of g' (same geometry as g)
+  __nv_bfloat16* out2;         // fwd: optional second copy of the activation in space-to-depth form (4C channels on the
+                               // (H/2, W/2) grid, R2 rows per plane) for the next stage's stride-2 convolutions
   float* stats;                // fwd: [K][ld_stats] (sum, sumsq) pairs;  bwd: (sum g', sum g'*xhat) pairs
   float* saved;                // [K][ld_saved] (mean, rstd) pairs
   float* Wflat;                // [K][ldw] state rows (gamma, beta, running stats)
   float* Gflat;                // [K][ldg] gradient rows (bwd) or null
   const int* nvalid;           // [K]
   const unsigned char* active; // [K] or null
-  long long ld_stats, ld_saved, ldw, ldg, R, Rup;
+  long long ld_stats, ld_saved, ldw, ldg, R, Rup, R2;
   int stats_off, saved_off, g_off, b_off, rm_off, rv_off;
   int K, C, B, H, W, relu, up;
   float momentum, eps;
@@ -101,7 +103,13 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = 0.f;
     }
-    *reinterpret_cast<uint4*>(a.out + off) = pack8(o);
+    const uint4 pk = pack8(o);
+    *reinterpret_cast<uint4*>(a.out + off) = pk;
+    if (a.out2) {
+      const int W2p = (a.W >> 1) + 1, S2 = ((a.H >> 1) + 1) * W2p, lead2 = W2p + 1;
+      const long long plane2 = ((long long)k * 4 + (((h & 1) << 1) | (w & 1))) * (a.C >> 3) + chunk;
+      *reinterpret_cast<uint4*>(a.out2 + (plane2 * a.R2 + lead2 + (long long)b * S2 + (h >> 1) * W2p + (w >> 1)) * 8) = pk;
+    }
   }
 }
 
@@ -316,12 +324,29 @@ extern "C" {
 
 // out = relu?( (y - mean)*rstd*gamma + beta (+ res) ); also saves (mean, rstd) and updates the running statistics.
 // stats: pairs (sum, sumsq) at stats[k*ld_stats + stats_off + 2c]; saved likewise.  Offsets g/b/rm/rv index Wflat rows.
+int dba_bn_apply_ex(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, float* stats,
+                    long long ld_stats, int stats_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
+                    long long ldw, int g_off, int b_off, int rm_off, int rv_off, const int* nvalid,
+                    const unsigned char* active, int K, int C, int B, int H, int W, long long R, int relu,
+                    float momentum, float eps, void* stream);
 int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long long ld_stats, int stats_off,
                  float* saved, long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off,
                  int rm_off, int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H,
                  int W, long long R, int relu, float momentum, float eps, void* stream) {
+  return dba_bn_apply_ex(y, res, out, nullptr, 0, stats, ld_stats, stats_off, saved, ld_saved, saved_off, Wflat, ldw,
+                         g_off, b_off, rm_off, rv_off, nvalid, active, K, C, B, H, W, R, relu, momentum, eps, stream);
+}
+// out_s2d (nullable): the activation is ALSO written in space-to-depth form ([K][4C/8][R_s2d][8] on the (H/2, W/2)
+// grid, parity plane p = 2*(h&1) + (w&1)), the operand form of the next stage's stride-2 convolutions.
+int dba_bn_apply_ex(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, float* stats,
+                    long long ld_stats, int stats_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
+                    long long ldw, int g_off, int b_off, int rm_off, int rv_off, const int* nvalid,
+                    const unsigned char* active, int K, int C, int B, int H, int W, long long R, int relu,
+                    float momentum, float eps, void* stream) {
   DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_bn_apply: K=%d C=%d B=%d", K, C, B);
+  DBA_REQUIRE(!out_s2d || (H % 2 == 0 && W % 2 == 0), "dba_bn_apply: space-to-depth output needs even H, W");
   BnArgs a{};
+  a.out2 = (__nv_bfloat16*)out_s2d; a.R2 = R_s2d;
   a.y = (const __nv_bfloat16*)y; a.res = (const __nv_bfloat16*)res; a.out = (__nv_bfloat16*)out;
   a.stats = stats; a.saved = saved; a.Wflat = Wflat; a.nvalid = nvalid; a.active = active;
   a.ld_stats = ld_stats; a.ld_saved = ld_saved; a.ldw = ldw; a.R = R;

@@ -371,6 +371,9 @@ class NativeResNet(LockStepTrainer):
         # gradient scratch per resolution level: g (block output grad), dz, da1, dx
         for w, r in zip(self.widths, self.ress):
             t[("g", r)] = [z(w, r) for _ in range(4)]
+        for bi, (c1, _, _) in enumerate(self.blocks):      # forward operands of the stride-2 layers (output pixels only)
+            if self._s2d_block(bi):
+                t[("s2d", bi)] = z(4 * c1.cin_p, c1.H // 2)
         if self.pool:
             t["pool_out"] = z(self.widths[0], self.ress[0])
             t["pool_g"] = z(self.widths[0], stem.H)
@@ -403,11 +406,12 @@ class NativeResNet(LockStepTrainer):
         self._train_bufs[K] = t
         return t
 
-    def _bn_apply(self, l: ConvL, K, y, out, res, relu, W, t, nvalid, active):
+    def _bn_apply(self, l: ConvL, K, y, out, res, relu, W, t, nvalid, active, out_s2d=None):
         e = self.spec.entries
         r = l.H // l.sub
-        native.check(self.lib.dba_bn_apply(
-            native.ptr(y), native.ptr(res), native.ptr(out), native.ptr(t["stats"]), t["stats"].stride(0),
+        native.check(self.lib.dba_bn_apply_ex(
+            native.ptr(y), native.ptr(res), native.ptr(out), native.ptr(out_s2d),
+            out_s2d.shape[2] if out_s2d is not None else 0, native.ptr(t["stats"]), t["stats"].stride(0),
             2 * l.bn_off, native.ptr(t["saved"]), t["saved"].stride(0), 2 * l.bn_off, native.ptr(W), W.stride(0),
             e[l.bn + ".weight"].offset, e[l.bn + ".bias"].offset, e[l.bn + ".running_mean"].offset,
             e[l.bn + ".running_var"].offset, native.ptr(nvalid), native.ptr(active), K, l.cout_p, self.B, r, r,
@@ -483,21 +487,29 @@ class NativeResNet(LockStepTrainer):
             native.check(lib.dba_maxpool_fwd(native.ptr(a0), native.ptr(x), K, self.widths[0], B, stem.H, stem.H,
                                              a0.shape[2], x.shape[2], native.stream()))
         inputs = []
-        for (c1, c2, sc) in self.blocks:
+        x_s2d = None           # space-to-depth copy of x when the block about to run opens with stride-2 convolutions
+        for bi, (c1, c2, sc) in enumerate(self.blocks):
             inputs.append(x)
             y1, a1 = t[("y", c1.name)], t[("a", c1.name)]
-            fconv(c1, x, y1)
+            if x_s2d is not None:
+                self._conv(x_s2d, pack, c1, K, B, y1, stats=st[:, 2 * c1.bn_off:], in_s2d=True)
+            else:
+                fconv(c1, x, y1)
             self._bn_apply(c1, K, y1, a1, None, True, W, t, nvalid, active)
             y2, out = t[("y", c2.name)], t[("a", c2.name)]
             fconv(c2, a1, y2)
             skip = x
             if sc is not None:
                 ys, as_ = t[("y", sc.name)], t[("a", sc.name)]
-                fconv(sc, x, ys)
+                if x_s2d is not None:
+                    self._conv(x_s2d, pack, sc, K, B, ys, stats=st[:, 2 * sc.bn_off:], in_s2d=True)
+                else:
+                    fconv(sc, x, ys)
                 self._bn_apply(sc, K, ys, as_, None, False, W, t, nvalid, active)
                 skip = as_
-            self._bn_apply(c2, K, y2, out, skip, True, W, t, nvalid, active)
-            x = out
+            nxt = t.get(("s2d", bi + 1))
+            self._bn_apply(c2, K, y2, out, skip, True, W, t, nvalid, active, out_s2d=nxt)
+            x, x_s2d = out, nxt
         # ---------------------------------------------------------------------- head (fwd + bwd)
         g = lv_g[self.head_H][0]
         native.check(lib.dba_head(native.ptr(x), native.ptr(W), W.stride(0), self.head_w_off, self.head_b_off,

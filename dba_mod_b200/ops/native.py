@@ -77,6 +77,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_head", [P, P, L, I, I, P, L, P, P, I, P, P, P, P, I, P, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_head_ex", [P, P, L, I, I, P, L, P, P, I, P, P, P, P, I, P, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_bn_apply", [P, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
+    _sig(lib, "dba_bn_apply_ex", [P, P, P, P, L, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
     _sig(lib, "dba_bn_backward", [P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
     _sig(lib, "dba_maxpool_fwd", [P, P, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_maxpool_bwd", [P, P, P, I, I, I, I, I, L, L, P])

@@ -151,6 +151,13 @@ int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long l
                  float* saved, long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off,
                  int rm_off, int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H,
                  int W, long long R, int relu, float momentum, float eps, void* stream);
+/* Same; out_s2d (nullable) receives a second copy of the activation in space-to-depth form for the next stage's
+ * stride-2 convolutions (see dba_conv_tc_ex). */
+int dba_bn_apply_ex(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, float* stats,
+                    long long ld_stats, int stats_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
+                    long long ldw, int g_off, int b_off, int rm_off, int rv_off, const int* nvalid,
+                    const unsigned char* active, int K, int C, int B, int H, int W, long long R, int relu,
+                    float momentum, float eps, void* stream);
 int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, void* gmask, float* sums,
                     long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
                     long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
