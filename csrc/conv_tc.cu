@@ -82,7 +82,9 @@ struct ConvArgs {
   int vlo, vhi;                // outputs are stored for vlo <= h, w < vhi only (a 'valid' convolution is the centre
                                // crop of the 'same' one: 5x5 pad 0 on 12x12 -> vlo = 2, vhi = 10)
   int in_s2d;
-  // Store Y (and only Y - Res stays in the plain layout) as the space-to-depth form of the (H, W) output.
+  // 1: store Y (and only Y - Res stays in the plain layout) as the space-to-depth form of the (H, W) output.
+  // 2: store Y - and read Res - at the even positions (2h, 2w) of the (2H, 2W) grid: the input gradient of a 1x1
+  //    stride-2 convolution computed on its own (half-resolution) grid and added in place into the full-grid gradient.
   int out_s2d;
   long long res_client_stride, res_plane_stride;
 };
@@ -364,6 +366,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           if (a.sub == 2) {
             st = st && !((h | w) & 1u);
             orow[i] = rrow[i] = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
+          } else if (a.out_s2d == 2) {
+            orow[i] = rrow[i] = (long long)a.leado + (long long)b * a.So + (2 * h) * a.Wpo + 2 * w;
           } else if (a.out_s2d) {
             rrow[i] = (long long)a.lead + qrow;
             orow[i] = (long long)(((h & 1u) << 1) | (w & 1u)) * (a.y_plane_stride >> 3) * (a.Cout >> 3)
@@ -515,23 +519,26 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   DBA_REQUIRE(scale == nullptr || shift != nullptr, "dba_conv_tc: scale needs shift (shift alone = bias epilogue)");
   DBA_REQUIRE(!(shift && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
   DBA_REQUIRE(!(in_s2d || out_s2d) || sub == 1, "dba_conv_tc: space-to-depth forms replace sub=2, pass sub=1");
-  DBA_REQUIRE(!out_s2d || (H % 2 == 0 && W % 2 == 0), "dba_conv_tc: out_s2d needs even H, W");
+  DBA_REQUIRE(out_s2d != 1 || (H % 2 == 0 && W % 2 == 0), "dba_conv_tc: out_s2d needs even H, W");
+  DBA_REQUIRE(out_s2d >= 0 && out_s2d <= 2, "dba_conv_tc: out mode %d", out_s2d);
   ConvArgs a{};
-  a.in_s2d = in_s2d ? 1 : 0; a.out_s2d = out_s2d ? 1 : 0;
+  a.in_s2d = in_s2d ? 1 : 0; a.out_s2d = out_s2d;
   a.X = (const __nv_bfloat16*)X; a.Wt = (const __nv_bfloat16*)Wt; a.Y = (__nv_bfloat16*)Y;
   a.Res = (const __nv_bfloat16*)Res; a.scale = scale; a.shift = shift; a.stats = stats;
   a.K = K; a.Cin = Cin; a.Cout = Cout; a.taps = ksize * ksize;
   a.H = H; a.W = W; a.Wp = W + 1; a.S = (H + 1) * a.Wp; a.lead = a.Wp + 1; a.B = B;
   a.relu = relu; a.sub = sub;
-  const int osub = out_s2d ? 2 : sub;
-  a.Ho = H / osub; a.Wo = W / osub; a.Wpo = a.Wo + 1; a.So = (a.Ho + 1) * a.Wpo; a.leado = a.Wpo + 1;
+  const int osub = out_s2d == 1 ? 2 : sub;
+  a.Ho = H / osub; a.Wo = W / osub;
+  if (out_s2d == 2) { a.Ho = 2 * H; a.Wo = 2 * W; }
+  a.Wpo = a.Wo + 1; a.So = (a.Ho + 1) * a.Wpo; a.leado = a.Wpo + 1;
   const long long R = dba_conv_rows(B, H, W), Ro = dba_conv_rows(B, a.Ho, a.Wo);
   a.x_plane_stride = R * 8;
   a.x_client_stride = x_shared ? 0 : (long long)(in_s2d ? 4 : 1) * (Cin / 8) * R * 8;
   a.y_plane_stride = Ro * 8;
-  a.y_client_stride = (long long)(out_s2d ? 4 : 1) * (Cout / 8) * Ro * 8;
-  a.res_plane_stride = out_s2d ? R * 8 : a.y_plane_stride;
-  a.res_client_stride = out_s2d ? (long long)(Cout / 8) * R * 8 : a.y_client_stride;
+  a.y_client_stride = (long long)(out_s2d == 1 ? 4 : 1) * (Cout / 8) * Ro * 8;
+  a.res_plane_stride = out_s2d == 1 ? R * 8 : a.y_plane_stride;
+  a.res_client_stride = out_s2d == 1 ? (long long)(Cout / 8) * R * 8 : a.y_client_stride;
   a.w_client_stride = w_client_stride;
   a.ss_stride = ss_stride;
   a.stats_stride = stats_stride;

@@ -233,7 +233,7 @@ extern "C" {
 // the caller once per step).  Cin / Cout are the padded channel counts of the planar buffers.
 static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
                         int Cin, int Cout, int cin_real, int cout_real, int ksize, int cgrp_pad, int cgrp_real,
-                        int npos, void* stream) {
+                        int npos, void* stream, long long x_client_stride = 0) {
   DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3 || ksize == 5), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
   DBA_REQUIRE(Cin % 16 == 0 && (Cin <= 256 || Cin % 256 == 0) && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d Cout=%d", Cin, Cout);
   WgArgs a{};
@@ -246,7 +246,7 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   body = (body + 511) / 512 * 512;
   const long long R = a.lead + body + a.Wp + 2;
   a.dy_plane = R * 8; a.dy_client = (long long)(Cout / 8) * R * 8;
-  a.x_plane = R * 8; a.x_client = (long long)(Cin / 8) * R * 8;
+  a.x_plane = R * 8; a.x_client = x_client_stride ? x_client_stride : (long long)(Cin / 8) * R * 8;
   a.body_chunks = (int)(((long long)B * S + kRowsK - 1) / kRowsK);
   a.nmb = (Cout + 127) / 128;
   a.N = Cin <= 256 ? Cin : 256;
@@ -284,6 +284,14 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
 int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
                  int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
   return wgrad_launch(dY, X, G, ldg, w_off, K, B, H, W, Cin, Cout, cin_real, cout_real, ksize, 0, 0, 0, stream);
+}
+
+// x_client_stride (elements): distance between the clients' X tensors when X is a channel slice of a wider tensor (the
+// parity-0 planes of a space-to-depth activation: weight gradient of a 1x1 stride-2 convolution on its output grid).
+int dba_wgrad_tc_ex(const void* dY, const void* X, long long x_client_stride, float* G, long long ldg, int w_off, int K,
+                    int B, int H, int W, int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
+  return wgrad_launch(dY, X, G, ldg, w_off, K, B, H, W, Cin, Cout, cin_real, cout_real, ksize, 0, 0, 0, stream,
+                      x_client_stride);
 }
 
 // Weight gradient of a linear layer applied to a flattened [c_real][npos] feature map (torch's x.view(-1, C*h*w)) that

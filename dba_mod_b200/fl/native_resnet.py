@@ -359,6 +359,7 @@ class NativeResNet(LockStepTrainer):
             return torch.zeros(K, c // 8, Geom(B, r, r).rows, 8, dtype=torch.bfloat16, device=dev)
 
         stem = self.layers[0]
+        s2d_sc = {sc.name for bi, (_, _, sc) in enumerate(self.blocks) if sc is not None and self._s2d_block(bi)}
         t = {"xin": z(stem.cin_p, stem.H), "labels": torch.zeros(K, B, dtype=torch.int32, device=dev)}
         for l in self.layers:
             ro = l.H // l.sub
@@ -366,6 +367,8 @@ class NativeResNet(LockStepTrainer):
             t[("a", l.name)] = z(l.cout_p, ro)
             if l.fold:
                 t[("dy", l.name)] = z(l.cout_p, ro)
+            elif l.ks == 1 and l.sub == 2 and l.name in s2d_sc:
+                t[("dy", l.name)] = z(l.cout_p, ro)           # shortcut of a space-to-depth block: stays compact
             else:
                 t[("dy", l.name)] = z(l.cout_p, l.H)          # on the input grid (zero-upsampled when sub == 2)
         # gradient scratch per resolution level: g (block output grad), dz, da1, dx
@@ -428,24 +431,31 @@ class NativeResNet(LockStepTrainer):
             e[l.bn + ".bias"].offset, native.ptr(nvalid), K, l.cout_p, self.B, r, r, y.shape[2], int(up),
             dy.shape[2], native.stream()))
 
-    def _wgrad(self, l: ConvL, K, dy, x, t):
+    def _wgrad(self, l: ConvL, K, dy, x, t, s2d=False):
         Gr = t["Gr"]
         e = self.spec.entries[l.name]
         if l.fold:
             cin, cin_real, ks, H = l.cin_p, l.ks * l.ks * l.cin, 1, l.H
         else:
             cin, cin_real, ks, H = l.cin_p, l.cin, l.ks, l.H
+        xcs = 0
+        if s2d:             # x is the space-to-depth tensor: its first cin/8 planes are the even-position pixels
+            H, xcs = l.H // 2, x.stride(0)
+
+        def launch():
+            native.check(self.lib.dba_wgrad_tc_ex(native.ptr(dy), native.ptr(x), xcs, native.ptr(Gr), Gr.stride(0),
+                                                  e.offset, K, self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks,
+                                                  native.stream()))
+
         if not self.overlap_wgrad:
-            native.check(self.lib.dba_wgrad_tc(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0), e.offset, K,
-                                               self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks, native.stream()))
+            launch()
             return
         # weight gradients are off the critical path (only the optimiser step needs them): they run on a side stream
         # (a parallel branch of the captured graph) next to the input-gradient / BatchNorm-backward chain
         main = torch.cuda.current_stream()
         self._side.wait_stream(main)
         with torch.cuda.stream(self._side):
-            native.check(self.lib.dba_wgrad_tc(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0), e.offset, K,
-                                               self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks, native.stream()))
+            launch()
 
     def _dgrad(self, l: ConvL, K, dy, pack, out, res=None):
         wt = self._wt(pack, l, transposed=True)
@@ -539,9 +549,22 @@ class NativeResNet(LockStepTrainer):
                 dx2 = pool_i[1]
                 self._dgrad(c1, K, dy1, pack, dx2)
                 dys = t[("dy", sc.name)]
-                self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
-                self._wgrad(sc, K, dys, xin_b, t)
-                self._dgrad(sc, K, dys, pack, dx, res=dx2)
+                xs = t.get(("s2d", bi))
+                if xs is not None:
+                    # 1x1 stride-2 shortcut on its own (half-resolution) grid: compact dys, weight gradient against the
+                    # parity-0 planes of the space-to-depth input, input gradient added in place at the even positions
+                    self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=False)
+                    self._wgrad(sc, K, dys, xs, t, s2d=True)
+                    wt = self._wt(pack, sc, transposed=True)
+                    ro = sc.H // 2
+                    native.check(self.lib.dba_conv_tc_ex(
+                        native.ptr(dys), native.ptr(wt), pack.stride(0), native.ptr(dx2), native.ptr(dx2), None, None, 0,
+                        None, 0, K, self.B, ro, ro, sc.cout_p, sc.cin_p, 1, 1, 0, 0, 0, 2, native.stream()))
+                    dx = dx2
+                else:
+                    self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
+                    self._wgrad(sc, K, dys, xin_b, t)
+                    self._dgrad(sc, K, dys, pack, dx, res=dx2)
             g = dx
         if self.pool:
             native.check(lib.dba_maxpool_bwd(native.ptr(a0), native.ptr(g), native.ptr(t["pool_g"]), K, self.widths[0], B,
