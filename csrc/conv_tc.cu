@@ -85,7 +85,11 @@ struct ConvArgs {
   // 1: store Y (and only Y - Res stays in the plain layout) as the space-to-depth form of the (H, W) output.
   // 2: store Y - and read Res - at the even positions (2h, 2w) of the (2H, 2W) grid: the input gradient of a 1x1
   //    stride-2 convolution computed on its own (half-resolution) grid and added in place into the full-grid gradient.
+  // 3: depth-to-space: the Cout = 4*C output channels are four parity groups; group p = 2*ph + pw of pixel (h, w) is
+  //    stored as the C channels of pixel (2h + ph, 2w + pw) of the plain (2H, 2W) tensor.  With 2x2 taps and the
+  //    re-packed weights of pack mode 3 this is the input gradient of a 3x3 stride-2 convolution from its compact dy.
   int out_s2d;
+  int cgrp;                    // out mode 3: channels per parity group (C)
   long long res_client_stride, res_plane_stride;
 };
 
@@ -155,6 +159,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       const int th = tap / a.ksz;
       shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
     }
+    if (a.ksz == 2) shift = (tap >> 1) * a.Wp + (tap & 1);        // 2x2 taps reaching down / right (out mode 3)
     if (npar == 4) {
       const int dh = tap / 3, dw = tap - dh * 3;
       shift = (dh == 0 ? -a.Wp : 0) + (dw == 0 ? -1 : 0)
@@ -350,11 +355,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       // which of this thread's rows (one per tile) are real output pixels, and where they go
       bool store[2];
       long long orow[2], rrow[2];                 // output row / residual row (differ only for out_s2d)
+      long long d2s_row[2];                       // out mode 3: row of pixel (2h, 2w) on the (2H, 2W) grid
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int t = t_first + i * t_step;
         store[i] = false;
-        orow[i] = rrow[i] = 0;
+        orow[i] = rrow[i] = d2s_row[i] = 0;
         if (t < a.T) {
           const unsigned int qrow = (unsigned int)(pass * a.T * kTileM + t * kTileM + q * 32 + lane);
           const unsigned int b = (unsigned int)(((unsigned long long)qrow * a.magicS) >> 40);
@@ -366,8 +372,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           if (a.sub == 2) {
             st = st && !((h | w) & 1u);
             orow[i] = rrow[i] = (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
-          } else if (a.out_s2d == 2) {
-            orow[i] = rrow[i] = (long long)a.leado + (long long)b * a.So + (2 * h) * a.Wpo + 2 * w;
+          } else if (a.out_s2d >= 2) {
+            orow[i] = rrow[i] = d2s_row[i] = (long long)a.leado + (long long)b * a.So + (2 * h) * a.Wpo + 2 * w;
           } else if (a.out_s2d) {
             rrow[i] = (long long)a.lead + qrow;
             orow[i] = (long long)(((h & 1u) << 1) | (w & 1u)) * (a.y_plane_stride >> 3) * (a.Cout >> 3)
@@ -415,7 +421,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             for (int j = 0; j < 32; ++j) sv[j] = fmaf(sv[j], u1[j], u2[j]);
           }
           if (!store[i]) continue;
-          const long long obase = (long long)((nb * a.NB + c0) >> 3) * a.y_plane_stride + orow[i] * 8;
+          long long obase = (long long)((nb * a.NB + c0) >> 3) * a.y_plane_stride + orow[i] * 8;
+          if (a.out_s2d == 3) {
+            const int cb = nb * a.NB + c0, par = cb / a.cgrp, cc = cb - par * a.cgrp;
+            obase = (long long)(cc >> 3) * a.y_plane_stride + (d2s_row[i] + (par >> 1) * a.Wpo + (par & 1)) * 8;
+          }
           if (rk) {
             uint4 r[4];
             const long long rbase = (long long)((nb * a.NB + c0) >> 3) * a.res_plane_stride + rrow[i] * 8;
@@ -513,14 +523,17 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
                    long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
                    int relu, int x_shared, int in_s2d, int out_s2d, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
-  DBA_REQUIRE(ksize == 1 || ksize == 3 || ksize == 5, "dba_conv_tc: ksize must be 1, 3 or 5, got %d", ksize);
+  DBA_REQUIRE(ksize == 1 || ksize == 3 || ksize == 5 || (ksize == 2 && out_s2d == 3),
+              "dba_conv_tc: ksize must be 1, 3 or 5 (2 with out mode 3), got %d", ksize);
   DBA_REQUIRE(Cin % 16 == 0 && Cout % 32 == 0, "dba_conv_tc: Cin (%d) %% 16 and Cout (%d) %% 32 must be 0", Cin, Cout);
   DBA_REQUIRE(sub == 1 || (sub == 2 && H % 2 == 0 && W % 2 == 0), "dba_conv_tc: sub=%d needs even H, W", sub);
   DBA_REQUIRE(scale == nullptr || shift != nullptr, "dba_conv_tc: scale needs shift (shift alone = bias epilogue)");
   DBA_REQUIRE(!(shift && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
   DBA_REQUIRE(!(in_s2d || out_s2d) || sub == 1, "dba_conv_tc: space-to-depth forms replace sub=2, pass sub=1");
   DBA_REQUIRE(out_s2d != 1 || (H % 2 == 0 && W % 2 == 0), "dba_conv_tc: out_s2d needs even H, W");
-  DBA_REQUIRE(out_s2d >= 0 && out_s2d <= 2, "dba_conv_tc: out mode %d", out_s2d);
+  DBA_REQUIRE(out_s2d >= 0 && out_s2d <= 3, "dba_conv_tc: out mode %d", out_s2d);
+  DBA_REQUIRE(out_s2d != 3 || (Cout % 4 == 0 && (Cout / 4) % 32 == 0 && Res == nullptr && stats == nullptr),
+              "dba_conv_tc: out mode 3 needs Cout = 4*C, C %% 32 == 0, no residual / statistics (Cout=%d)", Cout);
   ConvArgs a{};
   a.in_s2d = in_s2d ? 1 : 0; a.out_s2d = out_s2d;
   a.X = (const __nv_bfloat16*)X; a.Wt = (const __nv_bfloat16*)Wt; a.Y = (__nv_bfloat16*)Y;
@@ -530,13 +543,14 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   a.relu = relu; a.sub = sub;
   const int osub = out_s2d == 1 ? 2 : sub;
   a.Ho = H / osub; a.Wo = W / osub;
-  if (out_s2d == 2) { a.Ho = 2 * H; a.Wo = 2 * W; }
+  if (out_s2d >= 2) { a.Ho = 2 * H; a.Wo = 2 * W; }
+  a.cgrp = out_s2d == 3 ? Cout / 4 : Cout;
   a.Wpo = a.Wo + 1; a.So = (a.Ho + 1) * a.Wpo; a.leado = a.Wpo + 1;
   const long long R = dba_conv_rows(B, H, W), Ro = dba_conv_rows(B, a.Ho, a.Wo);
   a.x_plane_stride = R * 8;
   a.x_client_stride = x_shared ? 0 : (long long)(in_s2d ? 4 : 1) * (Cin / 8) * R * 8;
   a.y_plane_stride = Ro * 8;
-  a.y_client_stride = (long long)(out_s2d == 1 ? 4 : 1) * (Cout / 8) * Ro * 8;
+  a.y_client_stride = (long long)(out_s2d == 1 ? 4 : 1) * ((out_s2d == 3 ? Cout / 4 : Cout) / 8) * Ro * 8;
   a.res_plane_stride = out_s2d == 1 ? R * 8 : a.y_plane_stride;
   a.res_client_stride = out_s2d == 1 ? (long long)(Cout / 8) * R * 8 : a.y_client_stride;
   a.w_client_stride = w_client_stride;
@@ -545,7 +559,7 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   a.KB = Cin >= 64 ? 64 : Cin;
   if (in_s2d && ksize == 3 && a.KB > 32) a.KB = 32;      // four parity planes per k-block share the stage
   DBA_REQUIRE(Cin % a.KB == 0 && (a.KB == 16 || a.KB == 32 || a.KB == 64), "dba_conv_tc: unsupported Cin=%d", Cin);
-  a.halo = (ksize / 2) * (a.Wp + 1);
+  a.halo = ksize == 2 ? a.Wp + 1 : (ksize / 2) * (a.Wp + 1);
   a.ksz = ksize;
   a.vlo = g_conv_vlo; a.vhi = g_conv_vhi > 0 ? g_conv_vhi : (H > W ? H : W);
   const int kc = a.KB / 8;

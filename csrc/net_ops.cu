@@ -16,6 +16,9 @@ using namespace dba;
 // (stem); 2 = linear layer over a flattened [Cin][taps] feature map (torch's x.view(-1, C*h*w): source index
 // co*(Cin*taps) + ci*taps + tap), packed as a 1x1 convolution over channels n = tap*CinP + ci - forward
 // [1][taps*CinP/8][CoutP][8] (which IS the [taps][CinP/8][CoutP][8] layout), transposed [1][CoutP/8][taps*CinP][8].
+// 3 = 3x3 stride-2 convolution whose input gradient is computed in depth-to-space form (dba_conv_tc_ex out mode 3):
+// besides the forward pack, the transposed slot receives [4 taps (a,b)][CoutP/8][4*CinP][8] with
+// Wd[(a,b)][co][(2*ph+pw)*CinP + ci] = W[dh(ph,a)][dw(pw,b)][co][ci], dh(0,0) = 1, dh(1,0) = 2, dh(1,1) = 0, none for (0,1).
 #define PACK_FIELDS 9
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ W, long long ldw,
                                                            const int* __restrict__ table,
@@ -47,6 +50,29 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
     *reinterpret_cast<uint4*>(d + e[4] + (((long long)tap * (CinP >> 3) + c8) * CoutP + co) * 8) = pk;
   }
   if (e[5] < 0 || fold) return;
+  if (e[8] == 3) {
+    const long long nd = 4LL * (CoutP >> 3) * 4 * CinP;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nd; i += (long long)gridDim.x * blockDim.x) {
+      const int n = (int)(i % (4 * CinP));                 // output channel of the gradient conv: parity * CinP + ci
+      const int o8 = (int)((i / (4 * CinP)) % (CoutP >> 3));
+      const int t2 = (int)(i / ((long long)4 * CinP * (CoutP >> 3)));      // 2x2 tap (a, b)
+      const int par = n / CinP, ci = n - par * CinP;
+      const int ph = par >> 1, pw = par & 1, ta = t2 >> 1, tb = t2 & 1;
+      const int dh = ph == 0 ? (ta == 0 ? 1 : -1) : (ta == 0 ? 2 : 0);
+      const int dw = pw == 0 ? (tb == 0 ? 1 : -1) : (tb == 0 ? 2 : 0);
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int co = o8 * 8 + j;
+        v[j] = (dh >= 0 && dw >= 0 && co < Cout && ci < Cin) ? src[((long long)co * taps + dh * 3 + dw) * Cin + ci] : 0.f;
+      }
+      uint4 pk;
+      pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+      pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+      *reinterpret_cast<uint4*>(d + e[5] + (((long long)t2 * (CoutP >> 3) + o8) * (4 * CinP) + n) * 8) = pk;
+    }
+    return;
+  }
   // transposed pack for the input-gradient convolution: out channels become the reduction axis, taps are flipped
   const long long nt = (long long)taps * (CoutP >> 3) * CinP;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nt; i += (long long)gridDim.x * blockDim.x) {

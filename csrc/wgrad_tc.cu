@@ -41,6 +41,9 @@ struct WgArgs {
   // (taps*cin_real, cin_real, 1).  A linear layer over a flattened C x h x w map, run as a 1x1 convolution over
   // channels n = pos*cpad + c: ci -> (pos, c) with c < cgrp_real, destination (in_features, 1 per pos, npos per c).
   int cgrp_pad, cgrp_real, npos;
+  // s2d: X is the space-to-depth form (4*Cin channels, parity-major, on dY's grid) of a 3x3 stride-2 convolution's input;
+  // tap (dh, dw) reads parity plane (dh != 1, dw != 1) shifted by (dh == 0 ? -1 : 0, dw == 0 ? -1 : 0).
+  int s2d;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -56,7 +59,8 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   const uint32_t bytesA = mplanes * pitchA;
   const uint32_t rowsB = kRowsK + 2 * a.halo;
   const uint32_t pitchB = rowsB * 16u;
-  const uint32_t bytesB = nplanes * pitchB;
+  const int npar = a.s2d ? 4 : 1;
+  const uint32_t bytesB = (uint32_t)(npar * nplanes) * pitchB;
   uint8_t* smA = smem;
   uint8_t* smB = smA + (size_t)a.stages * bytesA;
   uint64_t* full = reinterpret_cast<uint64_t*>(smB + (size_t)a.stages * bytesB);
@@ -71,6 +75,11 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
     if (a.taps > 1) {
       const int th = tap / a.ksz;
       shift = (th - (a.ksz >> 1)) * a.Wp + (tap - th * a.ksz - (a.ksz >> 1));
+    }
+    if (a.s2d) {
+      const int dh = tap / 3, dw = tap - dh * 3;
+      shift = (dh == 0 ? -a.Wp : 0) + (dw == 0 ? -1 : 0)
+              + (int)((uint32_t)((dh != 1) * 2 + (dw != 1)) * (uint32_t)nplanes * (pitchB >> 4));
     }
     tap_shift[tap] = shift;
   }
@@ -114,13 +123,15 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
         }
         __syncwarp();
         const long long row = (long long)a.lead + (long long)ch * kRowsK;
-        for (int p = lane; p < mreal + nplanes; p += 32) {
-          if (p < mreal)
+        for (int p = lane; p < mreal + npar * nplanes; p += 32) {
+          if (p < mreal) {
             bulk_g2s(smA + (size_t)st * bytesA + (size_t)p * pitchA, dyk + (long long)p * a.dy_plane + row * 8, pitchA,
                      &full[st]);
-          else
-            bulk_g2s(smB + (size_t)st * bytesB + (size_t)(p - mreal) * pitchB,
-                     xk + (long long)(p - mreal) * a.x_plane + (row - a.halo) * 8, pitchB, &full[st]);
+          } else {
+            const int q = p - mreal, par = q / nplanes, j = q - par * nplanes;       // parity group, plane inside it
+            bulk_g2s(smB + (size_t)st * bytesB + (size_t)q * pitchB,
+                     xk + ((long long)par * (a.Cin >> 3) + j) * a.x_plane + (row - a.halo) * 8, pitchB, &full[st]);
+          }
         }
         if (++st == a.stages) { st = 0; ph ^= 1u; }
       }
@@ -233,23 +244,26 @@ extern "C" {
 // the caller once per step).  Cin / Cout are the padded channel counts of the planar buffers.
 static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
                         int Cin, int Cout, int cin_real, int cout_real, int ksize, int cgrp_pad, int cgrp_real,
-                        int npos, void* stream, long long x_client_stride = 0) {
+                        int npos, void* stream, long long x_client_stride = 0, int s2d = 0) {
   DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3 || ksize == 5), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
   DBA_REQUIRE(Cin % 16 == 0 && (Cin <= 256 || Cin % 256 == 0) && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d Cout=%d", Cin, Cout);
   WgArgs a{};
   a.dY = (const __nv_bfloat16*)dY; a.X = (const __nv_bfloat16*)X; a.G = G; a.ldg = ldg; a.w_off = w_off;
   a.K = K; a.Cout = Cout; a.Cin = Cin; a.cin_real = cin_real; a.cout_real = cout_real; a.taps = ksize * ksize;
   a.Wp = W + 1; a.lead = a.Wp + 1; a.halo = (ksize / 2) * (a.Wp + 1);
-  a.ksz = ksize; a.cgrp_pad = cgrp_pad; a.cgrp_real = cgrp_real; a.npos = npos;
+  a.ksz = ksize; a.cgrp_pad = cgrp_pad; a.cgrp_real = cgrp_real; a.npos = npos; a.s2d = s2d;
+  DBA_REQUIRE(!s2d || ksize == 3, "dba_wgrad_tc: the space-to-depth form is for 3x3 stride-2 convolutions");
   const long long S = (long long)(H + 1) * a.Wp;
   long long body = (long long)B * S;
   body = (body + 511) / 512 * 512;
   const long long R = a.lead + body + a.Wp + 2;
   a.dy_plane = R * 8; a.dy_client = (long long)(Cout / 8) * R * 8;
-  a.x_plane = R * 8; a.x_client = x_client_stride ? x_client_stride : (long long)(Cin / 8) * R * 8;
+  a.x_plane = R * 8;
+  a.x_client = x_client_stride ? x_client_stride : (long long)(s2d ? 4 : 1) * (Cin / 8) * R * 8;
   a.body_chunks = (int)(((long long)B * S + kRowsK - 1) / kRowsK);
   a.nmb = (Cout + 127) / 128;
   a.N = Cin <= 256 ? Cin : 256;
+  if (s2d && a.N > 64) a.N = 64;            // four parity groups of N channels share a stage
   a.nnblk = Cin / a.N;
   a.tpg = 512 / a.N;
   if (a.tpg > a.taps) a.tpg = a.taps;
@@ -260,7 +274,7 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   if (nsplit > a.body_chunks) nsplit = a.body_chunks;
   if (nsplit < 1) nsplit = 1;
   a.nsplit = nsplit;
-  const size_t bytesA = 16 * kRowsK * 16, bytesB = (size_t)(a.N / 8) * (kRowsK + 2 * a.halo) * 16;
+  const size_t bytesA = 16 * kRowsK * 16, bytesB = (size_t)(s2d ? 4 : 1) * (a.N / 8) * (kRowsK + 2 * a.halo) * 16;
   a.stages = 3;
   size_t need = a.stages * (bytesA + bytesB) + 1024;
   if (need > 220 * 1024) { a.stages = 2; need = a.stages * (bytesA + bytesB) + 1024; }
@@ -292,6 +306,13 @@ int dba_wgrad_tc_ex(const void* dY, const void* X, long long x_client_stride, fl
                     int B, int H, int W, int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream) {
   return wgrad_launch(dY, X, G, ldg, w_off, K, B, H, W, Cin, Cout, cin_real, cout_real, ksize, 0, 0, 0, stream,
                       x_client_stride);
+}
+
+// Weight gradient of a 3x3 stride-2 convolution on its OUTPUT grid (H, W): dY compact, X the space-to-depth form of the
+// layer's input ([K][4*Cin/8][R][8], R = dba_conv_rows(B, H, W)) - a quarter of the full-grid work.
+int dba_wgrad_tc_s2d(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
+                     int Cin, int Cout, int cin_real, int cout_real, void* stream) {
+  return wgrad_launch(dY, X, G, ldg, w_off, K, B, H, W, Cin, Cout, cin_real, cout_real, 3, 0, 0, 0, stream, 0, 1);
 }
 
 // Weight gradient of a linear layer applied to a flattened [c_real][npos] feature map (torch's x.view(-1, C*h*w)) that

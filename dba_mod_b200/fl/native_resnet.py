@@ -43,6 +43,7 @@ class ConvL:
     w_off: int = 0     # forward pack offset (elements, per client)
     wt_off: int = -1   # transposed pack offset
     bn_off: int = 0    # offset into the per-model scale/shift rows
+    d2s: bool = False  # 3x3 stride-2 layer of a space-to-depth block: transposed slot holds the depth-to-space pack
 
 
 class NativeResNet(LockStepTrainer):
@@ -63,6 +64,7 @@ class NativeResNet(LockStepTrainer):
         self.B = int(params["batch_size"])
         self.label_swap = int(params["poison_label_swap"])
         self.head_C, self.head_H = self.widths[-1], self.ress[-1]
+        self.use_s2d = bool(params.get("native_s2d", True))
         self._plan()
         self.can_eval = True
         self.supports_dist_loss = True
@@ -70,7 +72,6 @@ class NativeResNet(LockStepTrainer):
         self._train_bufs: Dict[int, dict] = {}
         self.mu, self.wd = float(params["momentum"]), float(params["decay"])
         self.eval_chunk = int(params.get("native_eval_chunk", 500))
-        self.use_s2d = bool(params.get("native_s2d", True))
         self.overlap_wgrad = bool(params.get("overlap_wgrad", True)) and device.type == "cuda"
         self._side = torch.cuda.Stream(device=device) if self.overlap_wgrad else None
         self._eval_bufs: Dict[Tuple[int, int], dict] = {}
@@ -99,6 +100,8 @@ class NativeResNet(LockStepTrainer):
                 self.blocks.append((c1, c2, sc))
                 res //= sub
                 cin = w
+        for bi, (c1, _, _) in enumerate(self.blocks):
+            c1.d2s = self._s2d_block(bi)
         off = 0
         bn_off = 0
         rows = []
@@ -117,11 +120,12 @@ class NativeResNet(LockStepTrainer):
             off += n_f
             if not l.fold:
                 l.wt_off = off
-                off += n_f
+                off += 16 * l.cin_p * l.cout_p if l.d2s else n_f      # [4 taps][Cout/8][4*Cin][8] for the d2s form
             l.bn_off = bn_off
             bn_off += l.cout
             e = sp.entries[l.name]
-            rows.append([e.offset, l.cout, l.cin, taps, l.w_off, l.wt_off, l.cin_p, l.cout_p, int(l.fold)])
+            rows.append([e.offset, l.cout, l.cin, taps, l.w_off, l.wt_off, l.cin_p, l.cout_p,
+                         3 if l.d2s else int(l.fold)])
             ent = sp.entries
             fold_rows.append([ent[l.bn + ".weight"].offset, ent[l.bn + ".bias"].offset,
                               ent[l.bn + ".running_mean"].offset, ent[l.bn + ".running_var"].offset, l.cout, l.bn_off])
@@ -367,8 +371,8 @@ class NativeResNet(LockStepTrainer):
             t[("a", l.name)] = z(l.cout_p, ro)
             if l.fold:
                 t[("dy", l.name)] = z(l.cout_p, ro)
-            elif l.ks == 1 and l.sub == 2 and l.name in s2d_sc:
-                t[("dy", l.name)] = z(l.cout_p, ro)           # shortcut of a space-to-depth block: stays compact
+            elif l.d2s or (l.ks == 1 and l.sub == 2 and l.name in s2d_sc):
+                t[("dy", l.name)] = z(l.cout_p, ro)           # stride-2 layers of a space-to-depth block: compact
             else:
                 t[("dy", l.name)] = z(l.cout_p, l.H)          # on the input grid (zero-upsampled when sub == 2)
         # gradient scratch per resolution level: g (block output grad), dz, da1, dx
@@ -443,9 +447,14 @@ class NativeResNet(LockStepTrainer):
             H, xcs = l.H // 2, x.stride(0)
 
         def launch():
-            native.check(self.lib.dba_wgrad_tc_ex(native.ptr(dy), native.ptr(x), xcs, native.ptr(Gr), Gr.stride(0),
-                                                  e.offset, K, self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks,
-                                                  native.stream()))
+            if s2d and ks == 3:
+                native.check(self.lib.dba_wgrad_tc_s2d(native.ptr(dy), native.ptr(x), native.ptr(Gr), Gr.stride(0),
+                                                       e.offset, K, self.B, H, H, cin, l.cout_p, cin_real, l.cout,
+                                                       native.stream()))
+            else:
+                native.check(self.lib.dba_wgrad_tc_ex(native.ptr(dy), native.ptr(x), xcs, native.ptr(Gr), Gr.stride(0),
+                                                      e.offset, K, self.B, H, H, cin, l.cout_p, cin_real, l.cout, ks,
+                                                      native.stream()))
 
         if not self.overlap_wgrad:
             launch()
@@ -538,30 +547,39 @@ class NativeResNet(LockStepTrainer):
             self._bn_bwd(c2, K, g, t[("y", c2.name)], t[("a", c2.name)], dy2, dz, W, t, nvalid, up=False)
             self._wgrad(c2, K, dy2, t[("a", c1.name)], t)
             self._dgrad(c2, K, dy2, pack, da1)
+            xs = t.get(("s2d", bi)) if c1.d2s else None
             self._bn_bwd(c1, K, da1, t[("y", c1.name)], t[("a", c1.name)], dy1, None, W, t, nvalid,
-                         up=(c1.sub == 2))
-            self._wgrad(c1, K, dy1, xin_b, t)
+                         up=(c1.sub == 2 and xs is None))
+            if xs is not None:
+                self._wgrad(c1, K, dy1, xs, t, s2d=True)
+            else:
+                self._wgrad(c1, K, dy1, xin_b, t)
             pool_i = [b for b in lv_g[r_in] if b is not g and b is not dz and b is not da1]
             dx = pool_i[0]
             if sc is None:
                 self._dgrad(c1, K, dy1, pack, dx, res=dz)
             else:
                 dx2 = pool_i[1]
-                self._dgrad(c1, K, dy1, pack, dx2)
                 dys = t[("dy", sc.name)]
-                xs = t.get(("s2d", bi))
                 if xs is not None:
-                    # 1x1 stride-2 shortcut on its own (half-resolution) grid: compact dys, weight gradient against the
-                    # parity-0 planes of the space-to-depth input, input gradient added in place at the even positions
+                    # Space-to-depth block.  3x3 stride-2 input gradient from the compact dy: 2x2 taps, depth-to-space
+                    # store (every pixel of the full-resolution gradient is written exactly once) ...
+                    ro = c1.H // 2
+                    wd = pack[:, c1.wt_off:]
+                    native.check(self.lib.dba_conv_tc_ex(
+                        native.ptr(dy1), native.ptr(wd), pack.stride(0), native.ptr(dx2), None, None, None, 0, None, 0,
+                        K, self.B, ro, ro, c1.cout_p, 4 * c1.cin_p, 2, 1, 0, 0, 0, 3, native.stream()))
+                    # ... and the 1x1 stride-2 shortcut on its own (half-resolution) grid: compact dys, weight gradient
+                    # against the parity-0 planes of the input, input gradient added in place at the even positions
                     self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=False)
                     self._wgrad(sc, K, dys, xs, t, s2d=True)
                     wt = self._wt(pack, sc, transposed=True)
-                    ro = sc.H // 2
                     native.check(self.lib.dba_conv_tc_ex(
                         native.ptr(dys), native.ptr(wt), pack.stride(0), native.ptr(dx2), native.ptr(dx2), None, None, 0,
                         None, 0, K, self.B, ro, ro, sc.cout_p, sc.cin_p, 1, 1, 0, 0, 0, 2, native.stream()))
                     dx = dx2
                 else:
+                    self._dgrad(c1, K, dy1, pack, dx2)
                     self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
                     self._wgrad(sc, K, dys, xin_b, t)
                     self._dgrad(sc, K, dys, pack, dx, res=dx2)

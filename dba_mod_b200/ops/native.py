@@ -68,6 +68,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_conv_tc_ex", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_conv_tc_valid", [P, P, L, P, P, P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_wgrad_tc_ex", [P, P, L, P, L, I, I, I, I, I, I, I, I, I, I, P])
+    _sig(lib, "dba_wgrad_tc_s2d", [P, P, P, L, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_wgrad_linear_chw", [P, P, P, L, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_maxpool2_fwd", [P, P, I, I, I, I, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_maxpool2_bwd_relu_bias", [P, P, P, P, L, I, I, I, I, I, I, I, I, I, I, I, L, L, P])

@@ -110,6 +110,8 @@ int dba_wgrad_tc(const void* dY, const void* X, float* G, long long ldg, int w_o
 
 int dba_wgrad_tc_ex(const void* dY, const void* X, long long x_client_stride, float* G, long long ldg, int w_off, int K,
                     int B, int H, int W, int Cin, int Cout, int cin_real, int cout_real, int ksize, void* stream);
+int dba_wgrad_tc_s2d(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
+                     int Cin, int Cout, int cin_real, int cout_real, void* stream);
 /* Weight gradient of a linear layer over a flattened [c_real][npos] map kept as channels n = pos*c_pad + c of a 1x1
  * grid (MnistNet fc1 after x.view(-1, 4*4*50), models/MnistNet.py:22-23). */
 int dba_wgrad_linear_chw(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int Cout,
