@@ -99,7 +99,7 @@ _DEFAULTS: Dict[str, Any] = {
     "multistep_lr_compat": "torch2",  # Q4: 'torch2' (decay only at integral milestones) | 'bisect'
     "native_net": True,           # cuda backend: use the native tensor-core executor where it covers the model
     "native_train": True,
-    "native_eval_chunk": 500,     # test images per evaluation pass (per model / input set)
+    "native_eval_chunk": 1000,    # upper bound on test images per evaluation pass (per model / input set)
     "cuda_graphs": True,          # replay the captured training step instead of ~125 launches per step
     "native_s2d": True,           # stride-2 convolutions from space-to-depth operands (output pixels only)
     "overlap_wgrad": True,        # weight-gradient kernels on a side stream / parallel graph branch

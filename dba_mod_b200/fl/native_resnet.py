@@ -183,28 +183,52 @@ class NativeResNet(LockStepTrainer):
         c1, _, sc = self.blocks[bi]
         return c1.sub == 2 and c1.ks == 3 and sc is not None and sc.sub == 2 and c1.H % 2 == 0
 
+    def _chunk_for(self, n: int) -> int:
+        """Images per evaluation pass: n split into equal passes of at most ``native_eval_chunk`` images (a rank that
+        holds 1250 test images runs 2 x 640, not 2 x 1000 or 3 x 500 with a mostly empty last pass)."""
+        cap = max(32, self.eval_chunk)
+        if n <= 0:
+            return min(cap, 256)
+        passes = (n + cap - 1) // cap
+        per = (n + passes - 1) // passes
+        return min(cap, (per + 31) // 32 * 32)
+
     def _ebufs(self, M: int, Bt: int, per_job_input: bool = False) -> dict:
-        key = (M, Bt, per_job_input)
-        if key in self._eval_bufs:
-            return self._eval_bufs[key]
-        dev = self.device
-        z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
+        """Activation buffers of an evaluation pass of M models x Bt images.  One set per (Bt, per_job_input), sized
+        for the largest M seen so far; smaller M use the leading slices (the per-model stride does not depend on M)."""
+        key = (Bt, per_job_input)
+        full = self._eval_bufs.get(key)
+        if full is None or full["cap"] < M:
+            if full is not None:
+                del self._eval_bufs[key]
+                full = None
+                torch.cuda.empty_cache()
+            cap = M
+            dev = self.device
+            z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
+            kin = cap if per_job_input else 1
+            stem = self.layers[0]
+            full = {"cap": cap, "stem_in": z(kin, stem.cin_p, stem.H), "lv": {}}
+            for w, r in zip(self.widths, self.ress):
+                full["lv"][r] = [z(cap, w, r) for _ in range(4)]
+            # space-to-depth form of a stage's output when the next stage opens with stride-2 convolutions
+            full["s2d"] = {}
+            for bi, (c1, _, _) in enumerate(self.blocks):
+                if self._s2d_block(bi):
+                    full["s2d"][bi] = z(cap, 4 * c1.cin_p, c1.H // 2)
+            if self.pool:
+                full["stem_out"] = z(cap, self.widths[0], stem.H)
+            full["labels"] = torch.zeros(kin, Bt, dtype=torch.int32, device=dev)
+            full["idx"] = torch.full((1, Bt), -1, dtype=torch.long, device=dev)
+            self._eval_bufs[key] = full
+        if full["cap"] == M:
+            return full
         kin = M if per_job_input else 1
-        stem = self.layers[0]
-        bufs = {"stem_in": z(kin, stem.cin_p, stem.H), "lv": {}}
-        for w, r in zip(self.widths, self.ress):
-            bufs["lv"][r] = [z(M, w, r) for _ in range(4)]
-        # space-to-depth form of a stage's output when the next stage opens with stride-2 convolutions
-        bufs["s2d"] = {}
-        for bi, (c1, _, _) in enumerate(self.blocks):
-            if self._s2d_block(bi):
-                bufs["s2d"][bi] = z(M, 4 * c1.cin_p, c1.H // 2)
+        view = {"cap": M, "stem_in": full["stem_in"][:kin], "lv": {r: [b[:M] for b in bs] for r, bs in full["lv"].items()},
+                "s2d": {bi: b[:M] for bi, b in full["s2d"].items()}, "labels": full["labels"][:kin], "idx": full["idx"]}
         if self.pool:
-            bufs["stem_out"] = z(M, self.widths[0], stem.H)
-        bufs["labels"] = torch.zeros(kin, Bt, dtype=torch.int32, device=dev)
-        bufs["idx"] = torch.full((1, Bt), -1, dtype=torch.long, device=dev)
-        self._eval_bufs[key] = bufs
-        return bufs
+            view["stem_out"] = full["stem_out"][:M]
+        return view
 
     @staticmethod
     def _shard(ids: torch.Tensor, shard) -> torch.Tensor:
@@ -233,7 +257,6 @@ class NativeResNet(LockStepTrainer):
     def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None):
         d, dev, lib = self.data, self.device, self.lib
         J = len(jobs)
-        Bt = self.eval_chunk
         models = models if models.stride(-1) == 1 else models.contiguous()
         Mw = models.shape[0]
         pack = self.pack_weights(models)
@@ -245,6 +268,7 @@ class NativeResNet(LockStepTrainer):
         id_sets = [self._shard(d.all_test_idx if sp == "clean" else d.poison_test_idx, shard) for sp, _ in jobs]
         ns = [int(t.numel()) for t in id_sets]
         nmax = max(ns) if ns else 0
+        Bt = self._chunk_for(nmax)
         bufs = self._ebufs(J, Bt, per_job_input=True)
         mf = torch.zeros(J, 1, device=dev)
         mi = torch.zeros(J, 1, 2, dtype=torch.int32, device=dev)
@@ -271,9 +295,9 @@ class NativeResNet(LockStepTrainer):
     def evaluate(self, models: torch.Tensor, split: str, trig_row: int, shard=None):
         d, dev, lib = self.data, self.device, self.lib
         M = models.shape[0]
-        Bt = self.eval_chunk
         ids_all = self._shard(d.all_test_idx if split == "clean" else d.poison_test_idx, shard)
         n = int(ids_all.numel())
+        Bt = self._chunk_for(n)
         models = models if models.stride(-1) == 1 else models.contiguous()
         pack = self.pack_weights(models)
         scale = torch.empty(M, self.bn_total, device=dev)
