@@ -10,11 +10,7 @@
 //             are computed at full resolution) and can emit g' for the identity-shortcut path.
 // Ragged batches: samples b >= nvalid[k] are padding; they are excluded from the statistics (count = nvalid*H*W),
 // produce zero activations and zero gradients.  Halo rows of every buffer are never written.
-#include <cooperative_groups.h>
-#include <cstdlib>
 #include "common.cuh"
-
-namespace cg = cooperative_groups;
 
 using namespace dba;
 
@@ -231,124 +227,6 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   }
 }
 
-// Fused backward: one thread-block CLUSTER per (client, 8-channel chunk).  Pass 1: every CTA of the cluster sums g' and
-// g'*xhat over its share of the rows; the partial sums meet through distributed shared memory (no global scratch, no
-// atomics, no second launch); pass 2: the same CTA re-reads the same rows - now L2-resident, the two-kernel version
-// re-read them after a sweep over the whole tensor - and writes dy.  Rank 0 stores d_gamma / d_beta.
-constexpr int kBwdThreads = 512;
-__global__ void __launch_bounds__(kBwdThreads) bn_bwd_fused_kernel(const BnArgs a) {
-  cg::cluster_group cluster = cg::this_cluster();
-  __shared__ float part[16];                 // this CTA's (sum g', sum g'*xhat) per channel of the chunk
-  __shared__ float red[2][kBwdThreads / 32][8];
-  __shared__ float s_sc[8], s_mg[8], s_mgx[8];
-  const int chunk = blockIdx.y, k = blockIdx.z;
-  const int nv = a.nvalid[k];
-  const int crank = (int)cluster.block_rank(), csize = (int)cluster.num_blocks();
-  float mean[8], rstd[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    mean[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * 8 + j)];
-    rstd[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * 8 + j) + 1];
-  }
-  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
-  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
-  const int stride = csize * kBwdThreads, q0 = crank * kBwdThreads + (int)threadIdx.x;
-  {
-    const int total = min(a.B, nv) * S;
-    float sg[8], sgx[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sg[j] = sgx[j] = 0.f;
-    for (int q = q0; q < total; q += stride) {
-      const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
-      if (h >= a.H || w >= a.W) continue;
-      const long long off = (plane + lead + q) * 8;
-      float g[8], y[8];
-      unpack8(*reinterpret_cast<const uint4*>(a.g + off), g);
-      unpack8(*reinterpret_cast<const uint4*>(a.y + off), y);
-      if (a.act) {
-        float o[8];
-        unpack8(*reinterpret_cast<const uint4*>(a.act + off), o);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        sg[j] += g[j];
-        sgx[j] += g[j] * (y[j] - mean[j]) * rstd[j];
-      }
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      sg[j] = warp_sum(sg[j]);
-      sgx[j] = warp_sum(sgx[j]);
-    }
-    if (lane == 0) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { red[0][warp][j] = sg[j]; red[1][warp][j] = sgx[j]; }
-    }
-    __syncthreads();
-    if (threadIdx.x < 16) {
-      const int which = threadIdx.x >> 3, j = threadIdx.x & 7;
-      float t = 0.f;
-      for (int w = 0; w < kBwdThreads / 32; ++w) t += red[which][w][j];
-      part[which * 8 + j] = t;
-    }
-  }
-  cluster.sync();                            // every CTA's partial sums are in its shared memory
-  if (threadIdx.x < 8) {
-    float sg = 0.f, sgx = 0.f;
-    for (int r = 0; r < csize; ++r) {        // fixed order: the result does not depend on scheduling
-      const float* rp = cluster.map_shared_rank(part, r);
-      sg += rp[threadIdx.x];
-      sgx += rp[8 + threadIdx.x];
-    }
-    const int c = chunk * 8 + threadIdx.x;
-    const float n = (float)nv * (float)(a.H * a.W);
-    s_sc[threadIdx.x] = a.Wflat[(long long)k * a.ldw + a.g_off + c] * rstd[threadIdx.x];
-    s_mg[threadIdx.x] = n > 0.f ? sg / n : 0.f;
-    s_mgx[threadIdx.x] = n > 0.f ? sgx / n : 0.f;
-    if (crank == 0 && a.Gflat) {
-      a.Gflat[(long long)k * a.ldg + a.g_off + c] = sgx;   // d gamma
-      a.Gflat[(long long)k * a.ldg + a.b_off + c] = sg;    // d beta
-    }
-  }
-  cluster.sync();                            // (also keeps every CTA's `part` alive until all peers have read it)
-  const int Wpu = 2 * a.W + 1, Su = (2 * a.H + 1) * Wpu, leadu = Wpu + 1;
-  const long long plane_up = ((long long)k * (a.C >> 3) + chunk) * a.Rup;
-  const int total = a.B * S;
-  for (int q = q0; q < total; q += stride) {
-    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
-    if (h >= a.H || w >= a.W) continue;
-    const long long off = (plane + lead + q) * 8;
-    float d[8], gm[8];
-    if (b < nv) {
-      float g[8], y[8];
-      unpack8(*reinterpret_cast<const uint4*>(a.g + off), g);
-      unpack8(*reinterpret_cast<const uint4*>(a.y + off), y);
-      if (a.act) {
-        float o[8];
-        unpack8(*reinterpret_cast<const uint4*>(a.act + off), o);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float xh = (y[j] - mean[j]) * rstd[j];
-        gm[j] = g[j];
-        d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) d[j] = gm[j] = 0.f;
-    }
-    if (a.gmask) *reinterpret_cast<uint4*>(a.gmask + off) = pack8(gm);
-    long long doff = off;
-    if (a.up) doff = (plane_up + leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w) * 8;
-    *reinterpret_cast<uint4*>(a.out + doff) = pack8(d);
-  }
-}
-
 // ------------------------------------------------------------------------------------------------ max pooling
 // MaxPool2d(3, stride 2, pad 1) on planar-8 activations (Tiny-ImageNet stem, models/resnet_tinyimagenet.py:147).
 // Inputs are post-ReLU (>= 0) and the halo rows / columns of the layout are zero, so the window can be read without
@@ -496,26 +374,6 @@ int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, voi
   a.ld_stats = ld_sums; a.ld_saved = ld_saved; a.ldw = ldw; a.ldg = ldg; a.R = R; a.Rup = Rup;
   a.stats_off = sums_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.up = up;
-  static const int fused = getenv("DBA_BN_FUSED") ? atoi(getenv("DBA_BN_FUSED")) : 1;
-  if (fused) {
-    // cluster size: enough CTAs for ~4 rows per thread and pass, at most 8 (portable cluster limit)
-    const int rows = B * (H + 1) * (W + 1);
-    int cx = 1;
-    while (cx < 8 && rows > cx * kBwdThreads * 4) cx *= 2;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(cx, C / 8, K);
-    cfg.blockDim = dim3(kBwdThreads, 1, 1);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = cx; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    DBA_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bn_bwd_fused_kernel, a));
-    DBA_COUNT_LAUNCH(1);
-    DBA_CHECK_LAUNCH();
-    return DBA_OK;
-  }
   const dim3 grid = bn_grid(B, H, W, C, K);
   bn_bwd_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   bn_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);

@@ -372,3 +372,33 @@ def test_space_to_depth_layout_round_trip():
     g = Geom(3, 8, 6)
     assert p.shape == (2, 1, g.rows, 8)
     torch.testing.assert_close(from_planar(p, 3, 8, 6, 5), x.bfloat16().float())
+
+
+def test_native_executor_planning_on_cpu():
+    """Planning logic of the native ResNet executor needs no GPU: layer table, space-to-depth blocks, evaluation
+    pass sizes, slab width ladder."""
+    import yaml
+    from dba_mod_b200.ops import native
+    if not native.available():
+        pytest.skip("libdba_b200.so not built")
+    from dba_mod_b200.config import Params
+    from dba_mod_b200.data import ImageData
+    from dba_mod_b200.fl.native_resnet import NativeResNet
+    from dba_mod_b200.models import initial_state
+    raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "cifar_params.yaml")))
+    raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=640, synthetic_test_size=100)
+    p = Params(raw)
+    data = ImageData(p, torch.device("cpu"))
+    spec, _, _ = initial_state("cifar", 1)
+    nx = NativeResNet(p, spec, data, torch.device("cpu"))
+    assert len(nx.layers) == 20 and len(nx.blocks) == 8
+    assert [l.name for l in nx.layers if l.d2s] == [f"layer{i}.0.conv1.weight" for i in (2, 3, 4)]
+    assert [nx._s2d_block(b) for b in range(8)] == [False, False, True, False, True, False, True, False]
+    # equal passes of at most native_eval_chunk images, multiples of 32
+    assert [nx._chunk_for(n) for n in (10000, 9000, 1250, 100)] == [1000, 1000, 640, 128]
+    assert all(nx._chunk_for(n) * -(-n // nx._chunk_for(n)) - n < 32 * -(-n // nx._chunk_for(n)) for n in (1250, 777, 4999))
+    # width ladder: at most one third idle rows, never wider than the round
+    for K in (3, 10, 80):
+        for k in range(1, K + 1):
+            w = NativeResNet._width(k, K)
+            assert k <= w <= K and (w - k) * 3 <= w
