@@ -148,6 +148,15 @@ class NativeMnist(LockStepTrainer):
         d, dev, lib = self.data, self.device, self.lib
         J, Bt = len(jobs), self.eval_chunk
         models = models if models.stride(-1) == 1 else models.contiguous()
+        id_sets = [self._shard(d.all_test_idx if sp == "clean" else d.poison_test_idx, shard) for sp, _ in jobs]
+        ns = [int(x.numel()) for x in id_sets]
+        order = sorted(range(J), key=lambda j: -ns[j])        # longest input sets first (see NativeResNet)
+        if order != list(range(J)):
+            jobs = [jobs[j] for j in order]
+            id_sets = [id_sets[j] for j in order]
+            ns = [ns[j] for j in order]
+            if not w_shared:
+                models = models[torch.tensor(order, device=dev)]
         pack = self.pack_weights(models)
         key = (J, Bt)
         if key not in self._eval_bufs:
@@ -155,8 +164,6 @@ class NativeMnist(LockStepTrainer):
         t = self._eval_bufs[key]
         Mw = models.shape[0]
         bias = self._bias(models, t["bias"][:Mw])
-        id_sets = [self._shard(d.all_test_idx if sp == "clean" else d.poison_test_idx, shard) for sp, _ in jobs]
-        ns = [int(x.numel()) for x in id_sets]
         nmax = max(ns) if ns else 0
         mf = torch.zeros(J, 1, device=dev)
         mi = torch.zeros(J, 1, 2, dtype=torch.int32, device=dev)
@@ -168,14 +175,18 @@ class NativeMnist(LockStepTrainer):
         e = self.e
         g1 = Geom(Bt, 1, 1)
         for s in range(0, nmax, Bt):
-            self._forward(J, Bt, t, pack, bias, d.test_x, d.test_y, idx_all[:, s:s + Bt], idx_all.stride(0), trow, pn,
+            Js = sum(1 for n in ns if n > s)
+            self._forward(Js, Bt, t, pack, bias, d.test_x, d.test_y, idx_all[:, s:s + Bt], idx_all.stride(0), trow, pn,
                           None, t["labels"], w_shared=w_shared)
             native.check(lib.dba_head_ex(native.ptr(t["h"]), native.ptr(models), 0 if w_shared else models.stride(0),
                                       e["fc2.weight"].offset, e["fc2.bias"].offset, None, 0, None,
                                       native.ptr(t["labels"]), 0, None, None, native.ptr(mf), native.ptr(mi), 1, None,
-                                      J, Bt, 500, 512, 1, 1, 10, g1.rows, native.stream()))
+                                      Js, Bt, 500, 512, 1, 1, 10, g1.rows, native.stream()))
         mf_c, mi_c = mf.cpu(), mi.cpu()
-        return [(float(mf_c[j, 0]), int(mi_c[j, 0, 0]), ns[j]) for j in range(J)]
+        out = [None] * J
+        for pos, j in enumerate(order):
+            out[j] = (float(mf_c[pos, 0]), int(mi_c[pos, 0, 0]), ns[pos])
+        return out
 
     @torch.no_grad()
     def evaluate_jobs(self, model: torch.Tensor, jobs, shard=None):

@@ -259,14 +259,23 @@ class NativeResNet(LockStepTrainer):
         J = len(jobs)
         models = models if models.stride(-1) == 1 else models.contiguous()
         Mw = models.shape[0]
+        id_sets = [self._shard(d.all_test_idx if sp == "clean" else d.poison_test_idx, shard) for sp, _ in jobs]
+        ns = [int(t.numel()) for t in id_sets]
+        # longest input sets first: the later passes then run on the leading jobs only (the backdoor test set is 10 %
+        # shorter than the clean one - its last pass would be all padding)
+        order = sorted(range(J), key=lambda j: -ns[j])
+        if order != list(range(J)):
+            jobs = [jobs[j] for j in order]
+            id_sets = [id_sets[j] for j in order]
+            ns = [ns[j] for j in order]
+            if not w_shared:
+                models = models[torch.tensor(order, device=dev)]
         pack = self.pack_weights(models)
         scale = torch.empty(Mw, self.bn_total, device=dev)
         shift = torch.empty(Mw, self.bn_total, device=dev)
         native.check(lib.dba_bn_fold(native.ptr(models), models.stride(0), native.ptr(self.fold_table),
                                      len(self.layers), Mw, native.ptr(scale), native.ptr(shift), scale.stride(0),
                                      BN_EPS, native.stream()))
-        id_sets = [self._shard(d.all_test_idx if sp == "clean" else d.poison_test_idx, shard) for sp, _ in jobs]
-        ns = [int(t.numel()) for t in id_sets]
         nmax = max(ns) if ns else 0
         Bt = self._chunk_for(nmax)
         bufs = self._ebufs(J, Bt, per_job_input=True)
@@ -279,17 +288,21 @@ class NativeResNet(LockStepTrainer):
             idx_all[j, :t.numel()] = t
         labels = bufs["labels"]
         for s in range(0, nmax, Bt):
+            Js = sum(1 for n in ns if n > s)           # jobs that still have images in this pass (a prefix)
             idx = idx_all[:, s:s + Bt]
-            self._forward_eval(J, Bt, idx, trow, pn, pack, scale, shift, bufs, labels, per_job=True,
+            self._forward_eval(Js, Bt, idx, trow, pn, pack, scale, shift, bufs, labels, per_job=True,
                                ld_idx=idx_all.stride(0), w_shared=w_shared)
             a = bufs["out"]
             native.check(lib.dba_head(native.ptr(a), native.ptr(models), 0 if w_shared else models.stride(0),
                                       self.head_w_off, self.head_b_off, None, 0, None, native.ptr(labels), 0, None,
-                                      None, native.ptr(mf), native.ptr(mi), 1, None, J, Bt, self.head_C, self.head_H,
+                                      None, native.ptr(mf), native.ptr(mi), 1, None, Js, Bt, self.head_C, self.head_H,
                                       self.head_H, self.ncls, Geom(Bt, self.head_H, self.head_H).rows,
                                       native.stream()))
         mf_c, mi_c = mf.cpu(), mi.cpu()
-        return [(float(mf_c[j, 0]), int(mi_c[j, 0, 0]), ns[j]) for j in range(J)]
+        out = [None] * J
+        for pos, j in enumerate(order):
+            out[j] = (float(mf_c[pos, 0]), int(mi_c[pos, 0, 0]), ns[pos])
+        return out
 
     @torch.no_grad()
     def evaluate(self, models: torch.Tensor, split: str, trig_row: int, shard=None):

@@ -53,6 +53,7 @@ def test_mnist_rounds_native_backend(native_lib):
     raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "mnist_params.yaml")))
     raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=6000, synthetic_test_size=1000,
                number_of_total_participants=20, adversary_list=[3, 7, 11, 15], internal_epochs=2, epochs=5, eta=1.0,
+               scale_weights_poison=5,
                **{"0_poison_epochs": [5], "1_poison_epochs": [5], "2_poison_epochs": [99], "3_poison_epochs": [99]})
     sim = Simulator(Params(raw), device=torch.device("cuda", 0), quiet=True, write_files=False)
     assert sim.backend.name == "cuda" and sim.backend.native_train and sim.backend.native_eval
