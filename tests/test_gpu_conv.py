@@ -125,3 +125,82 @@ def test_conv_space_to_depth_output_with_residual(native_lib):
     y2 = conv.conv_tc_s2d(y1, layout.pack_conv_weight(w2), K, B, H // 2, W // 2, 3, in_s2d=True)
     ref2 = _ref(got1, w2, 3, 2)
     torch.testing.assert_close(layout.from_planar(y2, B, H // 2, W // 2), ref2, rtol=2e-2, atol=3e-2)
+
+
+def _pack_with_kernel(w, mode):
+    """Runs dba_pack_weights on OHWI-flattened weights w [K, Cout, Cin, 3, 3]; returns (pack, fwd_off, t_off)."""
+    from dba_mod_b200.ops import native
+    lib = native.load()
+    K, Co, Ci = w.shape[:3]
+    flat = w.permute(0, 1, 3, 4, 2).reshape(K, -1).contiguous().float()             # [Cout][taps][Cin] per client
+    n_f, n_t = 9 * Ci * Co, (16 if mode == 3 else 9) * Ci * Co
+    table = torch.tensor([[0, Co, Ci, 9, 0, n_f, Ci, Co, mode]], dtype=torch.int32, device=w.device)
+    pack = torch.zeros(K, n_f + n_t, dtype=torch.bfloat16, device=w.device)
+    native.check(lib.dba_pack_weights(native.ptr(flat), flat.stride(0), native.ptr(table), 1, K, native.ptr(pack),
+                                      pack.stride(0), native.stream()))
+    return pack, 0, n_f
+
+
+@pytest.mark.parametrize("K,B,H,Cin,Cout", [(2, 3, 16, 32, 64), (1, 5, 8, 64, 128), (2, 2, 4, 128, 256)])
+def test_stride2_backward_on_the_output_grid(native_lib, K, B, H, Cin, Cout):
+    """3x3 stride-2 convolution, backward without the full grid: the input gradient as a 2x2-tap convolution of the
+    compact dy with depth-to-space store, the weight gradient against the space-to-depth input - both vs autograd."""
+    from dba_mod_b200.ops import layout, native
+    lib = native.load()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(4)
+    d = torch.device("cuda", 0)
+    Ho = H // 2
+    x = torch.randn(K, B, Cin, H, H, device=d).bfloat16().float()
+    w = (torch.randn(K, Cout, Cin, 3, 3, device=d) / (Cin * 9) ** 0.5).bfloat16().float()
+    dy = torch.randn(K, B, Cout, Ho, Ho, device=d).bfloat16().float()
+    ref_dx, ref_dw = [], []
+    for k in range(K):
+        xk, wk = x[k].clone().requires_grad_(True), w[k].clone().requires_grad_(True)
+        y = F.conv2d(xk, wk, None, 2, 1)
+        gx, gw = torch.autograd.grad(y, (xk, wk), dy[k])
+        ref_dx.append(gx); ref_dw.append(gw)
+    ref_dx, ref_dw = torch.stack(ref_dx), torch.stack(ref_dw)
+    pack, _, t_off = _pack_with_kernel(w, 3)
+    dyp = layout.to_planar(dy)
+    # input gradient
+    go = layout.Geom(B, H, H)
+    dx = torch.zeros(K, Cin // 8, go.rows, 8, dtype=torch.bfloat16, device=d)
+    wd = pack[:, t_off:]
+    native.check(lib.dba_conv_tc_ex(native.ptr(dyp), native.ptr(wd), pack.stride(0), native.ptr(dx), None, None, None, 0,
+                                    None, 0, K, B, Ho, Ho, Cout, 4 * Cin, 2, 1, 0, 0, 0, 3, native.stream()))
+    torch.cuda.synchronize()
+    got_dx = layout.from_planar(dx, B, H, H)
+    torch.testing.assert_close(got_dx, ref_dx, rtol=2e-2, atol=3e-2)
+    assert layout.halo_is_zero(dx, B, H, H)
+    # weight gradient
+    xs = layout.to_planar(layout.space_to_depth(x))
+    G = torch.zeros(K, 9 * Cin * Cout, device=d)
+    native.check(lib.dba_wgrad_tc_s2d(native.ptr(dyp), native.ptr(xs), native.ptr(G), G.stride(0), 0, K, B, Ho, Ho, Cin,
+                                      Cout, Cin, Cout, native.stream()))
+    torch.cuda.synchronize()
+    got_dw = G.view(K, Cout, 3, 3, Cin).permute(0, 1, 4, 2, 3)
+    scale = ref_dw.abs().max().item()
+    torch.testing.assert_close(got_dw, ref_dw, rtol=2e-2, atol=2e-2 * scale)
+
+
+def test_shortcut_input_gradient_added_in_place_at_even_pixels(native_lib):
+    """1x1 stride-2 convolution: dx[2h, 2w] += W^T dy[h, w] on the full-resolution gradient, other pixels untouched."""
+    from dba_mod_b200.ops import layout, native
+    lib = native.load()
+    torch.manual_seed(5)
+    d = torch.device("cuda", 0)
+    K, B, H, Cin, Cout = 2, 3, 16, 32, 64
+    Ho = H // 2
+    w = (torch.randn(K, Cout, Cin, 1, 1, device=d) / Cin ** 0.5).bfloat16().float()
+    dy = torch.randn(K, B, Cout, Ho, Ho, device=d).bfloat16().float()
+    base = torch.randn(K, B, Cin, H, H, device=d).bfloat16().float()
+    ref = base.clone()
+    ref[:, :, :, 0::2, 0::2] += torch.einsum("koc,kbohw->kbchw", w[..., 0, 0], dy)
+    wt = layout.pack_conv_weight(w.transpose(1, 2))                    # Cout -> Cin, 1x1: no tap flip needed
+    dx = layout.to_planar(base)
+    native.check(lib.dba_conv_tc_ex(native.ptr(layout.to_planar(dy)), native.ptr(wt), wt[0].numel(), native.ptr(dx),
+                                    native.ptr(dx), None, None, 0, None, 0, K, B, Ho, Ho, Cout, Cin, 1, 1, 0, 0, 0, 2,
+                                    native.stream()))
+    torch.cuda.synchronize()
+    torch.testing.assert_close(layout.from_planar(dx, B, H, H), ref, rtol=2e-2, atol=3e-2)
