@@ -203,37 +203,48 @@ class Simulator:
         self._log_handlers = []
 
     # ------------------------------------------------------------------------------------- client sharding
-    def _shard(self, names: List) -> List[int]:
-        """Slots of this rank.  Greedy longest-processing-time placement on the estimated step count, so the
-        attacker (3-10x more steps) does not share a GPU with many benign clients."""
+    def _placement(self, names: List, epoch: Optional[int] = None) -> List[int]:
+        """owner[slot] = rank.  Greedy makespan placement under the lock-step cost model: a rank's local phase costs
+        ``a * T + b * sum(steps)`` (T = its longest client; every step pays the launch floor ``a`` once, however many
+        clients share it), so a client goes to the rank whose cost grows least - long clients end up sharing their
+        floor with short ones instead of being balanced by step count alone."""
+        p = self.params
+        if epoch is not None:
+            plans = plan_clients(p, self.data, names, epoch)
+            steps = [pl.n_epochs * pl.nb for pl in plans]
+        else:
+            steps = []
+            for nm in names:
+                adv = p.adversary_index(nm) if (p["is_poison"] and nm in p["adversary_list"]) else -1
+                ne = p["internal_poison_epochs"] if adv >= 0 else p["internal_epochs"]
+                steps.append(self.data.batches_per_epoch(nm) * ne)
+        a, b = getattr(getattr(self.backend, "exec", None), "_STEP_COST", (1.0, 0.3))
+        T = [0] * self.world
+        S = [0] * self.world
+        owner = [0] * len(names)
+        for st, slot in sorted(((st, s) for s, st in enumerate(steps)), key=lambda t: (-t[0], t[1])):
+            r = min(range(self.world), key=lambda i: (a * max(T[i], st) + b * (S[i] + st), i))
+            T[r], S[r] = max(T[r], st), S[r] + st
+            owner[slot] = r
+        return owner
+
+    def _shard(self, names: List, epoch: Optional[int] = None) -> List[int]:
+        """Slots of this rank."""
         if self.world == 1:
             return list(range(len(names)))
-        p = self.params
-        cost = []
-        for s, nm in enumerate(names):
-            adv = p.adversary_index(nm) if (p["is_poison"] and nm in p["adversary_list"]) else -1
-            ne = p["internal_poison_epochs"] if adv >= 0 else p["internal_epochs"]
-            cost.append((self.data.batches_per_epoch(nm) * ne, s))
-        load = [0] * self.world
-        owner = {}
-        for c, s in sorted(cost, key=lambda t: (-t[0], t[1])):
-            r = min(range(self.world), key=lambda i: (load[i], i))
-            load[r] += c
-            owner[s] = r
+        owner = self._placement(names, epoch)
         return [s for s in range(len(names)) if owner[s] == self.rank]
 
-    def _owner_counts(self, names: List) -> Tuple[List[int], List[int]]:
+    def _owner_counts(self, names: List, epoch: Optional[int] = None) -> Tuple[List[int], List[int]]:
         """(rows per rank, global-slot order of the concatenated rank shards)."""
         if self.world == 1:
             return [len(names)], list(range(len(names)))
-        saved = self.rank
+        owner = self._placement(names, epoch)
         counts, order = [], []
         for r in range(self.world):
-            self.rank = r
-            sl = self._shard(names)
+            sl = [s for s in range(len(names)) if owner[s] == r]
             counts.append(len(sl))
             order += sl
-        self.rank = saved
         return counts, order
 
     # ------------------------------------------------------------------------------------------ the loop
@@ -293,9 +304,9 @@ class Simulator:
         logger.info(f"Server Epoch:{epoch} choose agents : {names}.")
         rep = RoundReport(epoch, list(names), list(adversaries))
         self._round_epoch, self._loan_tle = epoch, {}
-        my_slots = self._shard(names)
+        my_slots = self._shard(names, epoch)
         my_names = [names[s] for s in my_slots]
-        counts, order = self._owner_counts(names)
+        counts, order = self._owner_counts(names, epoch)
         if self.stream_inputs:
             self._stage_inputs(my_names)
         K, Df = len(my_names), self.spec.Df
