@@ -15,6 +15,8 @@
 //            applies the update (FedAvg scale + DP noise / plain sum) and stores the result into EVERY peer's replica
 //            (P2P stores) - reduce-scatter + update + all-gather in one launch, tile by tile;
 //   barrier  so that nobody reads a replica before all slices landed.
+// With NVLS (multicast mappings of the same buffers) phase 2 is one multimem.ld_reduce (sum formed inside the NVSwitch)
+// and one multimem.st (broadcast by the switch) per 16 bytes instead of `world` peer loads and `world` peer stores.
 // Tickets grow monotonically per call, so signal pads never need to be cleared.  All blocks of a launch must be
 // co-resident (grid <= 148): they wait on one another.
 #include "common.cuh"
@@ -31,7 +33,23 @@ struct PeerSet {
   float* replica[kMaxRanks];      // [D] global model (or any broadcast target) of each rank
   unsigned int* signal[kMaxRanks];  // [2 * kMaxRanks] tickets: slot phase*kMaxRanks + sender
   int rank, world;
+  // NVLS: multicast addresses of the staging / replica buffers (null = peer loads / stores).  A multimem.ld_reduce on
+  // stage_mc returns the sum over ALL ranks' staging vectors, reduced inside the NVSwitch; a multimem.st on replica_mc
+  // lands in every rank's replica.
+  float* stage_mc;
+  float* replica_mc;
 };
+
+__device__ __forceinline__ float4 mc_ld_reduce4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st4(float* p, const float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -87,6 +105,27 @@ __device__ __forceinline__ void reduce_scatter_update_gather(const PeerSet& ps, 
   const long long nvec = (hi - lo) >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (ps.stage_mc != nullptr) {
+    // NVLS path: one switch-reduced load and one multicast store per 16 bytes, whatever the number of ranks
+    for (; v + stride < nvec; v += 2 * stride) {
+      const long long i0 = lo + (v << 2), i1 = lo + ((v + stride) << 2);
+      const float4 a0 = mc_ld_reduce4(ps.stage_mc + i0), a1 = mc_ld_reduce4(ps.stage_mc + i1);
+      const float4 g0 = ld4(mine + i0), g1 = ld4(mine + i1);
+      float4 o0, o1;
+      o0.x = f(g0.x, a0.x, i0); o0.y = f(g0.y, a0.y, i0 + 1); o0.z = f(g0.z, a0.z, i0 + 2); o0.w = f(g0.w, a0.w, i0 + 3);
+      o1.x = f(g1.x, a1.x, i1); o1.y = f(g1.y, a1.y, i1 + 1); o1.z = f(g1.z, a1.z, i1 + 2); o1.w = f(g1.w, a1.w, i1 + 3);
+      mc_st4(ps.replica_mc + i0, o0);
+      mc_st4(ps.replica_mc + i1, o1);
+    }
+    for (; v < nvec; v += stride) {
+      const long long i0 = lo + (v << 2);
+      const float4 a0 = mc_ld_reduce4(ps.stage_mc + i0);
+      const float4 g0 = ld4(mine + i0);
+      float4 o0;
+      o0.x = f(g0.x, a0.x, i0); o0.y = f(g0.y, a0.y, i0 + 1); o0.z = f(g0.z, a0.z, i0 + 2); o0.w = f(g0.w, a0.w, i0 + 3);
+      mc_st4(ps.replica_mc + i0, o0);
+    }
+  }
   for (; v + stride < nvec; v += 2 * stride) {
     const long long i0 = lo + (v << 2), i1 = lo + ((v + stride) << 2);
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
@@ -202,6 +241,8 @@ static int fill_peers(PeerSet& ps, const void* const* stage, const void* const* 
     ps.replica[q] = (float*)replica[q];
     ps.signal[q] = (unsigned int*)signal[q];
   }
+  ps.stage_mc = nullptr;
+  ps.replica_mc = nullptr;
   return 0;
 }
 
@@ -221,6 +262,37 @@ int dba_fedavg_p2p(const float* W, long long ldw, int K, long long D, float coef
   DBA_REQUIRE(K >= 0 && D > 0, "dba_fedavg_p2p: K=%d D=%lld", K, D);
   fedavg_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(W, ldw, K, D, coef, sigma, seed, ps, counter, call_id,
                                                               total_clients);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+// NVLS variants: stage_mc / replica_mc are the multicast addresses of the same symmetric buffers (both non-null and
+// 16-byte aligned); phase 2 then uses multimem.ld_reduce / multimem.st (reduction inside the NVSwitch).
+int dba_fedavg_nvls(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
+                    const void* const* stage, const void* const* replica, const void* const* signal, void* stage_mc,
+                    void* replica_mc, int rank, int world, int total_clients, unsigned int* counter,
+                    unsigned int call_id, void* stream) {
+  PeerSet ps;
+  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_fedavg_nvls: bad rank/world %d/%d", rank,
+              world);
+  DBA_REQUIRE(K >= 0 && D > 0 && stage_mc && replica_mc, "dba_fedavg_nvls: K=%d D=%lld", K, D);
+  ps.stage_mc = (float*)stage_mc; ps.replica_mc = (float*)replica_mc;
+  fedavg_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(W, ldw, K, D, coef, sigma, seed, ps, counter, call_id,
+                                                              total_clients);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
+int dba_allreduce_axpby_nvls(long long D, float alpha, float beta, const void* const* stage,
+                             const void* const* replica, const void* const* signal, void* stage_mc, void* replica_mc,
+                             int rank, int world, unsigned int* counter, unsigned int call_id, void* stream) {
+  PeerSet ps;
+  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_allreduce_axpby_nvls: bad rank/world");
+  DBA_REQUIRE(D > 0 && stage_mc && replica_mc, "dba_allreduce_axpby_nvls: D=%lld", D);
+  ps.stage_mc = (float*)stage_mc; ps.replica_mc = (float*)replica_mc;
+  allreduce_axpby_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(D, alpha, beta, ps, counter, call_id);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;

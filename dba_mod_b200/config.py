@@ -102,6 +102,7 @@ _DEFAULTS: Dict[str, Any] = {
     "native_eval_chunk": 1000,    # upper bound on test images per evaluation pass (per model / input set)
     "cuda_graphs": True,          # replay the captured training step instead of ~125 launches per step
     "native_s2d": True,           # stride-2 convolutions from space-to-depth operands (output pixels only)
+    "nvls": "auto",               # fused collectives through NVSwitch multicast (multimem): auto = from 4 ranks on
     "overlap_wgrad": True,        # weight-gradient kernels on a side stream / parallel graph branch
     "prewarm": True,              # allocate slabs / capture step graphs for every batch width at start-up
     "compact_tail": True,         # clients that finished their local steps stop being computed (native trainer)

@@ -17,8 +17,8 @@ from ..ops import native
 
 class LockStepTrainer:
     # cost of one lock-step step over k clients (ms), measured on B200 with tools/gpu_step_cost.py (CIFAR ResNet-18,
-    # B = 64, graph replay): 1.52 ms at k = 1 ... 4.11 ms at k = 10; and of moving the carried state to another slab
-    _STEP_COST = (1.23, 0.285)
+    # B = 64, graph replay): 1.37 ms at k = 1 ... 3.56 ms at k = 10; and of moving the carried state to another slab
+    _STEP_COST = (1.13, 0.243)
     _CUT_COST = 0.25
 
     # Slab widths: every distinct width owns a full set of activation buffers and a captured graph, so segments run on

@@ -148,7 +148,7 @@ class Simulator:
             peer, err = None, None
             try:
                 from ..parallel.symm import PeerComm
-                peer = PeerComm(self.comm, self.spec.Df, self.device)
+                peer = PeerComm(self.comm, self.spec.Df, self.device, use_nvls=params.get("nvls", "auto"))
             except Exception as e:  # noqa: BLE001
                 err = e
             ok = torch.tensor([1.0 if peer is not None else 0.0], device=self.device)
@@ -156,7 +156,8 @@ class Simulator:
             if int(ok.item()) == self.world:
                 self.comm = peer
                 self.G = self.comm.set_global(self.G)
-                self.collective_path = "fused peer-memory kernels (NVLink P2P)"
+                self.collective_path = ("fused peer-memory kernels (NVLS multimem)" if getattr(peer, "use_nvls", False)
+                                        else "fused peer-memory kernels (NVLink P2P)")
             else:
                 logger.warning(f"peer-memory communicator unavailable ({err}); using the NCCL baseline collectives")
                 self.collective_path = "nccl baseline"

@@ -86,6 +86,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_wgrad_tc", [P, P, P, L, I, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_fedavg_p2p", [P, L, I, L, F, F, U, P, P, P, I, I, I, P, ctypes.c_uint, P])
     _sig(lib, "dba_allreduce_axpby_p2p", [L, F, F, P, P, P, I, I, P, ctypes.c_uint, P])
+    _sig(lib, "dba_fedavg_nvls", [P, L, I, L, F, F, U, P, P, P, P, P, I, I, I, P, ctypes.c_uint, P])
+    _sig(lib, "dba_allreduce_axpby_nvls", [L, F, F, P, P, P, P, P, I, I, P, ctypes.c_uint, P])
     _sig(lib, "dba_gram_ptrs", [P, I, L, P, P])
     _sig(lib, "dba_loan_train", [P, L, P, L, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, F, F,
                                  ctypes.c_uint, I, P])

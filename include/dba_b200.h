@@ -202,6 +202,15 @@ int dba_allreduce_axpby_p2p(long long D, float alpha, float beta, const void* co
                             unsigned int* counter, unsigned int call_id, void* stream);
 /* Gram matrix over feature rows given by (possibly peer-mapped) pointers: FoolsGold's gather fused into the cosine
  * GEMM (helper.py:544-555,574-577). */
+/* NVLS variants of the two kernels above: phase 2 through the multicast mappings of the staging / replica buffers
+ * (multimem.ld_reduce.add + multimem.st: the NVSwitch reduces and broadcasts). */
+int dba_fedavg_nvls(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
+                    const void* const* stage, const void* const* replica, const void* const* signal, void* stage_mc,
+                    void* replica_mc, int rank, int world, int total_clients, unsigned int* counter,
+                    unsigned int call_id, void* stream);
+int dba_allreduce_axpby_nvls(long long D, float alpha, float beta, const void* const* stage,
+                             const void* const* replica, const void* const* signal, void* stage_mc, void* replica_mc,
+                             int rank, int world, unsigned int* counter, unsigned int call_id, void* stream);
 int dba_gram_ptrs(const double* const* rows, int n, long long L, double* gram, void* stream);
 
 #ifdef __cplusplus

@@ -16,7 +16,7 @@ rank, world = comm.rank, comm.world
 dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
 torch.cuda.set_device(dev)
 D = 2802410
-pc = PeerComm(comm, D, dev)
+pc = PeerComm(comm, D, dev, use_nvls={"1": True, "0": False}.get(os.environ.get("DBA_NVLS", "auto"), "auto"))
 torch.manual_seed(1234)                       # identical streams on every rank
 G0 = torch.randn(D, device=dev)
 Kr = [3, 2, 1, 4, 2, 1, 3, 2][:world]
@@ -67,6 +67,7 @@ tf, tb = timeit(fused), timeit(baseline)
 flag = torch.tensor([1.0 if ok else 0.0], device=dev)
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
+    print(f"path: {'NVLS multimem' if pc.use_nvls else 'P2P loads/stores'} (multicast available: {pc.has_multicast})")
     print(f"fedavg fused p2p: {tf * 1e3:.1f} us   nccl baseline (sum + all_reduce + add): {tb * 1e3:.1f} us   "
           f"world {world} K_local {Kr[0]} D {D}", flush=True)
     print("P2P_OK" if flag.item() == 1.0 else "P2P_FAIL", flush=True)
