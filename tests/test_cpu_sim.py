@@ -154,3 +154,37 @@ def test_world_size_invariance_gloo(tmp_path, method):
     assert abs(a["acc"] - b["acc"]) < 1.0 and abs(a["asr"] - b["asr"]) < 2.0
     if a["w"] is not None:
         assert max(abs(x - y) for x, y in zip(sorted(a["w"]), sorted(b["w"]))) < 1e-3
+
+
+def test_client_placement_follows_the_lock_step_cost_model(tmp_path):
+    """Placement of a round's clients on ranks: everybody placed exactly once, the modelled makespan
+    (a * longest client + b * sum of steps per rank) is no worse than balancing by step count alone, and a long
+    attacker shares its launch floor with short clients instead of being isolated by step count."""
+    from dba_mod_b200.fl.schedule import plan_clients
+    sim = Simulator(Params(_mnist(synthetic_train_size=6000, internal_poison_epochs=6)), out_root=str(tmp_path),
+                    quiet=True, write_files=False)
+    p = sim.params
+    names = list(p["adversary_list"][:1]) + [n for n in sim.data.participants_list if n not in p["adversary_list"]][:9]
+    epoch = p.poison_epochs_of(0)[0]
+    steps = [pl.n_epochs * pl.nb for pl in plan_clients(p, sim.data, names, epoch)]
+    assert max(steps) >= 3 * sorted(steps)[len(steps) // 2]          # the attacker really is the long one
+    a, b = 1.0, 0.3
+
+    def makespan(owner, world):
+        return max(a * max([steps[s] for s in range(len(names)) if owner[s] == r], default=0)
+                   + b * sum(steps[s] for s in range(len(names)) if owner[s] == r) for r in range(world))
+
+    for world in (2, 3, 4):
+        sim.world = world
+        owner = sim._placement(names, epoch)
+        assert len(owner) == len(names) and set(owner) <= set(range(world))
+        counts, order = sim._owner_counts(names, epoch)
+        assert sum(counts) == len(names) and sorted(order) == list(range(len(names)))
+        load, lpt = [0] * world, [0] * len(names)               # plain longest-processing-time on step counts
+        for st, s in sorted(((st, s) for s, st in enumerate(steps)), key=lambda t: (-t[0], t[1])):
+            r = min(range(world), key=lambda i: (load[i], i))
+            load[r] += st
+            lpt[s] = r
+        assert makespan(owner, world) <= makespan(lpt, world) + 1e-9
+    sim.world = 1
+    sim.close()
