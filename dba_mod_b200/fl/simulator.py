@@ -77,6 +77,8 @@ class Simulator:
         self.rank, self.world = self.comm.rank, self.comm.world
         self.is_main = self.rank == 0
         self.write_files = write_files and self.is_main
+        # per-client CSV rows of the other ranks are only gathered when somebody writes them (same decision on all ranks)
+        self.gather_rows = bool(write_files)
         seed = int(params["seed"])
         # main.py:36-38,86 — one python / numpy stream drives partition shuffles, Dirichlet draws and selection
         self.py_rng = random.Random(seed)
@@ -557,7 +559,7 @@ class Simulator:
 
     def _emit_rows(self, rows_local, counts) -> None:
         rows = rows_local
-        if self.world > 1:
+        if self.world > 1 and self.gather_rows:
             import torch.distributed as dist
             gathered = [None] * self.world
             dist.all_gather_object(gathered, rows_local)
