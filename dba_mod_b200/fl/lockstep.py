@@ -194,7 +194,7 @@ class LockStepTrainer:
         dists = [False] + ([True] if (p["is_poison"] and float(p["alpha_loss"]) != 1.0) else [])
         if Kmax > 16:            # many clients per GPU: slabs are created on first use instead
             return
-        for K in sorted({self._width(k, Kmax) for k in range(1, Kmax + 1)} | {Kmax, max(Kmax - 1, 1)}):
+        for K in range(1, Kmax + 1):       # every K can be a round's home slab; the ladder widths are among them
             t = self._tbufs(K)
             t["st_idx"].fill_(-1); t["st_nvalid"].zero_(); t["st_active"].zero_(); t["st_lr"].zero_()
             for use_dist in dists:

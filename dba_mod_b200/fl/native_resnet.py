@@ -203,7 +203,9 @@ class NativeResNet(LockStepTrainer):
                 del self._eval_bufs[key]
                 full = None
                 torch.cuda.empty_cache()
-            cap = M
+            # (model, input set) pairs of a round: the clients' clean tests plus up to four extra tests per attacker -
+            # sized once so that the first attack round does not re-allocate inside its critical path
+            cap = max(M, int(self.params["no_models"]) + 4) if per_job_input and M > 1 else M
             dev = self.device
             z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
             kin = cap if per_job_input else 1

@@ -141,7 +141,8 @@ class Simulator:
         if (ex is not None and hasattr(ex, "prewarm") and getattr(self.backend, "native_train", False)
                 and params.get("compact_tail", True) and params.get("prewarm", True)):
             # every batch width a round can shrink to gets its slab and captured step graph now, not mid-round
-            kmax = min(int(params["no_models"]), (int(params["no_models"]) + self.world - 1) // self.world + 1)
+            # the cost-model placement can give one rank anything between 1 and no_models - (world - 1) clients
+            kmax = max(1, int(params["no_models"]) - (self.world - 1))
             ex.prewarm(kmax, params["aggregation_methods"] == C.AGGR_FOOLSGOLD)
         self.collective_path = "single process" if self.world == 1 else "torch.distributed baseline"
         if (self.world > 1 and self.device.type == "cuda" and params["fused_collectives"]
