@@ -29,8 +29,6 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly ONE JSON line: NCCL's version banner / debug output goes to a file instead
-os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/dba_nccl_%h_%p.log")
 
 METRIC = "fl_rounds_per_sec_cifar10_resnet18"
 
@@ -191,15 +189,15 @@ def run_own(args) -> dict:
 
 def run_reference(args) -> dict:
     W, K = args.warmup, args.steps
-    ref_dir = os.path.join(ROOT, "baseline", "_ref")
-    if not os.path.exists(os.path.join(ref_dir, "main.py")):
-        return {"impl": "reference", "unavailable": "baseline/_ref not present (reference source not installed)"}
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import ref_harness
+    if not ref_harness.reference_dir():
+        return {"impl": "reference", "unavailable": "neither baseline/_ref nor /root/reference holds the reference"}
     if int(os.environ.get("RANK", "0")) != 0:
         return {}          # the reference is a single-process, single-GPU program (config.py:2); other ranks idle
     try:
         import torch
-        sys.path.insert(0, os.path.join(ROOT, "baseline"))
-        from ref_harness import run_reference as _run
+        _run = ref_harness.run_reference
         raw = bench_params(W, K, windows=1)
         for k in ("synthetic_data",):
             raw.pop(k, None)
