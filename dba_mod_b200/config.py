@@ -85,6 +85,7 @@ _DEFAULTS: Dict[str, Any] = {
     "vis_trigger_split_test": False,
     "batch_track_distance": False,
     # ---- extensions of this framework (absent from the reference schema) ----
+    "resume_required": False,     # resumed_model: true with a missing checkpoint file is an error (else: warn, start fresh)
     "synthetic_data": None,       # None = auto (use real data when found under data_dir, else synthetic)
     "synthetic_train_size": None,
     "synthetic_test_size": None,

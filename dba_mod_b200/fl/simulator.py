@@ -122,13 +122,19 @@ class Simulator:
         self.start_epoch = 1
         if params["resumed_model"]:
             path = ckpt.resume_path(params, out_root if os.path.isdir(out_root) else "saved_models")
-            sd, ep, lr = ckpt.load_checkpoint(path)
-            flat, cnt = self.spec.flatten(sd)
-            self.start_epoch = ep + 1
-            if lr is not None:
-                params["lr"] = lr
-            logger.info(f"Loaded parameters from saved model: LR is {params['lr']} and current epoch is "
-                        f"{self.start_epoch}")
+            if os.path.exists(path) or params.get("resume_required", False):
+                sd, ep, lr = ckpt.load_checkpoint(path)
+                flat, cnt = self.spec.flatten(sd)
+                self.start_epoch = ep + 1
+                if lr is not None:
+                    params["lr"] = lr
+                logger.info(f"Loaded parameters from saved model: LR is {params['lr']} and current epoch is "
+                            f"{self.start_epoch}")
+            else:
+                # the shipped YAMLs resume from a pre-trained checkpoint that is not part of any repository
+                # (the reference dies in torch.load here); start from the random initialisation instead
+                logger.warning(f"resumed_model is set but {path} does not exist: starting from random "
+                               f"initialisation at epoch 1 (set resume_required: true to make this an error)")
         self.G = flat.to(self.device)
         self.G_cnt = cnt[: max(self.spec.n_counters, 0)].to(self.device) if self.spec.n_counters else \
             torch.zeros(0, dtype=torch.long, device=self.device)
