@@ -46,9 +46,23 @@ void dba_set_error(const char* fmt, ...);
 extern unsigned long long g_dba_launches;
 #define DBA_COUNT_LAUNCH(n) (g_dba_launches += (n))
 
+// Activation element mode of the tensor-core network kernels (conv / wgrad / BatchNorm / pooling / input stage / head /
+// weight packing).  0: bf16 activations, 8 channels per 16-byte chunk ("planar-8"), tcgen05.mma.kind::f16.
+// 1: fp32 activations, 4 channels per 16-byte chunk ("planar-4"), tcgen05.mma.kind::tf32 - the precision class of the
+// reference (fp32 tensors, TF32 convolutions: cuDNN's allow_tf32 default).  Both modes share ONE byte geometry: a
+// "row" is a 16-byte chunk, planes are arrays of rows, UMMA core matrices are 8 rows x 16 bytes, and one MMA consumes
+// 32 bytes of K per row, so every descriptor, pitch and shift below is mode-independent; only the number of channels
+// per chunk (V) and the MMA kind change.  Set once by the executor (dba_set_act_dtype); a library-wide mode like a
+// BLAS math mode, not a per-call argument.
+extern int g_dba_act_mode;
+
 namespace dba {
 
 constexpr int kNumSMs = 148;
+
+// 16-byte chunk <-> V floats (V = 8: bf16, V = 4: fp32)
+template <int V> __device__ __forceinline__ void chunk_unpack(const uint4 u, float (&f)[V]);
+template <int V> __device__ __forceinline__ uint4 chunk_pack(const float (&f)[V]);
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -196,11 +210,68 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn, i
          (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// kind::tf32: fp32 operands in shared memory, read as tf32 (10-bit mantissa) by the tensor core; K = 8 per instruction.
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+template <bool TF32>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                     uint32_t accumulate) {
+  if (TF32) umma_tf32(tmem_d, desc_a, desc_b, idesc, accumulate);
+  else umma_f16(tmem_d, desc_a, desc_b, idesc, accumulate);
+}
+// Instruction descriptor for kind::tf32: tf32 x tf32 -> fp32 (operand format code 2).
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(a_mn) << 15) |
+         (static_cast<uint32_t>(b_mn) << 16) | (static_cast<uint32_t>(N >> 3) << 17) |
+         (static_cast<uint32_t>(M >> 4) << 24);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
 }
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+
+template <> __device__ __forceinline__ void chunk_unpack<8>(const uint4 u, float (&f)[8]) {
+  f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
+  f[4] = bf16lo(u.z); f[5] = bf16hi(u.z); f[6] = bf16lo(u.w); f[7] = bf16hi(u.w);
+}
+template <> __device__ __forceinline__ void chunk_unpack<4>(const uint4 u, float (&f)[4]) {
+  f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+}
+template <> __device__ __forceinline__ uint4 chunk_pack<8>(const float (&f)[8]) {
+  uint4 p;
+  p.x = pack_bf16x2(f[0], f[1]); p.y = pack_bf16x2(f[2], f[3]);
+  p.z = pack_bf16x2(f[4], f[5]); p.w = pack_bf16x2(f[6], f[7]);
+  return p;
+}
+template <> __device__ __forceinline__ uint4 chunk_pack<4>(const float (&f)[4]) {
+  uint4 p;
+  p.x = __float_as_uint(f[0]); p.y = __float_as_uint(f[1]); p.z = __float_as_uint(f[2]); p.w = __float_as_uint(f[3]);
+  return p;
+}
+// One element of a planar buffer addressed in 16-byte rows: channel c of row r lives in chunk (c / V) * R + r.
+template <int V> __device__ __forceinline__ float elem_load(const uint4* base, long long row, int j);
+template <> __device__ __forceinline__ float elem_load<8>(const uint4* base, long long row, int j) {
+  return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base + row)[j]);
+}
+template <> __device__ __forceinline__ float elem_load<4>(const uint4* base, long long row, int j) {
+  return reinterpret_cast<const float*>(base + row)[j];
+}
+template <int V> __device__ __forceinline__ void elem_store(uint4* base, long long row, int j, float v);
+template <> __device__ __forceinline__ void elem_store<8>(uint4* base, long long row, int j, float v) {
+  reinterpret_cast<__nv_bfloat16*>(base + row)[j] = __float2bfloat16(v);
+}
+template <> __device__ __forceinline__ void elem_store<4>(uint4* base, long long row, int j, float v) {
+  reinterpret_cast<float*>(base + row)[j] = v;
+}
 
 }  // namespace dba

@@ -45,24 +45,25 @@ constexpr int kMaxSB = 16;      // weight-stream pipeline depth limit (barrier s
 constexpr int kThreads = 64 + 32 * kEpiWarps;
 
 struct ConvArgs {
-  const __nv_bfloat16* X;      // [Kx][Cin/8][R][8]
-  const __nv_bfloat16* Wt;     // [K][taps][Cin/8][Cout][8]
-  __nv_bfloat16* Y;            // [K][Cout/8][Ro][8]
-  const __nv_bfloat16* Res;    // optional, layout of Y
+  // All tensors are addressed in 16-byte chunks ("rows") holding V channels: V = 8 (bf16) or 4 (fp32 / tf32 mode).
+  const uint4* X;              // [Kx][Cin/V][R]
+  const uint4* Wt;             // [K][taps][Cin/V][Cout]
+  uint4* Y;                    // [K][Cout/V][Ro]
+  const uint4* Res;            // optional, layout of Y
   const float* scale;          // optional [K][Cout]
   const float* shift;          // optional [K][Cout]
   float* stats;                // optional [K][Cout][2]  (sum, sum of squares over stored outputs)
-  long long x_client_stride;   // elements; 0 = all clients read the same input (shared evaluation batch)
-  long long x_plane_stride;    // elements between channel-chunk planes (= R*8)
+  long long x_client_stride;   // rows; 0 = all clients read the same input (shared evaluation batch)
+  long long x_plane_stride;    // rows between channel-chunk planes (= R)
   long long y_client_stride, y_plane_stride;
-  long long w_client_stride;   // elements between the clients' packed weight sets (0 = one model for all)
+  long long w_client_stride;   // rows between the clients' packed weight sets (0 = one model for all)
   long long ss_stride;         // floats between the clients' scale / shift rows
   long long stats_stride;      // floats between the clients' statistics rows
   int K, Cin, Cout, taps;      // taps = 1 (1x1) or 9 (3x3, pad 1)
   int H, W, Wp, S, lead, B;    // input (= compute) geometry
   int T;                       // row tiles per pass
   int NB;                      // output channels per n-block (<= 256), Cout % NB == 0
-  int KB;                      // input channels per k-block (16, 32 or 64)
+  int KB;                      // input channels per k-block: 2, 4 or 8 chunks (bf16: 16 / 32 / 64, tf32: 8 / 16 / 32)
   int relu;
   int sub;                     // 1 = same grid, 2 = keep even (h, w) only (stride-2 convolution)
   int Ho, Wo, Wpo, So, leado;  // output geometry (equals input geometry when sub == 1)
@@ -122,16 +123,18 @@ __device__ __forceinline__ void warp_transpose_reduce32(float (&v)[32], int lane
 #define DBG_T0() long long t0__ = a.dbg ? clock64() : 0
 #define DBG_ADD(slot) do { if (a.dbg) { long long t1__ = clock64(); dbgacc[slot] += t1__ - t0__; t0__ = t1__; } } while (0)
 
-template <int KC2>
+template <int KC2, bool TF32>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) {
+  constexpr int V = TF32 ? 4 : 8;                // channels per 16-byte chunk
+  constexpr int NG = 32 / V;                     // chunks per 32-channel epilogue group
   long long dbgacc[4] = {0, 0, 0, 0};
   const long long dbg_start = a.dbg ? clock64() : 0;
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kc = a.KB >> 3;                      // 16-byte channel chunks per k-block
+  const int kc = a.KB / V;                       // 16-byte channel chunks per k-block
   const int nkb = a.Cin / a.KB;
   const int nnb = a.Cout / a.NB;
-  const int planes = a.Cin >> 3;
+  const int planes = a.Cin / V;
   const uint32_t pitchA = (uint32_t)a.rowsA * 16u;
   const int npar = (a.in_s2d && a.taps == 9) ? 4 : 1;      // parity planes staged per k-block
   const uint32_t bytesA = (uint32_t)(npar * kc) * pitchA;
@@ -201,8 +204,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
         const int group = item / a.num_pass;
         const int pass = item - group * a.num_pass;
         const int nb = group % nnb, k = group / nnb;
-        const __nv_bfloat16* xk = a.X + (long long)k * a.x_client_stride;
-        const __nv_bfloat16* wk = a.Wt + (long long)k * a.w_client_stride;
+        const uint4* xk = a.X + (long long)k * a.x_client_stride;
+        const uint4* wk = a.Wt + (long long)k * a.w_client_stride;
         if (a.resident && group != cur_group) {
           cur_group = group;
           if (lane == 0) {
@@ -214,7 +217,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             if (lane == 0) bulk_g2s(smB, wk, a.wbytes, &b_full[0]);            // [tap][plane][Cout][8] is contiguous
           } else {
             for (int tp = lane; tp < a.taps * planes; tp += 32)
-              bulk_g2s(smB + (size_t)tp * pitchB, wk + ((long long)tp * a.Cout + (long long)nb * a.NB) * 8, pitchB,
+              bulk_g2s(smB + (size_t)tp * pitchB, wk + ((long long)tp * a.Cout + (long long)nb * a.NB), pitchB,
                        &b_full[0]);
           }
           ++wloads;
@@ -231,7 +234,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           DBG_ADD(0);
           for (int i = lane; i < npar * kc; i += 32) {
             const int pp = i / kc, c = i - pp * kc;
-            const __nv_bfloat16* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0 * 8;
+            const uint4* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0;
             bulk_g2s(smA + (size_t)sa * bytesA + (size_t)i * pitchA, src, pitchA, &a_full[sa]);
           }
           pa.advance(a.SA);
@@ -243,11 +246,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
               mbar_arrive_expect_tx(&b_full[sb], bytesB);
             }
             __syncwarp();
-            const __nv_bfloat16* wsrc = wk + (((long long)tap * planes + kb * kc) * a.Cout + (long long)nb * a.NB) * 8;
+            const uint4* wsrc = wk + (((long long)tap * planes + kb * kc) * a.Cout + (long long)nb * a.NB);
             if (nnb == 1) {
               if (lane == 0) bulk_g2s(smB + (size_t)sb * bytesB, wsrc, bytesB, &b_full[sb]);   // kc planes contiguous
             } else if (lane < kc) {
-              bulk_g2s(smB + (size_t)sb * bytesB + (size_t)lane * pitchB, wsrc + (long long)lane * a.Cout * 8, pitchB,
+              bulk_g2s(smB + (size_t)sb * bytesB + (size_t)lane * pitchB, wsrc + (long long)lane * a.Cout, pitchB,
                        &b_full[sb]);
             }
             pb.advance(a.SB);
@@ -260,7 +263,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     if (elect_one()) {
       Pipe pa, pb, pacc;
       int cur_group = -1, wuses = 0;
-      const uint32_t idesc = umma_idesc_bf16(kTileM, a.NB, 0, 0);
+      const uint32_t idesc = TF32 ? umma_idesc_tf32(kTileM, a.NB, 0, 0) : umma_idesc_bf16(kTileM, a.NB, 0, 0);
       const uint32_t kstepA = (2u * pitchA) >> 4, kstepB = (2u * pitchB) >> 4;
       const uint64_t dBres = umma_desc_noswz(smem_u32(smB), pitchB, 128);      // + stage / tap offset in 16-byte units
       for (int item = item_lo; item < item_hi; ++item) {
@@ -300,11 +303,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             uint32_t d_tmem = tmem_base + (uint32_t)(as * accCols);
             uint64_t da = dA0 + (uint64_t)(int64_t)tap_shift[tap];    // halo + shift >= 0: no borrow out of the field
             for (int t = 0; t < a.T; ++t, d_tmem += (uint32_t)a.NB, da += (uint64_t)kTileM) {
-              umma_f16(d_tmem, da, dB0, idesc, first);
-              if (KC2 >= 2) umma_f16(d_tmem, da + kstepA, dB0 + kstepB, idesc, 1u);
+              umma<TF32>(d_tmem, da, dB0, idesc, first);
+              if (KC2 >= 2) umma<TF32>(d_tmem, da + kstepA, dB0 + kstepB, idesc, 1u);
               if (KC2 >= 4) {
-                umma_f16(d_tmem, da + 2 * kstepA, dB0 + 2 * kstepB, idesc, 1u);
-                umma_f16(d_tmem, da + 3 * kstepA, dB0 + 3 * kstepB, idesc, 1u);
+                umma<TF32>(d_tmem, da + 2 * kstepA, dB0 + 2 * kstepB, idesc, 1u);
+                umma<TF32>(d_tmem, da + 3 * kstepA, dB0 + 3 * kstepB, idesc, 1u);
               }
             }
             if (!a.resident) {
@@ -376,7 +379,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             orow[i] = rrow[i] = d2s_row[i] = (long long)a.leado + (long long)b * a.So + (2 * h) * a.Wpo + 2 * w;
           } else if (a.out_s2d) {
             rrow[i] = (long long)a.lead + qrow;
-            orow[i] = (long long)(((h & 1u) << 1) | (w & 1u)) * (a.y_plane_stride >> 3) * (a.Cout >> 3)
+            orow[i] = (long long)(((h & 1u) << 1) | (w & 1u)) * a.y_plane_stride * (a.Cout / V)
                       + (long long)a.leado + (long long)b * a.So + (h >> 1) * a.Wpo + (w >> 1);
           } else {
             orow[i] = rrow[i] = (long long)a.lead + qrow;
@@ -388,8 +391,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       mbar_wait(&acc_full[as], pacc.phase(a.NS));
       DBG_ADD(0);
       tc_fence_after();
-      __nv_bfloat16* yk = a.Y + (long long)k * a.y_client_stride;
-      const __nv_bfloat16* rk = a.Res ? a.Res + (long long)k * a.res_client_stride : nullptr;
+      uint4* yk = a.Y + (long long)k * a.y_client_stride;
+      const uint4* rk = a.Res ? a.Res + (long long)k * a.res_client_stride : nullptr;
       float* gs = a.stats ? a.stats + (long long)k * a.stats_stride + (long long)nb * a.NB * 2 : nullptr;
       for (int c0 = c_first; c0 < a.NB; c0 += c_step) {
         // u1/u2 hold scale/shift (evaluation epilogue) or the running sum / sum of squares (training epilogue);
@@ -421,22 +424,25 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             for (int j = 0; j < 32; ++j) sv[j] = fmaf(sv[j], u1[j], u2[j]);
           }
           if (!store[i]) continue;
-          long long obase = (long long)((nb * a.NB + c0) >> 3) * a.y_plane_stride + orow[i] * 8;
+          long long obase = (long long)((nb * a.NB + c0) / V) * a.y_plane_stride + orow[i];
           if (a.out_s2d == 3) {
             const int cb = nb * a.NB + c0, par = cb / a.cgrp, cc = cb - par * a.cgrp;
-            obase = (long long)(cc >> 3) * a.y_plane_stride + (d2s_row[i] + (par >> 1) * a.Wpo + (par & 1)) * 8;
+            obase = (long long)(cc / V) * a.y_plane_stride + (d2s_row[i] + (par >> 1) * a.Wpo + (par & 1));
           }
           if (rk) {
-            uint4 r[4];
-            const long long rbase = (long long)((nb * a.NB + c0) >> 3) * a.res_plane_stride + rrow[i] * 8;
+            const long long rbase = (long long)((nb * a.NB + c0) / V) * a.res_plane_stride + rrow[i];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) r[g] = *reinterpret_cast<const uint4*>(rk + rbase + g * a.res_plane_stride);
+            for (int g0 = 0; g0 < NG; g0 += 4) {       // four 16-byte loads in flight
+              uint4 r[4];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              sv[g * 8 + 0] += bf16lo(r[g].x); sv[g * 8 + 1] += bf16hi(r[g].x);
-              sv[g * 8 + 2] += bf16lo(r[g].y); sv[g * 8 + 3] += bf16hi(r[g].y);
-              sv[g * 8 + 4] += bf16lo(r[g].z); sv[g * 8 + 5] += bf16hi(r[g].z);
-              sv[g * 8 + 6] += bf16lo(r[g].w); sv[g * 8 + 7] += bf16hi(r[g].w);
+              for (int g = 0; g < 4; ++g) r[g] = rk[rbase + (g0 + g) * a.res_plane_stride];
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                float f[V];
+                chunk_unpack<V>(r[g], f);
+#pragma unroll
+                for (int j = 0; j < V; ++j) sv[(g0 + g) * V + j] += f[j];
+              }
             }
           }
           if (a.relu) {
@@ -444,19 +450,18 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             for (int j = 0; j < 32; ++j) sv[j] = fmaxf(sv[j], 0.f);
           }
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {            // 4 chunks of 8 channels -> 4 coalesced 16-byte stores
-            uint4 pk;
-            pk.x = pack_bf16x2(sv[g * 8 + 0], sv[g * 8 + 1]); pk.y = pack_bf16x2(sv[g * 8 + 2], sv[g * 8 + 3]);
-            pk.z = pack_bf16x2(sv[g * 8 + 4], sv[g * 8 + 5]); pk.w = pack_bf16x2(sv[g * 8 + 6], sv[g * 8 + 7]);
-            *reinterpret_cast<uint4*>(yk + obase + g * a.y_plane_stride) = pk;
+          for (int g = 0; g < NG; ++g) {           // 32 channels -> NG coalesced 16-byte stores
+            float f[V];
+#pragma unroll
+            for (int j = 0; j < V; ++j) f[j] = sv[g * V + j];
+            const uint4 pk = chunk_pack<V>(f);
+            yk[obase + g * a.y_plane_stride] = pk;
             if (gs) {
-              // statistics of the value as stored (bf16-rounded), so BatchNorm normalises exactly what it reads
-              const float r0 = bf16lo(pk.x), r1 = bf16hi(pk.x), r2 = bf16lo(pk.y), r3 = bf16hi(pk.y);
-              const float r4 = bf16lo(pk.z), r5 = bf16hi(pk.z), r6 = bf16lo(pk.w), r7 = bf16hi(pk.w);
-              u1[g * 8 + 0] += r0; u2[g * 8 + 0] += r0 * r0; u1[g * 8 + 1] += r1; u2[g * 8 + 1] += r1 * r1;
-              u1[g * 8 + 2] += r2; u2[g * 8 + 2] += r2 * r2; u1[g * 8 + 3] += r3; u2[g * 8 + 3] += r3 * r3;
-              u1[g * 8 + 4] += r4; u2[g * 8 + 4] += r4 * r4; u1[g * 8 + 5] += r5; u2[g * 8 + 5] += r5 * r5;
-              u1[g * 8 + 6] += r6; u2[g * 8 + 6] += r6 * r6; u1[g * 8 + 7] += r7; u2[g * 8 + 7] += r7 * r7;
+              // statistics of the value as stored (bf16-rounded in bf16 mode), so BatchNorm normalises exactly what
+              // it reads
+              chunk_unpack<V>(pk, f);
+#pragma unroll
+              for (int j = 0; j < V; ++j) { u1[g * V + j] += f[j]; u2[g * V + j] += f[j] * f[j]; }
             }
           }
         }
@@ -525,7 +530,10 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
   DBA_REQUIRE(ksize == 1 || ksize == 3 || ksize == 5 || (ksize == 2 && out_s2d == 3),
               "dba_conv_tc: ksize must be 1, 3 or 5 (2 with out mode 3), got %d", ksize);
-  DBA_REQUIRE(Cin % 16 == 0 && Cout % 32 == 0, "dba_conv_tc: Cin (%d) %% 16 and Cout (%d) %% 32 must be 0", Cin, Cout);
+  const bool tf32 = g_dba_act_mode == 1;
+  const int V = tf32 ? 4 : 8;
+  DBA_REQUIRE(Cin % (2 * V) == 0 && Cout % 32 == 0, "dba_conv_tc: Cin (%d) %% %d and Cout (%d) %% 32 must be 0", Cin,
+              2 * V, Cout);
   DBA_REQUIRE(sub == 1 || (sub == 2 && H % 2 == 0 && W % 2 == 0), "dba_conv_tc: sub=%d needs even H, W", sub);
   DBA_REQUIRE(scale == nullptr || shift != nullptr, "dba_conv_tc: scale needs shift (shift alone = bias epilogue)");
   DBA_REQUIRE(!(shift && stats), "dba_conv_tc: the affine epilogue and the statistics epilogue are exclusive");
@@ -536,8 +544,8 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
               "dba_conv_tc: out mode 3 needs Cout = 4*C, C %% 32 == 0, no residual / statistics (Cout=%d)", Cout);
   ConvArgs a{};
   a.in_s2d = in_s2d ? 1 : 0; a.out_s2d = out_s2d;
-  a.X = (const __nv_bfloat16*)X; a.Wt = (const __nv_bfloat16*)Wt; a.Y = (__nv_bfloat16*)Y;
-  a.Res = (const __nv_bfloat16*)Res; a.scale = scale; a.shift = shift; a.stats = stats;
+  a.X = (const uint4*)X; a.Wt = (const uint4*)Wt; a.Y = (uint4*)Y;
+  a.Res = (const uint4*)Res; a.scale = scale; a.shift = shift; a.stats = stats;
   a.K = K; a.Cin = Cin; a.Cout = Cout; a.taps = ksize * ksize;
   a.H = H; a.W = W; a.Wp = W + 1; a.S = (H + 1) * a.Wp; a.lead = a.Wp + 1; a.B = B;
   a.relu = relu; a.sub = sub;
@@ -547,22 +555,24 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   a.cgrp = out_s2d == 3 ? Cout / 4 : Cout;
   a.Wpo = a.Wo + 1; a.So = (a.Ho + 1) * a.Wpo; a.leado = a.Wpo + 1;
   const long long R = dba_conv_rows(B, H, W), Ro = dba_conv_rows(B, a.Ho, a.Wo);
-  a.x_plane_stride = R * 8;
-  a.x_client_stride = x_shared ? 0 : (long long)(in_s2d ? 4 : 1) * (Cin / 8) * R * 8;
-  a.y_plane_stride = Ro * 8;
-  a.y_client_stride = (long long)(out_s2d == 1 ? 4 : 1) * ((out_s2d == 3 ? Cout / 4 : Cout) / 8) * Ro * 8;
-  a.res_plane_stride = out_s2d == 1 ? R * 8 : a.y_plane_stride;
-  a.res_client_stride = out_s2d == 1 ? (long long)(Cout / 8) * R * 8 : a.y_client_stride;
-  a.w_client_stride = w_client_stride;
+  a.x_plane_stride = R;
+  a.x_client_stride = x_shared ? 0 : (long long)(in_s2d ? 4 : 1) * (Cin / V) * R;
+  a.y_plane_stride = Ro;
+  a.y_client_stride = (long long)(out_s2d == 1 ? 4 : 1) * ((out_s2d == 3 ? Cout / 4 : Cout) / V) * Ro;
+  a.res_plane_stride = out_s2d == 1 ? R : a.y_plane_stride;
+  a.res_client_stride = out_s2d == 1 ? (long long)(Cout / V) * R : a.y_client_stride;
+  DBA_REQUIRE(w_client_stride % V == 0, "dba_conv_tc: weight client stride %lld not a multiple of %d", w_client_stride, V);
+  a.w_client_stride = w_client_stride / V;          // the caller counts elements
   a.ss_stride = ss_stride;
   a.stats_stride = stats_stride;
-  a.KB = Cin >= 64 ? 64 : Cin;
-  if (in_s2d && ksize == 3 && a.KB > 32) a.KB = 32;      // four parity planes per k-block share the stage
-  DBA_REQUIRE(Cin % a.KB == 0 && (a.KB == 16 || a.KB == 32 || a.KB == 64), "dba_conv_tc: unsupported Cin=%d", Cin);
+  a.KB = Cin >= 8 * V ? 8 * V : Cin;                      // at most 128 bytes of K per row and stage
+  if (in_s2d && ksize == 3 && a.KB > 4 * V) a.KB = 4 * V;   // four parity planes per k-block share the stage
+  DBA_REQUIRE(Cin % a.KB == 0 && (a.KB == 2 * V || a.KB == 4 * V || a.KB == 8 * V), "dba_conv_tc: unsupported Cin=%d",
+              Cin);
   a.halo = ksize == 2 ? a.Wp + 1 : (ksize / 2) * (a.Wp + 1);
   a.ksz = ksize;
   a.vlo = g_conv_vlo; a.vhi = g_conv_vhi > 0 ? g_conv_vhi : (H > W ? H : W);
-  const int kc = a.KB / 8;
+  const int kc = a.KB / V;
   const long long body = (long long)B * a.S;
   // n-block and rows per pass: as many 128-row tiles as fit in TMEM (512 columns); when that leaves SMs idle, first
   // split wide output-channel blocks (halves the weight traffic per CTA), then shorten the passes.
@@ -591,7 +601,7 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
     const size_t bytesA = (size_t)npar * kc * a.rowsA * 16, bytesB = (size_t)kc * NB * 16;
     const size_t misc = 1024 + 2 * NB * sizeof(float) + 128;
     a.NS = (2 * T * NB <= 512) ? 2 : 1;
-    a.wbytes = (unsigned int)((size_t)a.taps * Cin * NB * 2);
+    a.wbytes = (unsigned int)((size_t)a.taps * (Cin / V) * NB * 16);
     a.resident = a.wbytes <= 100 * 1024 && 2 * bytesA + a.wbytes + misc <= budget;
     size_t breg;
     if (a.resident) {
@@ -624,17 +634,27 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   int dev = 0;
   DBA_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
-    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
-    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
-    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
     attr_set[dev] = true;
   }
   if (need < 120 * 1024) need = 120 * 1024;    // one CTA per SM: each CTA allocates all 512 TMEM columns
   const int grid = items < kNumSMs ? (int)items : kNumSMs;
-  const int kc2 = a.KB / 16;
-  if (kc2 == 4) conv_tc_kernel<4><<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
-  else if (kc2 == 2) conv_tc_kernel<2><<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
-  else conv_tc_kernel<1><<<grid, kThreads, need, (cudaStream_t)stream>>>(a);
+  const int kc2 = kc / 2;                      // MMAs (32 bytes of K each) per tap and k-block
+  const cudaStream_t st = (cudaStream_t)stream;
+  if (tf32) {
+    if (kc2 == 4) conv_tc_kernel<4, true><<<grid, kThreads, need, st>>>(a);
+    else if (kc2 == 2) conv_tc_kernel<2, true><<<grid, kThreads, need, st>>>(a);
+    else conv_tc_kernel<1, true><<<grid, kThreads, need, st>>>(a);
+  } else {
+    if (kc2 == 4) conv_tc_kernel<4, false><<<grid, kThreads, need, st>>>(a);
+    else if (kc2 == 2) conv_tc_kernel<2, false><<<grid, kThreads, need, st>>>(a);
+    else conv_tc_kernel<1, false><<<grid, kThreads, need, st>>>(a);
+  }
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
