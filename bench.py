@@ -115,6 +115,7 @@ def run_own(args) -> dict:
     comm = _dist_setup(args.gpus)
     W, K = args.warmup, args.steps
     raw = bench_params(W, K)
+    raw["compute_dtype"] = args.dtype
     if args.small:
         raw.update(synthetic_train_size=5000, synthetic_test_size=1000)
     params = Params(raw)
@@ -163,7 +164,8 @@ def run_own(args) -> dict:
     be = sim.backend
     out = {
         "metric": METRIC, "value": K / (ms / 1e3), "unit": "rounds/s", "n_gpus": comm.world, "steps": K, "warmup": W,
-        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": args.dtype if cuda else "fp32",
         "data": "synthetic CIFAR-10-shaped uint8 images (50000 train / 10000 test), random-init weights",
         "impl": "dba_mod_b200",
         "config": {"model": "CIFAR ResNet-18 (narrow 32/64/128/256, 2.8M params)", "global_batch": 640,
@@ -235,6 +237,9 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"],
+                    help="compute mode of the native executor: tf32 = fp32 activations + TF32 tensor-core math (the "
+                         "reference's precision class, default), bf16 = fast mode")
     ap.add_argument("--small", action="store_true", help="5000/1000 images (CPU smoke test only; not a valid number)")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: whatever libraries print while the benchmark runs (NCCL's version banner,

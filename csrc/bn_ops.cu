@@ -17,14 +17,17 @@ using namespace dba;
 namespace {
 
 struct BnArgs {
-  const __nv_bfloat16* y;      // raw conv output      [K][C/8][R][8]
-  const __nv_bfloat16* res;    // residual (fwd) or null
-  __nv_bfloat16* out;          // fwd: activation;  bwd: dy
-  const __nv_bfloat16* g;      // bwd: upstream gradient
-  const __nv_bfloat16* act;    // bwd: post-ReLU output of this BN (mask) or null
-  __nv_bfloat16* gmask;        // bwd: optional copy of g' (same geometry as g)
-  __nv_bfloat16* out2;         // fwd: optional second copy of the activation in space-to-depth form (4C channels on the
+  // planar buffers in 16-byte rows of V channels (V = 8: bf16 mode, V = 4: fp32 / tf32 mode)
+  const uint4* y;              // raw conv output      [K][C/V][R]
+  const uint4* res;            // residual (fwd) or null
+  uint4* out;                  // fwd: activation;  bwd: dy
+  const uint4* g;              // bwd: upstream gradient
+  const uint4* act;            // bwd: post-ReLU output of this BN (mask) or null
+  uint4* gmask;                // bwd: optional copy of g' (same geometry as g)
+  uint4* out2;                 // fwd: optional second copy of the activation in space-to-depth form (4C channels on the
                                // (H/2, W/2) grid, R2 rows per plane) for the next stage's stride-2 convolutions
+  uint2* out_split;            // tf32 mode, optional: bf16 hi/lo split copy of `out` ([K][2][C/8][R or Rup][8]) for wgrad
+  uint2* out2_split;           // tf32 mode, optional: split copy of out2 ([K][2][4C/8][R2][8])
   float* stats;                // fwd: [K][ld_stats] (sum, sumsq) pairs;  bwd: (sum g', sum g'*xhat) pairs
   float* saved;                // [K][ld_saved] (mean, rstd) pairs
   float* Wflat;                // [K][ldw] state rows (gamma, beta, running stats)
@@ -37,25 +40,15 @@ struct BnArgs {
   float momentum, eps;
 };
 
-__device__ __forceinline__ void unpack8(const uint4 u, float (&f)[8]) {
-  f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
-  f[4] = bf16lo(u.z); f[5] = bf16hi(u.z); f[6] = bf16lo(u.w); f[7] = bf16hi(u.w);
-}
-__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
-  uint4 p;
-  p.x = pack_bf16x2(f[0], f[1]); p.y = pack_bf16x2(f[2], f[3]);
-  p.z = pack_bf16x2(f[4], f[5]); p.w = pack_bf16x2(f[6], f[7]);
-  return p;
-}
-
-// grid (row blocks, C/8, K), 256 threads; each thread walks rows of one 8-channel plane.
+// grid (row blocks, C/V, K), 256 threads; each thread walks rows of one V-channel plane.
+template <int V>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
-  __shared__ float s_scale[8], s_shift[8];
+  __shared__ float s_scale[V], s_shift[V];
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int nv = a.nvalid[k];
   const float n = (float)nv * (float)(a.H * a.W);
-  if (threadIdx.x < 8) {
-    const int c = chunk * 8 + threadIdx.x;
+  if (threadIdx.x < V) {
+    const int c = chunk * V + threadIdx.x;
     float* w = a.Wflat + (long long)k * a.ldw;
     const float s1 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c];
     const float s2 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
@@ -77,103 +70,113 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   }
   __syncthreads();
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
-  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
+  const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
   const int total = a.B * S;
   for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
     const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
     if (h >= a.H || w >= a.W) continue;
-    const long long off = (plane + lead + q) * 8;
-    float o[8];
+    const long long off = plane + lead + q;
+    float o[V];
     if (b < nv) {
-      float v[8];
-      unpack8(*reinterpret_cast<const uint4*>(a.y + off), v);
+      float v[V];
+      chunk_unpack<V>(a.y[off], v);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = v[j] * s_scale[j] + s_shift[j];
+      for (int j = 0; j < V; ++j) o[j] = v[j] * s_scale[j] + s_shift[j];
       if (a.res) {
-        float r[8];
-        unpack8(*reinterpret_cast<const uint4*>(a.res + off), r);
+        float r[V];
+        chunk_unpack<V>(a.res[off], r);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] += r[j];
+        for (int j = 0; j < V; ++j) o[j] += r[j];
       }
       if (a.relu) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = fmaxf(o[j], 0.f);
+        for (int j = 0; j < V; ++j) o[j] = fmaxf(o[j], 0.f);
       }
     } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = 0.f;
+      for (int j = 0; j < V; ++j) o[j] = 0.f;
     }
-    const uint4 pk = pack8(o);
-    *reinterpret_cast<uint4*>(a.out + off) = pk;
+    const uint4 pk = chunk_pack_operand<V>(o);         // the activation is the next convolution's operand
+    a.out[off] = pk;
+    if constexpr (V == 4) {
+      if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.R, chunk, lead + q, o);
+    }
     if (a.out2) {
       const int W2p = (a.W >> 1) + 1, S2 = ((a.H >> 1) + 1) * W2p, lead2 = W2p + 1;
-      const long long plane2 = ((long long)k * 4 + (((h & 1) << 1) | (w & 1))) * (a.C >> 3) + chunk;
-      *reinterpret_cast<uint4*>(a.out2 + (plane2 * a.R2 + lead2 + (long long)b * S2 + (h >> 1) * W2p + (w >> 1)) * 8) = pk;
+      const int par = ((h & 1) << 1) | (w & 1);
+      const long long plane2 = ((long long)k * 4 + par) * (a.C / V) + chunk;
+      const long long row2 = lead2 + (long long)b * S2 + (h >> 1) * W2p + (w >> 1);
+      a.out2[plane2 * a.R2 + row2] = pk;
+      if constexpr (V == 4) {
+        if (a.out2_split) store_split(a.out2_split, k, (4 * a.C) >> 3, a.R2, par * (a.C >> 2) + chunk, row2, o);
+      }
     }
   }
 }
 
+template <int V>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
-  __shared__ float red[2][8][8];
+  __shared__ float red[2][8][V];
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int nv = a.nvalid[k];
-  float mean[8], rstd[8];
+  float mean[V], rstd[V];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    mean[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * 8 + j)];
-    rstd[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * 8 + j) + 1];
+  for (int j = 0; j < V; ++j) {
+    mean[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * V + j)];
+    rstd[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * V + j) + 1];
   }
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
-  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
+  const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
   const int total = min(a.B, nv) * S;
-  float sg[8], sgx[8];
+  float sg[V], sgx[V];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) sg[j] = sgx[j] = 0.f;
+  for (int j = 0; j < V; ++j) sg[j] = sgx[j] = 0.f;
   for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
     const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
     if (h >= a.H || w >= a.W) continue;
-    const long long off = (plane + lead + q) * 8;
-    float g[8], y[8];
-    unpack8(*reinterpret_cast<const uint4*>(a.g + off), g);
-    unpack8(*reinterpret_cast<const uint4*>(a.y + off), y);
+    const long long off = plane + lead + q;
+    float g[V], y[V];
+    chunk_unpack<V>(a.g[off], g);
+    chunk_unpack<V>(a.y[off], y);
     if (a.act) {
-      float o[8];
-      unpack8(*reinterpret_cast<const uint4*>(a.act + off), o);
+      float o[V];
+      chunk_unpack<V>(a.act[off], o);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+      for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < V; ++j) {
       sg[j] += g[j];
       sgx[j] += g[j] * (y[j] - mean[j]) * rstd[j];
     }
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int j = 0; j < V; ++j) {
     sg[j] = warp_sum(sg[j]);
     sgx[j] = warp_sum(sgx[j]);
   }
   if (lane == 0) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { red[0][warp][j] = sg[j]; red[1][warp][j] = sgx[j]; }
+    for (int j = 0; j < V; ++j) { red[0][warp][j] = sg[j]; red[1][warp][j] = sgx[j]; }
   }
   __syncthreads();
-  if (threadIdx.x < 16) {
-    const int which = threadIdx.x >> 3, j = threadIdx.x & 7;
+  if (threadIdx.x < 2 * V) {
+    const int which = threadIdx.x / V, j = threadIdx.x % V;
     float t = 0.f;
     for (int w = 0; w < 8; ++w) t += red[which][w][j];
-    if (t != 0.f) atomicAdd(&a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * (chunk * 8 + j) + which], t);
+    if (t != 0.f) atomicAdd(&a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * (chunk * V + j) + which], t);
   }
 }
 
+template <int V>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
-  __shared__ float s_sc[8], s_mg[8], s_mgx[8], s_mean[8], s_rstd[8];
+  __shared__ float s_sc[V], s_mg[V], s_mgx[V], s_mean[V], s_rstd[V];
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int nv = a.nvalid[k];
   const float n = (float)nv * (float)(a.H * a.W);
-  if (threadIdx.x < 8) {
-    const int c = chunk * 8 + threadIdx.x;
+  if (threadIdx.x < V) {
+    const int c = chunk * V + threadIdx.x;
     const float sg = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c];
     const float sgx = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
     const float mean = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c];
@@ -192,130 +195,148 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   __syncthreads();
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
   const int Wpu = 2 * a.W + 1, Su = (2 * a.H + 1) * Wpu, leadu = Wpu + 1;
-  const long long plane = ((long long)k * (a.C >> 3) + chunk) * a.R;
-  const long long plane_up = ((long long)k * (a.C >> 3) + chunk) * a.Rup;
+  const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
+  const long long plane_up = ((long long)k * (a.C / V) + chunk) * a.Rup;
   const int total = a.B * S;
   for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
     const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
     if (h >= a.H || w >= a.W) continue;
-    const long long off = (plane + lead + q) * 8;
-    float d[8], gm[8];
+    const long long off = plane + lead + q;
+    float d[V], gm[V];
     if (b < nv) {
-      float g[8], y[8];
-      unpack8(*reinterpret_cast<const uint4*>(a.g + off), g);
-      unpack8(*reinterpret_cast<const uint4*>(a.y + off), y);
+      float g[V], y[V];
+      chunk_unpack<V>(a.g[off], g);
+      chunk_unpack<V>(a.y[off], y);
       if (a.act) {
-        float o[8];
-        unpack8(*reinterpret_cast<const uint4*>(a.act + off), o);
+        float o[V];
+        chunk_unpack<V>(a.act[off], o);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+        for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < V; ++j) {
         const float xh = (y[j] - s_mean[j]) * s_rstd[j];
         gm[j] = g[j];
         d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
       }
     } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) d[j] = gm[j] = 0.f;
+      for (int j = 0; j < V; ++j) d[j] = gm[j] = 0.f;
     }
-    if (a.gmask) *reinterpret_cast<uint4*>(a.gmask + off) = pack8(gm);
-    long long doff = off;
-    if (a.up) doff = (plane_up + leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w) * 8;
-    *reinterpret_cast<uint4*>(a.out + doff) = pack8(d);
+    if (a.gmask) a.gmask[off] = chunk_pack<V>(gm);
+    long long doff = off, drow = lead + q;
+    if (a.up) {
+      drow = leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w;
+      doff = plane_up + drow;
+    }
+    a.out[doff] = chunk_pack_operand<V>(d);            // dy is the input-gradient convolution's operand
+    if constexpr (V == 4) {
+      if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.up ? a.Rup : a.R, chunk, drow, d);
+    }
   }
 }
 
 // ------------------------------------------------------------------------------------------------ max pooling
-// MaxPool2d(3, stride 2, pad 1) on planar-8 activations (Tiny-ImageNet stem, models/resnet_tinyimagenet.py:147).
+// MaxPool2d(3, stride 2, pad 1) on planar activations (Tiny-ImageNet stem, models/resnet_tinyimagenet.py:147).
 // Inputs are post-ReLU (>= 0) and the halo rows / columns of the layout are zero, so the window can be read without
 // bounds checks: a zero never beats a real maximum.  Backward is gather-style (no atomics): an input pixel receives
 // the gradient of every output window in which it is the first maximum in scan order (PyTorch's tie rule).
 struct PoolArgs {
-  const __nv_bfloat16* x;     // [K][C/8][Rin][8]   H x W grid
-  __nv_bfloat16* y;           // [K][C/8][Rout][8]  H/2 x W/2 grid (fwd out)
-  const __nv_bfloat16* gy;    // bwd: gradient wrt y
-  __nv_bfloat16* gx;          // bwd: gradient wrt x
+  const uint4* x;             // [K][C/V][Rin]   H x W grid
+  uint4* y;                   // [K][C/V][Rout]  H/2 x W/2 grid (fwd out)
+  const uint4* gy;            // bwd: gradient wrt y
+  uint4* gx;                  // bwd: gradient wrt x
+  uint2* y_split;             // fwd, tf32 mode, optional: bf16 hi/lo split copy of y for wgrad
   long long Rin, Rout;
   int K, C, B, H, W;
 };
-__device__ __forceinline__ uint4 max8(const uint4 a, const uint4 b) {
-  float x[8], y[8];
-  unpack8(a, x); unpack8(b, y);
+template <int V>
+__device__ __forceinline__ uint4 chunk_max(const uint4 a, const uint4 b) {
+  float x[V], y[V];
+  chunk_unpack<V>(a, x); chunk_unpack<V>(b, y);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) x[j] = fmaxf(x[j], y[j]);
-  return pack8(x);
+  for (int j = 0; j < V; ++j) x[j] = fmaxf(x[j], y[j]);
+  return chunk_pack<V>(x);
 }
+template <int V>
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const PoolArgs a) {
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int Ho = a.H >> 1, Wo = a.W >> 1;
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
   const int Wpo = Wo + 1, So = (Ho + 1) * Wpo, leado = Wpo + 1;
-  const long long pin = ((long long)k * (a.C >> 3) + chunk) * a.Rin, pout = ((long long)k * (a.C >> 3) + chunk) * a.Rout;
+  const long long pin = ((long long)k * (a.C / V) + chunk) * a.Rin, pout = ((long long)k * (a.C / V) + chunk) * a.Rout;
   const int total = a.B * Ho * Wo;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int wo = i % Wo, ho = (i / Wo) % Ho, b = i / (Wo * Ho);
     const long long c = pin + lead + (long long)b * S + (2 * ho) * Wp + 2 * wo;      // window centre (h=2ho, w=2wo)
-    uint4 m = *reinterpret_cast<const uint4*>(a.x + (c - Wp - 1) * 8);
+    uint4 m = a.x[c - Wp - 1];
 #pragma unroll
     for (int dh = -1; dh <= 1; ++dh)
 #pragma unroll
       for (int dw = -1; dw <= 1; ++dw)
-        if (dh != -1 || dw != -1) m = max8(m, *reinterpret_cast<const uint4*>(a.x + (c + dh * Wp + dw) * 8));
-    *reinterpret_cast<uint4*>(a.y + (pout + leado + (long long)b * So + ho * Wpo + wo) * 8) = m;
+        if (dh != -1 || dw != -1) m = chunk_max<V>(m, a.x[c + dh * Wp + dw]);
+    a.y[pout + leado + (long long)b * So + ho * Wpo + wo] = m;
+    if constexpr (V == 4) {
+      if (a.y_split) {
+        float f[4];
+        chunk_unpack<4>(m, f);
+        store_split(a.y_split, k, a.C >> 3, a.Rout, chunk, leado + (long long)b * So + ho * Wpo + wo, f);
+      }
+    }
   }
 }
+template <int V>
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const PoolArgs a) {
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int Ho = a.H >> 1, Wo = a.W >> 1;
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
   const int Wpo = Wo + 1, So = (Ho + 1) * Wpo, leado = Wpo + 1;
-  const long long pin = ((long long)k * (a.C >> 3) + chunk) * a.Rin, pout = ((long long)k * (a.C >> 3) + chunk) * a.Rout;
+  const long long pin = ((long long)k * (a.C / V) + chunk) * a.Rin, pout = ((long long)k * (a.C / V) + chunk) * a.Rout;
   const int total = a.B * a.H * a.W;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int w = i % a.W, h = (i / a.W) % a.H, b = i / (a.W * a.H);
     const long long me = pin + lead + (long long)b * S + h * Wp + w;
-    float xv[8], acc[8];
-    unpack8(*reinterpret_cast<const uint4*>(a.x + me * 8), xv);
+    float xv[V], acc[V];
+    chunk_unpack<V>(a.x[me], xv);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
     // output windows (ho, wo) with |2ho - h| <= 1 and |2wo - w| <= 1
     for (int ho = (h >> 1); ho <= ((h + 1) >> 1) && ho < Ho; ++ho)
       for (int wo = (w >> 1); wo <= ((w + 1) >> 1) && wo < Wo; ++wo) {
         const long long c = pin + lead + (long long)b * S + (2 * ho) * Wp + 2 * wo;
-        float g[8];
-        unpack8(*reinterpret_cast<const uint4*>(a.gy + (pout + leado + (long long)b * So + ho * Wpo + wo) * 8), g);
+        float g[V];
+        chunk_unpack<V>(a.gy[pout + leado + (long long)b * So + ho * Wpo + wo], g);
         // first maximum in scan order per channel; positions before `me` in the scan must be strictly smaller,
         // positions after it smaller or equal
-        bool first[8];
+        bool first[V];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) first[j] = true;
+        for (int j = 0; j < V; ++j) first[j] = true;
         const int my_dh = h - 2 * ho, my_dw = w - 2 * wo;
         for (int dh = -1; dh <= 1; ++dh)
           for (int dw = -1; dw <= 1; ++dw) {
             if (dh == my_dh && dw == my_dw) continue;
             const int hh = 2 * ho + dh, ww = 2 * wo + dw;
             if (hh < 0 || hh >= a.H || ww < 0 || ww >= a.W) continue;       // padding never wins (-inf in PyTorch)
-            float o[8];
-            unpack8(*reinterpret_cast<const uint4*>(a.x + (c + dh * Wp + dw) * 8), o);
+            float o[V];
+            chunk_unpack<V>(a.x[c + dh * Wp + dw], o);
             const bool before = dh < my_dh || (dh == my_dh && dw < my_dw);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) first[j] = first[j] && (before ? o[j] < xv[j] : o[j] <= xv[j]);
+            for (int j = 0; j < V; ++j) first[j] = first[j] && (before ? o[j] < xv[j] : o[j] <= xv[j]);
           }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += first[j] ? g[j] : 0.f;
+        for (int j = 0; j < V; ++j) acc[j] += first[j] ? g[j] : 0.f;
       }
-    *reinterpret_cast<uint4*>(a.gx + me * 8) = pack8(acc);
+    a.gx[me] = chunk_pack<V>(acc);
   }
 }
 
+inline int act_v() { return g_dba_act_mode == 1 ? 4 : 8; }
 inline dim3 bn_grid(int B, int H, int W, int C, int K) {
   const int total = B * (H + 1) * (W + 1);
   int rb = (total + 1023) / 1024;
   if (rb < 1) rb = 1;
   if (rb > 64) rb = 64;
-  return dim3(rb, C / 8, K);
+  return dim3(rb, C / act_v(), K);
 }
 
 }  // namespace
@@ -324,11 +345,20 @@ extern "C" {
 
 // out = relu?( (y - mean)*rstd*gamma + beta (+ res) ); also saves (mean, rstd) and updates the running statistics.
 // stats: pairs (sum, sumsq) at stats[k*ld_stats + stats_off + 2c]; saved likewise.  Offsets g/b/rm/rv index Wflat rows.
+int dba_bn_apply_split(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, void* out_split,
+                       void* out_s2d_split, float* stats, long long ld_stats, int stats_off, float* saved,
+                       long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off, int rm_off,
+                       int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H, int W,
+                       long long R, int relu, float momentum, float eps, void* stream);
 int dba_bn_apply_ex(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, float* stats,
                     long long ld_stats, int stats_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
                     long long ldw, int g_off, int b_off, int rm_off, int rv_off, const int* nvalid,
                     const unsigned char* active, int K, int C, int B, int H, int W, long long R, int relu,
-                    float momentum, float eps, void* stream);
+                    float momentum, float eps, void* stream) {
+  return dba_bn_apply_split(y, res, out, out_s2d, R_s2d, nullptr, nullptr, stats, ld_stats, stats_off, saved, ld_saved,
+                            saved_off, Wflat, ldw, g_off, b_off, rm_off, rv_off, nvalid, active, K, C, B, H, W, R, relu,
+                            momentum, eps, stream);
+}
 int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long long ld_stats, int stats_off,
                  float* saved, long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off,
                  int rm_off, int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H,
@@ -338,21 +368,26 @@ int dba_bn_apply(const void* y, const void* res, void* out, float* stats, long l
 }
 // out_s2d (nullable): the activation is ALSO written in space-to-depth form ([K][4C/8][R_s2d][8] on the (H/2, W/2)
 // grid, parity plane p = 2*(h&1) + (w&1)), the operand form of the next stage's stride-2 convolutions.
-int dba_bn_apply_ex(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, float* stats,
-                    long long ld_stats, int stats_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
-                    long long ldw, int g_off, int b_off, int rm_off, int rv_off, const int* nvalid,
-                    const unsigned char* active, int K, int C, int B, int H, int W, long long R, int relu,
-                    float momentum, float eps, void* stream) {
+// out_split / out_s2d_split (nullable, tf32 mode only): bf16 hi/lo split copies of out / out_s2d, the weight-gradient
+// kernel's operand form ([K][2][C/8][R][8], see store_split).
+int dba_bn_apply_split(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, void* out_split,
+                       void* out_s2d_split, float* stats, long long ld_stats, int stats_off, float* saved,
+                       long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off, int rm_off,
+                       int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H, int W,
+                       long long R, int relu, float momentum, float eps, void* stream) {
   DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_bn_apply: K=%d C=%d B=%d", K, C, B);
+  DBA_REQUIRE((!out_split && !out_s2d_split) || g_dba_act_mode == 1, "dba_bn_apply: split copies exist in tf32 mode only");
   DBA_REQUIRE(!out_s2d || (H % 2 == 0 && W % 2 == 0), "dba_bn_apply: space-to-depth output needs even H, W");
   BnArgs a{};
-  a.out2 = (__nv_bfloat16*)out_s2d; a.R2 = R_s2d;
-  a.y = (const __nv_bfloat16*)y; a.res = (const __nv_bfloat16*)res; a.out = (__nv_bfloat16*)out;
+  a.out2 = (uint4*)out_s2d; a.R2 = R_s2d;
+  a.out_split = (uint2*)out_split; a.out2_split = (uint2*)out_s2d_split;
+  a.y = (const uint4*)y; a.res = (const uint4*)res; a.out = (uint4*)out;
   a.stats = stats; a.saved = saved; a.Wflat = Wflat; a.nvalid = nvalid; a.active = active;
   a.ld_stats = ld_stats; a.ld_saved = ld_saved; a.ldw = ldw; a.R = R;
   a.stats_off = stats_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off; a.rm_off = rm_off; a.rv_off = rv_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.relu = relu; a.momentum = momentum; a.eps = eps;
-  bn_apply_kernel<<<bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream>>>(a);
+  if (act_v() == 4) bn_apply_kernel<4><<<bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream>>>(a);
+  else bn_apply_kernel<8><<<bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -362,34 +397,63 @@ int dba_bn_apply_ex(const void* y, const void* res, void* out, void* out_s2d, lo
 // dy: output, written on the (2H, 2W) grid at even positions when up != 0 (Rup = rows of that grid);
 // gmask: optional copy of the ReLU-masked upstream gradient; sums: scratch pairs [K][ld_sums] zeroed by the caller;
 // Gflat: d_gamma / d_beta are stored at g_off / b_off of the gradient rows.
+int dba_bn_backward_split(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
+                          float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
+                          float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
+                          const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
+                          void* stream);
 int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, void* gmask, float* sums,
                     long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off, float* Wflat,
                     long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
                     int B, int H, int W, long long R, int up, long long Rup, void* stream) {
+  return dba_bn_backward_split(g, y, act, dy, nullptr, gmask, sums, ld_sums, sums_off, saved, ld_saved, saved_off, Wflat,
+                               ldw, Gflat, ldg, g_off, b_off, nvalid, K, C, B, H, W, R, up, Rup, stream);
+}
+// dy_split (nullable, tf32 mode only): bf16 hi/lo split copy of dy for the weight-gradient kernel.
+int dba_bn_backward_split(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
+                          float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
+                          float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
+                          const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
+                          void* stream) {
   DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_bn_backward: K=%d C=%d B=%d", K, C, B);
+  DBA_REQUIRE(!dy_split || g_dba_act_mode == 1, "dba_bn_backward: split copies exist in tf32 mode only");
   BnArgs a{};
-  a.g = (const __nv_bfloat16*)g; a.y = (const __nv_bfloat16*)y; a.act = (const __nv_bfloat16*)act;
-  a.out = (__nv_bfloat16*)dy; a.gmask = (__nv_bfloat16*)gmask; a.stats = sums; a.saved = saved; a.Wflat = Wflat;
+  a.g = (const uint4*)g; a.y = (const uint4*)y; a.act = (const uint4*)act;
+  a.out = (uint4*)dy; a.gmask = (uint4*)gmask; a.stats = sums; a.out_split = (uint2*)dy_split; a.saved = saved; a.Wflat = Wflat;
   a.Gflat = Gflat; a.nvalid = nvalid;
   a.ld_stats = ld_sums; a.ld_saved = ld_saved; a.ldw = ldw; a.ldg = ldg; a.R = R; a.Rup = Rup;
   a.stats_off = sums_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.up = up;
   const dim3 grid = bn_grid(B, H, W, C, K);
-  bn_bwd_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
-  bn_bwd_apply_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  if (act_v() == 4) {
+    bn_bwd_reduce_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    bn_bwd_apply_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  } else {
+    bn_bwd_reduce_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    bn_bwd_apply_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  }
   DBA_COUNT_LAUNCH(2);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
 }
 
 // y = MaxPool2d(3, 2, 1)(x); x on the B x H x W grid, y on B x H/2 x W/2.  Rin / Rout = dba_conv_rows of the two grids.
+int dba_maxpool_fwd_split(const void* x, void* y, void* y_split, int K, int C, int B, int H, int W, long long Rin,
+                          long long Rout, void* stream);
 int dba_maxpool_fwd(const void* x, void* y, int K, int C, int B, int H, int W, long long Rin, long long Rout,
                     void* stream) {
+  return dba_maxpool_fwd_split(x, y, nullptr, K, C, B, H, W, Rin, Rout, stream);
+}
+int dba_maxpool_fwd_split(const void* x, void* y, void* y_split, int K, int C, int B, int H, int W, long long Rin,
+                          long long Rout, void* stream) {
   DBA_REQUIRE(K > 0 && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "dba_maxpool_fwd: K=%d C=%d H=%d W=%d", K, C, H, W);
-  PoolArgs a{(const __nv_bfloat16*)x, (__nv_bfloat16*)y, nullptr, nullptr, Rin, Rout, K, C, B, H, W};
+  DBA_REQUIRE(!y_split || g_dba_act_mode == 1, "dba_maxpool_fwd: split copies exist in tf32 mode only");
+  PoolArgs a{(const uint4*)x, (uint4*)y, nullptr, nullptr, (uint2*)y_split, Rin, Rout, K, C, B, H, W};
   int rb = (B * (H / 2) * (W / 2) + 1023) / 1024;
   if (rb > 64) rb = 64;
-  maxpool_fwd_kernel<<<dim3(rb < 1 ? 1 : rb, C / 8, K), 256, 0, (cudaStream_t)stream>>>(a);
+  const dim3 grid(rb < 1 ? 1 : rb, C / act_v(), K);
+  if (act_v() == 4) maxpool_fwd_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  else maxpool_fwd_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -398,10 +462,12 @@ int dba_maxpool_fwd(const void* x, void* y, int K, int C, int B, int H, int W, l
 int dba_maxpool_bwd(const void* x, const void* gy, void* gx, int K, int C, int B, int H, int W, long long Rin,
                     long long Rout, void* stream) {
   DBA_REQUIRE(K > 0 && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "dba_maxpool_bwd: K=%d C=%d H=%d W=%d", K, C, H, W);
-  PoolArgs a{(const __nv_bfloat16*)x, nullptr, (const __nv_bfloat16*)gy, (__nv_bfloat16*)gx, Rin, Rout, K, C, B, H, W};
+  PoolArgs a{(const uint4*)x, nullptr, (const uint4*)gy, (uint4*)gx, nullptr, Rin, Rout, K, C, B, H, W};
   int rb = (B * H * W + 1023) / 1024;
   if (rb > 64) rb = 64;
-  maxpool_bwd_kernel<<<dim3(rb < 1 ? 1 : rb, C / 8, K), 256, 0, (cudaStream_t)stream>>>(a);
+  const dim3 grid(rb < 1 ? 1 : rb, C / act_v(), K);
+  if (act_v() == 4) maxpool_bwd_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  else maxpool_bwd_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;

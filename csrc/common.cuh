@@ -258,6 +258,24 @@ template <> __device__ __forceinline__ uint4 chunk_pack<4>(const float (&f)[4]) 
   p.x = __float_as_uint(f[0]); p.y = __float_as_uint(f[1]); p.z = __float_as_uint(f[2]); p.w = __float_as_uint(f[3]);
   return p;
 }
+// fp32 -> nearest tf32 value (10-bit mantissa), kept in an fp32 register.  tcgen05 kind::tf32 reads fp32 operands by
+// dropping the low 13 mantissa bits (truncation); cuDNN's TF32 convolutions round to nearest.  Every kernel that
+// STORES a tensor which is later a tensor-core operand (activations, gradients w.r.t. conv outputs, packed weights)
+// rounds it here, so that the truncation is exact and the error matches the reference's TF32 path.
+__device__ __forceinline__ float tf32_rna(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+// chunk_pack for a tensor-core operand tensor: bf16 mode rounds by conversion, tf32 mode rounds to the tf32 grid.
+template <int V> __device__ __forceinline__ uint4 chunk_pack_operand(const float (&f)[V]);
+template <> __device__ __forceinline__ uint4 chunk_pack_operand<8>(const float (&f)[8]) { return chunk_pack<8>(f); }
+template <> __device__ __forceinline__ uint4 chunk_pack_operand<4>(const float (&f)[4]) {
+  uint4 p;
+  p.x = __float_as_uint(tf32_rna(f[0])); p.y = __float_as_uint(tf32_rna(f[1]));
+  p.z = __float_as_uint(tf32_rna(f[2])); p.w = __float_as_uint(tf32_rna(f[3]));
+  return p;
+}
 // One element of a planar buffer addressed in 16-byte rows: channel c of row r lives in chunk (c / V) * R + r.
 template <int V> __device__ __forceinline__ float elem_load(const uint4* base, long long row, int j);
 template <> __device__ __forceinline__ float elem_load<8>(const uint4* base, long long row, int j) {
@@ -265,6 +283,20 @@ template <> __device__ __forceinline__ float elem_load<8>(const uint4* base, lon
 }
 template <> __device__ __forceinline__ float elem_load<4>(const uint4* base, long long row, int j) {
   return reinterpret_cast<const float*>(base + row)[j];
+}
+// "Split" copy of one fp32 planar-4 chunk (tf32 mode): channels [4*chunk, 4*chunk + 4) of row `row` of client k as
+// bf16 hi = bf16(x) and lo = bf16(x - hi) halves of a [K][2][C/8][R][8] bf16 tensor (hi set, then lo set) - the operand
+// form of the weight-gradient kernel (csrc/wgrad_tc.cu).  `base` is addressed in 8-byte half chunks.
+__device__ __forceinline__ void store_split(uint2* base, long long k, long long planes8, long long R, int chunk,
+                                            long long row, const float (&f)[4]) {
+  const long long hi = (((k * 2) * planes8 + (chunk >> 1)) * R + row) * 2 + (chunk & 1);
+  uint2 ph, pl;
+  ph.x = pack_bf16x2(f[0], f[1]);
+  ph.y = pack_bf16x2(f[2], f[3]);
+  pl.x = pack_bf16x2(f[0] - bf16lo(ph.x), f[1] - bf16hi(ph.x));
+  pl.y = pack_bf16x2(f[2] - bf16lo(ph.y), f[3] - bf16hi(ph.y));
+  base[hi] = ph;
+  base[hi + planes8 * R * 2] = pl;
 }
 template <int V> __device__ __forceinline__ void elem_store(uint4* base, long long row, int j, float v);
 template <> __device__ __forceinline__ void elem_store<8>(uint4* base, long long row, int j, float v) {

@@ -454,7 +454,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
             float f[V];
 #pragma unroll
             for (int j = 0; j < V; ++j) f[j] = sv[g * V + j];
-            const uint4 pk = chunk_pack<V>(f);
+            // affine epilogue (evaluation, bias-only networks): the output is the next layer's operand -> tf32 grid
+            const uint4 pk = affine ? chunk_pack_operand<V>(f) : chunk_pack<V>(f);
             yk[obase + g * a.y_plane_stride] = pk;
             if (gs) {
               // statistics of the value as stored (bf16-rounded in bf16 mode), so BatchNorm normalises exactly what

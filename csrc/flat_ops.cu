@@ -10,6 +10,17 @@
 
 static char g_err[512] = "";
 unsigned long long g_dba_launches = 0;
+int g_dba_act_mode = 0;
+// Activation element mode of the network kernels: 0 = bf16 (kind::f16 MMA), 1 = fp32 activations with kind::tf32 MMA.
+extern "C" int dba_set_act_dtype(int mode) {
+  if (mode != 0 && mode != 1) {
+    dba_set_error("dba_set_act_dtype: mode %d (0 = bf16, 1 = tf32)", mode);
+    return DBA_ERR_ARG;
+  }
+  g_dba_act_mode = mode;
+  return DBA_OK;
+}
+extern "C" int dba_get_act_dtype() { return g_dba_act_mode; }
 extern "C" const char* dba_last_error() { return g_err; }
 void dba_set_error(const char* fmt, ...) {
   va_list ap;

@@ -174,6 +174,7 @@ extern "C" {
 // flatten = 1: y is [K][Ho*Wo*C/8][R1][8] on (B, 1, 1) with channel n = (i*Wo + j)*C + c, Ro = dba_conv_rows(B, 1, 1).
 int dba_maxpool2_fwd(const void* x, void* y, int K, int C, int B, int Hi, int Wi, int off, int Ho, int Wo, int flatten,
                      long long Ri, long long Ro, void* stream) {
+  DBA_REQUIRE(g_dba_act_mode == 0, "MnistNet pooling kernels run in bf16 mode only (dba_set_act_dtype(0))");
   DBA_REQUIRE(K > 0 && C % 8 == 0 && off >= 0 && off + 2 * Ho <= Hi && off + 2 * Wo <= Wi,
               "dba_maxpool2_fwd: K=%d C=%d window off=%d %dx%d on %dx%d", K, C, off, Ho, Wo, Hi, Wi);
   PoolArgs2 a{};
@@ -190,6 +191,7 @@ int dba_maxpool2_fwd(const void* x, void* y, int K, int C, int B, int Hi, int Wi
 int dba_maxpool2_bwd_relu_bias(const void* g, const void* x, void* dz, float* G, long long ldg, int b_off, int c_real,
                                int K, int C, int B, int Hi, int Wi, int off, int Ho, int Wo, int flatten, long long Ri,
                                long long Ro, void* stream) {
+  DBA_REQUIRE(g_dba_act_mode == 0, "MnistNet pooling kernels run in bf16 mode only (dba_set_act_dtype(0))");
   DBA_REQUIRE(K > 0 && C % 8 == 0 && off >= 0 && off + 2 * Ho <= Hi && off + 2 * Wo <= Wi,
               "dba_maxpool2_bwd: K=%d C=%d window off=%d %dx%d on %dx%d", K, C, off, Ho, Wo, Hi, Wi);
   PoolArgs2 a{};
@@ -205,6 +207,7 @@ int dba_maxpool2_bwd_relu_bias(const void* g, const void* x, void* dz, float* G,
 // dz = g * (act > 0) on the (B, H, W) grid, G[k*ldg + b_off + c] += sum dz (c < c_real).
 int dba_relu_bwd_bias(const void* g, const void* act, void* dz, float* G, long long ldg, int b_off, int c_real, int K,
                       int C, int B, int H, int W, long long R, void* stream) {
+  DBA_REQUIRE(g_dba_act_mode == 0, "MnistNet pooling kernels run in bf16 mode only (dba_set_act_dtype(0))");
   DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_relu_bwd_bias: K=%d C=%d B=%d", K, C, B);
   ReluArgs a{(const __nv_bfloat16*)g, (const __nv_bfloat16*)act, (__nv_bfloat16*)dz, G, R, ldg, b_off, c_real, K, C, B,
              H, W};

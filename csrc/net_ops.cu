@@ -20,81 +20,76 @@ using namespace dba;
 // besides the forward pack, the transposed slot receives [4 taps (a,b)][CoutP/8][4*CinP][8] with
 // Wd[(a,b)][co][(2*ph+pw)*CinP + ci] = W[dh(ph,a)][dw(pw,b)][co][ci], dh(0,0) = 1, dh(1,0) = 2, dh(1,1) = 0, none for (0,1).
 #define PACK_FIELDS 9
+template <int V>
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ W, long long ldw,
                                                            const int* __restrict__ table,
-                                                           __nv_bfloat16* __restrict__ dst, long long dst_client_stride) {
+                                                           uint4* __restrict__ dst, long long dst_client_stride) {
+  // dst is addressed in 16-byte chunks of V values (V = 8: bf16, V = 4: fp32); table offsets are in elements
   const int* e = table + blockIdx.y * PACK_FIELDS;
   const int k = blockIdx.z;
   const int Cout = e[1], Cin = e[2], taps = e[3], CinP = e[6], CoutP = e[7], fold = e[8] == 1, chw = e[8] == 2;
   const float* src = W + (long long)k * ldw + e[0];
-  __nv_bfloat16* d = dst + (long long)k * dst_client_stride;
+  uint4* d = dst + (long long)k * dst_client_stride;
   const int ptaps = fold ? 1 : taps;             // taps as seen by the kernel
   const int kreal = fold ? taps * Cin : Cin;     // real reduction length per packed tap
-  // forward pack: one thread per (tap, ci8, co) 16-byte group
-  const long long nf = (long long)ptaps * (CinP >> 3) * CoutP;
+  const int cinV = CinP / V, coutV = CoutP / V;
+  // forward pack: one thread per (tap, ciV, co) 16-byte group
+  const long long nf = (long long)ptaps * cinV * CoutP;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nf; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % (CinP >> 3));
-    const int co = (int)((i / (CinP >> 3)) % CoutP);
-    const int tap = (int)(i / ((long long)(CinP >> 3) * CoutP));
-    float v[8];
+    const int cv = (int)(i % cinV);
+    const int co = (int)((i / cinV) % CoutP);
+    const int tap = (int)(i / ((long long)cinV * CoutP));
+    float v[V];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int ci = c8 * 8 + j;
+    for (int j = 0; j < V; ++j) {
+      const int ci = cv * V + j;
       v[j] = (co < Cout && ci < kreal)
                  ? (chw ? src[(long long)co * (Cin * taps) + ci * taps + tap] : src[((long long)co * ptaps + tap) * kreal + ci])
                  : 0.f;
     }
-    uint4 pk;
-    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
-    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-    *reinterpret_cast<uint4*>(d + e[4] + (((long long)tap * (CinP >> 3) + c8) * CoutP + co) * 8) = pk;
+    d[e[4] / V + ((long long)tap * cinV + cv) * CoutP + co] = chunk_pack_operand<V>(v);
   }
   if (e[5] < 0 || fold) return;
   if (e[8] == 3) {
-    const long long nd = 4LL * (CoutP >> 3) * 4 * CinP;
+    const long long nd = 4LL * coutV * 4 * CinP;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nd; i += (long long)gridDim.x * blockDim.x) {
       const int n = (int)(i % (4 * CinP));                 // output channel of the gradient conv: parity * CinP + ci
-      const int o8 = (int)((i / (4 * CinP)) % (CoutP >> 3));
-      const int t2 = (int)(i / ((long long)4 * CinP * (CoutP >> 3)));      // 2x2 tap (a, b)
+      const int ov = (int)((i / (4 * CinP)) % coutV);
+      const int t2 = (int)(i / ((long long)4 * CinP * coutV));      // 2x2 tap (a, b)
       const int par = n / CinP, ci = n - par * CinP;
       const int ph = par >> 1, pw = par & 1, ta = t2 >> 1, tb = t2 & 1;
       const int dh = ph == 0 ? (ta == 0 ? 1 : -1) : (ta == 0 ? 2 : 0);
       const int dw = pw == 0 ? (tb == 0 ? 1 : -1) : (tb == 0 ? 2 : 0);
-      float v[8];
+      float v[V];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int co = o8 * 8 + j;
+      for (int j = 0; j < V; ++j) {
+        const int co = ov * V + j;
         v[j] = (dh >= 0 && dw >= 0 && co < Cout && ci < Cin) ? src[((long long)co * taps + dh * 3 + dw) * Cin + ci] : 0.f;
       }
-      uint4 pk;
-      pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
-      pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-      *reinterpret_cast<uint4*>(d + e[5] + (((long long)t2 * (CoutP >> 3) + o8) * (4 * CinP) + n) * 8) = pk;
+      d[e[5] / V + ((long long)t2 * coutV + ov) * (4 * CinP) + n] = chunk_pack_operand<V>(v);
     }
     return;
   }
   // transposed pack for the input-gradient convolution: out channels become the reduction axis, taps are flipped
-  const long long nt = (long long)taps * (CoutP >> 3) * CinP;
+  const long long nt = (long long)taps * coutV * CinP;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nt; i += (long long)gridDim.x * blockDim.x) {
     const int ci = (int)(i % CinP);
-    const int o8 = (int)((i / CinP) % (CoutP >> 3));
-    const int tap = (int)(i / ((long long)CinP * (CoutP >> 3)));
-    float v[8];
+    const int ov = (int)((i / CinP) % coutV);
+    const int tap = (int)(i / ((long long)CinP * coutV));
+    float v[V];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int co = o8 * 8 + j;
+    for (int j = 0; j < V; ++j) {
+      const int co = ov * V + j;
       v[j] = (co < Cout && ci < Cin)
                  ? (chw ? src[(long long)co * (Cin * taps) + ci * taps + tap] : src[((long long)co * taps + tap) * Cin + ci])
                  : 0.f;
     }
-    uint4 pk;
-    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
-    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+    const uint4 pk = chunk_pack_operand<V>(v);
     if (chw) {
-      *reinterpret_cast<uint4*>(d + e[5] + (((long long)o8 * taps + tap) * CinP + ci) * 8) = pk;
+      d[e[5] / V + ((long long)ov * taps + tap) * CinP + ci] = pk;
     } else {
       const int ftap = taps - 1 - tap;
-      *reinterpret_cast<uint4*>(d + e[5] + (((long long)ftap * (CoutP >> 3) + o8) * CinP + ci) * 8) = pk;
+      d[e[5] / V + ((long long)ftap * coutV + ov) * CinP + ci] = pk;
     }
   }
 }
@@ -102,7 +97,14 @@ extern "C" int dba_pack_weights(const float* W, long long ldw, const int* table,
                                 long long dst_client_stride, void* stream) {
   DBA_REQUIRE(n_layers > 0 && K > 0, "dba_pack_weights: n_layers=%d K=%d", n_layers, K);
   dim3 g(32, n_layers, K);
-  pack_weights_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, (__nv_bfloat16*)dst, dst_client_stride);
+  // dst_client_stride counts elements (bf16 or fp32) of the caller's pack tensor
+  if (g_dba_act_mode == 1) {
+    DBA_REQUIRE(dst_client_stride % 4 == 0, "dba_pack_weights: client stride %lld %% 4", dst_client_stride);
+    pack_weights_kernel<4><<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, (uint4*)dst, dst_client_stride / 4);
+  } else {
+    DBA_REQUIRE(dst_client_stride % 8 == 0, "dba_pack_weights: client stride %lld %% 8", dst_client_stride);
+    pack_weights_kernel<8><<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, (uint4*)dst, dst_client_stride / 8);
+  }
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -149,7 +151,8 @@ struct InputArgs {
   const long long* trig_row;     // [K]
   const long long* poison_n;     // [K]
   const unsigned char* flip;     // [K][ld_idx] or null
-  __nv_bfloat16* out;            // [K][KP/8][R][8]
+  uint4* out;                    // [K][KP/V][R] 16-byte rows of V values (V = 8: bf16, 4: fp32)
+  uint2* out_split;              // tf32 mode, optional: bf16 hi/lo split copy ([K][2][KP/8][R][8]) for the stem's wgrad
   int* labels_out;               // [K][B]
   int K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo, KP, label_swap;
   long long R;
@@ -158,14 +161,15 @@ struct InputArgs {
 // (client, sample, chunk) - the sample id, poison / flip flags, the (kh, kw, c) of the chunk's 8 im2col columns - is
 // block-uniform, so the per-thread work is one 32-bit division, 8 byte loads and one 16-byte store (the first version
 // decomposed a flat 64-bit index per thread and spent its time in integer division: 0.5 TB/s of stores).
+template <int V>
 __global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
   const int Wp = a.Wo + 1, S = (a.Ho + 1) * Wp, lead = Wp + 1;
-  const int nchunk = a.KP >> 3;
+  const int nchunk = a.KP / V;
   const int b = blockIdx.y;
   const int k = blockIdx.z / nchunk, chunk = blockIdx.z - k * nchunk;
-  __shared__ int s_dh[8], s_dw[8], s_c[8];
-  if (threadIdx.x < 8) {
-    const int e = chunk * 8 + threadIdx.x;
+  __shared__ int s_dh[V], s_dw[V], s_c[V];
+  if (threadIdx.x < V) {
+    const int e = chunk * V + threadIdx.x;
     int c = -1, dh = 0, dw = 0;
     if (e < a.ks * a.ks * a.C) {
       const int tap = e / a.C;
@@ -182,13 +186,13 @@ __global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
   const bool flip = a.flip && a.flip[(long long)k * a.ld_idx + b];
   const unsigned char* img = a.data + (id < 0 ? 0 : id) * (long long)a.Hi * a.Wi * a.C;
   const unsigned char* tm = a.trig + a.trig_row[k] * (long long)a.Hi * a.Wi;
-  __nv_bfloat16* dst = a.out + (((long long)k * nchunk + chunk) * a.R + lead + (long long)b * S) * 8;
+  uint4* dst = a.out + (((long long)k * nchunk + chunk) * a.R + lead + (long long)b * S);
   const int npix = a.Ho * a.Wo;
   for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
     const int ho = pix / a.Wo, wo = pix - ho * a.Wo;
-    float v[8];
+    float v[V];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < V; ++j) {
       float x = 0.f;
       const int c = s_c[j];
       if (id >= 0 && c >= 0) {
@@ -200,27 +204,44 @@ __global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
       }
       v[j] = x;
     }
-    uint4 pk;
-    pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
-    pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
-    *reinterpret_cast<uint4*>(dst + (long long)(ho * Wp + wo) * 8) = pk;
+    dst[ho * Wp + wo] = chunk_pack_operand<V>(v);
+    if constexpr (V == 4) {
+      if (a.out_split) store_split(a.out_split, k, a.KP >> 3, a.R, chunk, lead + (long long)b * S + ho * Wp + wo, v);
+    }
   }
   if (a.labels_out && chunk == 0 && blockIdx.x == 0 && threadIdx.x == 0)
     a.labels_out[k * a.B + b] = id < 0 ? -1 : (poisoned ? a.label_swap : (int)a.labels[id]);
 }
+extern "C" int dba_input_stage_image_split(const void* data, const long long* labels, const long long* idx,
+                                           long long ld_idx, const void* trig, const long long* trig_row,
+                                           const long long* poison_n, const void* flip, void* out, void* out_split,
+                                           int* labels_out, int K, int B, int Hi, int Wi, int C, int ks, int stride,
+                                           int pad, int Ho, int Wo, int KP, int label_swap, long long R, void* stream);
 extern "C" int dba_input_stage_image(const void* data, const long long* labels, const long long* idx, long long ld_idx,
                                      const void* trig, const long long* trig_row, const long long* poison_n,
                                      const void* flip, void* out, int* labels_out, int K, int B, int Hi, int Wi, int C,
                                      int ks, int stride, int pad, int Ho, int Wo, int KP, int label_swap, long long R,
                                      void* stream) {
+  return dba_input_stage_image_split(data, labels, idx, ld_idx, trig, trig_row, poison_n, flip, out, nullptr, labels_out,
+                                     K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo, KP, label_swap, R, stream);
+}
+// out_split (nullable, tf32 mode only): bf16 hi/lo split copy of the im2col'd input, the stem weight gradient's operand.
+extern "C" int dba_input_stage_image_split(const void* data, const long long* labels, const long long* idx,
+                                           long long ld_idx, const void* trig, const long long* trig_row,
+                                           const long long* poison_n, const void* flip, void* out, void* out_split,
+                                           int* labels_out, int K, int B, int Hi, int Wi, int C, int ks, int stride,
+                                           int pad, int Ho, int Wo, int KP, int label_swap, long long R, void* stream) {
+  DBA_REQUIRE(!out_split || g_dba_act_mode == 1, "dba_input_stage_image: split copies exist in tf32 mode only");
   DBA_REQUIRE(K > 0 && B > 0 && KP % 16 == 0 && KP >= ks * ks * C, "dba_input_stage_image: K=%d B=%d KP=%d", K, B, KP);
   InputArgs a{(const unsigned char*)data, labels, idx, ld_idx, (const unsigned char*)trig, trig_row, poison_n,
-              (const unsigned char*)flip, (__nv_bfloat16*)out, labels_out, K, B, Hi, Wi, C, ks, stride, pad, Ho, Wo,
-              KP, label_swap, R};
-  DBA_REQUIRE(B <= 65535 && (long long)K * (KP / 8) <= 65535, "dba_input_stage_image: grid too large (B=%d K=%d)", B, K);
+              (const unsigned char*)flip, (uint4*)out, (uint2*)out_split, labels_out, K, B, Hi, Wi, C, ks, stride, pad,
+              Ho, Wo, KP, label_swap, R};
+  const int V = g_dba_act_mode == 1 ? 4 : 8;
+  DBA_REQUIRE(B <= 65535 && (long long)K * (KP / V) <= 65535, "dba_input_stage_image: grid too large (B=%d K=%d)", B, K);
   int gx = (Ho * Wo + 255) / 256;
   if (gx > 64) gx = 64;
-  input_stage_kernel<<<dim3(gx, B, K * (KP / 8)), 256, 0, (cudaStream_t)stream>>>(a);
+  if (V == 4) input_stage_kernel<4><<<dim3(gx, B, K * (KP / 4)), 256, 0, (cudaStream_t)stream>>>(a);
+  else input_stage_kernel<8><<<dim3(gx, B, K * (KP / 8)), 256, 0, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -233,10 +254,10 @@ extern "C" int dba_input_stage_image(const void* data, const long long* labels, 
 // activation (planar bf16, scaled by 1/(n_valid*H*W)), and fp32 atomics into the flat gradient slab for the linear
 // weight / bias.  Metric slots: metrics_f[k][slot] += loss, metrics_i[k][slot][0] += correct, [1] += count.
 struct HeadArgs {
-  const __nv_bfloat16* act;  // [K][C/8][R][8]
+  const uint4* act;          // [K][Cp/V][R] 16-byte rows of V channels (V = 8: bf16, 4: fp32)
   const float* Wflat;        // [K][ldw]
   float* Gflat;              // [K][ldg] or null (evaluation)
-  __nv_bfloat16* dact;       // [K][C/8][R][8] or null
+  uint4* dact;               // same layout, or null
   const int* labels;         // [Kl][B]   (Kl = 1 when labels are shared by all models)
   const int* nvalid;         // [K] or null (=> every sample with label >= 0 counts, loss is a SUM)
   const long long* slot;     // [K] metric column (internal epoch) or null -> column 0
@@ -251,7 +272,7 @@ struct HeadArgs {
 // linear layer is first summed in shared memory and leaves the block as one atomic per weight (the first version
 // issued ncls*C global atomics per sample on the same addresses: 68 us for 64 samples).
 constexpr int kHeadWarps = 16;
-template <int MAXC, int MAXCLS, bool SMEM_GRAD>
+template <int MAXC, int MAXCLS, bool SMEM_GRAD, int V>
 __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a) {
   extern __shared__ float s_gw[];               // [ncls][C] + [ncls]  (SMEM_GRAD && training only)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -263,19 +284,18 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
   }
   const int label = b < a.B ? a.labels[(a.shared_labels ? 0 : k) * a.B + b] : -1;
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
-  const long long plane = a.R * 8;
-  const __nv_bfloat16* act = a.act + (long long)k * (a.Cp >> 3) * plane;
+  const long long plane = a.R;                   // rows per channel-chunk plane
+  const uint4* act = a.act + (long long)k * (a.Cp / V) * plane;
   constexpr int PER = MAXC / 32;
   const float inv_hw = 1.f / (float)(a.H * a.W);
   if (b < a.B && label < 0 && a.dact) {        // padding sample: contributes nothing, its gradient rows must be zero
-    __nv_bfloat16* d = a.dact + (long long)k * (a.Cp >> 3) * plane;
+    uint4* d = a.dact + (long long)k * (a.Cp / V) * plane;
     for (int i = 0; i < PER; ++i) {
       const int c = lane + 32 * i;
       if (c < a.C)
         for (int h = 0; h < a.H; ++h)
           for (int w = 0; w < a.W; ++w)
-            d[(long long)(c >> 3) * plane + ((long long)lead + (long long)b * S + h * Wp + w) * 8 + (c & 7)] =
-                __float2bfloat16(0.f);
+            elem_store<V>(d, (long long)(c / V) * plane + (long long)lead + (long long)b * S + h * Wp + w, c % V, 0.f);
     }
   }
   if (label >= 0) {
@@ -285,10 +305,10 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
       const int c = lane + 32 * i;
       float sum = 0.f;
       if (c < a.C) {
-        const __nv_bfloat16* p = act + (long long)(c >> 3) * plane + (c & 7);
+        const uint4* p = act + (long long)(c / V) * plane;
         for (int h = 0; h < a.H; ++h)
           for (int w = 0; w < a.W; ++w)
-            sum += __bfloat162float(p[((long long)lead + (long long)b * S + h * Wp + w) * 8]);
+            sum += elem_load<V>(p, (long long)lead + (long long)b * S + h * Wp + w, c % V);
       }
       pooled[i] = sum * inv_hw;
     }
@@ -346,15 +366,15 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
         }
       }
       if (a.dact) {
-        __nv_bfloat16* d = a.dact + (long long)k * (a.Cp >> 3) * plane;
+        uint4* d = a.dact + (long long)k * (a.Cp / V) * plane;
 #pragma unroll
         for (int i = 0; i < PER; ++i) {
           const int c = lane + 32 * i;
           if (c < a.C) {
-            const __nv_bfloat16 g = __float2bfloat16(dpooled[i] * inv_hw);
+            const float g = dpooled[i] * inv_hw;
             for (int h = 0; h < a.H; ++h)
               for (int w = 0; w < a.W; ++w)
-                d[(long long)(c >> 3) * plane + ((long long)lead + (long long)b * S + h * Wp + w) * 8 + (c & 7)] = g;
+                elem_store<V>(d, (long long)(c / V) * plane + (long long)lead + (long long)b * S + h * Wp + w, c % V, g);
           }
         }
       }
@@ -387,19 +407,31 @@ extern "C" int dba_head_ex(const void* act, const float* Wflat, long long ldw, i
                            const long long* slot, float* metrics_f, int* metrics_i, int ld_m, unsigned char* nan_flag,
                            int K, int B, int C, int c_pad, int H, int W, int ncls, long long R, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && C <= 512 && ncls <= 200, "dba_head: K=%d B=%d C=%d ncls=%d", K, B, C, ncls);
-  HeadArgs a{(const __nv_bfloat16*)act, Wflat, Gflat, (__nv_bfloat16*)dact, labels, nvalid, slot, metrics_f, metrics_i,
+  HeadArgs a{(const uint4*)act, Wflat, Gflat, (uint4*)dact, labels, nvalid, slot, metrics_f, metrics_i,
              nan_flag, ldw, ldg, R, w_off, b_off, K, B, C, H, W, ncls, ld_m, shared_labels, c_pad};
   DBA_REQUIRE(c_pad >= C && c_pad % 8 == 0, "dba_head: c_pad=%d for C=%d", c_pad, C);
   DBA_REQUIRE(K <= 65535, "dba_head: K=%d too large for grid.y", K);
   const dim3 grid((B + kHeadWarps - 1) / kHeadWarps, K);
   const size_t gsm = (size_t)(ncls * C + ncls) * sizeof(float);
   const bool smem_grad = Gflat != nullptr && gsm <= 40 * 1024;
-  if (C <= 256 && ncls <= 16) {
-    if (smem_grad) head_kernel<256, 16, true><<<grid, kHeadWarps * 32, gsm, (cudaStream_t)stream>>>(a);
-    else head_kernel<256, 16, false><<<grid, kHeadWarps * 32, 0, (cudaStream_t)stream>>>(a);
+  const cudaStream_t st = (cudaStream_t)stream;
+  const int nt = kHeadWarps * 32;
+  if (g_dba_act_mode == 1) {
+    if (C <= 256 && ncls <= 16) {
+      if (smem_grad) head_kernel<256, 16, true, 4><<<grid, nt, gsm, st>>>(a);
+      else head_kernel<256, 16, false, 4><<<grid, nt, 0, st>>>(a);
+    } else {
+      if (smem_grad) head_kernel<512, 200, true, 4><<<grid, nt, gsm, st>>>(a);
+      else head_kernel<512, 200, false, 4><<<grid, nt, 0, st>>>(a);
+    }
   } else {
-    if (smem_grad) head_kernel<512, 200, true><<<grid, kHeadWarps * 32, gsm, (cudaStream_t)stream>>>(a);
-    else head_kernel<512, 200, false><<<grid, kHeadWarps * 32, 0, (cudaStream_t)stream>>>(a);
+    if (C <= 256 && ncls <= 16) {
+      if (smem_grad) head_kernel<256, 16, true, 8><<<grid, nt, gsm, st>>>(a);
+      else head_kernel<256, 16, false, 8><<<grid, nt, 0, st>>>(a);
+    } else {
+      if (smem_grad) head_kernel<512, 200, true, 8><<<grid, nt, gsm, st>>>(a);
+      else head_kernel<512, 200, false, 8><<<grid, nt, 0, st>>>(a);
+    }
   }
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();

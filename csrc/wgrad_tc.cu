@@ -12,18 +12,26 @@
 // Work item = (client, 128-wide block of Cout, tap group, slice of the row range); partial results are added into
 // the fp32 gradient slab with vector reductions (red.global.add.v4.f32), rows of Cin being contiguous thanks to the
 // [Cout][tap][Cin] internal weight order.
+//
+// tf32 mode (fp32 activations): tcgen05 accepts MN-major 32-bit operands only in the 128B-swizzle / 32-byte-atom
+// shared-memory layout, and TMA loads with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B faulted on this driver (DESIGN.md
+// section 6b), so the weight gradient keeps bf16 MN-major operands but loses no precision against TF32: its operands
+// are the "split" copies the producing kernels store next to every fp32 tensor, x = hi + lo with hi = bf16(x),
+// lo = bf16(x - hi) (16 mantissa bits, TF32 has 10), and every k-step issues three MMAs into the same accumulator:
+// hi*hi + hi*lo + lo*hi (the dropped lo*lo term is below 2^-17 relative).
 #include "common.cuh"
 
 using namespace dba;
 
 namespace {
 
-constexpr int kRowsK = 128;     // reduction rows per pipeline stage
 constexpr int kThreadsW = 192;
 
 struct WgArgs {
   const __nv_bfloat16* dY;     // [K][Cout/8][R][8]  (zero on halo rows and on padding samples)
   const __nv_bfloat16* X;      // [K][Cin/8][R][8]
+                               // split mode: [K][2][C/8][R][8], the lo set dy_lo / x_lo elements after the hi set
+  long long dy_lo, x_lo;
   float* G;                    // [K][ldg] gradient rows; this layer's weights at w_off, layout [Cout][taps][cin_real]
   long long dy_plane, dy_client, x_plane, x_client, ldg;
   int w_off;
@@ -50,17 +58,22 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+template <bool SPLIT>
 __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int kRowsK = SPLIT ? 64 : 128;                  // reduction rows per pipeline stage
+  constexpr int NSET = SPLIT ? 2 : 1;                       // operand sets per stage (hi, lo)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mplanes = 16;                                   // M = 128 -> 16 planes of 8 output channels
   const int nplanes = a.N >> 3;
   const uint32_t pitchA = kRowsK * 16u;
-  const uint32_t bytesA = mplanes * pitchA;
+  const uint32_t setA = mplanes * pitchA;                   // one operand set of A
+  const uint32_t bytesA = NSET * setA;
   const uint32_t rowsB = kRowsK + 2 * a.halo;
   const uint32_t pitchB = rowsB * 16u;
   const int npar = a.s2d ? 4 : 1;
-  const uint32_t bytesB = (uint32_t)(npar * nplanes) * pitchB;
+  const uint32_t setB = (uint32_t)(npar * nplanes) * pitchB;
+  const uint32_t bytesB = NSET * setB;
   uint8_t* smA = smem;
   uint8_t* smB = smA + (size_t)a.stages * bytesA;
   uint64_t* full = reinterpret_cast<uint64_t*>(smB + (size_t)a.stages * bytesB);
@@ -119,18 +132,21 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       for (int ch = c0; ch < c1; ++ch) {
         if (lane == 0) {
           mbar_wait(&empty[st], ph ^ 1u);
-          mbar_arrive_expect_tx(&full[st], (uint32_t)mreal * pitchA + bytesB);
+          mbar_arrive_expect_tx(&full[st], NSET * (uint32_t)mreal * pitchA + bytesB);
         }
         __syncwarp();
         const long long row = (long long)a.lead + (long long)ch * kRowsK;
-        for (int p = lane; p < mreal + npar * nplanes; p += 32) {
+        const int per_set = mreal + npar * nplanes;
+        for (int pp = lane; pp < NSET * per_set; pp += 32) {
+          const int set = pp >= per_set ? 1 : 0, p = pp - set * per_set;           // 0 = hi (or the only) set, 1 = lo
           if (p < mreal) {
-            bulk_g2s(smA + (size_t)st * bytesA + (size_t)p * pitchA, dyk + (long long)p * a.dy_plane + row * 8, pitchA,
-                     &full[st]);
+            bulk_g2s(smA + (size_t)st * bytesA + (size_t)set * setA + (size_t)p * pitchA,
+                     dyk + (long long)set * a.dy_lo + (long long)p * a.dy_plane + row * 8, pitchA, &full[st]);
           } else {
             const int q = p - mreal, par = q / nplanes, j = q - par * nplanes;       // parity group, plane inside it
-            bulk_g2s(smB + (size_t)st * bytesB + (size_t)q * pitchB,
-                     xk + ((long long)par * (a.Cin >> 3) + j) * a.x_plane + (row - a.halo) * 8, pitchB, &full[st]);
+            bulk_g2s(smB + (size_t)st * bytesB + (size_t)set * setB + (size_t)q * pitchB,
+                     xk + (long long)set * a.x_lo + ((long long)par * (a.Cin >> 3) + j) * a.x_plane + (row - a.halo) * 8,
+                     pitchB, &full[st]);
           }
         }
         if (++st == a.stages) { st = 0; ph ^= 1u; }
@@ -163,9 +179,19 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
             const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.N);
             const uint64_t dB1 = dB0 + (uint64_t)(int64_t)shift;
             umma_f16(d_tmem, dA0, dB1, idesc, acc0);
+            if (SPLIT) {                            // + hi*lo + lo*hi
+              umma_f16(d_tmem, dA0, dB1 + (uint64_t)(setB >> 4), idesc, 1u);
+              umma_f16(d_tmem, dA0 + (uint64_t)(setA >> 4), dB1, idesc, 1u);
+            }
 #pragma unroll
-            for (int ks = 1; ks < kRowsK / 16; ++ks)
-              umma_f16(d_tmem, dA0 + (uint64_t)(ks * 16), dB1 + (uint64_t)(ks * 16), idesc, 1u);
+            for (int ks = 1; ks < kRowsK / 16; ++ks) {
+              const uint64_t da = dA0 + (uint64_t)(ks * 16), db = dB1 + (uint64_t)(ks * 16);
+              umma_f16(d_tmem, da, db, idesc, 1u);
+              if (SPLIT) {
+                umma_f16(d_tmem, da, db + (uint64_t)(setB >> 4), idesc, 1u);
+                umma_f16(d_tmem, da + (uint64_t)(setA >> 4), db, idesc, 1u);
+              }
+            }
           }
           umma_commit(&empty[s]);
         }
@@ -246,7 +272,10 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
                         int Cin, int Cout, int cin_real, int cout_real, int ksize, int cgrp_pad, int cgrp_real,
                         int npos, void* stream, long long x_client_stride = 0, int s2d = 0) {
   DBA_REQUIRE(K > 0 && B > 0 && (ksize == 1 || ksize == 3 || ksize == 5), "dba_wgrad_tc: K=%d B=%d ksize=%d", K, B, ksize);
-  DBA_REQUIRE(Cin % 16 == 0 && (Cin <= 256 || Cin % 256 == 0) && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d Cout=%d", Cin, Cout);
+  // tf32 mode: dY / X are the bf16 hi/lo split copies ([K][2][C/8][R][8]) of the fp32 tensors
+  const bool split = g_dba_act_mode == 1;
+  const int kRowsK = split ? 64 : 128, nmax = split ? 128 : 256;
+  DBA_REQUIRE(Cin % 16 == 0 && Cout % 8 == 0, "dba_wgrad_tc: Cin=%d Cout=%d", Cin, Cout);
   WgArgs a{};
   a.dY = (const __nv_bfloat16*)dY; a.X = (const __nv_bfloat16*)X; a.G = G; a.ldg = ldg; a.w_off = w_off;
   a.K = K; a.Cout = Cout; a.Cin = Cin; a.cin_real = cin_real; a.cout_real = cout_real; a.taps = ksize * ksize;
@@ -257,13 +286,18 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   long long body = (long long)B * S;
   body = (body + 511) / 512 * 512;
   const long long R = a.lead + body + a.Wp + 2;
-  a.dy_plane = R * 8; a.dy_client = (long long)(Cout / 8) * R * 8;
+  const int nset = split ? 2 : 1;
+  a.dy_plane = R * 8; a.dy_client = (long long)nset * (Cout / 8) * R * 8;
   a.x_plane = R * 8;
-  a.x_client = x_client_stride ? x_client_stride : (long long)(s2d ? 4 : 1) * (Cin / 8) * R * 8;
+  a.x_client = x_client_stride ? x_client_stride : (long long)nset * (s2d ? 4 : 1) * (Cin / 8) * R * 8;
+  a.dy_lo = a.dy_client / 2; a.x_lo = a.x_client / 2;       // the lo set follows the hi set inside a client's block
   a.body_chunks = (int)(((long long)B * S + kRowsK - 1) / kRowsK);
   a.nmb = (Cout + 127) / 128;
-  a.N = Cin <= 256 ? Cin : 256;
-  if (s2d && a.N > 64) a.N = 64;            // four parity groups of N channels share a stage
+  // accumulator width: the largest multiple of 16 dividing Cin that fits the stage (four parity groups share it in the
+  // space-to-depth form)
+  const int ncap = s2d ? nmax / 4 : nmax;
+  a.N = Cin <= ncap ? Cin : ncap;
+  while (a.N > 16 && Cin % a.N != 0) a.N -= 16;
   a.nnblk = Cin / a.N;
   a.tpg = 512 / a.N;
   if (a.tpg > a.taps) a.tpg = a.taps;
@@ -274,7 +308,8 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   if (nsplit > a.body_chunks) nsplit = a.body_chunks;
   if (nsplit < 1) nsplit = 1;
   a.nsplit = nsplit;
-  const size_t bytesA = 16 * kRowsK * 16, bytesB = (size_t)(s2d ? 4 : 1) * (a.N / 8) * (kRowsK + 2 * a.halo) * 16;
+  const size_t bytesA = (size_t)nset * 16 * kRowsK * 16;
+  const size_t bytesB = (size_t)nset * (s2d ? 4 : 1) * (a.N / 8) * (kRowsK + 2 * a.halo) * 16;
   a.stages = 3;
   size_t need = a.stages * (bytesA + bytesB) + 1024;
   if (need > 220 * 1024) { a.stages = 2; need = a.stages * (bytesA + bytesB) + 1024; }
@@ -283,13 +318,15 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   int dev = 0;
   DBA_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
-    DBA_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    DBA_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
     attr_set[dev] = true;
   }
   if (need < 120 * 1024) need = 120 * 1024;
   const int items = base_items * nsplit;
   const int grid = items < kNumSMs ? items : kNumSMs;
-  wgrad_tc_kernel<<<grid, kThreadsW, need, (cudaStream_t)stream>>>(a);
+  if (split) wgrad_tc_kernel<true><<<grid, kThreadsW, need, (cudaStream_t)stream>>>(a);
+  else wgrad_tc_kernel<false><<<grid, kThreadsW, need, (cudaStream_t)stream>>>(a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;

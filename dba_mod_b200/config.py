@@ -93,7 +93,9 @@ _DEFAULTS: Dict[str, Any] = {
     "seed": 1,                    # main.py:36-38,86 hard-code 1
     "client_eval": True,          # Q16: per-client full-test-set evaluation each round
     "backend": "auto",            # auto | torch | cuda
-    "compute_dtype": "bf16",      # MMA operand type on the cuda backend
+    # cuda backend, ResNet executors: 'tf32' = fp32 activations + tcgen05 kind::tf32 (the reference's precision class:
+    # fp32 tensors, TF32 convolutions), 'bf16' = bf16 activations + kind::f16 (fast mode, half the bytes)
+    "compute_dtype": "tf32",
     "replicas_per_gpu": 0,        # 0 = all clients of a rank in one batched group
     "n_gpus": 0,                  # 0 = all visible
     "fused_collectives": True,    # False = NCCL baseline path for the aggregation collectives
@@ -158,6 +160,8 @@ class Params(dict):
                 raise ParamsError(f"'{key}' must be {types}, got {v!r}")
         if self["type"] not in ALL_TYPES:
             raise ParamsError(f"unknown type {self['type']!r}; expected one of {ALL_TYPES}")
+        if self["compute_dtype"] not in ("tf32", "bf16"):
+            raise ParamsError(f"compute_dtype must be 'tf32' or 'bf16', got {self['compute_dtype']!r}")
         if self["aggregation_methods"] not in AGGREGATORS:
             raise ParamsError(f"unknown aggregation_methods {self['aggregation_methods']!r}")
         if self["poison_lr"] is None:

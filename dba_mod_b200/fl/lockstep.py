@@ -26,6 +26,12 @@ class LockStepTrainer:
     # clients per round that is 13 slab sets instead of up to 80.
     _LADDER = (1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512)
 
+    compute_dtype = "bf16"
+
+    def _enter(self) -> None:
+        """Selects this executor's activation element mode in the native library (library-wide switch)."""
+        native.set_act_dtype(self.compute_dtype)
+
     @classmethod
     def _width(cls, k: int, K: int) -> int:
         for w in cls._LADDER:
@@ -164,6 +170,7 @@ class LockStepTrainer:
     def _replay(self, K: int, t: dict, flags: tuple, use_graph: bool = True) -> None:
         """One step on slab t: eager the first time (lazy kernel attributes), then capture, then graph replays."""
         want_grad_sum, with_flip, use_dist = flags
+        self._enter()
         gkey = ("graph",) + flags
         g = t.get(gkey)
         if not use_graph:

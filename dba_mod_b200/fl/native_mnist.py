@@ -36,6 +36,7 @@ class NativeMnist(LockStepTrainer):
             raise ImportError("NativeMnist covers the MNIST network only")
         self.params, self.spec, self.data, self.device = params, spec, data, device
         self.lib = native.load()
+        self.compute_dtype = "bf16"        # the MnistNet pooling kernels (csrc/mnist_ops.cu) exist in bf16 only
         self.B = int(params["batch_size"])
         self.label_swap = int(params["poison_label_swap"])
         self.mu, self.wd = float(params["momentum"]), float(params["decay"])
@@ -81,6 +82,7 @@ class NativeMnist(LockStepTrainer):
         return v
 
     def pack_weights(self, W: torch.Tensor, out=None) -> torch.Tensor:
+        self._enter()
         K = W.shape[0]
         if out is None:
             out = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=self.device)
@@ -145,6 +147,7 @@ class NativeMnist(LockStepTrainer):
         return ids[r * per:min(n, (r + 1) * per)]
 
     def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None):
+        self._enter()
         d, dev, lib = self.data, self.device, self.lib
         J, Bt = len(jobs), self.eval_chunk
         models = models if models.stride(-1) == 1 else models.contiguous()

@@ -51,6 +51,10 @@ class NativeResNet(LockStepTrainer):
         self.params, self.spec, self.data, self.device = params, spec, data, device
         self.lib = native.load()
         self.kind = params["type"]
+        # activation element mode: tf32 = fp32 activations / TF32 tensor-core math (the reference's precision class),
+        # bf16 = the fast mode (half the bytes, twice the MMA rate)
+        self.compute_dtype = str(params.get("compute_dtype", "tf32"))
+        self.adt, self.V = native.act_layout(self.compute_dtype)
         if self.kind == C.TYPE_CIFAR:       # models/resnet_cifar.py:67-104
             self.widths, self.ress, self.ncls = [32, 64, 128, 256], [32, 16, 8, 4], 10
             self.stem = dict(ks=3, stride=1, pad=1, res=32)
@@ -138,23 +142,28 @@ class NativeResNet(LockStepTrainer):
         self.head_b_off = sp.entries[self.head + ".bias"].offset
 
     # ------------------------------------------------------------------------------------------ helpers
+    def _enter(self) -> None:
+        """Every public entry point selects this executor's activation mode in the native library first."""
+        native.set_act_dtype(self.compute_dtype)
+
     def pack_weights(self, W: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        self._enter()
         K = W.shape[0]
         if out is None:
-            out = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=self.device)
+            out = torch.zeros(K, self.pack_elems, dtype=self.adt, device=self.device)
         native.check(self.lib.dba_pack_weights(native.ptr(W), W.stride(0), native.ptr(self.pack_table),
                                                len(self.layers), K, native.ptr(out), out.stride(0), native.stream()))
         return out
 
     def _wt(self, pack: torch.Tensor, l: ConvL, transposed: bool = False) -> torch.Tensor:
-        K = pack.shape[0]
+        V = self.V
         if l.fold:
-            return pack[:, l.w_off:l.w_off + l.cin_p * l.cout_p].unflatten(1, (1, l.cin_p // 8, l.cout_p, 8))
+            return pack[:, l.w_off:l.w_off + l.cin_p * l.cout_p].unflatten(1, (1, l.cin_p // V, l.cout_p, V))
         taps = l.ks * l.ks
         n = taps * l.cin_p * l.cout_p
         if transposed:
-            return pack[:, l.wt_off:l.wt_off + n].unflatten(1, (taps, l.cout_p // 8, l.cin_p, 8))
-        return pack[:, l.w_off:l.w_off + n].unflatten(1, (taps, l.cin_p // 8, l.cout_p, 8))
+            return pack[:, l.wt_off:l.wt_off + n].unflatten(1, (taps, l.cout_p // V, l.cin_p, V))
+        return pack[:, l.w_off:l.w_off + n].unflatten(1, (taps, l.cin_p // V, l.cout_p, V))
 
     def _conv(self, x, pack, l: ConvL, K, B, out, res=None, scale=None, shift=None, relu=False, stats=None,
               x_shared=False, w_shared=False, in_s2d=False, out_s2d=False):
@@ -207,7 +216,7 @@ class NativeResNet(LockStepTrainer):
             # sized once so that the first attack round does not re-allocate inside its critical path
             cap = max(M, int(self.params["no_models"]) + 4) if per_job_input and M > 1 else M
             dev = self.device
-            z = lambda k, c, r: torch.zeros(k, c // 8, Geom(Bt, r, r).rows, 8, dtype=torch.bfloat16, device=dev)  # noqa: E731
+            z = lambda k, c, r: torch.zeros(k, c // self.V, Geom(Bt, r, r).rows, self.V, dtype=self.adt, device=dev)  # noqa: E731
             kin = cap if per_job_input else 1
             stem = self.layers[0]
             full = {"cap": cap, "stem_in": z(kin, stem.cin_p, stem.H), "lv": {}}
@@ -257,6 +266,7 @@ class NativeResNet(LockStepTrainer):
         return self._eval_general(models, jobs, False, shard)
 
     def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None):
+        self._enter()
         d, dev, lib = self.data, self.device, self.lib
         J = len(jobs)
         models = models if models.stride(-1) == 1 else models.contiguous()
@@ -308,6 +318,7 @@ class NativeResNet(LockStepTrainer):
 
     @torch.no_grad()
     def evaluate(self, models: torch.Tensor, split: str, trig_row: int, shard=None):
+        self._enter()
         d, dev, lib = self.data, self.device, self.lib
         M = models.shape[0]
         ids_all = self._shard(d.all_test_idx if split == "clean" else d.poison_test_idx, shard)
@@ -399,29 +410,51 @@ class NativeResNet(LockStepTrainer):
         dev, B = self.device, self.B
 
         def z(c, r):
-            return torch.zeros(K, c // 8, Geom(B, r, r).rows, 8, dtype=torch.bfloat16, device=dev)
+            return torch.zeros(K, c // self.V, Geom(B, r, r).rows, self.V, dtype=self.adt, device=dev)
+
+        split = self.compute_dtype == "tf32"
+
+        def zs(c, r):
+            """bf16 hi/lo split copy of a z(c, r) tensor: the weight-gradient operand form in tf32 mode."""
+            if not split:
+                return None
+            return torch.zeros(K, 2, c // 8, Geom(B, r, r).rows, 8, dtype=torch.bfloat16, device=dev)
 
         stem = self.layers[0]
         s2d_sc = {sc.name for bi, (_, _, sc) in enumerate(self.blocks) if sc is not None and self._s2d_block(bi)}
         t = {"xin": z(stem.cin_p, stem.H), "labels": torch.zeros(K, B, dtype=torch.int32, device=dev)}
+        t[("split", "xin")] = zs(stem.cin_p, stem.H)
         for l in self.layers:
             ro = l.H // l.sub
             t[("y", l.name)] = z(l.cout_p, ro)
             t[("a", l.name)] = z(l.cout_p, ro)
+            t[("split", "a", l.name)] = zs(l.cout_p, ro)
             if l.fold:
-                t[("dy", l.name)] = z(l.cout_p, ro)
+                rdy = ro
             elif l.d2s or (l.ks == 1 and l.sub == 2 and l.name in s2d_sc):
-                t[("dy", l.name)] = z(l.cout_p, ro)           # stride-2 layers of a space-to-depth block: compact
+                rdy = ro                                      # stride-2 layers of a space-to-depth block: compact
             else:
-                t[("dy", l.name)] = z(l.cout_p, l.H)          # on the input grid (zero-upsampled when sub == 2)
+                rdy = l.H                                     # on the input grid (zero-upsampled when sub == 2)
+            t[("dy", l.name)] = z(l.cout_p, rdy)
+            t[("split", "dy", l.name)] = zs(l.cout_p, rdy)
         # gradient scratch per resolution level: g (block output grad), dz, da1, dx
         for w, r in zip(self.widths, self.ress):
             t[("g", r)] = [z(w, r) for _ in range(4)]
         for bi, (c1, _, _) in enumerate(self.blocks):      # forward operands of the stride-2 layers (output pixels only)
             if self._s2d_block(bi):
                 t[("s2d", bi)] = z(4 * c1.cin_p, c1.H // 2)
+                t[("split", "s2d", bi)] = zs(4 * c1.cin_p, c1.H // 2)
+        # plain tensor -> its split copy (looked up by the weight-gradient launcher)
+        t["split_of"] = {}
+        for key, v in list(t.items()):
+            if isinstance(key, tuple) and key[0] == "split" and v is not None:
+                src = t[key[1]] if len(key) == 2 else t[key[1:]]
+                t["split_of"][src.data_ptr()] = v
         if self.pool:
             t["pool_out"] = z(self.widths[0], self.ress[0])
+            t[("split", "pool_out")] = zs(self.widths[0], self.ress[0])
+            if split:
+                t["split_of"][t["pool_out"].data_ptr()] = t[("split", "pool_out")]
             t["pool_g"] = z(self.widths[0], stem.H)
         t["stats"] = torch.zeros(K, 2 * self.bn_total, device=dev)
         t["saved"] = torch.zeros(K, 2 * self.bn_total, device=dev)
@@ -448,16 +481,19 @@ class NativeResNet(LockStepTrainer):
         t["st_lr"] = torch.zeros(K, dtype=torch.float32, device=dev)
         t["trig_row"] = torch.zeros(K, dtype=torch.long, device=dev)
         t["poison_n"] = torch.zeros(K, dtype=torch.long, device=dev)
-        t["pack"] = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=dev)
+        t["pack"] = torch.zeros(K, self.pack_elems, dtype=self.adt, device=dev)
         self._train_bufs[K] = t
         return t
 
     def _bn_apply(self, l: ConvL, K, y, out, res, relu, W, t, nvalid, active, out_s2d=None):
         e = self.spec.entries
         r = l.H // l.sub
-        native.check(self.lib.dba_bn_apply_ex(
+        so = t["split_of"]
+        native.check(self.lib.dba_bn_apply_split(
             native.ptr(y), native.ptr(res), native.ptr(out), native.ptr(out_s2d),
-            out_s2d.shape[2] if out_s2d is not None else 0, native.ptr(t["stats"]), t["stats"].stride(0),
+            out_s2d.shape[2] if out_s2d is not None else 0, native.ptr(so.get(out.data_ptr())),
+            native.ptr(so.get(out_s2d.data_ptr())) if out_s2d is not None else None,
+            native.ptr(t["stats"]), t["stats"].stride(0),
             2 * l.bn_off, native.ptr(t["saved"]), t["saved"].stride(0), 2 * l.bn_off, native.ptr(W), W.stride(0),
             e[l.bn + ".weight"].offset, e[l.bn + ".bias"].offset, e[l.bn + ".running_mean"].offset,
             e[l.bn + ".running_var"].offset, native.ptr(nvalid), native.ptr(active), K, l.cout_p, self.B, r, r,
@@ -467,8 +503,9 @@ class NativeResNet(LockStepTrainer):
         e = self.spec.entries
         r = l.H // l.sub
         Gr = t["Gr"]
-        native.check(self.lib.dba_bn_backward(
-            native.ptr(g), native.ptr(y), native.ptr(act), native.ptr(dy), native.ptr(gmask), native.ptr(t["sums"]),
+        native.check(self.lib.dba_bn_backward_split(
+            native.ptr(g), native.ptr(y), native.ptr(act), native.ptr(dy), native.ptr(t["split_of"].get(dy.data_ptr())),
+            native.ptr(gmask), native.ptr(t["sums"]),
             t["sums"].stride(0), 2 * l.bn_off, native.ptr(t["saved"]), t["saved"].stride(0), 2 * l.bn_off,
             native.ptr(W), W.stride(0), native.ptr(Gr), Gr.stride(0), e[l.bn + ".weight"].offset,
             e[l.bn + ".bias"].offset, native.ptr(nvalid), K, l.cout_p, self.B, r, r, y.shape[2], int(up),
@@ -481,6 +518,8 @@ class NativeResNet(LockStepTrainer):
             cin, cin_real, ks, H = l.cin_p, l.ks * l.ks * l.cin, 1, l.H
         else:
             cin, cin_real, ks, H = l.cin_p, l.cin, l.ks, l.H
+        if self.compute_dtype == "tf32":        # operands = the bf16 hi/lo split copies stored next to the fp32 tensors
+            dy, x = t["split_of"][dy.data_ptr()], t["split_of"][x.data_ptr()]
         xcs = 0
         if s2d:             # x is the space-to-depth tensor: its first cin/8 planes are the even-position pixels
             H, xcs = l.H // 2, x.stride(0)
@@ -516,6 +555,7 @@ class NativeResNet(LockStepTrainer):
         """One lock-step SGD step of K clients: ~125 kernel launches, no host decisions (CUDA-graph capturable).
         All inputs come from the persistent staging tensors st_* filled by train()."""
         from ..ops import flat
+        self._enter()
         lib, d, B, Dp = self.lib, self.data, self.B, self.spec.Dp
         W, Gr, V = t["W"], t["Gr"], t["V"]
         nvalid, active, slot = t["st_nvalid"], t["st_active"], t["st_slot"]
@@ -524,10 +564,10 @@ class NativeResNet(LockStepTrainer):
         lv_g = {r: t[("g", r)] for r in self.ress}
         pack = self.pack_weights(W, t["pack"])
         t["stats"].zero_(); t["sums"].zero_(); Gr.zero_()
-        native.check(lib.dba_input_stage_image(
+        native.check(lib.dba_input_stage_image_split(
             native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(t["st_idx"]), t["st_idx"].stride(0),
             native.ptr(self.trig_u8), native.ptr(t["trig_row"]), native.ptr(t["poison_n"]),
-            native.ptr(t["st_flip"]) if with_flip else None, native.ptr(t["xin"]),
+            native.ptr(t["st_flip"]) if with_flip else None, native.ptr(t["xin"]), native.ptr(t[("split", "xin")]),
             native.ptr(t["labels"]), K, B, d.H, d.W, d.C, self.stem["ks"], self.stem["stride"], self.stem["pad"],
             stem.H, stem.H, stem.cin_p, self.label_swap, t["xin"].shape[2], native.stream()))
         st = t["stats"]
@@ -542,8 +582,9 @@ class NativeResNet(LockStepTrainer):
         x = a0
         if self.pool:
             x = t["pool_out"]
-            native.check(lib.dba_maxpool_fwd(native.ptr(a0), native.ptr(x), K, self.widths[0], B, stem.H, stem.H,
-                                             a0.shape[2], x.shape[2], native.stream()))
+            native.check(lib.dba_maxpool_fwd_split(native.ptr(a0), native.ptr(x), native.ptr(t[("split", "pool_out")]), K,
+                                                   self.widths[0], B, stem.H, stem.H, a0.shape[2], x.shape[2],
+                                                   native.stream()))
         inputs = []
         x_s2d = None           # space-to-depth copy of x when the block about to run opens with stride-2 convolutions
         for bi, (c1, c2, sc) in enumerate(self.blocks):

@@ -36,24 +36,30 @@ class Geom:
         return self.lead + body + self.Wp + 2
 
 
-def to_planar(x: torch.Tensor, cpad: int = None) -> torch.Tensor:
-    """x [K, B, C, H, W] float -> bf16 [K, Cp/8, R, 8] (channels zero-padded to ``cpad``)."""
+def _v(dtype) -> int:
+    """Channels per 16-byte chunk: 8 for bf16 (planar-8), 4 for fp32 (planar-4, the tf32 mode)."""
+    return 4 if dtype == torch.float32 else 8
+
+
+def to_planar(x: torch.Tensor, cpad: int = None, dtype=torch.bfloat16) -> torch.Tensor:
+    """x [K, B, C, H, W] float -> ``dtype`` [K, Cp/V, R, V] (channels zero-padded to ``cpad``)."""
     K, B, C, H, W = x.shape
+    V = _v(dtype)
     Cp = cpad or ((C + 7) // 8 * 8)
     g = Geom(B, H, W)
-    buf = torch.zeros(K, Cp // 8, g.rows, 8, dtype=torch.bfloat16, device=x.device)
-    body = torch.zeros(K, B, H + 1, g.Wp, Cp, dtype=torch.bfloat16, device=x.device)
-    body[:, :, :H, :W, :C] = x.permute(0, 1, 3, 4, 2).to(torch.bfloat16)
-    body = body.reshape(K, B * g.S, Cp // 8, 8).permute(0, 2, 1, 3)
+    buf = torch.zeros(K, Cp // V, g.rows, V, dtype=dtype, device=x.device)
+    body = torch.zeros(K, B, H + 1, g.Wp, Cp, dtype=dtype, device=x.device)
+    body[:, :, :H, :W, :C] = x.permute(0, 1, 3, 4, 2).to(dtype)
+    body = body.reshape(K, B * g.S, Cp // V, V).permute(0, 2, 1, 3)
     buf[:, :, g.lead:g.lead + B * g.S] = body
     return buf
 
 
 def from_planar(y: torch.Tensor, B: int, H: int, W: int, C: int = None) -> torch.Tensor:
-    """bf16 [K, Cp/8, R, 8] -> float [K, B, C, H, W]."""
+    """[K, Cp/V, R, V] (bf16 or fp32) -> float [K, B, C, H, W]."""
     K, C8 = y.shape[:2]
     g = Geom(B, H, W)
-    body = y[:, :, g.lead:g.lead + B * g.S].permute(0, 2, 1, 3).reshape(K, B, H + 1, g.Wp, C8 * 8)
+    body = y[:, :, g.lead:g.lead + B * g.S].permute(0, 2, 1, 3).reshape(K, B, H + 1, g.Wp, C8 * y.shape[3])
     out = body[:, :, :H, :W].permute(0, 1, 4, 2, 3).float()
     return out[:, :, :C] if C is not None else out
 
@@ -78,23 +84,24 @@ def halo_is_zero(y: torch.Tensor, B: int, H: int, W: int) -> bool:
     K, C8 = y.shape[:2]
     g = Geom(B, H, W)
     t = y.clone()
-    body = t[:, :, g.lead:g.lead + B * g.S].reshape(K, C8, B, H + 1, g.Wp, 8)
+    body = t[:, :, g.lead:g.lead + B * g.S].reshape(K, C8, B, H + 1, g.Wp, y.shape[3])
     body[:, :, :, :H, :W] = 0
     return bool((t == 0).all())
 
 
-def pack_conv_weight(w: torch.Tensor, cin_pad: int = None, cout_pad: int = None) -> torch.Tensor:
-    """w [K, Cout, Cin, kh, kw] -> bf16 [K, kh*kw, Cin_p/8, Cout_p, 8]."""
+def pack_conv_weight(w: torch.Tensor, cin_pad: int = None, cout_pad: int = None, dtype=torch.bfloat16) -> torch.Tensor:
+    """w [K, Cout, Cin, kh, kw] -> ``dtype`` [K, kh*kw, Cin_p/V, Cout_p, V]."""
     K, Co, Ci, kh, kw = w.shape
+    V = _v(dtype)
     Cip = cin_pad or ((Ci + 15) // 16 * 16)
     Cop = cout_pad or ((Co + 31) // 32 * 32)
     wp = torch.zeros(K, Cop, Cip, kh, kw, dtype=torch.float32, device=w.device)
     wp[:, :Co, :Ci] = w
-    t = wp.permute(0, 3, 4, 2, 1).reshape(K, kh * kw, Cip // 8, 8, Cop).permute(0, 1, 2, 4, 3)
-    return t.contiguous().to(torch.bfloat16)
+    t = wp.permute(0, 3, 4, 2, 1).reshape(K, kh * kw, Cip // V, V, Cop).permute(0, 1, 2, 4, 3)
+    return t.contiguous().to(dtype)
 
 
-def pack_conv_weight_T(w: torch.Tensor) -> torch.Tensor:
+def pack_conv_weight_T(w: torch.Tensor, dtype=torch.bfloat16) -> torch.Tensor:
     """Weights for the input-gradient (dgrad) pass run as a forward convolution: roles of Cin/Cout swapped and the
     3x3 taps flipped:  w'[k][ci][co][2-kh][2-kw] = w[k][co][ci][kh][kw]."""
-    return pack_conv_weight(w.transpose(1, 2).flip(-1, -2))
+    return pack_conv_weight(w.transpose(1, 2).flip(-1, -2), dtype=dtype)

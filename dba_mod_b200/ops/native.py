@@ -48,6 +48,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_launch_count", [], c_ulonglong)
     _sig(lib, "dba_reset_launch_count", [], None)
     _sig(lib, "dba_add_launch_count", [c_ulonglong], None)
+    _sig(lib, "dba_set_act_dtype", [I])
+    _sig(lib, "dba_get_act_dtype", [], c_int)
     _sig(lib, "dba_sgd_step", [P, L, P, P, P, L, P, P, I, L, F, F, P])
     _sig(lib, "dba_scale_rows", [P, L, P, L, P, I, L, P])
     _sig(lib, "dba_dist_grad", [P, L, P, L, P, L, P, P, P, P, P, I, F, I, L, P])
@@ -80,6 +82,11 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_head_ex", [P, P, L, I, I, P, L, P, P, I, P, P, P, P, I, P, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_bn_apply", [P, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
     _sig(lib, "dba_bn_apply_ex", [P, P, P, P, L, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F, P])
+    _sig(lib, "dba_bn_apply_split", [P, P, P, P, L, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F,
+                                     P])
+    _sig(lib, "dba_bn_backward_split", [P, P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
+    _sig(lib, "dba_maxpool_fwd_split", [P, P, P, I, I, I, I, I, L, L, P])
+    _sig(lib, "dba_input_stage_image_split", [P, P, P, L, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_bn_backward", [P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
     _sig(lib, "dba_maxpool_fwd", [P, P, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_maxpool_bwd", [P, P, P, I, I, I, I, I, L, L, P])
@@ -94,6 +101,25 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_loan_eval", [P, L, I, P, P, P, L, P, P, I, P, P, P])
     _LIB = lib
     return lib
+
+
+ACT_DTYPES = {"bf16": 0, "tf32": 1}
+
+
+def set_act_dtype(name: str) -> None:
+    """Activation element mode of the network kernels (library-wide, like a BLAS math mode): ``bf16`` = bf16
+    activations, 8 channels per 16-byte chunk, ``tcgen05.mma.kind::f16``; ``tf32`` = fp32 activations, 4 channels per
+    chunk, ``kind::tf32`` - the reference's precision class (fp32 tensors, TF32 convolutions)."""
+    check(load().dba_set_act_dtype(ACT_DTYPES[name]))
+
+
+def act_dtype() -> str:
+    return "tf32" if load().dba_get_act_dtype() == 1 else "bf16"
+
+
+def act_layout(name: str):
+    """(torch dtype, channels per 16-byte chunk) of the planar activation / packed weight buffers of a mode."""
+    return (torch.float32, 4) if name == "tf32" else (torch.bfloat16, 8)
 
 
 def check(rc: int) -> None:

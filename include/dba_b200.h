@@ -167,6 +167,33 @@ int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, voi
                     long long ldw, float* Gflat, long long ldg, int g_off, int b_off, const int* nvalid, int K, int C,
                     int B, int H, int W, long long R, int up, long long Rup, void* stream);
 
+/* tf32 mode only: the same three kernels also storing bf16 hi/lo "split" copies ([K][2][C/8][R][8]: hi = bf16(x),
+ * lo = bf16(x - hi)) of what they write - the operand form of the weight-gradient kernel, which then issues
+ * hi*hi + hi*lo + lo*hi (16 mantissa bits; the tensor core takes MN-major 32-bit operands only in a swizzled layout
+ * that planar-4 rows cannot be loaded into).  Null split pointers = no copy. */
+int dba_bn_apply_split(const void* y, const void* res, void* out, void* out_s2d, long long R_s2d, void* out_split,
+                       void* out_s2d_split, float* stats, long long ld_stats, int stats_off, float* saved,
+                       long long ld_saved, int saved_off, float* Wflat, long long ldw, int g_off, int b_off, int rm_off,
+                       int rv_off, const int* nvalid, const unsigned char* active, int K, int C, int B, int H, int W,
+                       long long R, int relu, float momentum, float eps, void* stream);
+int dba_bn_backward_split(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
+                          float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
+                          float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
+                          const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
+                          void* stream);
+int dba_maxpool_fwd_split(const void* x, void* y, void* y_split, int K, int C, int B, int H, int W, long long Rin,
+                          long long Rout, void* stream);
+int dba_input_stage_image_split(const void* data, const long long* labels, const long long* idx, long long ld_idx,
+                                const void* trig, const long long* trig_row, const long long* poison_n, const void* flip,
+                                void* out, void* out_split, int* labels_out, int K, int B, int Hi, int Wi, int C, int ks,
+                                int stride, int pad, int Ho, int Wo, int KP, int label_swap, long long R, void* stream);
+
+/* Activation element mode of all network kernels above (library-wide): 0 = bf16 activations, 8 channels per 16-byte
+ * chunk, tcgen05 kind::f16; 1 = fp32 activations, 4 channels per chunk, kind::tf32 - the reference's precision class
+ * (fp32 tensors with TF32 convolutions, cuDNN's default).  No counterpart in the reference (it has no native code). */
+int dba_set_act_dtype(int mode);
+int dba_get_act_dtype(void);
+
 /* MaxPool2d(3, 2, 1) forward / backward on planar-8 activations (Tiny-ImageNet stem, resnet_tinyimagenet.py:147). */
 int dba_maxpool_fwd(const void* x, void* y, int K, int C, int B, int H, int W, long long Rin, long long Rout,
                     void* stream);

@@ -1,4 +1,5 @@
-"""tcgen05 implicit-GEMM convolution vs torch fp32 conv2d on the same bf16-rounded operands."""
+"""tcgen05 implicit-GEMM convolution vs torch fp32 conv2d on the same operand values (rounded to what the tensor core
+reads: bf16, or tf32 = fp32 with the low 13 mantissa bits dropped), in both activation modes."""
 import pytest
 import torch
 import torch.nn.functional as F
@@ -14,32 +15,36 @@ SHAPES = [  # K, B, H, W, Cin, Cout, ksize, sub
     (1, 3, 8, 8, 128, 128, 3, 1),
     (1, 2, 2, 2, 512, 512, 3, 1),
     (2, 64, 32, 32, 32, 32, 3, 1),
+    (2, 5, 32, 32, 32, 32, 1, 1),          # CIFAR stem: 3x3x3 patch folded to a 1x1 convolution over 32 columns
+    (1, 3, 16, 16, 16, 32, 3, 1),          # Cin = 16 (one bf16 k-step / two tf32 k-steps)
+    (1, 3, 32, 32, 192, 64, 1, 1),         # Tiny-ImageNet stem: 7x7x3 patch folded to 192 columns
+    (2, 3, 2, 2, 512, 512, 1, 2),          # Tiny-ImageNet layer4 shortcut
 ]
 
 
-def _ref(x, w, ksize, sub):
+def _ref(x, w, ksize, sub, act):
     K = x.shape[0]
-    xb, wb = x.bfloat16().float(), w.bfloat16().float()
+    xb, wb = act.round(x), act.round(w)
     return torch.stack([F.conv2d(xb[k], wb[k], None, sub, ksize // 2) for k in range(K)])
 
 
 @pytest.mark.parametrize("K,B,H,W,Cin,Cout,ksize,sub", SHAPES)
-def test_conv_raw(native_lib, K, B, H, W, Cin, Cout, ksize, sub):
+def test_conv_raw(native_lib, act, K, B, H, W, Cin, Cout, ksize, sub):
     from dba_mod_b200.ops import conv, layout
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(0)
     d = torch.device("cuda", 0)
     x = torch.randn(K, B, Cin, H, W, device=d)
     w = torch.randn(K, Cout, Cin, ksize, ksize, device=d) / (Cin * ksize * ksize) ** 0.5
-    y = conv.conv_tc(layout.to_planar(x), layout.pack_conv_weight(w), K, B, H, W, ksize, sub)
+    y = conv.conv_tc(layout.to_planar(x, dtype=act.dtype), layout.pack_conv_weight(w, dtype=act.dtype), K, B, H, W, ksize, sub)
     torch.cuda.synchronize()
     got = layout.from_planar(y, B, H // sub, W // sub)
-    ref = _ref(x, w, ksize, sub)
-    torch.testing.assert_close(got, ref, rtol=2e-2, atol=2e-2)
+    ref = _ref(x, w, ksize, sub, act)
+    torch.testing.assert_close(got, ref, rtol=act.rtol, atol=act.atol)
     assert layout.halo_is_zero(y, B, H // sub, W // sub)
 
 
-def test_conv_eval_epilogue_and_shared_input(native_lib):
+def test_conv_eval_epilogue_and_shared_input(native_lib, act):
     from dba_mod_b200.ops import conv, layout
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(1)
@@ -49,15 +54,15 @@ def test_conv_eval_epilogue_and_shared_input(native_lib):
     w = torch.randn(K, Cout, Cin, 3, 3, device=d) / (Cin * 9) ** 0.5
     res = torch.randn(K, B, Cout, H, W, device=d)
     scale, shift = torch.rand(K, Cout, device=d) + 0.5, torch.randn(K, Cout, device=d)
-    y = conv.conv_tc(layout.to_planar(x), layout.pack_conv_weight(w), K, B, H, W, 3, 1, relu=True,
-                     res=layout.to_planar(res), scale=scale, shift=shift, x_shared=True)
+    y = conv.conv_tc(layout.to_planar(x, dtype=act.dtype), layout.pack_conv_weight(w, dtype=act.dtype), K, B, H, W, 3, 1, relu=True,
+                     res=layout.to_planar(res, dtype=act.dtype), scale=scale, shift=shift, x_shared=True)
     got = layout.from_planar(y, B, H, W)
-    ref = _ref(x.expand(K, -1, -1, -1, -1), w, 3, 1)
-    ref = F.relu(ref * scale[:, None, :, None, None] + shift[:, None, :, None, None] + res.bfloat16().float())
-    torch.testing.assert_close(got, ref, rtol=2e-2, atol=3e-2)
+    ref = _ref(x.expand(K, -1, -1, -1, -1), w, 3, 1, act)
+    ref = F.relu(ref * scale[:, None, :, None, None] + shift[:, None, :, None, None] + act.store(res))
+    torch.testing.assert_close(got, ref, rtol=act.rtol, atol=1.5 * act.atol)
 
 
-def test_conv_stats(native_lib):
+def test_conv_stats(native_lib, act):
     from dba_mod_b200.ops import conv, layout
     torch.manual_seed(2)
     d = torch.device("cuda", 0)
@@ -65,7 +70,7 @@ def test_conv_stats(native_lib):
     x = torch.randn(K, B, Cin, H, W, device=d)
     w = torch.randn(K, Cout, Cin, 3, 3, device=d) / (Cin * 9) ** 0.5
     stats = torch.zeros(K, Cout, 2, device=d)
-    y = conv.conv_tc(layout.to_planar(x), layout.pack_conv_weight(w), K, B, H, W, 3, 1, stats=stats)
+    y = conv.conv_tc(layout.to_planar(x, dtype=act.dtype), layout.pack_conv_weight(w, dtype=act.dtype), K, B, H, W, 3, 1, stats=stats)
     got = layout.from_planar(y, B, H, W)
     s1 = got.sum(dim=(1, 3, 4))
     s2 = (got * got).sum(dim=(1, 3, 4))
@@ -83,7 +88,7 @@ S2D_SHAPES = [  # K, B, H, W (input grid), Cin, Cout, ksize
 
 
 @pytest.mark.parametrize("K,B,H,W,Cin,Cout,ksize", S2D_SHAPES)
-def test_conv_stride2_from_space_to_depth_input(native_lib, K, B, H, W, Cin, Cout, ksize):
+def test_conv_stride2_from_space_to_depth_input(native_lib, act, K, B, H, W, Cin, Cout, ksize):
     """Stride-2 convolutions computed on the output grid only, from the parity-plane form of their input."""
     from dba_mod_b200.ops import conv, layout
     torch.backends.cudnn.allow_tf32 = False
@@ -91,18 +96,18 @@ def test_conv_stride2_from_space_to_depth_input(native_lib, K, B, H, W, Cin, Cou
     d = torch.device("cuda", 0)
     x = torch.randn(K, B, Cin, H, W, device=d)
     w = torch.randn(K, Cout, Cin, ksize, ksize, device=d) / (Cin * ksize * ksize) ** 0.5
-    xs = layout.to_planar(layout.space_to_depth(x))
+    xs = layout.to_planar(layout.space_to_depth(x), dtype=act.dtype)
     stats = torch.zeros(K, Cout, 2, device=d)
-    y = conv.conv_tc_s2d(xs, layout.pack_conv_weight(w), K, B, H // 2, W // 2, ksize, in_s2d=True, stats=stats)
+    y = conv.conv_tc_s2d(xs, layout.pack_conv_weight(w, dtype=act.dtype), K, B, H // 2, W // 2, ksize, in_s2d=True, stats=stats)
     torch.cuda.synchronize()
     got = layout.from_planar(y, B, H // 2, W // 2)
-    ref = _ref(x, w, ksize, 2)
-    torch.testing.assert_close(got, ref, rtol=2e-2, atol=2e-2)
+    ref = _ref(x, w, ksize, 2, act)
+    torch.testing.assert_close(got, ref, rtol=act.rtol, atol=act.atol)
     assert layout.halo_is_zero(y, B, H // 2, W // 2)
     torch.testing.assert_close(stats[..., 0], got.sum((1, 3, 4)), rtol=1e-3, atol=2e-2)
 
 
-def test_conv_space_to_depth_output_with_residual(native_lib):
+def test_conv_space_to_depth_output_with_residual(native_lib, act):
     """The producer side: folded-BN + residual + ReLU epilogue storing the parity-plane form, then a stride-2
     convolution consuming it equals the plain two-layer computation."""
     from dba_mod_b200.ops import conv, layout
@@ -115,19 +120,19 @@ def test_conv_space_to_depth_output_with_residual(native_lib):
     w2 = torch.randn(K, C2, C, 3, 3, device=d) / (C * 9) ** 0.5
     res = torch.randn(K, B, C, H, W, device=d)
     scale, shift = torch.rand(K, C, device=d) + 0.5, torch.randn(K, C, device=d)
-    y1 = conv.conv_tc_s2d(layout.to_planar(x), layout.pack_conv_weight(w1), K, B, H, W, 3, out_s2d=True, relu=True,
-                          res=layout.to_planar(res), scale=scale, shift=shift)
-    ref1 = F.relu(_ref(x, w1, 3, 1) * scale[:, None, :, None, None] + shift[:, None, :, None, None]
-                  + res.bfloat16().float())
+    y1 = conv.conv_tc_s2d(layout.to_planar(x, dtype=act.dtype), layout.pack_conv_weight(w1, dtype=act.dtype), K, B, H, W, 3, out_s2d=True, relu=True,
+                          res=layout.to_planar(res, dtype=act.dtype), scale=scale, shift=shift)
+    ref1 = F.relu(_ref(x, w1, 3, 1, act) * scale[:, None, :, None, None] + shift[:, None, :, None, None]
+                  + act.store(res))
     got1 = layout.depth_to_space(layout.from_planar(y1, B, H // 2, W // 2))
-    torch.testing.assert_close(got1, ref1, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(got1, ref1, rtol=act.rtol, atol=1.5 * act.atol)
     assert layout.halo_is_zero(y1, B, H // 2, W // 2)
-    y2 = conv.conv_tc_s2d(y1, layout.pack_conv_weight(w2), K, B, H // 2, W // 2, 3, in_s2d=True)
-    ref2 = _ref(got1, w2, 3, 2)
-    torch.testing.assert_close(layout.from_planar(y2, B, H // 2, W // 2), ref2, rtol=2e-2, atol=3e-2)
+    y2 = conv.conv_tc_s2d(y1, layout.pack_conv_weight(w2, dtype=act.dtype), K, B, H // 2, W // 2, 3, in_s2d=True)
+    ref2 = _ref(got1, w2, 3, 2, act)
+    torch.testing.assert_close(layout.from_planar(y2, B, H // 2, W // 2), ref2, rtol=act.rtol, atol=1.5 * act.atol)
 
 
-def _pack_with_kernel(w, mode):
+def _pack_with_kernel(w, mode, act):
     """Runs dba_pack_weights on OHWI-flattened weights w [K, Cout, Cin, 3, 3]; returns (pack, fwd_off, t_off)."""
     from dba_mod_b200.ops import native
     lib = native.load()
@@ -135,14 +140,14 @@ def _pack_with_kernel(w, mode):
     flat = w.permute(0, 1, 3, 4, 2).reshape(K, -1).contiguous().float()             # [Cout][taps][Cin] per client
     n_f, n_t = 9 * Ci * Co, (16 if mode == 3 else 9) * Ci * Co
     table = torch.tensor([[0, Co, Ci, 9, 0, n_f, Ci, Co, mode]], dtype=torch.int32, device=w.device)
-    pack = torch.zeros(K, n_f + n_t, dtype=torch.bfloat16, device=w.device)
+    pack = torch.zeros(K, n_f + n_t, dtype=act.dtype, device=w.device)
     native.check(lib.dba_pack_weights(native.ptr(flat), flat.stride(0), native.ptr(table), 1, K, native.ptr(pack),
                                       pack.stride(0), native.stream()))
     return pack, 0, n_f
 
 
 @pytest.mark.parametrize("K,B,H,Cin,Cout", [(2, 3, 16, 32, 64), (1, 5, 8, 64, 128), (2, 2, 4, 128, 256)])
-def test_stride2_backward_on_the_output_grid(native_lib, K, B, H, Cin, Cout):
+def test_stride2_backward_on_the_output_grid(native_lib, act, K, B, H, Cin, Cout):
     """3x3 stride-2 convolution, backward without the full grid: the input gradient as a 2x2-tap convolution of the
     compact dy with depth-to-space store, the weight gradient against the space-to-depth input - both vs autograd."""
     from dba_mod_b200.ops import layout, native
@@ -151,9 +156,9 @@ def test_stride2_backward_on_the_output_grid(native_lib, K, B, H, Cin, Cout):
     torch.manual_seed(4)
     d = torch.device("cuda", 0)
     Ho = H // 2
-    x = torch.randn(K, B, Cin, H, H, device=d).bfloat16().float()
-    w = (torch.randn(K, Cout, Cin, 3, 3, device=d) / (Cin * 9) ** 0.5).bfloat16().float()
-    dy = torch.randn(K, B, Cout, Ho, Ho, device=d).bfloat16().float()
+    x = act.round(torch.randn(K, B, Cin, H, H, device=d))
+    w = (act.round(torch.randn(K, Cout, Cin, 3, 3, device=d) / (Cin * 9) ** 0.5))
+    dy = act.round(torch.randn(K, B, Cout, Ho, Ho, device=d))
     ref_dx, ref_dw = [], []
     for k in range(K):
         xk, wk = x[k].clone().requires_grad_(True), w[k].clone().requires_grad_(True)
@@ -161,30 +166,36 @@ def test_stride2_backward_on_the_output_grid(native_lib, K, B, H, Cin, Cout):
         gx, gw = torch.autograd.grad(y, (xk, wk), dy[k])
         ref_dx.append(gx); ref_dw.append(gw)
     ref_dx, ref_dw = torch.stack(ref_dx), torch.stack(ref_dw)
-    pack, _, t_off = _pack_with_kernel(w, 3)
-    dyp = layout.to_planar(dy)
+    pack, _, t_off = _pack_with_kernel(w, 3, act)
+    dyp = layout.to_planar(dy, dtype=act.dtype)
     # input gradient
     go = layout.Geom(B, H, H)
-    dx = torch.zeros(K, Cin // 8, go.rows, 8, dtype=torch.bfloat16, device=d)
+    dx = torch.zeros(K, Cin // act.V, go.rows, act.V, dtype=act.dtype, device=d)
     wd = pack[:, t_off:]
     native.check(lib.dba_conv_tc_ex(native.ptr(dyp), native.ptr(wd), pack.stride(0), native.ptr(dx), None, None, None, 0,
                                     None, 0, K, B, Ho, Ho, Cout, 4 * Cin, 2, 1, 0, 0, 0, 3, native.stream()))
     torch.cuda.synchronize()
     got_dx = layout.from_planar(dx, B, H, H)
-    torch.testing.assert_close(got_dx, ref_dx, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(got_dx, ref_dx, rtol=act.rtol, atol=1.5 * act.atol)
     assert layout.halo_is_zero(dx, B, H, H)
     # weight gradient
-    xs = layout.to_planar(layout.space_to_depth(x))
+    xs = layout.to_planar(layout.space_to_depth(x), dtype=act.dtype)
     G = torch.zeros(K, 9 * Cin * Cout, device=d)
+    if act.name == "tf32":      # weight-gradient operands are the bf16 hi/lo split copies in this mode
+        def split(t):
+            hi = t.bfloat16()
+            return torch.stack([layout.to_planar(hi.float()), layout.to_planar((t - hi.float()).bfloat16().float())],
+                               1).contiguous()
+        dyp, xs = split(dy), split(layout.space_to_depth(x))
     native.check(lib.dba_wgrad_tc_s2d(native.ptr(dyp), native.ptr(xs), native.ptr(G), G.stride(0), 0, K, B, Ho, Ho, Cin,
                                       Cout, Cin, Cout, native.stream()))
     torch.cuda.synchronize()
     got_dw = G.view(K, Cout, 3, 3, Cin).permute(0, 1, 4, 2, 3)
     scale = ref_dw.abs().max().item()
-    torch.testing.assert_close(got_dw, ref_dw, rtol=2e-2, atol=2e-2 * scale)
+    torch.testing.assert_close(got_dw, ref_dw, rtol=2e-2, atol=act.atol * scale)
 
 
-def test_shortcut_input_gradient_added_in_place_at_even_pixels(native_lib):
+def test_shortcut_input_gradient_added_in_place_at_even_pixels(native_lib, act):
     """1x1 stride-2 convolution: dx[2h, 2w] += W^T dy[h, w] on the full-resolution gradient, other pixels untouched."""
     from dba_mod_b200.ops import layout, native
     lib = native.load()
@@ -192,15 +203,16 @@ def test_shortcut_input_gradient_added_in_place_at_even_pixels(native_lib):
     d = torch.device("cuda", 0)
     K, B, H, Cin, Cout = 2, 3, 16, 32, 64
     Ho = H // 2
-    w = (torch.randn(K, Cout, Cin, 1, 1, device=d) / Cin ** 0.5).bfloat16().float()
-    dy = torch.randn(K, B, Cout, Ho, Ho, device=d).bfloat16().float()
-    base = torch.randn(K, B, Cin, H, H, device=d).bfloat16().float()
+    w = (act.round(torch.randn(K, Cout, Cin, 1, 1, device=d) / Cin ** 0.5))
+    dy = act.round(torch.randn(K, B, Cout, Ho, Ho, device=d))
+    base = act.round(torch.randn(K, B, Cin, H, H, device=d))
     ref = base.clone()
     ref[:, :, :, 0::2, 0::2] += torch.einsum("koc,kbohw->kbchw", w[..., 0, 0], dy)
-    wt = layout.pack_conv_weight(w.transpose(1, 2))                    # Cout -> Cin, 1x1: no tap flip needed
-    dx = layout.to_planar(base)
-    native.check(lib.dba_conv_tc_ex(native.ptr(layout.to_planar(dy)), native.ptr(wt), wt[0].numel(), native.ptr(dx),
+    wt = layout.pack_conv_weight(w.transpose(1, 2), dtype=act.dtype)                    # Cout -> Cin, 1x1: no tap flip needed
+    dx = layout.to_planar(base, dtype=act.dtype)
+    dyp = layout.to_planar(dy, dtype=act.dtype)
+    native.check(lib.dba_conv_tc_ex(native.ptr(dyp), native.ptr(wt), wt[0].numel(), native.ptr(dx),
                                     native.ptr(dx), None, None, 0, None, 0, K, B, Ho, Ho, Cout, Cin, 1, 1, 0, 0, 0, 2,
                                     native.stream()))
     torch.cuda.synchronize()
-    torch.testing.assert_close(layout.from_planar(dx, B, H, H), ref, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(layout.from_planar(dx, B, H, H), ref, rtol=act.rtol, atol=1.5 * act.atol)

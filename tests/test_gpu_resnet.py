@@ -1,9 +1,12 @@
-"""Native ResNet executor (tcgen05 conv chain, bf16) vs the batched torch formulation (fp32) on a B200."""
+"""Native ResNet executor (tcgen05 conv chain) vs the batched torch formulation (fp32, TF32 off) on a B200, in both
+compute modes: ``tf32`` (fp32 activations, kind::tf32 MMA - the default, the reference's precision class) is held to
+tight bands, ``bf16`` (the opt-in fast mode) to the bands torch's own bf16 autocast achieves on this network."""
 import pytest
 import torch
 import yaml
 
 pytestmark = pytest.mark.gpu
+MODES = ["tf32", "bf16"]
 
 
 def _setup(train=1500, test=700, **over):
@@ -20,12 +23,13 @@ def _setup(train=1500, test=700, **over):
     return p, dev, data, spec, flat.to(dev)
 
 
-def test_native_eval_matches_torch(native_lib):
+@pytest.mark.parametrize("mode", MODES)
+def test_native_eval_matches_torch(native_lib, mode):
     from dba_mod_b200.fl.native_resnet import NativeResNet
     from dba_mod_b200.fl.torch_backend import TorchBackend
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    p, dev, data, spec, flat = _setup()
+    p, dev, data, spec, flat = _setup(compute_dtype=mode)
     torch.manual_seed(0)
     M = 3
     models = flat[None].repeat(M, 1)
@@ -40,8 +44,8 @@ def test_native_eval_matches_torch(native_lib):
         torch.cuda.synchronize()
         assert n0 == n1
         rel = ((l1 - l0).abs() / l0.abs()).max().item()
-        assert rel < 0.03, (split, trig, l0.tolist(), l1.tolist())
-        assert (c1 - c0).abs().max().item() <= max(3, 0.03 * n0), (c0.tolist(), c1.tolist())
+        assert rel < (2e-3 if mode == "tf32" else 0.03), (split, trig, l0.tolist(), l1.tolist())
+        assert (c1 - c0).abs().max().item() <= (2 if mode == "tf32" else max(3, 0.03 * n0)), (c0.tolist(), c1.tolist())
 
 
 def _one_step_schedule(p, data, names, dev, T=1):
@@ -51,19 +55,22 @@ def _one_step_schedule(p, data, names, dev, T=1):
     return build_schedule(p, data, plans, 1, dev, g)
 
 
-def test_native_train_gradients_match_autograd(native_lib):
-    """One SGD step of K=3 clients (one of them poisoning): per-tensor gradients of the native bf16 pipeline vs fp32
-    autograd of the batched torch formulation.
+@pytest.mark.parametrize("mode", MODES)
+def test_native_train_gradients_match_autograd(native_lib, mode):
+    """One SGD step of K=3 clients (one of them poisoning): per-tensor gradients of the native pipeline vs TRUE fp32
+    autograd (cuDNN TF32 off) of the batched torch formulation.
 
-    Tolerance calibration (tools/gpu_calib_bf16.py, profiles/calib_bf16_vs_fp32.txt): torch's own bf16 autocast of this
-    network at random init agrees with its fp32 gradients to cosine 0.918 (stem) ... 0.985 (layer4.1.conv2), 1.000
-    (linear) with norm ratios within 1.5 %; batch-statistics BatchNorm + ReLU make early-layer gradients that
-    sensitive to activation rounding.  The native pipeline measures 0.93 ... 0.99, 1.000 on the same scale."""
+    A random-init ResNet with batch-statistics BatchNorm amplifies operand rounding, so the yardstick for the tf32
+    mode is the reference's own precision class measured on the same batches: torch with cuDNN TF32 convolutions
+    deviates from true fp32 by 1 - cos = 5e-3 (stem) ... 1e-4 (layer4) (tools/gpu_calib_modes.py,
+    profiles/r2/calib_modes.txt; the native tf32 mode measures 1e-2 ... 1e-4); the native mode must stay within 3.5x of
+    the yardstick per tensor.  The bf16 fast mode
+    is held to what torch's own bf16 autocast achieves (profiles/calib_bf16_vs_fp32.txt)."""
     from dba_mod_b200.fl.native_resnet import NativeResNet
     from dba_mod_b200.fl.torch_backend import TorchBackend
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    p, dev, data, spec, flat = _setup(train=1280, test=200, sampling_dirichlet=False,
+    p, dev, data, spec, flat = _setup(train=1280, test=200, sampling_dirichlet=False, compute_dtype=mode,
                                       **{"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 1,
                                          "lr": 0.0, "poison_lr": 0.0})
     names = [17, 3, 5]
@@ -82,31 +89,49 @@ def test_native_train_gradients_match_autograd(native_lib):
     Wn = W0.clone()
     rn = nx.train(sch, Wn, cnt.clone(), W0.clone(), True)
     torch.cuda.synchronize()
+    yard = None
+    if mode == "tf32":           # the reference's precision class on the same batches: cuDNN TF32 convolutions
+        torch.backends.cudnn.allow_tf32 = True
+        yard = TorchBackend(p, spec, data, dev).train(sch, W0.clone(), cnt.clone(), W0.clone(), True).grad_sum
+        torch.backends.cudnn.allow_tf32 = False
+    cosf = torch.nn.functional.cosine_similarity
     bad = []
     for name in spec.param_names:
         e = spec.entries[name]
         a = rt.grad_sum[:, e.offset:e.offset + e.numel]
         b = rn.grad_sum[:, e.offset:e.offset + e.numel]
-        cos = torch.nn.functional.cosine_similarity(a, b, dim=1).min().item()
+        cos = cosf(a, b, dim=1).min().item()
         ratio = (b.norm(dim=1) / a.norm(dim=1).clamp(min=1e-12))
+        dev_r = (ratio - 1).abs().max().item()
         # BatchNorm gamma / beta gradients are 32..256-element sums with heavy cancellation -> looser band
         small = len(e.shape) == 1 and name != "linear.bias"
-        cmin, rmax = (0.75, 0.3) if small else (0.90, 0.1)
-        if not (cos >= cmin) or not ((ratio - 1).abs().max().item() <= rmax):
+        if mode == "tf32":
+            y = yard[:, e.offset:e.offset + e.numel]
+            err_y = 1.0 - cosf(a, y, dim=1).min().item()
+            dev_y = ((y.norm(dim=1) / a.norm(dim=1).clamp(min=1e-12)) - 1).abs().max().item()
+            ok = (1.0 - cos) <= 3.5 * err_y + 2e-4 and dev_r <= 2.5 * dev_y + (0.04 if small else 0.015)
+        else:                    # bf16 activations and gradients in HBM (profiles/calib_bf16_vs_fp32.txt)
+            cmin, rmax = (0.75, 0.4) if small else (0.90, 0.1)
+            ok = cos >= cmin and dev_r <= rmax
+        if not ok:
             bad.append((name, round(cos, 4), [round(float(v), 3) for v in ratio]))
     assert not bad, bad
     # metrics of the step and BatchNorm running statistics
     torch.testing.assert_close(rn.count, rt.count)
-    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, rtol=3e-2, atol=3e-2)
-    torch.testing.assert_close(Wn[:, spec.Dp:], Wt[:, spec.Dp:], rtol=5e-2, atol=5e-3)
+    tol = dict(rtol=3e-3, atol=3e-3) if mode == "tf32" else dict(rtol=3e-2, atol=3e-2)
+    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, **tol)
+    tol = dict(rtol=5e-3, atol=5e-4) if mode == "tf32" else dict(rtol=5e-2, atol=5e-3)
+    torch.testing.assert_close(Wn[:, spec.Dp:], Wt[:, spec.Dp:], **tol)
 
 
-def test_native_train_multi_step_tracks_torch(native_lib):
+@pytest.mark.parametrize("mode", MODES)
+def test_native_train_multi_step_tracks_torch(native_lib, mode):
     from dba_mod_b200.fl.native_resnet import NativeResNet
     from dba_mod_b200.fl.torch_backend import TorchBackend
     torch.backends.cudnn.allow_tf32 = False
-    p, dev, data, spec, flat = _setup(train=1500, test=200, **{"0_poison_epochs": [1], "internal_epochs": 2,
-                                                               "internal_poison_epochs": 3, "lr": 0.05})
+    p, dev, data, spec, flat = _setup(train=1500, test=200, compute_dtype=mode,
+                                      **{"0_poison_epochs": [1], "internal_epochs": 2, "internal_poison_epochs": 3,
+                                         "lr": 0.05})
     names = [17, 3]
     sch = _one_step_schedule(p, data, names, dev)
     K = len(names)
@@ -121,8 +146,10 @@ def test_native_train_multi_step_tracks_torch(native_lib):
     assert torch.equal(ct, cn)
     dt, dn = (Wt - W0)[:, :spec.Dp], (Wn - W0)[:, :spec.Dp]
     cos = torch.nn.functional.cosine_similarity(dt, dn, dim=1)
-    assert bool(torch.isfinite(dn).all()) and cos.min().item() > 0.8, cos.tolist()
-    assert ((dn.norm(dim=1) / dt.norm(dim=1)) - 1).abs().max().item() < 0.15
+    # a few dozen SGD steps of a random-init network amplify rounding differences (lr 0.05, momentum 0.9)
+    cmin, rmax = (0.90, 0.06) if mode == "tf32" else (0.8, 0.15)
+    assert bool(torch.isfinite(dn).all()) and cos.min().item() > cmin, cos.tolist()
+    assert ((dn.norm(dim=1) / dt.norm(dim=1)) - 1).abs().max().item() < rmax
     torch.testing.assert_close(rn.count, rt.count)
     torch.testing.assert_close(rn.poison_count, rt.poison_count)
 
@@ -135,7 +162,8 @@ def test_tail_compaction_matches_full_width_run(native_lib):
     segmented run is as close to a full-width run as two full-width runs are to each other (fp32 atomics in the
     BatchNorm statistics make a random-init bf16 ResNet visibly non-reproducible run to run)."""
     from dba_mod_b200.fl.native_resnet import NativeResNet
-    over = {"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 3, "lr": 0.02}
+    over = {"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 3, "lr": 0.02,
+            "compute_dtype": "bf16"}
     p, dev, data, spec, flat = _setup(train=1500, test=200, **over)
     names = [17, 3, 5]
     sch = _one_step_schedule(p, data, names, dev)
@@ -222,14 +250,16 @@ def _setup_tiny(train=640, test=200, **over):
     return p, dev, data, spec, flat.to(dev)
 
 
-def test_tiny_native_eval_and_train(native_lib):
+@pytest.mark.parametrize("mode", MODES)
+def test_tiny_native_eval_and_train(native_lib, mode):
     """Tiny-ImageNet ResNet-18 (7x7 stride-2 stem as a tensor-core GEMM over im2col'd patches, max-pool, 64..512
     channels, 200-way head) on the native executor vs the batched torch formulation."""
     from dba_mod_b200.fl.native_resnet import NativeResNet
     from dba_mod_b200.fl.torch_backend import TorchBackend
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    p, dev, data, spec, flat = _setup_tiny(**{"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 1,
+    p, dev, data, spec, flat = _setup_tiny(compute_dtype=mode,
+                                           **{"0_poison_epochs": [1], "internal_epochs": 1, "internal_poison_epochs": 1,
                                               "lr": 0.0, "poison_lr": 0.0})
     torch.manual_seed(0)
     M = 2
@@ -242,7 +272,8 @@ def test_tiny_native_eval_and_train(native_lib):
     for split, trig in [("clean", 0), ("poison", 1)]:
         l0, c0, n0 = tb.evaluate(models, split, trig)
         l1, c1, n1 = nx.evaluate(models, split, trig)
-        assert n0 == n1 and ((l1 - l0).abs() / l0.abs()).max().item() < 0.03, (l0.tolist(), l1.tolist())
+        assert n0 == n1 and ((l1 - l0).abs() / l0.abs()).max().item() < (2e-3 if mode == "tf32" else 0.03), \
+            (l0.tolist(), l1.tolist())
     names = [0, 3]
     sch = _one_step_schedule(p, data, names, dev)
     K = len(names)
@@ -254,8 +285,10 @@ def test_tiny_native_eval_and_train(native_lib):
     rn = nx.train(sch, Wn, cnt.clone(), W0.clone(), True)
     torch.cuda.synchronize()
     torch.testing.assert_close(rn.count, rt.count)
-    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, rtol=3e-2, atol=3e-2)
+    torch.testing.assert_close(rn.loss_sum, rt.loss_sum, **(dict(rtol=2e-3, atol=2e-3) if mode == "tf32"
+                                                             else dict(rtol=3e-2, atol=3e-2)))
     bad = []
+    cmin, rmax = (0.97, 0.05) if mode == "tf32" else (0.85, 0.15)
     for name in spec.param_names:
         e = spec.entries[name]
         if len(e.shape) == 1 and name != "fc.bias":
@@ -264,7 +297,7 @@ def test_tiny_native_eval_and_train(native_lib):
         b = rn.grad_sum[:, e.offset:e.offset + e.numel]
         cos = torch.nn.functional.cosine_similarity(a, b, dim=1).min().item()
         ratio = (b.norm(dim=1) / a.norm(dim=1).clamp(min=1e-12))
-        if not (cos >= 0.85) or not ((ratio - 1).abs().max().item() <= 0.15):
+        if not (cos >= cmin) or not ((ratio - 1).abs().max().item() <= rmax):
             bad.append((name, round(cos, 4), [round(float(v), 3) for v in ratio]))
     assert not bad, bad
 
