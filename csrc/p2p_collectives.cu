@@ -2,23 +2,26 @@
 // torch.distributed._symmetric_memory; no NCCL call on these paths).
 //
 // Reference: the reduction / broadcast points R1-R4 of SURVEY §2.3 - helper.py:193-257 (FedAvg accumulate + apply),
-// helper.py:295-418 (Weiszfeld weighted averages), helper.py:534-572 (FoolsGold gather + weighted reduce), and the
-// global->client copy image_train.py:26-32.  The reference does them with Python loops on one device.
+// helper.py:295-418 (RFA / Weiszfeld), helper.py:534-572 (FoolsGold gather + weighted reduce), and the global->client
+// copy image_train.py:26-32.  The reference does them with Python loops on one device.
 //
-// Protocol.  Every rank launches the same kernel on its own GPU.  `peers[q]` are the device addresses of rank q's
-// symmetric staging buffer, global-model replica and signal pad, mapped into this process.  A kernel has up to three
-// phases separated by a cross-GPU barrier:
-//   phase 1  local K-way reduce of the client rows into this rank's staging vector (plain HBM traffic);
-//   barrier  (grid-wide arrival counter -> last block publishes this rank's ticket in every peer's signal pad with
-//            st.release.sys; every block then spins with ld.acquire.sys until all peers' tickets arrived);
-//   phase 2  rank r owns slice r of the vector: it loads that slice from every peer's staging buffer (P2P loads),
-//            applies the update (FedAvg scale + DP noise / plain sum) and stores the result into EVERY peer's replica
-//            (P2P stores) - reduce-scatter + update + all-gather in one launch, tile by tile;
-//   barrier  so that nobody reads a replica before all slices landed.
-// With NVLS (multicast mappings of the same buffers) phase 2 is one multimem.ld_reduce (sum formed inside the NVSwitch)
-// and one multimem.st (broadcast by the switch) per 16 bytes instead of `world` peer loads and `world` peer stores.
-// Tickets grow monotonically per call, so signal pads never need to be cleared.  All blocks of a launch must be
-// co-resident (grid <= 148): they wait on one another.
+// Protocol.  Every rank launches the same kernel on its own GPU (cooperative launch: all blocks are guaranteed
+// co-resident, they wait on one another).  `stage[q]`, `replica[q]`, `aux[q]`, `signal[q]`, `mail[q]` are the device
+// addresses of rank q's symmetric buffers mapped into this process.  A kernel is a sequence of phases separated by a
+// cross-GPU barrier:
+//   local phase   e.g. the K-way (weighted) reduce of this rank's client rows into its staging vector (HBM traffic);
+//   barrier       per-phase arrival counter on this GPU; the last block publishes (optionally after writing a small
+//                 scalar payload into every peer's mailbox) this rank's ticket in every peer's signal pad with
+//                 st.release.sys; then the lanes of one warp per block poll the peers' tickets in parallel with
+//                 ld.acquire.sys;
+//   owner phase   rank r owns slice r of the vector: it loads that slice from every peer's staging buffer (P2P loads),
+//                 applies the update (FedAvg scale + DP noise / axpby / Weiszfeld normalisation) and stores the result
+//                 into EVERY peer's target buffer (P2P stores) - reduce-scatter + update + all-gather, tile by tile;
+//   barrier       so that nobody reads a target before all slices landed.
+// With NVLS (multicast mappings of the same buffers) the owner phase is one multimem.ld_reduce (sum formed inside the
+// NVSwitch) and one multimem.st (broadcast by the switch) per 16 bytes instead of `world` peer loads / stores.
+// Tickets grow monotonically per call, so signal pads never need clearing.  A wait that exceeds ~4 s sets the error
+// flag (a peer died or never launched) and falls through instead of hanging the GPU; the host checks the flag.
 #include "common.cuh"
 #include <curand_kernel.h>
 
@@ -27,15 +30,21 @@ using namespace dba;
 namespace {
 
 constexpr int kMaxRanks = 8;
+constexpr int kMaxPhases = 8;
+constexpr int kCollThreads = 512;      // one block per SM: 16 warps keep enough 16-byte loads in flight per SM
+constexpr long long kSpinBudget = 8000000000LL;      // clock64 ticks (~4 s): far beyond any legitimate wait
 
 struct PeerSet {
-  float* stage[kMaxRanks];        // [D] partial sums of each rank
-  float* replica[kMaxRanks];      // [D] global model (or any broadcast target) of each rank
-  unsigned int* signal[kMaxRanks];  // [2 * kMaxRanks] tickets: slot phase*kMaxRanks + sender
+  float* stage[kMaxRanks];          // [D] partial sums of each rank
+  float* replica[kMaxRanks];        // [D] target of the owner phase on each rank (global model or auxiliary vector)
+  unsigned int* signal[kMaxRanks];  // [kMaxPhases * kMaxRanks] tickets: slot phase*kMaxRanks + sender
+  double* mail[kMaxRanks];          // [kMaxPhases * kMaxRanks * 2] scalar payloads travelling with a ticket
+  unsigned int* counter;            // [kMaxPhases] arrival counters of THIS GPU (reset by the last arriver)
+  int* err;                         // [1] error flag of THIS GPU (1 = barrier timeout)
   int rank, world;
-  // NVLS: multicast addresses of the staging / replica buffers (null = peer loads / stores).  A multimem.ld_reduce on
+  // NVLS: multicast addresses of the staging / target buffers (null = peer loads / stores).  A multimem.ld_reduce on
   // stage_mc returns the sum over ALL ranks' staging vectors, reduced inside the NVSwitch; a multimem.st on replica_mc
-  // lands in every rank's replica.
+  // lands in every rank's target.
   float* stage_mc;
   float* replica_mc;
 };
@@ -60,24 +69,44 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
   return v;
 }
 
-// Cross-GPU barrier usable inside a kernel whose blocks are all resident.  `counter` is a per-GPU arrival counter
-// (monotonic), `ticket` identifies (call, phase).
-__device__ void grid_and_peer_barrier(const PeerSet& ps, unsigned int* counter, unsigned int arrivals_target,
-                                      int phase, unsigned int ticket) {
+// Cross-GPU barrier inside a cooperative kernel.  `ticket` identifies the call (same on all ranks, strictly increasing
+// per phase slot).  pay0 / pay1: scalars this rank sends to every peer with the ticket (read them after the barrier
+// with mail_read); pass has_payload = false when there is nothing to send.
+__device__ void grid_and_peer_barrier(const PeerSet& ps, int phase, unsigned int ticket, bool has_payload = false,
+                                      double pay0 = 0.0, double pay1 = 0.0) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
-    const unsigned int prev = atomicAdd(counter, 1u);
-    if (prev + 1 == arrivals_target) {        // last block of this GPU: publish to every peer (incl. self)
-      for (int q = 0; q < ps.world; ++q) st_release_sys(ps.signal[q] + phase * kMaxRanks + ps.rank, ticket);
+    const unsigned int prev = atomicAdd(ps.counter + phase, 1u);
+    if (prev + 1 == gridDim.x) {              // last block of this GPU: publish to every peer (incl. self)
+      ps.counter[phase] = 0;                  // everybody has arrived: the counter is free for the next call
+      for (int q = 0; q < ps.world; ++q) {
+        if (has_payload) {
+          double* m = ps.mail[q] + ((long long)phase * kMaxRanks + ps.rank) * 2;
+          m[0] = pay0;
+          m[1] = pay1;
+        }
+        st_release_sys(ps.signal[q] + phase * kMaxRanks + ps.rank, ticket);
+      }
     }
-    for (int q = 0; q < ps.world; ++q) {
+  }
+  if (threadIdx.x < 32) {                     // lane q polls peer q's ticket: one round trip for all peers
+    const int q = threadIdx.x;
+    if (q < ps.world) {
       const unsigned int* flag = ps.signal[ps.rank] + phase * kMaxRanks + q;
-      while ((int)(ld_acquire_sys(flag) - ticket) < 0) { __nanosleep(64); }
+      const long long t0 = clock64();
+      while ((int)(ld_acquire_sys(flag) - ticket) < 0) {
+        __nanosleep(32);
+        if (clock64() - t0 > kSpinBudget) { *ps.err = 1; break; }
+      }
     }
+    __syncwarp();
     __threadfence_system();
   }
   __syncthreads();
+}
+__device__ __forceinline__ double mail_read(const PeerSet& ps, int phase, int sender, int which) {
+  return ps.mail[ps.rank][((long long)phase * kMaxRanks + sender) * 2 + which];
 }
 
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
@@ -94,9 +123,9 @@ __device__ __forceinline__ void owned_slice(long long D, int rank, int world, lo
   if (hi > D) hi = D;
 }
 
-// Phase 2 worker shared by both kernels: out = f(own value, sum over all peers' staging vectors) for the owned slice,
-// written to every peer's replica.  Remote loads have ~2-3 us latency, so every thread keeps world x 2 independent
-// 16-byte loads in flight before it touches the data.
+// Owner phase shared by all kernels: out = f(own value, sum over all peers' staging vectors, index) for the owned
+// slice, written to every peer's target.  Remote loads have ~2-3 us latency, so every thread keeps world x 2
+// independent 16-byte loads in flight (4 switch-reduced loads on the NVLS path) before it touches the data.
 template <typename F>
 __device__ __forceinline__ void reduce_scatter_update_gather(const PeerSet& ps, long long D, F f) {
   long long lo, hi;
@@ -107,15 +136,20 @@ __device__ __forceinline__ void reduce_scatter_update_gather(const PeerSet& ps, 
   long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (ps.stage_mc != nullptr) {
     // NVLS path: one switch-reduced load and one multicast store per 16 bytes, whatever the number of ranks
-    for (; v + stride < nvec; v += 2 * stride) {
-      const long long i0 = lo + (v << 2), i1 = lo + ((v + stride) << 2);
-      const float4 a0 = mc_ld_reduce4(ps.stage_mc + i0), a1 = mc_ld_reduce4(ps.stage_mc + i1);
-      const float4 g0 = ld4(mine + i0), g1 = ld4(mine + i1);
-      float4 o0, o1;
-      o0.x = f(g0.x, a0.x, i0); o0.y = f(g0.y, a0.y, i0 + 1); o0.z = f(g0.z, a0.z, i0 + 2); o0.w = f(g0.w, a0.w, i0 + 3);
-      o1.x = f(g1.x, a1.x, i1); o1.y = f(g1.y, a1.y, i1 + 1); o1.z = f(g1.z, a1.z, i1 + 2); o1.w = f(g1.w, a1.w, i1 + 3);
-      mc_st4(ps.replica_mc + i0, o0);
-      mc_st4(ps.replica_mc + i1, o1);
+    for (; v + 3 * stride < nvec; v += 4 * stride) {
+      float4 a[4], g[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) a[u] = mc_ld_reduce4(ps.stage_mc + lo + ((v + u * stride) << 2));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) g[u] = ld4(mine + lo + ((v + u * stride) << 2));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = lo + ((v + u * stride) << 2);
+        float4 o;
+        o.x = f(g[u].x, a[u].x, i); o.y = f(g[u].y, a[u].y, i + 1); o.z = f(g[u].z, a[u].z, i + 2);
+        o.w = f(g[u].w, a[u].w, i + 3);
+        mc_st4(ps.replica_mc + i, o);
+      }
     }
     for (; v < nvec; v += stride) {
       const long long i0 = lo + (v << 2);
@@ -163,34 +197,43 @@ __device__ __forceinline__ void reduce_scatter_update_gather(const PeerSet& ps, 
   }
 }
 
-// F1: FedAvg fused with delta extraction, cross-GPU reduce, global update (+DP noise) and broadcast of the new model
-// into every replica.
-__global__ void __launch_bounds__(256) fedavg_p2p_kernel(const float* __restrict__ W, long long ldw, int K, long long D,
-                                                         float coef, float sigma, unsigned long long seed,
-                                                         PeerSet ps, unsigned int* counter, unsigned int call_id,
-                                                         int total_clients) {
-  float* stage = ps.stage[ps.rank];
-  // phase 1: local sum of client states (the -n*G term is applied once, in phase 2, with the global client count)
+// Local phase shared by the kernels:  stage[i] = sum_k c_k * (W[k][i] - (sub ? G[i] : 0)),  c_k = coef_s[k] (shared
+// memory) or 1.  Subtracting the replica per row (instead of n*G after the sum) keeps the small client deltas from
+// being cancelled against the large weights - the same arithmetic as the single-GPU kernel and the reference.
+__device__ __forceinline__ void local_rows_reduce(const float* __restrict__ W, long long ldw, int K, long long D,
+                                                  const float* __restrict__ G, const float* coef_s, float* stage) {
   const long long nvec = D >> 2;
-  const bool vec_ok = (ldw & 3) == 0 && (((uintptr_t)W & 15) == 0);
+  const bool vec_ok = (ldw & 3) == 0 && (((uintptr_t)W & 15) == 0) && (!G || ((uintptr_t)G & 15) == 0);
   if (vec_ok) {
     for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int k = 0; k < K; ++k) acc = add4(acc, ld4(W + k * ldw + (v << 2)));
+      const float4 g = G ? ld4(G + (v << 2)) : acc;
+      for (int k = 0; k < K; ++k) {
+        const float4 w = ld4(W + k * ldw + (v << 2));
+        const float c = coef_s ? coef_s[k] : 1.f;
+        acc.x += c * (w.x - g.x); acc.y += c * (w.y - g.y); acc.z += c * (w.z - g.z); acc.w += c * (w.w - g.w);
+      }
       st4(stage + (v << 2), acc);
     }
   }
   for (long long i = (vec_ok ? (nvec << 2) : 0) + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < D;
        i += (long long)gridDim.x * blockDim.x) {
     float acc = 0.f;
-    for (int k = 0; k < K; ++k) acc += W[k * ldw + i];
+    const float g = G ? G[i] : 0.f;
+    for (int k = 0; k < K; ++k) acc += (coef_s ? coef_s[k] : 1.f) * (W[k * ldw + i] - g);
     stage[i] = acc;
   }
-  grid_and_peer_barrier(ps, counter, (2 * call_id + 1) * gridDim.x, 0, 2 * call_id + 1);
-  // phase 2: this rank reduces + updates its slice and scatters it to all replicas
-  const float n = (float)total_clients;
+}
+
+// F1: FedAvg fused with delta extraction, cross-GPU reduce, global update (+DP noise) and broadcast of the new model
+// into every replica:  G += coef * sum over ALL ranks' rows of (W[k] - G).
+__global__ void __launch_bounds__(kCollThreads) fedavg_p2p_kernel(const float* __restrict__ W, long long ldw, int K, long long D,
+                                                         float coef, float sigma, unsigned long long seed,
+                                                         PeerSet ps, unsigned int ticket) {
+  local_rows_reduce(W, ldw, K, D, ps.replica[ps.rank], nullptr, ps.stage[ps.rank]);
+  grid_and_peer_barrier(ps, 0, ticket);
   reduce_scatter_update_gather(ps, D, [=](float g, float acc, long long i) {
-    float out = g + coef * (acc - n * g);
+    float out = g + coef * acc;
     if (sigma > 0.f) {
       curandStatePhilox4_32_10_t st;
       curand_init(seed, (unsigned long long)i, 0, &st);
@@ -198,19 +241,163 @@ __global__ void __launch_bounds__(256) fedavg_p2p_kernel(const float* __restrict
     }
     return out;
   });
-  grid_and_peer_barrier(ps, counter, (2 * call_id + 2) * gridDim.x, 1, 2 * call_id + 2);
+  grid_and_peer_barrier(ps, 1, ticket);
 }
 
-// Generic fused all-reduce (sum) of the ranks' staging vectors into every replica:  replica[q][i] = beta*replica[q][i]
-// + alpha * sum_r stage[r][i].  Used per Weiszfeld iteration (median) and for FoolsGold's weighted gradient reduce
-// fused with the server SGD step (alpha = -lr*eta/n, beta = 1 - lr*decay).
-__global__ void __launch_bounds__(256) allreduce_axpby_p2p_kernel(long long D, float alpha, float beta, PeerSet ps,
-                                                                  unsigned int* counter, unsigned int call_id) {
-  grid_and_peer_barrier(ps, counter, (2 * call_id + 1) * gridDim.x, 0, 2 * call_id + 1);
+// Fused weighted all-reduce:  target[i] = beta*target[i] + alpha * sum over all ranks of (sum_k wv[k] * S[k][i]).
+// K > 0: the local weighted K-way reduce of the rows S is phase 1 of the same launch (FoolsGold's weighted gradient
+// reduce + server SGD step: alpha = -lr*eta/n, beta = 1 - lr*decay, helper.py:280-290,561-570).  K == 0: the staging
+// vector was filled by the caller (plain all-reduce of a vector).
+__global__ void __launch_bounds__(kCollThreads) axpby_p2p_kernel(const float* __restrict__ S, long long lds, int K,
+                                                        const double* __restrict__ wv, long long D, float alpha,
+                                                        float beta, PeerSet ps, unsigned int ticket) {
+  extern __shared__ float coef_s[];
+  if (K > 0) {
+    for (int k = threadIdx.x; k < K; k += blockDim.x) coef_s[k] = wv ? (float)wv[k] : 1.f;
+    __syncthreads();
+    local_rows_reduce(S, lds, K, D, nullptr, coef_s, ps.stage[ps.rank]);
+  }
+  grid_and_peer_barrier(ps, 0, ticket);
   reduce_scatter_update_gather(ps, D, [=](float g, float acc, long long) {
     return (beta != 0.f ? beta * g : 0.f) + alpha * acc;
   });
-  grid_and_peer_barrier(ps, counter, (2 * call_id + 2) * gridDim.x, 1, 2 * call_id + 2);
+  grid_and_peer_barrier(ps, 1, ticket);
+}
+
+// F2: ONE Weiszfeld iteration of the geometric median over the client deltas (W[k] - G) of ALL ranks
+// (helper.py:295-373) in one launch per rank: local weights from the local distances -> local weighted partial sum
+// -> barrier carrying (local weight sum, local objective part) -> every rank forms the global weight sum / objective
+// and runs the convergence test on identical numbers -> owner phase: median slice = sum_r stage_r / weight sum,
+// stored into every rank's median buffer -> barrier -> local squared distances to the new median (accumulated for the
+// next launch).  Launch `it` tests the objective of iteration it-1 (deferred by one launch so that it needs no
+// barrier of its own); launch maxiter+1 only tests and publishes the per-client results.
+struct WzArgs {
+  const float* W;              // [K][ldw] local client states
+  long long ldw, D;
+  const float* G;              // [D] global model (local replica)
+  const float* alphas;         // [K] n_c / sum over ALL clients of n
+  double* dist2;               // [2][kmax] squared distances of the local clients (parity buffers)
+  float* wts;                  // [K] normalised weights of the previous launch's iteration
+  float* wv;                   // [K] reported weights (Q8 semantics, see flat_ops.cu)
+  double* obj;                 // [2] objective by launch parity
+  int* state;                  // [4]: done, iterations, oracle calls, parity slot of the last objective
+  float* const* table;         // [world] symmetric result tables [2][n_total]: wv and distance of every client
+  int K, kmax, it, maxiter, slot0, n_total;
+  float eps;
+  double ftol;
+};
+__global__ void __launch_bounds__(kCollThreads) weiszfeld_p2p_kernel(WzArgs a, PeerSet ps, unsigned int ticket) {
+  extern __shared__ float w_s[];             // [K] un-normalised weights of this launch
+  __shared__ double red[32];
+  __shared__ double s_tot[2];
+  if (a.state[0]) return;                    // converged in an earlier launch: identical decision on every rank
+  const bool first = a.it == 0, last = a.it == a.maxiter + 1;
+  const int par = a.it & 1;
+  // ---- local weights and scalars (every block computes them: K <= 1024 values)
+  double wsum = 0.0, opart = 0.0;
+  for (int c = threadIdx.x; c < a.K; c += blockDim.x) {
+    const double d = first ? 0.0 : sqrt(a.dist2[(long long)par * a.kmax + c]);
+    const float w = first ? a.alphas[c] : a.alphas[c] / fmaxf(a.eps, (float)d);
+    w_s[c] = w;
+    wsum += (double)w;
+    opart += (double)a.alphas[c] * d;
+  }
+  wsum = block_sum(wsum, red, true);
+  opart = block_sum(opart, red, true);
+  if (blockIdx.x == 0)                       // the other parity buffer collects this launch's distances
+    for (int c = threadIdx.x; c < a.K; c += blockDim.x) a.dist2[(long long)(par ^ 1) * a.kmax + c] = 0.0;
+  __syncthreads();
+  if (!last) local_rows_reduce(a.W, a.ldw, a.K, a.D, a.G, w_s, ps.stage[ps.rank]);
+  grid_and_peer_barrier(ps, 2, ticket, true, wsum, opart);
+  // ---- global scalars, summed in rank order on every rank
+  if (threadIdx.x == 0) {
+    double tw = 0.0, ob = 0.0;
+    for (int q = 0; q < ps.world; ++q) { tw += mail_read(ps, 2, q, 0); ob += mail_read(ps, 2, q, 1); }
+    s_tot[0] = tw;
+    s_tot[1] = ob;
+  }
+  __syncthreads();
+  const double tot_w = s_tot[0], obj = s_tot[1];
+  bool conv = false;
+  if (!first) {                              // test the iteration computed by the previous launch (t = it - 1)
+    const bool first_t = a.it == 1;
+    const double prev = a.obj[par ^ 1];
+    conv = !first_t && fabs(prev - obj) < a.ftol * obj;
+    const int iters_before = a.state[1];
+    if (blockIdx.x == 0) {
+      if (first_t || !conv || iters_before == 0)
+        for (int c = threadIdx.x; c < a.K; c += blockDim.x) a.wv[c] = a.wts[c];
+    }
+    __syncthreads();
+  }
+  const bool finish = conv || last;
+  if (!finish) {
+    const float inv = (float)(1.0 / tot_w);
+    if (blockIdx.x == 0)
+      for (int c = threadIdx.x; c < a.K; c += blockDim.x) a.wts[c] = w_s[c] * inv;
+    // ---- owner phase: normalised median slice into every rank's median buffer
+    reduce_scatter_update_gather(ps, a.D, [=](float, float acc, long long) { return acc * inv; });
+    grid_and_peer_barrier(ps, 3, ticket);
+    // ---- local squared distances to the new median (double accumulation, one atomic per block and client)
+    const float* med = ps.replica[ps.rank];
+    for (int c = 0; c < a.K; ++c) {
+      const float* x = a.W + c * a.ldw;
+      double acc = 0.0;
+      for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < a.D;
+           i += (long long)gridDim.x * blockDim.x) {
+        const float d = x[i] - a.G[i] - med[i];
+        acc += (double)d * (double)d;
+      }
+      acc = block_sum(acc, red);
+      if (threadIdx.x == 0) atomicAdd(&a.dist2[(long long)(par ^ 1) * a.kmax + c], acc);
+    }
+  } else {
+    // ---- publish (wv, distance) of the local clients into every rank's result table
+    if (blockIdx.x == 0) {
+      for (int c = threadIdx.x; c < a.K; c += blockDim.x) {
+        const float d = (float)sqrt(a.dist2[(long long)par * a.kmax + c]);
+        const float w = a.wv[c];
+        for (int q = 0; q < ps.world; ++q) {
+          a.table[q][a.slot0 + c] = w;
+          a.table[q][a.n_total + a.slot0 + c] = d;
+        }
+      }
+    }
+    grid_and_peer_barrier(ps, 4, ticket);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    a.obj[par] = obj;
+    a.state[3] = par;                        // where the last objective lives
+    if (!first) {
+      a.state[2] += 1;
+      if (a.it > 1) a.state[1] += 1;
+      if (finish) a.state[0] = 1;
+    }
+  }
+}
+
+// Standalone cross-GPU barrier (stream-ordered): everything the peers enqueued before their matching call is
+// complete and visible when this kernel ends - replaces cudaDeviceSynchronize + an NCCL barrier.
+__global__ void __launch_bounds__(64) peer_barrier_kernel(PeerSet ps, unsigned int ticket) {
+  grid_and_peer_barrier(ps, 5, ticket);
+}
+
+// out[j][:] = *rows[j] for j < n: rows may live on other GPUs (peer-mapped pointers): the gather is a set of NVLink
+// loads into THIS GPU's memory (evaluation exchange of client models, simulator._run_eval_jobs_balanced).
+__global__ void __launch_bounds__(256) gather_rows_ptrs_kernel(const float* const* __restrict__ rows, int n, long long D,
+                                                               float* __restrict__ out, long long ldo) {
+  const int j = blockIdx.y;
+  const float* src = rows[j];
+  float* dst = out + (long long)j * ldo;
+  const long long nvec = D >> 2;
+  const bool vec_ok = (((uintptr_t)src | (uintptr_t)dst) & 15) == 0;
+  if (vec_ok) {
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x)
+      st4(dst + (v << 2), ld4(src + (v << 2)));
+  }
+  for (long long i = (vec_ok ? (nvec << 2) : 0) + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < D;
+       i += (long long)gridDim.x * blockDim.x)
+    dst[i] = src[i];
 }
 
 // F3 (gather part): Gram matrix over feature rows that live on DIFFERENT GPUs - rows are read through peer pointers
@@ -231,80 +418,159 @@ __global__ void __launch_bounds__(256) gram_ptrs_kernel(const double* const* __r
   }
 }
 
-static int fill_peers(PeerSet& ps, const void* const* stage, const void* const* replica, const void* const* signal,
-                      int rank, int world) {
-  if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world) return 1;
-  ps.rank = rank;
-  ps.world = world;
-  for (int q = 0; q < world; ++q) {
-    ps.stage[q] = (float*)stage[q];
-    ps.replica[q] = (float*)replica[q];
-    ps.signal[q] = (unsigned int*)signal[q];
-  }
-  ps.stage_mc = nullptr;
-  ps.replica_mc = nullptr;
-  return 0;
+// ---------------------------------------------------------------------------------------------- host side
+// One communicator context per process (one process per GPU).
+struct PeerCtx {
+  bool ready = false;
+  PeerSet ps{};
+  float* aux[kMaxRanks];
+  float* table[kMaxRanks];
+  float** table_dev = nullptr;     // device copy of the table pointers
+  float* stage_mc = nullptr;
+  float* replica_mc = nullptr;
+  float* aux_mc = nullptr;
+  unsigned int ticket = 0;
+  int grid = 0;
+  int table_cap = 0;
+};
+PeerCtx g_ctx;
+
+// Cooperative launch: the driver refuses the launch when the grid cannot be co-resident (instead of a deadlock of
+// blocks waiting for peers that were never scheduled).
+template <typename... Args>
+cudaError_t coop_launch(void (*kernel)(Args...), int grid, int block, size_t smem, cudaStream_t st, Args... args) {
+  void* argv[] = {(void*)&args...};
+  return cudaLaunchCooperativeKernel((const void*)kernel, dim3(grid), dim3(block), argv, smem, st);
+}
+
+PeerSet peers_for(int target, bool nvls) {
+  PeerSet ps = g_ctx.ps;
+  if (target == 1)
+    for (int q = 0; q < ps.world; ++q) ps.replica[q] = g_ctx.aux[q];
+  ps.stage_mc = nvls ? g_ctx.stage_mc : nullptr;
+  ps.replica_mc = nvls ? (target == 1 ? g_ctx.aux_mc : g_ctx.replica_mc) : nullptr;
+  return ps;
 }
 
 }  // namespace
 
 extern "C" {
 
-// stage / replica / signal: host arrays of `world` device pointers (peer-mapped symmetric memory).  signal pads need
-// 2*8 uint32 each, zero-initialised once.  counter: one zero-initialised uint32 in local device memory per GPU.
-// call_id: 0, 1, 2, ... identical on all ranks, strictly increasing per (signal pad, counter) pair.
-int dba_fedavg_p2p(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
-                   const void* const* stage, const void* const* replica, const void* const* signal, int rank,
-                   int world, int total_clients, unsigned int* counter, unsigned int call_id, void* stream) {
-  PeerSet ps;
-  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_fedavg_p2p: bad rank/world %d/%d", rank,
+// Registers the symmetric buffers of this process' communicator.  stage / replica / aux: [D] floats per rank;
+// signal: 64 uint32 per rank, mail: 128 doubles per rank, table: 2*table_cap floats per rank - all zero-initialised,
+// all peer-mapped (host arrays of `world` device pointers).  *_mc: multicast addresses (nullable).  counters: 8
+// zero-initialised uint32, err: 1 zero-initialised int, table_dev: room for `world` pointers - local device memory.
+int dba_peer_init(int rank, int world, const void* const* stage, const void* const* replica, const void* const* aux,
+                  const void* const* signal, const void* const* mail, const void* const* table, int table_cap,
+                  void* stage_mc, void* replica_mc, void* aux_mc, unsigned int* counters, int* err, void* table_dev) {
+  DBA_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "dba_peer_init: bad rank/world %d/%d", rank,
               world);
-  DBA_REQUIRE(K >= 0 && D > 0, "dba_fedavg_p2p: K=%d D=%lld", K, D);
-  fedavg_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(W, ldw, K, D, coef, sigma, seed, ps, counter, call_id,
-                                                              total_clients);
-  DBA_COUNT_LAUNCH(1);
-  DBA_CHECK_LAUNCH();
+  PeerCtx& c = g_ctx;
+  c = PeerCtx();
+  c.ps.rank = rank;
+  c.ps.world = world;
+  for (int q = 0; q < world; ++q) {
+    c.ps.stage[q] = (float*)stage[q];
+    c.ps.replica[q] = (float*)replica[q];
+    c.aux[q] = (float*)aux[q];
+    c.ps.signal[q] = (unsigned int*)signal[q];
+    c.ps.mail[q] = (double*)mail[q];
+    c.table[q] = (float*)table[q];
+  }
+  c.ps.counter = counters;
+  c.ps.err = err;
+  c.stage_mc = (float*)stage_mc; c.replica_mc = (float*)replica_mc; c.aux_mc = (float*)aux_mc;
+  c.table_cap = table_cap;
+  c.table_dev = (float**)table_dev;
+  DBA_CHECK_CUDA(cudaMemcpy(c.table_dev, c.table, sizeof(float*) * world, cudaMemcpyHostToDevice));
+  // one block per SM, as many as can be co-resident (cooperative launch requirement)
+  int dev = 0, sms = 0, coop = 0, occ = 0;
+  DBA_CHECK_CUDA(cudaGetDevice(&dev));
+  DBA_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  DBA_CHECK_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+  DBA_REQUIRE(coop != 0, "dba_peer_init: device %d does not support cooperative launches", dev);
+  DBA_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, weiszfeld_p2p_kernel, kCollThreads, 4096));
+  DBA_REQUIRE(occ >= 1, "dba_peer_init: the collective kernels do not fit on an SM");
+  c.grid = sms;
+  c.ready = true;
   return DBA_OK;
 }
 
-// NVLS variants: stage_mc / replica_mc are the multicast addresses of the same symmetric buffers (both non-null and
-// 16-byte aligned); phase 2 then uses multimem.ld_reduce / multimem.st (reduction inside the NVSwitch).
-int dba_fedavg_nvls(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
-                    const void* const* stage, const void* const* replica, const void* const* signal, void* stage_mc,
-                    void* replica_mc, int rank, int world, int total_clients, unsigned int* counter,
-                    unsigned int call_id, void* stream) {
-  PeerSet ps;
-  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_fedavg_nvls: bad rank/world %d/%d", rank,
-              world);
-  DBA_REQUIRE(K >= 0 && D > 0 && stage_mc && replica_mc, "dba_fedavg_nvls: K=%d D=%lld", K, D);
-  ps.stage_mc = (float*)stage_mc; ps.replica_mc = (float*)replica_mc;
-  fedavg_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(W, ldw, K, D, coef, sigma, seed, ps, counter, call_id,
-                                                              total_clients);
+/* 0 = fine; 1 = a cross-GPU barrier timed out on this GPU (a peer died or never launched the matching kernel). */
+int dba_peer_error(void) {
+  if (!g_ctx.ready) return 0;
+  int e = 0;
+  if (cudaMemcpy(&e, g_ctx.ps.err, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return 2;
+  return e;
+}
+
+// G (the replica) += coef * sum over ALL ranks' client rows (W[k] - G)  (+ sigma*N(0,1)), new G in every replica.
+int dba_peer_fedavg(const float* W, long long ldw, int K, long long D, float coef, float sigma,
+                    unsigned long long seed, int nvls, void* stream) {
+  DBA_REQUIRE(g_ctx.ready, "dba_peer_fedavg: dba_peer_init has not been called");
+  DBA_REQUIRE(K >= 0 && D > 0, "dba_peer_fedavg: K=%d D=%lld", K, D);
+  PeerSet ps = peers_for(0, nvls != 0);
+  DBA_CHECK_CUDA(coop_launch(fedavg_p2p_kernel, g_ctx.grid, kCollThreads, 0, (cudaStream_t)stream, W, ldw, K, D, coef, sigma, seed,
+                             ps, ++g_ctx.ticket));
   DBA_COUNT_LAUNCH(1);
-  DBA_CHECK_LAUNCH();
   return DBA_OK;
 }
 
-int dba_allreduce_axpby_nvls(long long D, float alpha, float beta, const void* const* stage,
-                             const void* const* replica, const void* const* signal, void* stage_mc, void* replica_mc,
-                             int rank, int world, unsigned int* counter, unsigned int call_id, void* stream) {
-  PeerSet ps;
-  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_allreduce_axpby_nvls: bad rank/world");
-  DBA_REQUIRE(D > 0 && stage_mc && replica_mc, "dba_allreduce_axpby_nvls: D=%lld", D);
-  ps.stage_mc = (float*)stage_mc; ps.replica_mc = (float*)replica_mc;
-  allreduce_axpby_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(D, alpha, beta, ps, counter, call_id);
+// target (0 = replica, 1 = aux)[:D] = beta*target + alpha * sum over all ranks of (K > 0 ? sum_k wv[k]*S[k] : stage).
+int dba_peer_axpby(const float* S, long long lds, int K, const double* wv, long long D, float alpha, float beta,
+                   int target, int nvls, void* stream) {
+  DBA_REQUIRE(g_ctx.ready, "dba_peer_axpby: dba_peer_init has not been called");
+  DBA_REQUIRE(D > 0 && K >= 0 && K <= 4096, "dba_peer_axpby: D=%lld K=%d", D, K);
+  PeerSet ps = peers_for(target, nvls != 0);
+  DBA_CHECK_CUDA(coop_launch(axpby_p2p_kernel, g_ctx.grid, kCollThreads, (size_t)K * sizeof(float), (cudaStream_t)stream, S, lds, K,
+                             wv, D, alpha, beta, ps, ++g_ctx.ticket));
   DBA_COUNT_LAUNCH(1);
-  DBA_CHECK_LAUNCH();
   return DBA_OK;
 }
 
-int dba_allreduce_axpby_p2p(long long D, float alpha, float beta, const void* const* stage,
-                            const void* const* replica, const void* const* signal, int rank, int world,
-                            unsigned int* counter, unsigned int call_id, void* stream) {
-  PeerSet ps;
-  DBA_REQUIRE(fill_peers(ps, stage, replica, signal, rank, world) == 0, "dba_allreduce_axpby_p2p: bad rank/world");
-  DBA_REQUIRE(D > 0, "dba_allreduce_axpby_p2p: D=%lld", D);
-  allreduce_axpby_p2p_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(D, alpha, beta, ps, counter, call_id);
+// Whole RFA loop over the deltas (W[k] - G) of all ranks: maxiter + 2 launches per rank, no host synchronisation,
+// no NCCL.  Results: median in every rank's aux buffer; wv / distances of ALL clients (global slot order; this rank's
+// K clients start at slot0) in this rank's result table [2][n_total]; state = (done, iterations, oracle calls);
+// obj[(iterations ...)] see weiszfeld_p2p_kernel.  dist2: 2*kmax doubles, wts / wv: K floats, obj: 2 doubles,
+// state: 4 ints - local scratch owned by the caller, zeroed here.
+int dba_peer_weiszfeld(const float* W, long long ldw, int K, long long D, const float* G, const float* alphas,
+                       int maxiter, float eps, double ftol, int slot0, int n_total, double* dist2, int kmax, float* wts,
+                       float* wv, double* obj, int* state, void* stream) {
+  DBA_REQUIRE(g_ctx.ready, "dba_peer_weiszfeld: dba_peer_init has not been called");
+  DBA_REQUIRE(K >= 0 && K <= kmax && kmax <= 1024 && D > 0 && n_total <= g_ctx.table_cap && slot0 + K <= n_total,
+              "dba_peer_weiszfeld: K=%d kmax=%d D=%lld n_total=%d slot0=%d", K, kmax, D, n_total, slot0);
+  cudaStream_t st = (cudaStream_t)stream;
+  DBA_CHECK_CUDA(cudaMemsetAsync(state, 0, 4 * sizeof(int), st));
+  DBA_CHECK_CUDA(cudaMemsetAsync(obj, 0, 2 * sizeof(double), st));
+  DBA_CHECK_CUDA(cudaMemsetAsync(dist2, 0, 2 * (size_t)kmax * sizeof(double), st));
+  WzArgs a{W, ldw, D, G, alphas, dist2, wts, wv, obj, state, g_ctx.table_dev, K, kmax, 0, maxiter, slot0, n_total, eps,
+           ftol};
+  PeerSet ps = peers_for(1, false);         // the median lives in the auxiliary vector
+  for (int it = 0; it <= maxiter + 1; ++it) {
+    a.it = it;
+    DBA_CHECK_CUDA(coop_launch(weiszfeld_p2p_kernel, g_ctx.grid, kCollThreads, (size_t)(K > 0 ? K : 1) * sizeof(float), st, a, ps,
+                               ++g_ctx.ticket));
+    DBA_COUNT_LAUNCH(1);
+  }
+  return DBA_OK;
+}
+
+// Stream-ordered barrier across all ranks (every rank must call it the same number of times).
+int dba_peer_barrier(void* stream) {
+  DBA_REQUIRE(g_ctx.ready, "dba_peer_barrier: dba_peer_init has not been called");
+  PeerSet ps = peers_for(0, false);
+  DBA_CHECK_CUDA(coop_launch(peer_barrier_kernel, 1, 64, 0, (cudaStream_t)stream, ps, ++g_ctx.ticket));
+  DBA_COUNT_LAUNCH(1);
+  return DBA_OK;
+}
+
+// rows: DEVICE array of n pointers to float rows of length D (local or peer-mapped) -> out[n][ldo] in local memory.
+int dba_gather_rows_ptrs(const float* const* rows, int n, long long D, float* out, long long ldo, void* stream) {
+  DBA_REQUIRE(n > 0 && n <= 65535 && D > 0 && ldo >= D, "dba_gather_rows_ptrs: n=%d D=%lld ldo=%lld", n, D, ldo);
+  int gx = (int)((D / 4 + 255) / 256);
+  if (gx > 64) gx = 64;
+  if (gx < 1) gx = 1;
+  gather_rows_ptrs_kernel<<<dim3(gx, n), 256, 0, (cudaStream_t)stream>>>(rows, n, D, out, ldo);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;

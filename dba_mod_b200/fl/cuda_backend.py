@@ -131,10 +131,10 @@ class CudaBackend(TorchBackend):
             S = grad_sum if grad_sum is not None else torch.zeros(0, Dp, device=self.device)
             flat.foolsgold_apply_(G, S.contiguous(), wv_local.double().contiguous(), Dp, eta / n_clients, lr, decay)
             return True
-        if hasattr(comm, "allreduce_axpby_"):
-            part = (wv_local.float()[:, None] * grad_sum[:, :Dp]).sum(0) if grad_sum is not None and grad_sum.shape[0] \
-                else torch.zeros(Dp, device=self.device)
-            comm.allreduce_axpby_(part.contiguous(), -lr * eta / n_clients, 1.0 - lr * decay, n=Dp, target="replica")
+        if hasattr(comm, "weighted_reduce_"):
+            # F3b: local weighted K-way reduce + cross-GPU reduce + server SGD step + broadcast in one launch per rank
+            S = grad_sum if grad_sum is not None else torch.zeros(0, Dp, device=self.device)
+            comm.weighted_reduce_(S, wv_local, Dp, -lr * eta / n_clients, 1.0 - lr * decay)
             return True
         return False
 

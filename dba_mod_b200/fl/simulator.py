@@ -165,6 +165,9 @@ class Simulator:
             if int(ok.item()) == self.world:
                 self.comm = peer
                 self.G = self.comm.set_global(self.G)
+                # evaluation exchange area: every client's model plus the attackers' extra tests of a round
+                n_adv = len(params["adversary_list"]) if params["is_poison"] else 0
+                peer.reserve_rows((int(params["no_models"]) + 4 * n_adv + 4) * self.spec.Df)
                 self.collective_path = ("fused peer-memory kernels (NVLS multimem)" if getattr(peer, "use_nvls", False)
                                         else "fused peer-memory kernels (NVLink P2P)")
             else:
@@ -313,7 +316,7 @@ class Simulator:
                                             self.py_rng)
         logger.info(f"Server Epoch:{epoch} choose agents : {names}.")
         rep = RoundReport(epoch, list(names), list(adversaries))
-        self._round_epoch, self._loan_tle = epoch, {}
+        self._round_epoch, self._loan_tle, self._round_names = epoch, {}, list(names)
         my_slots = self._shard(names, epoch)
         my_names = [names[s] for s in my_slots]
         counts, order = self._owner_counts(names, epoch)
@@ -357,6 +360,8 @@ class Simulator:
         # ---------------- global evaluation (main.py:195-231)
         with self.timer.phase("global_eval"):
             self._global_eval(epoch, rep)
+        if hasattr(self.comm, "check"):
+            self.comm.check()            # a timed-out cross-GPU barrier (dead peer) surfaces here, once per round
 
         if self.write_files:
             self.ckpt_writer.save_model(self.state_dict(), epoch, rep.poison_loss if p["is_poison"] else rep.global_loss)
@@ -454,12 +459,8 @@ class Simulator:
             gn, dn = be.global_norm(W[scaling]).cpu(), be.dist_norm(W[scaling], anchor[scaling]).cpu()
             for j, k in enumerate(scaling):
                 logger.info(f"Norm before scaling: {float(gn[j])}. Distance: {float(dn[j])}")
-        do_eval = bool(p["client_eval"])
         pre = W[scaling].clone() if scaling else None
-        if do_eval and not is_loan:
-            for j, k in enumerate(scaling):         # image_train.py:148-164: tests of the unscaled poisoned model
-                jobs.append(("clean", -1, pre[j], k, "pre_clean"))
-                jobs.append(("poison", 0, pre[j], k, "pre_poison"))
+        pre_of = {k: j for j, k in enumerate(scaling)}
         if scaling:
             sc = torch.tensor([plans[k].scale for k in scaling], device=self.device)
             sub = W[scaling]
@@ -474,15 +475,10 @@ class Simulator:
                 logger.info(f"Scaled Norm after poisoning: {float(gn[j])}, distance: {float(dn[j])}")
                 if not is_loan:
                     rows.append((my_slots[k], "scale", [epoch, float(dn[j])]))
-        if do_eval:
-            for k, pl in enumerate(plans):
-                if is_loan or not pl.poisoning:                       # loan_train.py:198-201 / image_train.py:268-271
-                    jobs.append(("clean", -1, W[k], k, "clean"))
-                if p["is_poison"] and pl.poisoning:                   # image_train.py:274-282
-                    jobs.append(("poison", 0, W[k], k, "poison"))
-                if p["is_poison"] and pl.adv_index >= 0:              # image_train.py:285-295
-                    jobs.append(("poison", pl.adv_index + 1, W[k], k, "agent"))
-        results = self._run_eval_jobs(jobs)
+        for split, trig, k, tag in self._eval_job_meta(plans):
+            row = pre[pre_of[k]] if tag.startswith("pre_") else W[k]
+            jobs.append((split, trig, row, k, tag))
+        results = self._run_eval_jobs(jobs, epoch)
         order_tags = ["pre_clean", "pre_poison", "clean", "poison", "agent"]
         for k, pl in enumerate(plans):
             slot = my_slots[k]
@@ -508,10 +504,32 @@ class Simulator:
                     if p["vis_trigger_split_test"]:
                         self.metrics.trigger_agent_test_vis(epoch, acc, f"{pl.name}_trigger")
 
-    def _run_eval_jobs(self, jobs) -> Dict[Tuple[int, str], Tuple[float, float, int, int]]:
+    def _eval_job_meta(self, plans: List[ClientPlan]) -> List[Tuple[str, int, int, str]]:
+        """(split, trigger row, client index, tag) of every per-client evaluation that follows local training, in the
+        order they are run.  Depends on the round plan only, so every rank can also derive the other ranks' lists."""
+        p = self.params
+        is_loan = p["type"] == C.TYPE_LOAN
+        out: List[Tuple[str, int, int, str]] = []
+        if not p["client_eval"]:
+            return out
+        scaling = [k for k, pl in enumerate(plans) if pl.poisoning and not p["baseline"]]
+        if not is_loan:
+            for k in scaling:                       # image_train.py:148-164: tests of the unscaled poisoned model
+                out.append(("clean", -1, k, "pre_clean"))
+                out.append(("poison", 0, k, "pre_poison"))
+        for k, pl in enumerate(plans):
+            if is_loan or not pl.poisoning:                       # loan_train.py:198-201 / image_train.py:268-271
+                out.append(("clean", -1, k, "clean"))
+            if p["is_poison"] and pl.poisoning:                   # image_train.py:274-282
+                out.append(("poison", 0, k, "poison"))
+            if p["is_poison"] and pl.adv_index >= 0:              # image_train.py:285-295
+                out.append(("poison", pl.adv_index + 1, k, "agent"))
+        return out
+
+    def _run_eval_jobs(self, jobs, epoch=None) -> Dict[Tuple[int, str], Tuple[float, float, int, int]]:
         pairs = getattr(self.backend, "evaluate_pairs", None)
         if pairs is not None and self.world > 1:
-            out = self._run_eval_jobs_balanced(jobs, pairs)
+            out = self._run_eval_jobs_balanced(jobs, pairs, epoch)
             if out is not None:
                 return out
         if pairs is not None and jobs:
@@ -534,22 +552,32 @@ class Simulator:
                 out[(k, tag)] = (float(loss[j]) / n if n else 0, acc, int(correct[j]), n)
         return out
 
-    def _run_eval_jobs_balanced(self, jobs, pairs):
+    def _run_eval_jobs_balanced(self, jobs, pairs, epoch=None):
         """Several ranks: the client -> rank placement is uneven (10 clients on 8 GPUs, attackers with extra tests),
         so the models to evaluate are exchanged (~11 MB each over NVLink) and EVERY rank evaluates ALL
         (model, input set) pairs on its own slice of the test split; the (loss, correct, count) sums are then
-        all-reduced and each rank keeps the rows of its own jobs."""
-        import torch.distributed as dist
-        meta_local = [(j[0], max(j[1], 0)) for j in jobs]
-        gathered = [None] * self.world
-        dist.all_gather_object(gathered, meta_local)
+        all-reduced and each rank keeps the rows of its own jobs.  Every rank derives all ranks' job lists from the
+        round plan (no metadata exchange); with the peer-memory communicator the models are pulled over NVLink by a
+        gather kernel and the sums go through the fused all-reduce - no NCCL call, no pickling."""
+        names = self._round_names
+        ep = self._round_epoch if epoch is None else epoch
+        owner = self._placement(names, self._round_epoch)
+        gathered = []
+        for r in range(self.world):
+            nm_r = [names[s] for s in range(len(names)) if owner[s] == r]
+            meta = self._eval_job_meta(plan_clients(self.params, self.data, nm_r, ep))
+            gathered.append([(m[0], max(m[1], 0)) for m in meta])
+        assert gathered[self.rank] == [(j[0], max(j[1], 0)) for j in jobs], "evaluation job lists out of step"
         counts = [len(g) for g in gathered]
         total = sum(counts)
         if total == 0:
             return {}
         Df = self.spec.Df
         mine = torch.stack([j[2][:Df] for j in jobs]) if jobs else torch.zeros(0, Df, device=self.device)
-        models_all = self.comm.all_gather_rows(mine.contiguous(), counts)
+        if hasattr(self.comm, "gather_rows"):
+            models_all = self.comm.gather_rows(mine.contiguous(), counts)
+        else:
+            models_all = self.comm.all_gather_rows(mine.contiguous(), counts)
         jobs_all = [m for g in gathered for m in g]
         res = pairs(models_all, jobs_all, shard=(self.rank, self.world))
         if res is None:
@@ -618,12 +646,30 @@ class Simulator:
             fused = getattr(be, "geometric_median_states", None)
             if fused is not None and comm.world == 1:
                 res = fused(W, self.G, [all_ns[s] for s in order], int(p["geom_median_maxiter"]))
+            elif hasattr(comm, "weiszfeld") and self.device.type == "cuda":
+                # F2: one fused launch per Weiszfeld iteration and rank, convergence decided on the device
+                tot = float(sum(all_ns.values())) or 1.0
+                a_loc = torch.tensor([all_ns[s] / tot for s in my_slots], dtype=torch.float32, device=self.device)
+                n_tot = len(names)
+                med, table, state, obj = comm.weiszfeld(W, self.G, a_loc, sum(counts[: self.rank]), n_tot,
+                                                        int(p["geom_median_maxiter"]))
+                st, tb, ob = state.cpu(), table.cpu(), obj.cpu()           # the round's only RFA read-back
+                comm.check()
+                iters = int(st[1])
+                res = agg.RFAResult(int(st[2]), [float(v) for v in tb[0].tolist()], [float(v) for v in tb[1].tolist()],
+                                    med, float(ob[int(st[3])]), iters)
             else:
                 delta = W - self.G[None, :]
                 ns = torch.tensor(num_samples, dtype=torch.float64, device=self.device)
                 res = agg.geometric_median(delta, ns, [all_ns[s] for s in order], counts,
                                            maxiter=int(p["geom_median_maxiter"]), comm=comm)
-            agg.rfa_update_(self.G, res, float(p["eta"]), sigma, comm, self.noise_gen)
+            if hasattr(comm, "weiszfeld") and comm.world > 1 and self.device.type == "cuda":
+                # every rank holds the same median and draws the same DP noise (shared seed): no broadcast
+                self.G.add_(res.median[: self.G.numel()], alpha=float(p["eta"]))
+                if sigma is not None:
+                    self.G.add_(agg.dp_noise_like(self.G, sigma, self.noise_gen))
+            else:
+                agg.rfa_update_(self.G, res, float(p["eta"]), sigma, comm, self.noise_gen)
             logger.info(f"[rfa agg] iters: {res.iters}, objective: {res.objective}, weight: {res.wv}")
             wv, alphas = res.wv, res.distances
         else:
@@ -657,9 +703,10 @@ class Simulator:
                 self.metrics.alpha_vis(epoch, a_, str(nm), nm in adversaries)
 
     def _gather_num_samples(self, num_samples, counts, order, n) -> Dict[int, float]:
-        t = torch.tensor(num_samples, dtype=torch.float64, device=self.device).reshape(-1, 1)
-        allv = self.comm.all_gather_rows(t, counts).reshape(-1).tolist()
-        return {s: v for s, v in zip(order, allv)}
+        """Samples seen by every selected client in its last internal epoch = its partition size (every rank knows
+        the partition, so nothing is exchanged)."""
+        names = self._round_names
+        return {s: float(self.data.client_size(names[s])) for s in range(n)}
 
     def _log_poison_ratio(self, tag, names, all_ns) -> None:
         p = self.params

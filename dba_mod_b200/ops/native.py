@@ -91,10 +91,13 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_maxpool_fwd", [P, P, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_maxpool_bwd", [P, P, P, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_wgrad_tc", [P, P, P, L, I, I, I, I, I, I, I, I, I, I, P])
-    _sig(lib, "dba_fedavg_p2p", [P, L, I, L, F, F, U, P, P, P, I, I, I, P, ctypes.c_uint, P])
-    _sig(lib, "dba_allreduce_axpby_p2p", [L, F, F, P, P, P, I, I, P, ctypes.c_uint, P])
-    _sig(lib, "dba_fedavg_nvls", [P, L, I, L, F, F, U, P, P, P, P, P, I, I, I, P, ctypes.c_uint, P])
-    _sig(lib, "dba_allreduce_axpby_nvls", [L, F, F, P, P, P, P, P, I, I, P, ctypes.c_uint, P])
+    _sig(lib, "dba_peer_init", [I, I, P, P, P, P, P, P, I, P, P, P, P, P, P])
+    _sig(lib, "dba_peer_error", [], c_int)
+    _sig(lib, "dba_peer_fedavg", [P, L, I, L, F, F, U, I, P])
+    _sig(lib, "dba_peer_axpby", [P, L, I, P, L, F, F, I, I, P])
+    _sig(lib, "dba_peer_weiszfeld", [P, L, I, L, P, P, I, F, D, I, I, P, I, P, P, P, P, P])
+    _sig(lib, "dba_peer_barrier", [P])
+    _sig(lib, "dba_gather_rows_ptrs", [P, I, L, P, L, P])
     _sig(lib, "dba_gram_ptrs", [P, I, L, P, P])
     _sig(lib, "dba_loan_train", [P, L, P, L, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, F, F,
                                  ctypes.c_uint, I, P])

@@ -43,10 +43,27 @@ def maybe_spawn(params, argv: List[str]) -> bool:
         env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(n), MASTER_ADDR="127.0.0.1",
                    MASTER_PORT=str(port))
         procs.append(subprocess.Popen([sys.executable] + argv, env=env))
+    # poll all children: the first failure takes the others down (their kernels would otherwise wait for a dead
+    # peer until the barrier time-out)
+    import time
     rc = 0
-    for p in procs:
-        rc = p.wait() or rc
+    alive = list(procs)
+    while alive and rc == 0:
+        for p in list(alive):
+            r = p.poll()
+            if r is not None:
+                alive.remove(p)
+                rc = rc or r
+        if alive and rc == 0:
+            time.sleep(0.2)
     if rc:
+        for p in alive:
+            p.terminate()
+        for p in alive:
+            try:
+                p.wait(timeout=10)
+            except subprocess.TimeoutExpired:
+                p.kill()
         raise SystemExit(rc)
     return True
 

@@ -217,27 +217,36 @@ int dba_loan_eval(const float* W, long long ldw, int M, const float* X, const lo
 
 /* ---- peer-memory fused collectives (csrc/p2p_collectives.cu) ---------------------------------------------------- */
 
-/* FedAvg over all ranks: local K-way reduce -> cross-GPU reduce of the owned slice over NVLink peer loads -> update
- * (+DP noise) -> peer stores into every replica.  Reference: helper.py:193-257 + the copy image_train.py:26-32. */
-int dba_fedavg_p2p(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
-                   const void* const* stage, const void* const* replica, const void* const* signal, int rank,
-                   int world, int total_clients, unsigned int* counter, unsigned int call_id, void* stream);
-/* replica = beta*replica + alpha*sum_r stage_r on every rank (Weiszfeld averages helper.py:395-418, FoolsGold weighted
- * gradient reduce + server step helper.py:561-570,280-290). */
-int dba_allreduce_axpby_p2p(long long D, float alpha, float beta, const void* const* stage,
-                            const void* const* replica, const void* const* signal, int rank, int world,
-                            unsigned int* counter, unsigned int call_id, void* stream);
+/* One communicator context per process (one process per GPU).  Registers the symmetric buffers (host arrays of `world`
+ * peer-mapped device pointers: stage / replica / aux [D] floats, signal 64 uint32, mail 128 doubles, table 2*table_cap
+ * floats; *_mc = multicast addresses or null; counters 8 uint32, err 1 int, table_dev `world` pointers: local). */
+int dba_peer_init(int rank, int world, const void* const* stage, const void* const* replica, const void* const* aux,
+                  const void* const* signal, const void* const* mail, const void* const* table, int table_cap,
+                  void* stage_mc, void* replica_mc, void* aux_mc, unsigned int* counters, int* err, void* table_dev);
+/* 0 = fine, 1 = a cross-GPU barrier timed out on this GPU (a peer died or never launched the matching kernel). */
+int dba_peer_error(void);
+/* F1, FedAvg over all ranks in ONE cooperative launch per rank: local K-way reduce of (W[k] - G) -> barrier -> owner
+ * reduces its slice over NVLink peer loads (or multimem.ld_reduce when nvls != 0) -> update (+DP noise) -> peer /
+ * multicast stores into every replica -> barrier.  Reference: helper.py:193-257 + the copy image_train.py:26-32. */
+int dba_peer_fedavg(const float* W, long long ldw, int K, long long D, float coef, float sigma,
+                    unsigned long long seed, int nvls, void* stream);
+/* target (0 = replica, 1 = aux) = beta*target + alpha * sum over all ranks of (K > 0 ? sum_k wv[k]*S[k] : staging
+ * vector).  F3b: FoolsGold's weighted gradient reduce + server step (helper.py:561-570,280-290) with the local
+ * weighted reduce as phase 1 of the launch; K = 0: plain fused all-reduce of the staging vector. */
+int dba_peer_axpby(const float* S, long long lds, int K, const double* wv, long long D, float alpha, float beta,
+                   int target, int nvls, void* stream);
+/* F2, RFA / Weiszfeld over the deltas (W[k] - G) of all ranks (helper.py:295-418): one launch per iteration per rank
+ * (local weights + weighted partial sum, scalars in the ticket mailbox, normalised median into every rank's aux
+ * buffer, local distances, device-side convergence test), maxiter + 2 launches, no host synchronisation, no NCCL. */
+int dba_peer_weiszfeld(const float* W, long long ldw, int K, long long D, const float* G, const float* alphas,
+                       int maxiter, float eps, double ftol, int slot0, int n_total, double* dist2, int kmax, float* wts,
+                       float* wv, double* obj, int* state, void* stream);
+/* Stream-ordered barrier across all ranks. */
+int dba_peer_barrier(void* stream);
+/* out[j][:] = *rows[j] (rows: device array of local or peer-mapped pointers): NVLink gather into local memory. */
+int dba_gather_rows_ptrs(const float* const* rows, int n, long long D, float* out, long long ldo, void* stream);
 /* Gram matrix over feature rows given by (possibly peer-mapped) pointers: FoolsGold's gather fused into the cosine
  * GEMM (helper.py:544-555,574-577). */
-/* NVLS variants of the two kernels above: phase 2 through the multicast mappings of the staging / replica buffers
- * (multimem.ld_reduce.add + multimem.st: the NVSwitch reduces and broadcasts). */
-int dba_fedavg_nvls(const float* W, long long ldw, int K, long long D, float coef, float sigma, unsigned long long seed,
-                    const void* const* stage, const void* const* replica, const void* const* signal, void* stage_mc,
-                    void* replica_mc, int rank, int world, int total_clients, unsigned int* counter,
-                    unsigned int call_id, void* stream);
-int dba_allreduce_axpby_nvls(long long D, float alpha, float beta, const void* const* stage,
-                             const void* const* replica, const void* const* signal, void* stage_mc, void* replica_mc,
-                             int rank, int world, unsigned int* counter, unsigned int call_id, void* stream);
 int dba_gram_ptrs(const double* const* rows, int n, long long L, double* gram, void* stream);
 
 #ifdef __cplusplus

@@ -22,11 +22,14 @@ raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=4000, 
 raw["0_poison_epochs"] = [2]
 comm = make_comm()
 sim = Simulator(Params(raw), comm=comm, quiet=True, write_files=False)
+nccl0 = getattr(sim.comm, "nccl_calls", None)
 reps = sim.run()
+nccl_in_rounds = (sim.comm.nccl_calls - nccl0) if nccl0 is not None else None
 if comm.rank == 0:
     print("RESULT " + json.dumps({"norm": float(sim.G.double().norm()), "acc": reps[-1].global_acc,
                                   "asr": reps[-1].poison_acc, "w": reps[-1].agg_weights,
                                   "path": sim.collective_path, "backend": sim.backend.name,
+                                  "nccl_calls_in_rounds": nccl_in_rounds,
                                   "native": [bool(getattr(sim.backend, "native_train", False)),
                                              bool(getattr(sim.backend, "native_eval", False))]}), flush=True)
 sim.close()
