@@ -44,6 +44,8 @@ struct BnArgs {
 template <int V>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   __shared__ float s_scale[V], s_shift[V];
+  pdl_trigger();
+  pdl_wait();
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int nv = a.nvalid[k];
   const float n = (float)nv * (float)(a.H * a.W);
@@ -117,6 +119,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
 template <int V>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   __shared__ float red[2][8][V];
+  pdl_trigger();
+  pdl_wait();
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int nv = a.nvalid[k];
   float mean[V], rstd[V];
@@ -172,6 +176,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
 template <int V>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   __shared__ float s_sc[V], s_mg[V], s_mgx[V], s_mean[V], s_rstd[V];
+  pdl_trigger();
+  pdl_wait();
   const int chunk = blockIdx.y, k = blockIdx.z;
   const int nv = a.nvalid[k];
   const float n = (float)nv * (float)(a.H * a.W);
@@ -386,8 +392,8 @@ int dba_bn_apply_split(const void* y, const void* res, void* out, void* out_s2d,
   a.ld_stats = ld_stats; a.ld_saved = ld_saved; a.ldw = ldw; a.R = R;
   a.stats_off = stats_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off; a.rm_off = rm_off; a.rv_off = rv_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.relu = relu; a.momentum = momentum; a.eps = eps;
-  if (act_v() == 4) bn_apply_kernel<4><<<bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream>>>(a);
-  else bn_apply_kernel<8><<<bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream>>>(a);
+  if (act_v() == 4) launch_pdl(bn_apply_kernel<4>, bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream, a);
+  else launch_pdl(bn_apply_kernel<8>, bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream, a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -426,11 +432,11 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.up = up;
   const dim3 grid = bn_grid(B, H, W, C, K);
   if (act_v() == 4) {
-    bn_bwd_reduce_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
-    bn_bwd_apply_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    launch_pdl(bn_bwd_reduce_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
+    launch_pdl(bn_bwd_apply_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
   } else {
-    bn_bwd_reduce_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
-    bn_bwd_apply_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    launch_pdl(bn_bwd_reduce_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
+    launch_pdl(bn_bwd_apply_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
   }
   DBA_COUNT_LAUNCH(2);
   DBA_CHECK_LAUNCH();

@@ -56,9 +56,36 @@ extern unsigned long long g_dba_launches;
 // BLAS math mode, not a per-call argument.
 extern int g_dba_act_mode;
 
+// Programmatic dependent launch (1 = on): consecutive kernels of a stream / captured graph are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so kernel N+1's blocks may be scheduled - and run their prologue
+// (shared-memory carve-up, mbarrier init, TMEM allocation, tap tables) - while kernel N drains.
+extern int g_dba_pdl;
+
 namespace dba {
 
 constexpr int kNumSMs = 148;
+
+// Every kernel launched through launch_pdl() calls pdl_trigger() first (lets the NEXT kernel's blocks be scheduled as
+// soon as all of this kernel's blocks have started) and pdl_wait() before it touches global memory (returns when the
+// PREVIOUS kernel has completed and its writes are visible).  Both are no-ops for a kernel launched the plain way.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = g_dba_pdl ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // 16-byte chunk <-> V floats (V = 8: bf16, V = 4: fp32)
 template <int V> __device__ __forceinline__ void chunk_unpack(const uint4 u, float (&f)[V]);

@@ -178,6 +178,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], kEpiWarps); }
     mbar_fence_init();
   }
+  pdl_trigger();                                // the next kernel's blocks may be scheduled from now on
   if (warp == 1) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
@@ -186,6 +187,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                                   // everything above overlapped the previous kernel's tail
 
   // contiguous range of work items for this CTA; item = (k * nnb + nb) * num_pass + pass
   const long long items = (long long)a.K * nnb * a.num_pass;
@@ -648,13 +650,13 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   const int kc2 = kc / 2;                      // MMAs (32 bytes of K each) per tap and k-block
   const cudaStream_t st = (cudaStream_t)stream;
   if (tf32) {
-    if (kc2 == 4) conv_tc_kernel<4, true><<<grid, kThreads, need, st>>>(a);
-    else if (kc2 == 2) conv_tc_kernel<2, true><<<grid, kThreads, need, st>>>(a);
-    else conv_tc_kernel<1, true><<<grid, kThreads, need, st>>>(a);
+    if (kc2 == 4) launch_pdl(conv_tc_kernel<4, true>, grid, kThreads, need, st, a);
+    else if (kc2 == 2) launch_pdl(conv_tc_kernel<2, true>, grid, kThreads, need, st, a);
+    else launch_pdl(conv_tc_kernel<1, true>, grid, kThreads, need, st, a);
   } else {
-    if (kc2 == 4) conv_tc_kernel<4, false><<<grid, kThreads, need, st>>>(a);
-    else if (kc2 == 2) conv_tc_kernel<2, false><<<grid, kThreads, need, st>>>(a);
-    else conv_tc_kernel<1, false><<<grid, kThreads, need, st>>>(a);
+    if (kc2 == 4) launch_pdl(conv_tc_kernel<4, false>, grid, kThreads, need, st, a);
+    else if (kc2 == 2) launch_pdl(conv_tc_kernel<2, false>, grid, kThreads, need, st, a);
+    else launch_pdl(conv_tc_kernel<1, false>, grid, kThreads, need, st, a);
   }
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();

@@ -11,6 +11,9 @@
 static char g_err[512] = "";
 unsigned long long g_dba_launches = 0;
 int g_dba_act_mode = 0;
+int g_dba_pdl = 1;
+extern "C" void dba_set_pdl(int on) { g_dba_pdl = on ? 1 : 0; }
+extern "C" int dba_get_pdl() { return g_dba_pdl; }
 // Activation element mode of the network kernels: 0 = bf16 (kind::f16 MMA), 1 = fp32 activations with kind::tf32 MMA.
 extern "C" int dba_set_act_dtype(int mode) {
   if (mode != 0 && mode != 1) {

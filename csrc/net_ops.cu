@@ -25,6 +25,8 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
                                                            const int* __restrict__ table,
                                                            uint4* __restrict__ dst, long long dst_client_stride) {
   // dst is addressed in 16-byte chunks of V values (V = 8: bf16, V = 4: fp32); table offsets are in elements
+  pdl_trigger();
+  pdl_wait();
   const int* e = table + blockIdx.y * PACK_FIELDS;
   const int k = blockIdx.z;
   const int Cout = e[1], Cin = e[2], taps = e[3], CinP = e[6], CoutP = e[7], fold = e[8] == 1, chw = e[8] == 2;
@@ -100,10 +102,10 @@ extern "C" int dba_pack_weights(const float* W, long long ldw, const int* table,
   // dst_client_stride counts elements (bf16 or fp32) of the caller's pack tensor
   if (g_dba_act_mode == 1) {
     DBA_REQUIRE(dst_client_stride % 4 == 0, "dba_pack_weights: client stride %lld %% 4", dst_client_stride);
-    pack_weights_kernel<4><<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, (uint4*)dst, dst_client_stride / 4);
+    launch_pdl(pack_weights_kernel<4>, g, 256, 0, (cudaStream_t)stream, W, ldw, table, (uint4*)dst, dst_client_stride / 4);
   } else {
     DBA_REQUIRE(dst_client_stride % 8 == 0, "dba_pack_weights: client stride %lld %% 8", dst_client_stride);
-    pack_weights_kernel<8><<<g, 256, 0, (cudaStream_t)stream>>>(W, ldw, table, (uint4*)dst, dst_client_stride / 8);
+    launch_pdl(pack_weights_kernel<8>, g, 256, 0, (cudaStream_t)stream, W, ldw, table, (uint4*)dst, dst_client_stride / 8);
   }
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
@@ -163,6 +165,8 @@ struct InputArgs {
 // decomposed a flat 64-bit index per thread and spent its time in integer division: 0.5 TB/s of stores).
 template <int V>
 __global__ void __launch_bounds__(256) input_stage_kernel(const InputArgs a) {
+  pdl_trigger();
+  pdl_wait();
   const int Wp = a.Wo + 1, S = (a.Ho + 1) * Wp, lead = Wp + 1;
   const int nchunk = a.KP / V;
   const int b = blockIdx.y;
@@ -240,8 +244,8 @@ extern "C" int dba_input_stage_image_split(const void* data, const long long* la
   DBA_REQUIRE(B <= 65535 && (long long)K * (KP / V) <= 65535, "dba_input_stage_image: grid too large (B=%d K=%d)", B, K);
   int gx = (Ho * Wo + 255) / 256;
   if (gx > 64) gx = 64;
-  if (V == 4) input_stage_kernel<4><<<dim3(gx, B, K * (KP / 4)), 256, 0, (cudaStream_t)stream>>>(a);
-  else input_stage_kernel<8><<<dim3(gx, B, K * (KP / 8)), 256, 0, (cudaStream_t)stream>>>(a);
+  if (V == 4) launch_pdl(input_stage_kernel<4>, dim3(gx, B, K * (KP / 4)), 256, 0, (cudaStream_t)stream, a);
+  else launch_pdl(input_stage_kernel<8>, dim3(gx, B, K * (KP / 8)), 256, 0, (cudaStream_t)stream, a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -271,10 +275,12 @@ struct HeadArgs {
 // Block = kHeadWarps samples of ONE client (grid.x = blocks per client, grid.y = client), so the gradient of the
 // linear layer is first summed in shared memory and leaves the block as one atomic per weight (the first version
 // issued ncls*C global atomics per sample on the same addresses: 68 us for 64 samples).
-constexpr int kHeadWarps = 16;
+constexpr int kHeadWarps = 4;       // 16 blocks per client at B = 64: the head is latency-bound, not atomics-bound
 template <int MAXC, int MAXCLS, bool SMEM_GRAD, int V>
 __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a) {
   extern __shared__ float s_gw[];               // [ncls][C] + [ncls]  (SMEM_GRAD && training only)
+  pdl_trigger();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k = blockIdx.y, b = blockIdx.x * kHeadWarps + warp;
   const bool train = a.Gflat != nullptr;
@@ -418,19 +424,19 @@ extern "C" int dba_head_ex(const void* act, const float* Wflat, long long ldw, i
   const int nt = kHeadWarps * 32;
   if (g_dba_act_mode == 1) {
     if (C <= 256 && ncls <= 16) {
-      if (smem_grad) head_kernel<256, 16, true, 4><<<grid, nt, gsm, st>>>(a);
-      else head_kernel<256, 16, false, 4><<<grid, nt, 0, st>>>(a);
+      if (smem_grad) launch_pdl(head_kernel<256, 16, true, 4>, grid, nt, gsm, st, a);
+      else launch_pdl(head_kernel<256, 16, false, 4>, grid, nt, 0, st, a);
     } else {
-      if (smem_grad) head_kernel<512, 200, true, 4><<<grid, nt, gsm, st>>>(a);
-      else head_kernel<512, 200, false, 4><<<grid, nt, 0, st>>>(a);
+      if (smem_grad) launch_pdl(head_kernel<512, 200, true, 4>, grid, nt, gsm, st, a);
+      else launch_pdl(head_kernel<512, 200, false, 4>, grid, nt, 0, st, a);
     }
   } else {
     if (C <= 256 && ncls <= 16) {
-      if (smem_grad) head_kernel<256, 16, true, 8><<<grid, nt, gsm, st>>>(a);
-      else head_kernel<256, 16, false, 8><<<grid, nt, 0, st>>>(a);
+      if (smem_grad) launch_pdl(head_kernel<256, 16, true, 8>, grid, nt, gsm, st, a);
+      else launch_pdl(head_kernel<256, 16, false, 8>, grid, nt, 0, st, a);
     } else {
-      if (smem_grad) head_kernel<512, 200, true, 8><<<grid, nt, gsm, st>>>(a);
-      else head_kernel<512, 200, false, 8><<<grid, nt, 0, st>>>(a);
+      if (smem_grad) launch_pdl(head_kernel<512, 200, true, 8>, grid, nt, gsm, st, a);
+      else launch_pdl(head_kernel<512, 200, false, 8>, grid, nt, 0, st, a);
     }
   }
   DBA_COUNT_LAUNCH(1);

@@ -103,6 +103,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
     mbar_init(acc_empty, 4);
     mbar_fence_init();
   }
+  pdl_trigger();
   if (warp == 1) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
 
   const int items = a.K * a.nmb * a.ngroups * a.nnblk * a.nsplit;
   // real planes of dY available for this M block (the rest of the 16 planes stays unloaded: rows >= Cout of D are
@@ -325,8 +327,8 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   if (need < 120 * 1024) need = 120 * 1024;
   const int items = base_items * nsplit;
   const int grid = items < kNumSMs ? items : kNumSMs;
-  if (split) wgrad_tc_kernel<true><<<grid, kThreadsW, need, (cudaStream_t)stream>>>(a);
-  else wgrad_tc_kernel<false><<<grid, kThreadsW, need, (cudaStream_t)stream>>>(a);
+  if (split) launch_pdl(wgrad_tc_kernel<true>, grid, kThreadsW, need, (cudaStream_t)stream, a);
+  else launch_pdl(wgrad_tc_kernel<false>, grid, kThreadsW, need, (cudaStream_t)stream, a);
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;

@@ -48,6 +48,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_launch_count", [], c_ulonglong)
     _sig(lib, "dba_reset_launch_count", [], None)
     _sig(lib, "dba_add_launch_count", [c_ulonglong], None)
+    _sig(lib, "dba_set_pdl", [I], None)
+    _sig(lib, "dba_get_pdl", [], c_int)
     _sig(lib, "dba_set_act_dtype", [I])
     _sig(lib, "dba_get_act_dtype", [], c_int)
     _sig(lib, "dba_sgd_step", [P, L, P, P, P, L, P, P, I, L, F, F, P])
@@ -102,6 +104,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_loan_train", [P, L, P, L, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, F, F,
                                  ctypes.c_uint, I, P])
     _sig(lib, "dba_loan_eval", [P, L, I, P, P, P, L, P, P, I, P, P, P])
+    if os.environ.get("DBA_PDL") is not None:      # A/B switch for programmatic dependent launch (default: on)
+        lib.dba_set_pdl(int(os.environ["DBA_PDL"]))
     _LIB = lib
     return lib
 

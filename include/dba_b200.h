@@ -192,6 +192,10 @@ int dba_input_stage_image_split(const void* data, const long long* labels, const
  * chunk, tcgen05 kind::f16; 1 = fp32 activations, 4 channels per chunk, kind::tf32 - the reference's precision class
  * (fp32 tensors with TF32 convolutions, cuDNN's default).  No counterpart in the reference (it has no native code). */
 int dba_set_act_dtype(int mode);
+/* Programmatic dependent launch between consecutive network kernels (default on): a kernel's blocks are scheduled, and
+ * run their prologue, while its predecessor drains.  No counterpart in the reference. */
+void dba_set_pdl(int on);
+int dba_get_pdl(void);
 int dba_get_act_dtype(void);
 
 /* MaxPool2d(3, 2, 1) forward / backward on planar-8 activations (Tiny-ImageNet stem, resnet_tinyimagenet.py:147). */
