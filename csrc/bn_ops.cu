@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
     const float s2 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
     const float mean = n > 0.f ? s1 / n : 0.f;
     const float var = n > 0.f ? fmaxf(s2 / n - mean * mean, 0.f) : 0.f;
-    const float rstd = rsqrtf(var + a.eps);
+    const float rstd = 1.f / sqrtf(var + a.eps);
     const float sc = w[a.g_off + c] * rstd;
     s_scale[threadIdx.x] = sc;
     s_shift[threadIdx.x] = w[a.b_off + c] - mean * sc;

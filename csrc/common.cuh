@@ -44,7 +44,8 @@ void dba_set_error(const char* fmt, ...);
 
 // Counts kernel launches made by this library (bench.py reports it as gpu_launches).
 extern unsigned long long g_dba_launches;
-#define DBA_COUNT_LAUNCH(n) (g_dba_launches += (n))
+// (atomic: entry points may be called from several host threads, e.g. dba_rows_sqdist_noalloc from a monitor thread)
+#define DBA_COUNT_LAUNCH(n) ((void)__atomic_fetch_add(&g_dba_launches, (unsigned long long)(n), __ATOMIC_RELAXED))
 
 // Activation element mode of the tensor-core network kernels (conv / wgrad / BatchNorm / pooling / input stage / head /
 // weight packing).  0: bf16 activations, 8 channels per 16-byte chunk ("planar-8"), tcgen05.mma.kind::f16.

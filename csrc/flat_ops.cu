@@ -8,7 +8,7 @@
 #include <curand_kernel.h>
 #include <stdarg.h>
 
-static char g_err[512] = "";
+static thread_local char g_err[512] = "";        // per host thread: dba_last_error() reports the caller's own failure
 unsigned long long g_dba_launches = 0;
 int g_dba_act_mode = 0;
 int g_dba_pdl = 1;
@@ -34,7 +34,7 @@ void dba_set_error(const char* fmt, ...) {
 extern "C" unsigned long long dba_launch_count() { return g_dba_launches; }
 extern "C" void dba_reset_launch_count() { g_dba_launches = 0; }
 // Kernels launched by replaying a captured CUDA graph are accounted for by the caller (n per replay).
-extern "C" void dba_add_launch_count(unsigned long long n) { g_dba_launches += n; }
+extern "C" void dba_add_launch_count(unsigned long long n) { DBA_COUNT_LAUNCH(n); }
 
 using namespace dba;
 
@@ -228,7 +228,11 @@ extern "C" int dba_rows_sqdist(const float* X, long long ldx, const float* Y, lo
 //   * all calls share the one array, which still holds the previous call's partial sums.  Nothing has to start at
 //     zero: stage 1 overwrites every slot stage 2 reads.  But two calls whose kernels can overlap on the GPU
 //     (different streams, no ordering between them) race on it - order them yourself;
-//   * no cudaMalloc, cudaFree or other allocating routine is called, here or in anything this function calls.
+//   * no cudaMalloc, cudaFree or other allocating routine is called, here or in anything this function calls;
+//   * the device that owns X / out / the stream must be the CURRENT device of the calling thread (the array's address
+//     is looked up and remembered per current device);
+//   * host-side state is safe to share between threads: the per-device address cache is written without a lock, but
+//     every writer stores the same value (idempotent), the launch counter is atomic and the error text is per thread.
 #define DBA_NOALLOC_MAX_ROWS 64
 static __device__ __align__(256) double g_noalloc_sqdist_scratch[DBA_NOALLOC_MAX_ROWS * DBA_SQDIST_BLOCKS];
 #define DBA_NOALLOC_MAX_DEVICES 64

@@ -143,13 +143,13 @@ __global__ void __launch_bounds__(THREADS) loan_train_kernel(const LoanTrainArgs
         if (acc > mx) { mx = acc; arg = j; }
       }
       float se = 0.f;
-      for (int j = 0; j < F3; ++j) se += __expf(lg[j] - mx);
-      const float lse = mx + __logf(se);
+      for (int j = 0; j < F3; ++j) se += expf(lg[j] - mx);
+      const float lse = mx + logf(se);
       if (lab >= 0) {
         my_loss = (lse - lg[lab]) * inv_n;
         my_ok = arg == lab;
         bad = !isfinite(lse);
-        for (int j = 0; j < F3; ++j) d3[b * F3 + j] = (__expf(lg[j] - lse) - (j == lab ? 1.f : 0.f)) * inv_n;
+        for (int j = 0; j < F3; ++j) d3[b * F3 + j] = (expf(lg[j] - lse) - (j == lab ? 1.f : 0.f)) * inv_n;
       } else {
         for (int j = 0; j < F3; ++j) d3[b * F3 + j] = 0.f;
       }
@@ -266,8 +266,8 @@ __global__ void __launch_bounds__(256) loan_eval_kernel(const LoanEvalArgs a) {
       if (acc > mx) { mx = acc; arg = j; }
     }
     float se = 0.f;
-    for (int j = 0; j < F3; ++j) se += __expf(lg[j] - mx);
-    my_loss += (double)(mx + __logf(se) - lg[lab]);
+    for (int j = 0; j < F3; ++j) se += expf(lg[j] - mx);
+    my_loss += (double)(mx + logf(se) - lg[lab]);
     ok += arg == lab;
   }
   my_loss = block_sum(my_loss, redd, false);

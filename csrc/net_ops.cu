@@ -122,7 +122,7 @@ __global__ void bn_fold_kernel(const float* __restrict__ W, long long ldw, const
   const int k = blockIdx.z;
   const float* w = W + (long long)k * ldw;
   for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < e[4]; c += gridDim.x * blockDim.x) {
-    const float s = w[e[0] + c] * rsqrtf(w[e[3] + c] + eps);
+    const float s = w[e[0] + c] * (1.f / sqrtf(w[e[3] + c] + eps));
     scale[(long long)k * ld_out + e[5] + c] = s;
     shift[(long long)k * ld_out + e[5] + c] = w[e[1] + c] - w[e[2] + c] * s;
   }
@@ -335,8 +335,8 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
       if (part > mx) { mx = part; arg = j; }
     }
     float se = 0.f;
-    for (int j = 0; j < a.ncls; ++j) se += __expf(logit[j] - mx);
-    const float lse = mx + __logf(se);
+    for (int j = 0; j < a.ncls; ++j) se += expf(logit[j] - mx);
+    const float lse = mx + logf(se);
     const float loss = lse - logit[label];
     const int slot = a.slot ? (int)a.slot[k] : 0;
     const bool finite = isfinite(lse);
@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(kHeadWarps * 32) head_kernel(const HeadArgs a)
 #pragma unroll
       for (int i = 0; i < PER; ++i) dpooled[i] = 0.f;
       for (int j = 0; j < a.ncls; ++j) {
-        const float dl = (__expf(logit[j] - lse) - (j == label ? 1.f : 0.f)) * inv_n;
+        const float dl = (expf(logit[j] - lse) - (j == label ? 1.f : 0.f)) * inv_n;
 #pragma unroll
         for (int i = 0; i < PER; ++i) {
           const int c = lane + 32 * i;

@@ -43,7 +43,9 @@ int dba_rows_sqdist(const float* X, long long ldx, const float* Y, long long ldy
  * their own pool, or cudaMalloc's device-wide synchronisation is not acceptable where they run).  The partial sums
  * go to a 64 KiB array built into the library, so: at most dba_rows_sqdist_noalloc_max_rows() (64) rows per call,
  * larger calls are refused; the first call on a device resolves the array's address and should happen before any
- * stream capture; calls that may overlap on the GPU race on the shared array.  No counterpart in the reference
+ * stream capture; calls that may overlap on the GPU race on the shared array; the device owning the buffers / stream
+ * must be the calling thread's current device; callable from several host threads (address cache idempotent, launch
+ * counter atomic, error text per thread).  No counterpart in the reference
  * (it has no native code and no scratch buffers). */
 int dba_rows_sqdist_noalloc_max_rows(void);
 int dba_rows_sqdist_noalloc(const float* X, long long ldx, const float* Y, long long ldy, const float* Z, int K,

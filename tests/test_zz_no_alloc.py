@@ -32,7 +32,8 @@ def test_noalloc_matches_scratch_version_on_two_calls(native_lib):
     assert max_rows == 64
     torch.manual_seed(11)
     scratch = torch.empty(int(lib.dba_rows_sqdist_scratch_elems(max_rows)), dtype=torch.float64, device=dev)
-    calls = [(10, 2797610, True, True, True), (3, 5529, False, True, False)]   # (rows, n, per-row Y, Z, sqrt)
+    # (rows, n, per-row Y, Z, sqrt); the last call fills the whole built-in array (64 rows = the limit)
+    calls = [(10, 2797610, True, True, True), (3, 5529, False, True, False), (max_rows, 70001, True, False, True)]
     for K, n, per_row_y, use_z, take_sqrt in calls:
         X = torch.randn(K, n, device=dev)
         Y = torch.randn(K if per_row_y else 1, n, device=dev)
