@@ -6,8 +6,9 @@ path.  The reference cannot run as-is on this image, so the harne
   1. ``visdom`` is not installed           -> a stub module whose ``Visdom`` object ignores every call
   2. ``matplotlib`` is not installed       -> stub ``matplotlib.pyplot``
   3. ``yaml.load(f)`` without a Loader     -> defaulted to ``FullLoader`` (PyYAML >= 6 made it mandatory)
-  4. no network / datasets                 -> ``torchvision.datasets.CIFAR10 / MNIST`` replaced by in-memory synthetic
-                                              datasets of the same shape (the generator this framework's arm uses too)
+  4. no network / datasets                 -> ``torchvision.datasets.CIFAR10 / MNIST / ImageFolder`` replaced by in-memory
+                                              synthetic datasets of the same shape (the generator this framework's arm
+                                              uses too)
   5. ``DataLoader(num_workers=8)``         -> ``num_workers=0`` (in-memory tensors; worker start-up would only slow the
                                               reference down)
   6. ``saved_models/`` must pre-exist      -> run inside a scratch working directory that has it
@@ -90,7 +91,7 @@ def _install_stubs():
     yaml.load = _load
 
 
-def _install_synthetic_datasets(train_size, test_size):
+def _install_synthetic_datasets(train_size, test_size, data_seed=None):
     import numpy as np
     import torch
     import torch.utils.data as tud
@@ -102,12 +103,15 @@ def _install_synthetic_datasets(train_size, test_size):
 
     def _arrays(kind):
         if kind not in cache:
-            cache[kind] = synthetic.make_images(kind, train_size, test_size, seed=1234)
+            cache[kind] = synthetic.make_images(kind, train_size, test_size,
+                                                seed=synthetic.DATA_SEED if data_seed is None else data_seed)
         return cache[kind]
 
-    def _make(kind):
+    def _make(kind, folder=False):
         class _Synth(tud.Dataset):
-            def __init__(self, root=None, train=True, download=False, transform=None, **kw):
+            def __init__(self, root=None, transform=None, train=True, download=False, **kw):
+                if folder:                       # ImageFolder(root, transform): the split is in the path
+                    train = "train" in str(root)
                 xtr, ytr, xte, yte = _arrays(kind)
                 x, y = (xtr, ytr) if train else (xte, yte)
                 self.data = x.numpy() if kind != "mnist" else x.numpy()[..., 0]
@@ -121,6 +125,10 @@ def _install_synthetic_datasets(train_size, test_size):
                 img = self.data[i]
                 if img.ndim == 2:
                     img = img[:, :, None]
+                if folder:                       # ImageFolder yields PIL images (RandomHorizontalFlip needs one)
+                    from PIL import Image
+                    img = Image.fromarray(np.ascontiguousarray(img))
+                    return (self.transform(img) if self.transform is not None else img), self.targets[i]
                 if self.transform is not None:
                     img = self.transform(np.ascontiguousarray(img))
                 return img, self.targets[i]
@@ -128,6 +136,7 @@ def _install_synthetic_datasets(train_size, test_size):
 
     datasets.CIFAR10 = _make("cifar")
     datasets.MNIST = _make("mnist")
+    datasets.ImageFolder = _make("tiny-imagenet-200", folder=True)    # ./data/tiny-imagenet-200/{train,val}
 
     _DL = tud.DataLoader
     _orig_init = _DL.__init__
@@ -163,7 +172,8 @@ def _install_int_add_guard():
     ref_helper.Helper.geometric_median_update = _wrap(ref_helper.Helper.geometric_median_update)
 
 
-def run_reference(params: dict, warmup: int, steps: int, train_size=None, test_size=None, log_path=None) -> dict:
+def run_reference(params: dict, warmup: int, steps: int, train_size=None, test_size=None, log_path=None,
+                  data_seed=None, records: bool = False) -> dict:
     """Runs rounds 1 .. warmup+steps of the reference with ``params`` (a dict in the reference's YAML schema) and
     returns {'ms_per_round': ..., 'round_end_times': [...], 'global_acc': ..., ...}."""
     import torch
@@ -182,9 +192,10 @@ def run_reference(params: dict, warmup: int, steps: int, train_size=None, test_s
     if params.get("type") == "loan":      # the reference reads ./data/loan/loan_XX.csv (loan_helper.py:117-140)
         sys.path.insert(0, ROOT)
         from dba_mod_b200.data import synthetic
-        synthetic.write_loan_csvs(os.path.join(work, "data", "loan"), int(train_size or 60000))
+        synthetic.write_loan_csvs(os.path.join(work, "data", "loan"), int(train_size or 60000),
+                                  synthetic.DATA_SEED if data_seed is None else data_seed)
     _install_stubs()
-    _install_synthetic_datasets(train_size, test_size)
+    _install_synthetic_datasets(train_size, test_size, data_seed)
     sys.path.insert(0, REF)
     import utils.csv_record as csv_record  # reference's (REF first on sys.path; namespace differs from ours)
     _install_int_add_guard()
@@ -226,6 +237,12 @@ def run_reference(params: dict, warmup: int, steps: int, train_size=None, test_s
         out["poison_acc"] = pr[-1][3] if pr else None
     except Exception:  # noqa: BLE001
         pass
+    if records:      # everything the reference recorded, round by round (utils/csv_record.py:4-19)
+        out["records"] = {"test": [list(r) for r in csv_record.test_result],
+                          "poison": [list(r) for r in csv_record.posiontest_result],
+                          "trigger": [list(r) for r in csv_record.poisontriggertest_result],
+                          "weight": [list(r) for r in csv_record.weight_result],
+                          "scale": [list(r) for r in csv_record.scale_result]}
     shutil.rmtree(work, ignore_errors=True)
     return out
 

@@ -33,18 +33,66 @@ sys.path.insert(0, ROOT)
 METRIC = "fl_rounds_per_sec_cifar10_resnet18"
 
 
-def bench_params(warmup: int, steps: int, windows: int = 2) -> dict:
+def metric_name(config: str) -> str:
+    return METRIC if config == "cifar_fedavg" else f"fl_rounds_per_sec_{config}"
+
+
+def data_label(p) -> str:
+    t = p["type"]
+    if t == "loan":
+        return f"synthetic LOAN-shaped table ({p.get('synthetic_train_size') or 60000} rows, 91 features, 51 states), random-init weights"
+    shape = {"cifar": "CIFAR-10-shaped uint8 images (50000 train / 10000 test)",
+             "mnist": "MNIST-shaped uint8 images (60000 train / 10000 test)",
+             "tiny-imagenet-200": "Tiny-ImageNet-shaped uint8 images (100000 train / 10000 test, 64x64, 200 classes)"}[t]
+    return f"synthetic {shape}, random-init weights"
+
+
+def dtype_label(p, be, cuda: bool) -> str:
+    """Compute dtype of the native executor that actually ran (LOAN is an fp32 CUDA-core MLP, MnistNet's executor is
+    bf16-only, the ResNets follow compute_dtype)."""
+    if not cuda:
+        return "fp32"
+    ex = getattr(be, "exec", None)
+    if p["type"] == "loan":
+        return "fp32"
+    return getattr(ex, "compute_dtype", "fp32") if ex is not None else "fp32"
+
+
+# --config: the BASELINE.json configurations (the headline is the default).  name -> (yaml, overrides, description)
+CONFIGS = {
+    "cifar_fedavg": ("cifar_params.yaml", {}, "CIFAR ResNet-18 (narrow 32/64/128/256, 2.8M params), 100 clients / 10 per "
+                     "round, DBA 4 local triggers scale 100, FedAvg"),
+    "cifar_rfa": ("cifar_params.yaml", {"aggregation_methods": "geom_median"}, "CIFAR ResNet-18, 100 / 10, DBA, RFA"),
+    "cifar_foolsgold": ("cifar_params.yaml", {"aggregation_methods": "foolsgold"},
+                        "CIFAR ResNet-18, 100 / 10, DBA, FoolsGold"),
+    "cifar_rfa_1000": ("cifar_params.yaml", {"aggregation_methods": "geom_median", "number_of_total_participants": 1000,
+                                             "no_models": 80, "native_eval_chunk": 250},
+                       "CIFAR ResNet-18, RFA geometric median, 1000 clients / 80 per round"),
+    "tiny_foolsgold": ("tiny_params.yaml", {"aggregation_methods": "foolsgold", "native_eval_chunk": 250,
+                                            "dirichlet_alpha": 0.5},
+                       "Tiny-ImageNet ResNet-18 (64x64, 200 classes), 100 / 10, DBA, FoolsGold"),
+    "loan_fedavg": ("loan_params.yaml", {"synthetic_train_size": 200000, "number_of_total_participants": 51},
+                    "LOAN MLP 91-46-23-9, 51 state clients / 10 per round, DBA feature triggers, FedAvg"),
+    "mnist_fedavg": ("mnist_params.yaml", {}, "MnistNet, 100 clients / 10 per round, DBA 4-part trigger, FedAvg"),
+}
+
+
+def bench_params(warmup: int, steps: int, windows: int = 2, config: str = "cifar_fedavg") -> dict:
     import yaml
-    with open(os.path.join(ROOT, "utils", "cifar_params.yaml")) as f:
+    fname, over, _ = CONFIGS[config]
+    with open(os.path.join(ROOT, "utils", fname)) as f:
         p = yaml.safe_load(f)
     p["resumed_model"] = False
     p["save_model"] = False
     p["synthetic_data"] = True
     p["epochs"] = warmup + windows * steps
-    # shipped schedule: resume at 200, adversaries strike at 203/205/207/209 -> same offsets inside every timed window
-    for i in range(4):
-        p[f"{i}_poison_epochs"] = [warmup + w * steps + 3 + 2 * i for w in range(windows)
-                                   if 3 + 2 * i <= steps]
+    p.update(over)
+    # shipped schedules resume from a checkpoint and strike at rounds r, r+2, r+4, r+6 -> the same offsets are placed
+    # inside every timed window (single-shot attacks of the adversaries, 3 / 5 / 7 / 9 rounds into the window)
+    for i in range(int(p.get("trigger_num", 0))):
+        if f"{i}_poison_epochs" in p:
+            p[f"{i}_poison_epochs"] = [warmup + w * steps + 3 + 2 * i for w in range(windows)
+                                       if 3 + 2 * i <= steps]
     return p
 
 
@@ -114,7 +162,7 @@ def run_own(args) -> dict:
 
     comm = _dist_setup(args.gpus)
     W, K = args.warmup, args.steps
-    raw = bench_params(W, K)
+    raw = bench_params(W, K, config=args.config)
     raw["compute_dtype"] = args.dtype
     if args.small:
         raw.update(synthetic_train_size=5000, synthetic_test_size=1000)
@@ -122,6 +170,7 @@ def run_own(args) -> dict:
     cuda = torch.cuda.is_available()
     sim = Simulator(params, comm=comm, quiet=True, write_files=False)
     dev = sim.device
+    be = sim.backend
 
     def sync():
         comm.barrier()
@@ -161,16 +210,18 @@ def run_own(args) -> dict:
     ms, wall_ms, clocks, launches, reps = timed_window(False)
     sim.prepare_streaming()            # one-time pinning of the host data set (not part of any round)
     ms_e2e, wall_e2e, _, _, reps2 = timed_window(True)
-    be = sim.backend
     out = {
-        "metric": METRIC, "value": K / (ms / 1e3), "unit": "rounds/s", "n_gpus": comm.world, "steps": K, "warmup": W,
+        "metric": metric_name(args.config), "value": K / (ms / 1e3), "unit": "rounds/s", "n_gpus": comm.world,
+        "steps": K, "warmup": W,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": args.dtype if cuda else "fp32",
-        "data": "synthetic CIFAR-10-shaped uint8 images (50000 train / 10000 test), random-init weights",
+        "dtype": dtype_label(params, be, cuda),
+        "data": data_label(params),
         "impl": "dba_mod_b200",
-        "config": {"model": "CIFAR ResNet-18 (narrow 32/64/128/256, 2.8M params)", "global_batch": 640,
-                   "seq_len": None, "clients_total": 100, "clients_per_round": 10, "batch_size": 64,
-                   "aggregation": "FedAvg", "attack": "DBA 4 local triggers, scale 100",
+        "config": {"name": args.config, "model": CONFIGS[args.config][2],
+                   "global_batch": int(params["no_models"]) * int(params["batch_size"]),
+                   "seq_len": None, "clients_total": int(params["number_of_total_participants"]),
+                   "clients_per_round": int(params["no_models"]), "batch_size": int(params["batch_size"]),
+                   "aggregation": params["aggregation_methods"], "attack": "DBA, single-shot, scaled",
                    "parallelism": f"client-sharded x{comm.world}", "timed_l2": "inputs larger than L2 (no flush)",
                    "per_client_eval": True, "backend": be.name,
                    "native_train": bool(getattr(be, "native_train", False)),
@@ -200,13 +251,15 @@ def run_reference(args) -> dict:
     try:
         import torch
         _run = ref_harness.run_reference
-        raw = bench_params(W, K, windows=1)
+        raw = bench_params(W, K, windows=1, config=args.config)
         for k in ("synthetic_data",):
             raw.pop(k, None)
         sampler = ClockSampler(0) if torch.cuda.is_available() else None
         if sampler:
             sampler.start()
-        small = (5000, 1000) if args.small else (None, None)
+        small = (5000, 1000) if args.small else (raw.get("synthetic_train_size"), raw.get("synthetic_test_size"))
+        for k in ("synthetic_train_size", "synthetic_test_size", "native_eval_chunk"):
+            raw.pop(k, None)
         res = _run(raw, W, K, train_size=small[0], test_size=small[1],
                    log_path=os.path.join(ROOT, "gpurun_out", "reference_run.log") if os.path.isdir(
                        os.path.join(ROOT, "gpurun_out")) else None)
@@ -217,13 +270,17 @@ def run_reference(args) -> dict:
     if ms is None:
         return {"impl": "reference", "unavailable": f"reference finished only {res.get('rounds')} rounds"}
     return {
-        "metric": METRIC, "value": 1e3 / ms, "unit": "rounds/s", "n_gpus": 1, "steps": K, "warmup": W,
-        "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32/tf32",
-        "data": "synthetic CIFAR-10-shaped uint8 images (50000 train / 10000 test), random-init weights",
+        "metric": metric_name(args.config), "value": 1e3 / ms, "unit": "rounds/s", "n_gpus": 1, "steps": K,
+        "warmup": W,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "fp32" if raw["type"] == "loan" else "tf32",      # fp32 tensors, cuDNN TF32 convolutions (torch default)
+        "data": data_label(raw),
         "impl": "reference",
-        "config": {"model": "CIFAR ResNet-18 (narrow 32/64/128/256, 2.8M params)", "global_batch": 640,
-                   "clients_total": 100, "clients_per_round": 10, "batch_size": 64, "aggregation": "FedAvg",
-                   "attack": "DBA 4 local triggers, scale 100", "parallelism": "single process, single GPU",
+        "config": {"name": args.config, "model": CONFIGS[args.config][2],
+                   "global_batch": int(raw["no_models"]) * int(raw["batch_size"]),
+                   "clients_total": int(raw["number_of_total_participants"]), "clients_per_round": int(raw["no_models"]),
+                   "batch_size": int(raw["batch_size"]), "aggregation": raw["aggregation_methods"],
+                   "attack": "DBA, single-shot, scaled", "parallelism": "single process, single GPU",
                    "note": "wall-clock between round ends after cuda synchronize; H2D per batch is part of its stock path"},
         "e2e": {"value": 1e3 / ms, "unit": "rounds/s", "h2d_bytes_per_step": None, "d2h_bytes_per_step": None},
         "gpu_launches": None, "clocks": clocks,
@@ -237,6 +294,8 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--config", default="cifar_fedavg", choices=sorted(CONFIGS),
+                    help="which BASELINE.json configuration to time (default: the headline)")
     ap.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"],
                     help="compute mode of the native executor: tf32 = fp32 activations + TF32 tensor-core math (the "
                          "reference's precision class, default), bf16 = fast mode")

@@ -87,6 +87,7 @@ _DEFAULTS: Dict[str, Any] = {
     # ---- extensions of this framework (absent from the reference schema) ----
     "resume_required": False,     # resumed_model: true with a missing checkpoint file is an error (else: warn, start fresh)
     "synthetic_data": None,       # None = auto (use real data when found under data_dir, else synthetic)
+    "synthetic_seed": None,       # seed of the synthetic data generator (None = data.synthetic.DATA_SEED)
     "synthetic_train_size": None,
     "synthetic_test_size": None,
     "data_dir": "./data",

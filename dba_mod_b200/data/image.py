@@ -124,7 +124,9 @@ class ImageData:
                 raise FileNotFoundError(f"{kind}: no data set under {params.get('data_dir')!r} and synthetic_data is false")
         self.is_synthetic = arrays is None
         if arrays is None:
-            arrays = synthetic.make_images(kind, params.get("synthetic_train_size"), params.get("synthetic_test_size"))
+            sseed = params.get("synthetic_seed")
+            arrays = synthetic.make_images(kind, params.get("synthetic_train_size"), params.get("synthetic_test_size"),
+                                           synthetic.DATA_SEED if sseed is None else int(sseed))
         xtr, ytr, xte, yte = arrays
         self.H, self.W, self.Cin = int(xtr.shape[1]), int(xtr.shape[2]), int(xtr.shape[3])
         self.C = self.Cin

@@ -55,7 +55,9 @@ class LoanData:
         else:
             if want_syn is False:
                 raise FileNotFoundError(f"no loan_XX.csv files under {loan_dir!r} and synthetic_data is false")
-            tables = synthetic.make_loan(int(params.get("synthetic_train_size") or 60000))
+            sseed = params.get("synthetic_seed")
+            tables = synthetic.make_loan(int(params.get("synthetic_train_size") or 60000),
+                                         synthetic.DATA_SEED if sseed is None else int(sseed))
             columns = synthetic.loan_feature_names()
             self.is_synthetic = True
         self.state_names: List[str] = list(tables.keys())
