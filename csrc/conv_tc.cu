@@ -500,7 +500,6 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
 }  // namespace
 
 static long long* g_conv_dbg = nullptr;
-static thread_local int g_conv_vlo = 0, g_conv_vhi = 0;     // set by dba_conv_tc_valid around one launch
 static int g_conv_dbg_shift = 0;
 
 extern "C" {
@@ -526,10 +525,10 @@ long long dba_conv_rows(int B, int H, int W) {
 // in_s2d / out_s2d: space-to-depth forms for stride-2 convolutions (see ConvArgs).  With in_s2d, (H, W) is the
 // OUTPUT grid of the stride-2 convolution (the grid X' lives on), X' has 4*Cin channels and sub must be 1.  With
 // out_s2d, Y gets 4*Cout channels on the (H/2, W/2) grid; Res (if any) stays a plain (H, W) tensor.
-int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
-                   const float* scale, const float* shift, long long ss_stride, float* stats,
-                   long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
-                   int relu, int x_shared, int in_s2d, int out_s2d, void* stream) {
+static int conv_launch(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                       const float* scale, const float* shift, long long ss_stride, float* stats,
+                       long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                       int relu, int x_shared, int in_s2d, int out_s2d, int vlo, int vhi, void* stream) {
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
   DBA_REQUIRE(ksize == 1 || ksize == 3 || ksize == 5 || (ksize == 2 && out_s2d == 3),
               "dba_conv_tc: ksize must be 1, 3 or 5 (2 with out mode 3), got %d", ksize);
@@ -574,7 +573,7 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
               Cin);
   a.halo = ksize == 2 ? a.Wp + 1 : (ksize / 2) * (a.Wp + 1);
   a.ksz = ksize;
-  a.vlo = g_conv_vlo; a.vhi = g_conv_vhi > 0 ? g_conv_vhi : (H > W ? H : W);
+  a.vlo = vlo; a.vhi = vhi > 0 ? vhi : (H > W ? H : W);
   const int kc = a.KB / V;
   const long long body = (long long)B * a.S;
   // n-block and rows per pass: as many 128-row tiles as fit in TMEM (512 columns); when that leaves SMs idle, first
@@ -613,7 +612,7 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
     } else {
       // Streamed weights: as many stages as fit (<= kMaxSB).  A CTA that owns few row tiles is bound by the latency of
       // its own weight stream (K = 1, 256 channels: 295 KB per CTA at 32 KB in flight = 11 B/clk); deeper is faster.
-      static const int sb_cap = getenv("DBA_CONV_SB") ? atoi(getenv("DBA_CONV_SB")) : kMaxSB;
+      const int sb_cap = kMaxSB;
       long long sb = budget > 2 * bytesA + misc ? (long long)((budget - 2 * bytesA - misc) / bytesB) : 0;
       a.SB = sb > sb_cap ? sb_cap : (int)sb;
       if (a.SB < 2) a.SB = 2;
@@ -663,6 +662,14 @@ int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, voi
   return DBA_OK;
 }
 
+int dba_conv_tc_ex(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
+                   const float* scale, const float* shift, long long ss_stride, float* stats,
+                   long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
+                   int relu, int x_shared, int in_s2d, int out_s2d, void* stream) {
+  return conv_launch(X, Wt, w_client_stride, Y, Res, scale, shift, ss_stride, stats, stats_stride, K, B, H, W, Cin, Cout,
+                     ksize, sub, relu, x_shared, in_s2d, out_s2d, 0, 0, stream);
+}
+
 // 'Valid' (unpadded) convolution as the centre crop of the padded one: only outputs with vlo <= h, w < vhi are stored
 // (at their position on the input grid); everything else as dba_conv_tc_ex.  With ksize = 5 the operand block reaches
 // 2*(W+1)+2 rows beyond a pass on either side: X needs (W+2) zero rows of slack before its first and after its last
@@ -671,11 +678,8 @@ int dba_conv_tc_valid(const void* X, const void* Wt, long long w_client_stride, 
                       const float* scale, const float* shift, long long ss_stride, float* stats,
                       long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int relu,
                       int x_shared, int vlo, int vhi, void* stream) {
-  g_conv_vlo = vlo; g_conv_vhi = vhi;
-  const int rc = dba_conv_tc_ex(X, Wt, w_client_stride, Y, Res, scale, shift, ss_stride, stats, stats_stride, K, B, H, W,
-                                Cin, Cout, ksize, 1, relu, x_shared, 0, 0, stream);
-  g_conv_vlo = 0; g_conv_vhi = 0;
-  return rc;
+  return conv_launch(X, Wt, w_client_stride, Y, Res, scale, shift, ss_stride, stats, stats_stride, K, B, H, W, Cin, Cout,
+                     ksize, 1, relu, x_shared, 0, 0, vlo, vhi, stream);
 }
 
 int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,

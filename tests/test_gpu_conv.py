@@ -216,3 +216,69 @@ def test_shortcut_input_gradient_added_in_place_at_even_pixels(native_lib, act):
                                     native.stream()))
     torch.cuda.synchronize()
     torch.testing.assert_close(layout.from_planar(dx, B, H, H), ref, rtol=act.rtol, atol=1.5 * act.atol)
+
+
+def _guarded(shape, dtype, dev, guard=8192, fill=0.0):
+    """A zero tensor of ``shape`` carved out of a larger allocation whose guard bands (``guard`` elements before and
+    after) hold a sentinel: any out-of-bounds store of a kernel shows up as a changed sentinel."""
+    n = 1
+    for s_ in shape:
+        n *= s_
+    base = torch.full((n + 2 * guard,), 777.0, dtype=dtype, device=dev)
+    view = base[guard:guard + n].view(shape)
+    view.fill_(fill)
+    return base, view, guard
+
+
+def _guards_intact(base, guard):
+    return bool((base[:guard] == 777.0).all()) and bool((base[-guard:] == 777.0).all())
+
+
+@pytest.mark.parametrize("K,B,H,Cin,Cout,ks,sub", [(2, 3, 8, 32, 64, 3, 1), (1, 5, 4, 256, 256, 3, 1),
+                                                    (2, 7, 16, 64, 128, 1, 2), (1, 64, 32, 32, 32, 3, 1)])
+def test_conv_and_wgrad_write_nothing_outside_their_buffers(native_lib, act, K, B, H, Cin, Cout, ks, sub):
+    """Out-of-bounds canary (compute-sanitizer is closed on this pool): output / gradient buffers sit between sentinel
+    bands, inputs are followed by sentinels too (an over-read would put 777s into the result and fail the numerics)."""
+    from dba_mod_b200.ops import layout, native
+    lib = native.load()
+    torch.manual_seed(7)
+    d = torch.device("cuda", 0)
+    x = act.round(torch.randn(K, B, Cin, H, H, device=d))
+    w = act.round(torch.randn(K, Cout, Cin, ks, ks, device=d) / (Cin * ks * ks) ** 0.5)
+    xp0, wt0 = layout.to_planar(x, dtype=act.dtype), layout.pack_conv_weight(w, dtype=act.dtype)
+    bx, xp, gx = _guarded(tuple(xp0.shape), act.dtype, d)
+    xp.copy_(xp0)
+    bw, wt, gw = _guarded(tuple(wt0.shape), act.dtype, d)
+    wt.copy_(wt0)
+    Ho = H // sub
+    go = layout.Geom(B, Ho, Ho)
+    by, y, gy = _guarded((K, Cout // act.V, go.rows, act.V), act.dtype, d)
+    stats_b, stats, gs = _guarded((K, Cout, 2), torch.float32, d)
+    native.check(lib.dba_conv_tc(native.ptr(xp), native.ptr(wt), native.ptr(y), None, None, None, native.ptr(stats), K, B,
+                                 H, H, Cin, Cout, ks, sub, 0, 0, 0, native.stream()))
+    torch.cuda.synchronize()
+    assert _guards_intact(by, gy) and _guards_intact(stats_b, gs) and _guards_intact(bx, gx) and _guards_intact(bw, gw)
+    got = layout.from_planar(y, B, Ho, Ho)
+    torch.testing.assert_close(got, _ref(x, w, ks, sub, act), rtol=act.rtol, atol=act.atol)
+    assert layout.halo_is_zero(y, B, Ho, Ho)
+    if sub == 1:        # weight gradient of the same layer, gradient slab between sentinels
+        dy = act.round(torch.randn(K, B, Cout, H, H, device=d))
+
+        def operand(t):
+            if act.name == "tf32":
+                hi = t.bfloat16()
+                return torch.stack([layout.to_planar(hi.float()), layout.to_planar((t - hi.float()).bfloat16().float())],
+                                   1).contiguous()
+            return layout.to_planar(t, dtype=act.dtype)
+        dy0, x0 = operand(dy), operand(x)
+        bd, dyp, gd = _guarded(tuple(dy0.shape), dy0.dtype, d)
+        dyp.copy_(dy0)
+        bx2, xp2, gx2 = _guarded(tuple(x0.shape), x0.dtype, d)
+        xp2.copy_(x0)
+        nG = Cout * ks * ks * Cin
+        bG, G, gG = _guarded((K, nG), torch.float32, d)
+        native.check(lib.dba_wgrad_tc(native.ptr(dyp), native.ptr(xp2), native.ptr(G), G.stride(0), 0, K, B, H, H, Cin,
+                                      Cout, Cin, Cout, ks, native.stream()))
+        torch.cuda.synchronize()
+        assert _guards_intact(bG, gG) and _guards_intact(bd, gd) and _guards_intact(bx2, gx2)
+        assert bool(torch.isfinite(G).all()) and float(G.abs().max()) < 1e4      # no sentinel leaked into the sums
