@@ -16,9 +16,11 @@ from ..ops import native
 
 
 class LockStepTrainer:
-    # cost of one lock-step step over k clients (ms), measured on B200 with tools/gpu_step_cost.py (CIFAR ResNet-18,
-    # B = 64, graph replay): 1.37 ms at k = 1 ... 3.56 ms at k = 10; and of moving the carried state to another slab
-    _STEP_COST = (1.13, 0.243)
+    # cost model of one lock-step step over k clients: a + b*k (ms).  The class value is only the fallback (CIFAR
+    # ResNet-18, tf32, B = 64, graph replay with programmatic dependent launch: 1.70 ms at k = 1 ... 5.95 ms at k = 10,
+    # tools/gpu_step_cost.py); ``prewarm`` replaces it per executor by timing the captured step graphs of the model
+    # actually being trained.  _CUT_COST: moving the carried state to another slab.
+    _STEP_COST = (1.23, 0.472)
     _CUT_COST = 0.25
 
     # Slab widths: every distinct width owns a full set of activation buffers and a captured graph, so segments run on
@@ -40,14 +42,14 @@ class LockStepTrainer:
         return K
 
     @classmethod
-    def _segments(cls, steps: List[int], max_cuts: int = 4) -> List[tuple]:
+    def _segments(cls, steps: List[int], max_cuts: int = 4, cost=None) -> List[tuple]:
         """Split the lock-step schedule into [(rows, lo, hi)] so that clients that finished stop being computed.
 
         Clients hold different numbers of samples (Dirichlet partition) and attackers train
         ``internal_poison_epochs`` x longer, so T = max steps while the average client is done much earlier: without
         this a round of 10 clients runs at ~57% utilisation.  Cut points are chosen by dynamic programming over the
         distinct step counts (cost model above); each segment runs on a slab sized for the clients still active."""
-        a, b = cls._STEP_COST
+        a, b = cost if cost is not None else cls._STEP_COST
         K = len(steps)
         T = max(steps) if steps else 0
         if K == 0 or T == 0:
@@ -112,7 +114,8 @@ class LockStepTrainer:
                     "flip": sch.flip.to(torch.uint8) if sch.flip is not None else None}
         flags = (bool(want_grad_sum), sch.flip is not None, use_dist)
         steps = list(sch.steps_host) if len(sch.steps_host) == K else [sch.T] * K
-        segs = self._segments(steps) if bool(p.get("compact_tail", True)) else [(list(range(K)), 0, sch.T)]
+        segs = self._segments(steps, cost=self._STEP_COST) if bool(p.get("compact_tail", True)) \
+            else [(list(range(K)), 0, sch.T)]
         carry = ("V", "gs", "anchor") if use_dist else ("V", "gs")
         for rows, lo, hi in segs:
             if self._width(len(rows), K) == K:       # (nearly) everybody still active: stay on the home slab
@@ -212,3 +215,32 @@ class LockStepTrainer:
                 t[key].zero_()
             if t["cnt"].numel():
                 t["cnt"].zero_()
+        self._calibrate_step_cost(Kmax, (bool(want_grad_sum), with_flip, False))
+
+    def _calibrate_step_cost(self, Kmax: int, flags: tuple) -> None:
+        """a + b*k from the captured step graphs of THIS model / mode / batch size: replay k = 1 and k = Kmax a few
+        times on idle slabs (the kernels do the same work for padding samples) and time them with CUDA events."""
+        if Kmax < 2 or self.device.type != "cuda":
+            return
+        gkey = ("graph",) + flags
+        ms = {}
+        for K in (1, Kmax):
+            g = self._tbufs(K).get(gkey)
+            if g is None:
+                return
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g.replay()
+            e0.record()
+            for _ in range(3):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize(self.device)
+            ms[K] = e0.elapsed_time(e1) / 3
+            t = self._tbufs(K)
+            for key in ("V", "mf", "mi", "nan", "gs", "mf_dist", "W"):
+                t[key].zero_()
+            if t["cnt"].numel():
+                t["cnt"].zero_()
+        b = max((ms[Kmax] - ms[1]) / (Kmax - 1), 1e-3)
+        a = max(ms[1] - b, 1e-3)
+        self._STEP_COST = (a, b)

@@ -150,6 +150,12 @@ class Simulator:
             # the cost-model placement can give one rank anything between 1 and no_models - (world - 1) clients
             kmax = max(1, int(params["no_models"]) - (self.world - 1))
             ex.prewarm(kmax, params["aggregation_methods"] == C.AGGR_FOOLSGOLD)
+            if self.world > 1:
+                # the measured cost model drives the client placement, which every rank must compute identically:
+                # everybody adopts rank 0's measurement (start-up plumbing, before the first round)
+                c = torch.tensor(ex._STEP_COST, dtype=torch.float64, device=self.device)
+                self.comm.broadcast_(c, 0)
+                ex._STEP_COST = (float(c[0]), float(c[1]))
         self.collective_path = "single process" if self.world == 1 else "torch.distributed baseline"
         if (self.world > 1 and self.device.type == "cuda" and params["fused_collectives"]
                 and not hasattr(self.comm, "fedavg_")):
