@@ -242,6 +242,195 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------ fused backward
+// Reduce + apply in ONE launch: the row blocks of a (client, channel-plane) pair form a thread-block cluster; every CTA
+// reduces its slice, the partial sums are exchanged through distributed shared memory (fixed summation order, no
+// atomics, no zeroed scratch), and every CTA applies the result to the same slice, which it re-reads from L2.
+// Saves one launch + one grid drain per BatchNorm layer of a training step and makes d_gamma / d_beta deterministic.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ float dsmem_ld(const float* local, uint32_t rank) {
+  uint32_t addr = (uint32_t)__cvta_generic_to_shared(local), raddr;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(addr), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(raddr) : "memory");
+  return v;
+}
+
+constexpr int kBnU = 4;        // rows in flight per thread (independent 16-byte loads)
+
+// grid (cluster size X, C/V, K), cluster (X, 1, 1), 256 threads.
+template <int V>
+__global__ void __launch_bounds__(256) bn_bwd_fused_kernel(const BnArgs a) {
+  __shared__ float red[2][8][V];
+  __shared__ float part[2][V];
+  __shared__ float s_sc[V], s_mg[V], s_mgx[V], s_mean[V], s_rstd[V];
+  pdl_trigger();
+  pdl_wait();
+  const int chunk = blockIdx.y, k = blockIdx.z;
+  const int nv = a.nvalid[k];
+  const float n = (float)nv * (float)(a.H * a.W);
+  float mean[V], rstd[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    mean[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * V + j)];
+    rstd[j] = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * (chunk * V + j) + 1];
+  }
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
+  const int stride = gridDim.x * blockDim.x;
+  const int q0 = blockIdx.x * blockDim.x + threadIdx.x;
+  // ---------------------------------------------------------------- pass 1: sums of g' and g' * xhat over the slice
+  {
+    const int total = min(a.B, nv) * S;
+    float sg[V], sgx[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) sg[j] = sgx[j] = 0.f;
+    for (int qb = q0; qb < total; qb += stride * kBnU) {
+      uint4 rg[kBnU], ry[kBnU], ro[kBnU];
+      bool ok[kBnU];
+#pragma unroll
+      for (int u = 0; u < kBnU; ++u) {
+        const int q = qb + u * stride;
+        const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+        ok[u] = q < total && h < a.H && w < a.W;
+        if (ok[u]) {
+          const long long off = plane + lead + q;
+          rg[u] = a.g[off];
+          ry[u] = a.y[off];
+          if (a.act) ro[u] = a.act[off];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kBnU; ++u) {
+        if (!ok[u]) continue;
+        float g[V], y[V];
+        chunk_unpack<V>(rg[u], g);
+        chunk_unpack<V>(ry[u], y);
+        if (a.act) {
+          float o[V];
+          chunk_unpack<V>(ro[u], o);
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          sg[j] += g[j];
+          sgx[j] += g[j] * (y[j] - mean[j]) * rstd[j];
+        }
+      }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      sg[j] = warp_sum(sg[j]);
+      sgx[j] = warp_sum(sgx[j]);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) { red[0][warp][j] = sg[j]; red[1][warp][j] = sgx[j]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 * V) {
+      const int which = threadIdx.x / V, j = threadIdx.x % V;
+      float t = 0.f;
+      for (int w = 0; w < 8; ++w) t += red[which][w][j];
+      part[which][j] = t;
+    }
+  }
+  cluster_arrive();
+  cluster_wait();                               // every CTA's partial sums are in its shared memory
+  if (threadIdx.x < V) {
+    const int j = threadIdx.x, c = chunk * V + j;
+    float sg = 0.f, sgx = 0.f;
+    for (uint32_t r = 0; r < gridDim.x; ++r) {   // rank order: the same sum in every CTA, run to run
+      sg += dsmem_ld(&part[0][j], r);
+      sgx += dsmem_ld(&part[1][j], r);
+    }
+    const float gamma = a.Wflat[(long long)k * a.ldw + a.g_off + c];
+    const float mean_c = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c];
+    const float rstd_c = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c + 1];
+    s_sc[j] = gamma * rstd_c;
+    s_mg[j] = n > 0.f ? sg / n : 0.f;
+    s_mgx[j] = n > 0.f ? sgx / n : 0.f;
+    s_mean[j] = mean_c;
+    s_rstd[j] = rstd_c;
+    if (cluster_ctarank() == 0 && a.Gflat) {
+      a.Gflat[(long long)k * a.ldg + a.g_off + c] = sgx;   // d gamma
+      a.Gflat[(long long)k * a.ldg + a.b_off + c] = sg;    // d beta
+    }
+  }
+  cluster_arrive();                             // done reading the peers' shared memory (waited for before exit)
+  __syncthreads();
+  // ---------------------------------------------------------------- pass 2: dy (and g') for the same slice
+  {
+    const int Wpu = 2 * a.W + 1, Su = (2 * a.H + 1) * Wpu, leadu = Wpu + 1;
+    const long long plane_up = ((long long)k * (a.C / V) + chunk) * a.Rup;
+    const int total = a.B * S;
+    for (int qb = q0; qb < total; qb += stride * kBnU) {
+      uint4 rg[kBnU], ry[kBnU], ro[kBnU];
+      bool ok[kBnU];
+      int bb[kBnU], hh[kBnU], ww[kBnU];
+#pragma unroll
+      for (int u = 0; u < kBnU; ++u) {
+        const int q = qb + u * stride;
+        const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+        bb[u] = b; hh[u] = h; ww[u] = w;
+        ok[u] = q < total && h < a.H && w < a.W;
+        if (ok[u] && b < nv) {
+          const long long off = plane + lead + q;
+          rg[u] = a.g[off];
+          ry[u] = a.y[off];
+          if (a.act) ro[u] = a.act[off];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kBnU; ++u) {
+        if (!ok[u]) continue;
+        const int q = qb + u * stride;
+        const long long off = plane + lead + q;
+        float d[V], gm[V];
+        if (bb[u] < nv) {
+          float g[V], y[V];
+          chunk_unpack<V>(rg[u], g);
+          chunk_unpack<V>(ry[u], y);
+          if (a.act) {
+            float o[V];
+            chunk_unpack<V>(ro[u], o);
+#pragma unroll
+            for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            const float xh = (y[j] - s_mean[j]) * s_rstd[j];
+            gm[j] = g[j];
+            d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) d[j] = gm[j] = 0.f;
+        }
+        if (a.gmask) a.gmask[off] = chunk_pack<V>(gm);
+        long long doff = off, drow = lead + q;
+        if (a.up) {
+          drow = leadu + (long long)bb[u] * Su + (2 * hh[u]) * Wpu + 2 * ww[u];
+          doff = plane_up + drow;
+        }
+        a.out[doff] = chunk_pack_operand<V>(d);          // dy is the input-gradient convolution's operand
+        if constexpr (V == 4) {
+          if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.up ? a.Rup : a.R, chunk, drow, d);
+        }
+      }
+    }
+  }
+  cluster_wait();                               // no CTA leaves while a peer may still read its partial sums
+}
+
 // ------------------------------------------------------------------------------------------------ max pooling
 // MaxPool2d(3, stride 2, pad 1) on planar activations (Tiny-ImageNet stem, models/resnet_tinyimagenet.py:147).
 // Inputs are post-ReLU (>= 0) and the halo rows / columns of the layout are zero, so the window can be read without
@@ -334,6 +523,28 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const PoolArgs a) {
       }
     a.gx[me] = chunk_pack<V>(acc);
   }
+}
+
+int g_bn_fused = 1;
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_cluster_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, int cluster_x, cudaStream_t st,
+                                      Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cluster_x;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = g_dba_pdl ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 2;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 inline int act_v() { return g_dba_act_mode == 1 ? 4 : 8; }
@@ -430,7 +641,20 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
   a.ld_stats = ld_sums; a.ld_saved = ld_saved; a.ldw = ldw; a.ldg = ldg; a.R = R; a.Rup = Rup;
   a.stats_off = sums_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.up = up;
-  const dim3 grid = bn_grid(B, H, W, C, K);
+  dim3 grid = bn_grid(B, H, W, C, K);
+  if (g_bn_fused) {
+    // one cluster per (client, channel plane): as many row blocks as keep ~148 SMs busy, at most 8 (portable size)
+    const long long pairs = (long long)(C / act_v()) * K;
+    int X = (int)((2 * kNumSMs + pairs - 1) / pairs);
+    if (X > (int)grid.x) X = (int)grid.x;
+    X = X >= 8 ? 8 : X >= 4 ? 4 : X >= 2 ? 2 : 1;
+    grid.x = X;
+    if (act_v() == 4) launch_cluster_pdl(bn_bwd_fused_kernel<4>, grid, 256, X, (cudaStream_t)stream, a);
+    else launch_cluster_pdl(bn_bwd_fused_kernel<8>, grid, 256, X, (cudaStream_t)stream, a);
+    DBA_COUNT_LAUNCH(1);
+    DBA_CHECK_LAUNCH();
+    return DBA_OK;
+  }
   if (act_v() == 4) {
     launch_pdl(bn_bwd_reduce_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
     launch_pdl(bn_bwd_apply_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
@@ -442,6 +666,11 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
   DBA_CHECK_LAUNCH();
   return DBA_OK;
 }
+
+// 1 (default): BatchNorm backward = one cluster launch per layer; 0: the two-kernel form (reduce with atomics into the
+// caller-zeroed `sums` scratch, then apply).  Both produce the same dy; the fused form needs no zeroed scratch.
+void dba_set_bn_fused(int on) { g_bn_fused = on ? 1 : 0; }
+int dba_get_bn_fused() { return g_bn_fused; }
 
 // y = MaxPool2d(3, 2, 1)(x); x on the B x H x W grid, y on B x H/2 x W/2.  Rin / Rout = dba_conv_rows of the two grids.
 int dba_maxpool_fwd_split(const void* x, void* y, void* y_split, int K, int C, int B, int H, int W, long long Rin,

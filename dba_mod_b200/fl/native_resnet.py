@@ -563,7 +563,9 @@ class NativeResNet(LockStepTrainer):
         stem = self.layers[0]
         lv_g = {r: t[("g", r)] for r in self.ress}
         pack = self.pack_weights(W, t["pack"])
-        t["stats"].zero_(); t["sums"].zero_(); Gr.zero_()
+        t["stats"].zero_(); Gr.zero_()
+        if not lib.dba_get_bn_fused():          # only the two-kernel BatchNorm backward accumulates into scratch
+            t["sums"].zero_()
         native.check(lib.dba_input_stage_image_split(
             native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(t["st_idx"]), t["st_idx"].stride(0),
             native.ptr(self.trig_u8), native.ptr(t["trig_row"]), native.ptr(t["poison_n"]),

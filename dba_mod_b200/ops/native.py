@@ -50,6 +50,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_add_launch_count", [c_ulonglong], None)
     _sig(lib, "dba_set_pdl", [I], None)
     _sig(lib, "dba_get_pdl", [], c_int)
+    _sig(lib, "dba_set_bn_fused", [I], None)
+    _sig(lib, "dba_get_bn_fused", [], c_int)
     _sig(lib, "dba_set_act_dtype", [I])
     _sig(lib, "dba_get_act_dtype", [], c_int)
     _sig(lib, "dba_sgd_step", [P, L, P, P, P, L, P, P, I, L, F, F, P])
@@ -106,6 +108,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_loan_eval", [P, L, I, P, P, P, L, P, P, I, P, P, P])
     if os.environ.get("DBA_PDL") is not None:      # A/B switch for programmatic dependent launch (default: on)
         lib.dba_set_pdl(int(os.environ["DBA_PDL"]))
+    if os.environ.get("DBA_BN_FUSED") is not None:  # A/B switch: cluster-fused BatchNorm backward (default: on)
+        lib.dba_set_bn_fused(int(os.environ["DBA_BN_FUSED"]))
     _LIB = lib
     return lib
 

@@ -198,6 +198,10 @@ int dba_set_act_dtype(int mode);
  * run their prologue, while its predecessor drains.  No counterpart in the reference. */
 void dba_set_pdl(int on);
 int dba_get_pdl(void);
+/* BatchNorm backward as one thread-block-cluster launch per layer (default on; partial sums exchanged through
+ * distributed shared memory, `sums` scratch unused) or as reduce + apply kernels (0; `sums` must be zeroed). */
+void dba_set_bn_fused(int on);
+int dba_get_bn_fused(void);
 int dba_get_act_dtype(void);
 
 /* MaxPool2d(3, 2, 1) forward / backward on planar-8 activations (Tiny-ImageNet stem, resnet_tinyimagenet.py:147). */

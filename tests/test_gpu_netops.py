@@ -75,11 +75,13 @@ def test_wgrad_matches_autograd(native_lib, act, K, B, H, Cin, Cout, ks, cin_rea
 
 
 # ------------------------------------------------------------------------------------------------- BatchNorm
+@pytest.mark.parametrize("fused", [1, 0], ids=["cluster", "twokernel"])
 @pytest.mark.parametrize("C,H,B,nvalid", [(32, 8, 6, [6, 3]), (64, 16, 5, [5, 5]), (512, 2, 7, [7, 4]),
-                                          (256, 4, 9, [1, 9])])
-def test_batchnorm_forward_backward(native_lib, act, C, H, B, nvalid):
+                                          (256, 4, 9, [1, 9]), (32, 32, 20, [20, 13])])
+def test_batchnorm_forward_backward(native_lib, act, C, H, B, nvalid, fused):
     """BatchNorm(train) + residual + ReLU forward from the conv-epilogue statistics, and its backward, for K = 2
-    clients with ragged batches (samples b >= nvalid[k] are padding)."""
+    clients with ragged batches (samples b >= nvalid[k] are padding).  The backward runs as one thread-block-cluster
+    launch (partial sums over distributed shared memory; the last shape uses clusters of 8) and as reduce + apply."""
     from dba_mod_b200.ops import layout, native
     lib = native.load()
     torch.manual_seed(1)
@@ -131,12 +133,17 @@ def test_batchnorm_forward_backward(native_lib, act, C, H, B, nvalid):
     gmask = torch.zeros_like(yp)
     dsplit = torch.zeros_like(osplit) if osplit is not None else None
     gp = _planar(gup, act)
-    native.check(lib.dba_bn_backward_split(native.ptr(gp), native.ptr(yp), native.ptr(out), native.ptr(dy),
-                                           native.ptr(dsplit), native.ptr(gmask), native.ptr(sums), sums.stride(0), 0,
-                                           native.ptr(saved), saved.stride(0), 0, native.ptr(Wf), Wf.stride(0),
-                                           native.ptr(Gf), Gf.stride(0), 0, C, native.ptr(nv), K, C, B, H, H, g.rows, 0,
-                                           g.rows, native.stream()))
-    torch.cuda.synchronize()
+    was = lib.dba_get_bn_fused()
+    lib.dba_set_bn_fused(fused)
+    try:
+        native.check(lib.dba_bn_backward_split(native.ptr(gp), native.ptr(yp), native.ptr(out), native.ptr(dy),
+                                               native.ptr(dsplit), native.ptr(gmask), native.ptr(sums), sums.stride(0), 0,
+                                               native.ptr(saved), saved.stride(0), 0, native.ptr(Wf), Wf.stride(0),
+                                               native.ptr(Gf), Gf.stride(0), 0, C, native.ptr(nv), K, C, B, H, H, g.rows,
+                                               0, g.rows, native.stream()))
+        torch.cuda.synchronize()
+    finally:
+        lib.dba_set_bn_fused(was)
     gdy, gm = layout.from_planar(dy, B, H, H), layout.from_planar(gmask, B, H, H)
     if dsplit is not None:
         torch.testing.assert_close(_unsplit(dsplit, B, H, H), gdy, rtol=6e-4, atol=1e-7)

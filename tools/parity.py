@@ -27,12 +27,24 @@ sys.path.insert(0, ROOT)
 ATTACK_ROUNDS = (8, 10, 12, 14)
 
 
-def params_for(agg: str, rounds: int, train: int, test: int) -> dict:
+def _overrides(spec) -> dict:
+    """``--set eta=1,scale_weights_poison=10``: YAML-typed overrides applied to BOTH arms."""
+    import yaml
+    out = {}
+    for item in (spec or "").split(","):
+        if item.strip():
+            k, v = item.split("=", 1)
+            out[k.strip()] = yaml.safe_load(v)
+    return out
+
+
+def params_for(agg: str, rounds: int, train: int, test: int, overrides=None) -> dict:
     import yaml
     raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "cifar_params.yaml")))
     raw.update(resumed_model=False, save_model=False, epochs=rounds, aggregation_methods=agg)
     for i, r in enumerate(ATTACK_ROUNDS):
         raw[f"{i}_poison_epochs"] = [r]
+    raw.update(_overrides(overrides))
     return raw
 
 
@@ -41,7 +53,7 @@ def run_own(agg, seed, a):
     from dba_mod_b200.config import Params
     from dba_mod_b200.fl.simulator import Simulator
     from dba_mod_b200.parallel.launcher import make_comm
-    raw = params_for(agg, a.rounds, a.train, a.test)
+    raw = params_for(agg, a.rounds, a.train, a.test, a.set)
     raw.update(synthetic_data=True, synthetic_train_size=a.train, synthetic_test_size=a.test,
                synthetic_seed=1234 + seed, seed=1 + seed, compute_dtype=a.dtype)
     comm = make_comm()
@@ -64,7 +76,7 @@ def run_ref(agg, seed, a):
     import tempfile
     tmp = tempfile.mktemp(suffix=".json")
     cmd = [sys.executable, os.path.abspath(__file__), "_refone", "--agg", agg, "--seed", str(seed), "--rounds",
-           str(a.rounds), "--train", str(a.train), "--test", str(a.test), "--out", tmp]
+           str(a.rounds), "--train", str(a.train), "--test", str(a.test), "--out", tmp, "--set", a.set or ""]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0 or not os.path.exists(tmp):
         raise RuntimeError(f"reference run failed: {r.stderr[-1500:]}")
@@ -76,7 +88,7 @@ def run_ref(agg, seed, a):
 def _ref_one(agg, seed, a):
     sys.path.insert(0, os.path.join(ROOT, "baseline"))
     import ref_harness
-    raw = params_for(agg, a.rounds, a.train, a.test)
+    raw = params_for(agg, a.rounds, a.train, a.test, a.set)
     res = ref_harness.run_reference(raw, 0, a.rounds, train_size=a.train, test_size=a.test, data_seed=1234 + seed,
                                     records=True)
     rec = res["records"]
@@ -107,7 +119,7 @@ def cmd_run(a):
     aggs = a.aggs.split(",")
     seeds = [int(s) for s in a.seeds.split(",")]
     results = {"arm": a.arm, "dtype": a.dtype if a.arm == "own" else "tf32 (cuDNN)", "rounds": a.rounds,
-               "train": a.train, "test": a.test, "runs": {}}
+               "train": a.train, "test": a.test, "overrides": a.set or "", "runs": {}}
     for agg in aggs:
         for s in seeds:
             t0 = time.time()
@@ -150,10 +162,13 @@ def cmd_report(a):
     L = []
     L.append("# Accuracy / ASR parity: dba_mod_b200 vs the unmodified reference (through the compat shim)\n")
     L.append(f"Generated by `tools/parity.py report` from {', '.join('`' + os.path.basename(f) + '`' for f in a.files)}.\n")
-    L.append("Setting: shipped CIFAR DBA YAML from a random initialisation, synthetic CIFAR-shaped data "
+    ov = arms[0].get("overrides") or ""
+    L.append(("Setting: shipped CIFAR DBA YAML" + (f" with `{ov}`" if ov else "") +
+              " from a random initialisation, synthetic CIFAR-shaped data ")
+             +
              f"({arms[0]['train']} train / {arms[0]['test']} test images, generator seed 1234 + s, identical bytes for "
              f"all arms), {arms[0]['rounds']} rounds, the four adversaries strike once each in rounds "
-             f"{', '.join(map(str, ATTACK_ROUNDS))} with their local trigger (scale 100).  Mean over seeds; the number "
+             f"{', '.join(map(str, ATTACK_ROUNDS))} with their local trigger (scale_weights_poison as configured).  Mean over seeds; the number "
              "in brackets is the spread (max - min) over seeds.\n")
     L.append("Tolerance bands applied below (batch order, dropout-free nets but different sample orders and cuDNN "
              "algorithms make single runs differ; the reference itself is not reproducible run to run):\n"
@@ -248,9 +263,11 @@ if __name__ == "__main__":
     r.add_argument("--test", type=int, default=2000)
     r.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"])
     r.add_argument("--out", default="gpurun_out/parity_own.json")
+    r.add_argument("--set", default="", help="key=value,... overrides of the shipped YAML, applied to both arms")
     o = sub.add_parser("_refone")
     o.add_argument("--agg"); o.add_argument("--seed", type=int); o.add_argument("--rounds", type=int)
     o.add_argument("--train", type=int); o.add_argument("--test", type=int); o.add_argument("--out")
+    o.add_argument("--set", default="")
     p = sub.add_parser("report")
     p.add_argument("files", nargs="+")
     a = ap.parse_args()
