@@ -525,7 +525,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const PoolArgs a) {
   }
 }
 
-int g_bn_fused = 1;
+int g_bn_fused = 0;   // measured slower than reduce + apply (K = 1: 1.65 vs 1.59 ms / step, K = 10: 6.36 vs 5.96)
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_cluster_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, int cluster_x, cudaStream_t st,
@@ -627,11 +627,12 @@ int dba_bn_backward(const void* g, const void* y, const void* act, void* dy, voi
                                ldw, Gflat, ldg, g_off, b_off, nvalid, K, C, B, H, W, R, up, Rup, stream);
 }
 // dy_split (nullable, tf32 mode only): bf16 hi/lo split copy of dy for the weight-gradient kernel.
-int dba_bn_backward_split(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
-                          float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
-                          float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
-                          const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
-                          void* stream) {
+// sums_ready != 0: the sums were accumulated by the convolution that produced g (dba_conv_tc_dgrad_bn): apply only.
+int dba_bn_backward_ex(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
+                       float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
+                       float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
+                       const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
+                       int sums_ready, void* stream) {
   DBA_REQUIRE(K > 0 && C % 8 == 0 && B > 0, "dba_bn_backward: K=%d C=%d B=%d", K, C, B);
   DBA_REQUIRE(!dy_split || g_dba_act_mode == 1, "dba_bn_backward: split copies exist in tf32 mode only");
   BnArgs a{};
@@ -642,7 +643,7 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
   a.stats_off = sums_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.up = up;
   dim3 grid = bn_grid(B, H, W, C, K);
-  if (g_bn_fused) {
+  if (g_bn_fused && !sums_ready) {
     // one cluster per (client, channel plane): as many row blocks as keep ~148 SMs busy, at most 8 (portable size)
     const long long pairs = (long long)(C / act_v()) * K;
     int X = (int)((2 * kNumSMs + pairs - 1) / pairs);
@@ -656,19 +657,28 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
     return DBA_OK;
   }
   if (act_v() == 4) {
-    launch_pdl(bn_bwd_reduce_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
+    if (!sums_ready) launch_pdl(bn_bwd_reduce_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
     launch_pdl(bn_bwd_apply_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
   } else {
-    launch_pdl(bn_bwd_reduce_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
+    if (!sums_ready) launch_pdl(bn_bwd_reduce_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
     launch_pdl(bn_bwd_apply_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
   }
-  DBA_COUNT_LAUNCH(2);
+  DBA_COUNT_LAUNCH(sums_ready ? 1 : 2);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
 }
+int dba_bn_backward_split(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
+                          float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
+                          float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
+                          const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
+                          void* stream) {
+  return dba_bn_backward_ex(g, y, act, dy, dy_split, gmask, sums, ld_sums, sums_off, saved, ld_saved, saved_off, Wflat, ldw,
+                            Gflat, ldg, g_off, b_off, nvalid, K, C, B, H, W, R, up, Rup, 0, stream);
+}
 
-// 1 (default): BatchNorm backward = one cluster launch per layer; 0: the two-kernel form (reduce with atomics into the
-// caller-zeroed `sums` scratch, then apply).  Both produce the same dy; the fused form needs no zeroed scratch.
+// 1: BatchNorm backward = one cluster launch per layer; 0 (default): the two-kernel form (reduce with atomics into the
+// caller-zeroed `sums` scratch, then apply).  Both produce the same dy; the fused form needs no zeroed scratch and is
+// deterministic, but clusters of <= 8 CTAs walk long row slices twice and lose to 64 row blocks x 2 launches.
 void dba_set_bn_fused(int on) { g_bn_fused = on ? 1 : 0; }
 int dba_get_bn_fused() { return g_bn_fused; }
 

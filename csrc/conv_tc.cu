@@ -42,7 +42,17 @@ namespace {
 constexpr int kTileM = 128;
 constexpr int kEpiWarps = 8;                  // two warps per TMEM lane quadrant
 constexpr int kMaxSB = 16;      // weight-stream pipeline depth limit (barrier slots)
-constexpr int kThreads = 64 + 32 * kEpiWarps;
+// Producer warps.  Measured (tools/gpu_bulk_probe.cu): a warp has ONE cp.async.bulk instruction in flight - the next one
+// issues ~500 cycles + ~55 cycles per active lane later, however many pipeline stages are free - so a single producer
+// warp feeds 8 KB weight stages at ~10 B/clk (1 KB rows: 930 cycles per stage against ~300 cycles of MMAs).  Stages are
+// therefore dealt to kProd warps by stage index (stage s belongs to warp s % kProd: one owner per mbarrier, so nobody
+// can run a whole phase ahead of a barrier it waits on).
+constexpr int kProd = 3;
+constexpr int kMmaWarp = kProd;
+constexpr int kEpiWarp0 = kProd + 1;
+constexpr int kEpiThread0 = 32 * kEpiWarp0;
+constexpr int kThreads = kEpiThread0 + 32 * kEpiWarps;
+static_assert(kEpiWarp0 % 4 == 0, "epilogue warp e must sit on TMEM lane quadrant e & 3");
 
 struct ConvArgs {
   // All tensors are addressed in 16-byte chunks ("rows") holding V channels: V = 8 (bf16) or 4 (fp32 / tf32 mode).
@@ -92,6 +102,13 @@ struct ConvArgs {
   int out_s2d;
   int cgrp;                    // out mode 3: channels per parity group (C)
   long long res_client_stride, res_plane_stride;
+  // Input-gradient convolutions whose output g feeds a BatchNorm backward: the epilogue also accumulates that layer's
+  // reduction sums (sum g', sum g' * xhat; g' = g masked by the layer's ReLU) into `stats`, so bn_bwd_reduce is not
+  // launched.  bn_y / bn_act (nullable: no ReLU) have Y's geometry; bn_saved = (mean, rstd) pairs per channel.
+  const uint4* bn_y;
+  const uint4* bn_act;
+  const float* bn_saved;
+  long long bn_saved_stride;
 };
 
 struct Pipe {
@@ -153,10 +170,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   float* ss_s = reinterpret_cast<float*>(tmem_slot + 4);     // [2][NB] scale / shift of the current weight group
-  int* tap_shift = reinterpret_cast<int*>(ss_s + 2 * a.NB);  // [taps] A-view offset of every tap (16-byte units)
+  float* mr_s = ss_s + 2 * a.NB;                             // [2][NB] mean / rstd (BatchNorm-backward sums mode)
+  int* tap_shift = reinterpret_cast<int*>(ss_s + 4 * a.NB);  // [taps] A-view offset of every tap (16-byte units)
 
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + a.taps) {      // per-tap view offsets, computed once
-    const int tap = threadIdx.x - 64;
+  if (threadIdx.x >= kEpiThread0 && threadIdx.x < kEpiThread0 + a.taps) {      // per-tap view offsets, computed once
+    const int tap = threadIdx.x - kEpiThread0;
     int shift = 0;
     if (a.taps > 1) {
       const int th = tap / a.ksz;
@@ -182,7 +200,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     mbar_fence_init();
   }
   pdl_trigger();                                // the next kernel's blocks may be scheduled from now on
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
@@ -197,11 +215,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
   const int item_lo = (int)(items * blockIdx.x / gridDim.x);
   const int item_hi = (int)(items * (blockIdx.x + 1) / gridDim.x);
   const int accCols = a.T * a.NB;               // columns of one accumulator set
-  if (warp == 0) {
-    // ================================================================= producer
-    // The whole warp runs the loop: lane 0 waits for the free stage and posts the expected byte count, then the lanes
-    // issue the stage's bulk copies in parallel (one elected thread issuing 8 one-KB copies per stage was the limit
-    // of every layer whose output channels are split over CTAs: ~100 cycles per copy against 280 cycles of MMAs).
+  if (warp < kProd) {
+    // ================================================================= producers
+    // Every producer warp walks the same sequence of load events and keeps the same pipeline positions, but issues
+    // only the stages it owns (A stage s: warp (kProd - 1 - s) % kProd, B stage s: warp s % kProd; the resident weight
+    // set: warp 0).  Within a stage the lanes issue the bulk copies in parallel, lane 0 waits for the free stage and
+    // posts the byte count.
     {
       Pipe pa, pb;
       int cur_group = -1, wloads = 0;
@@ -213,57 +232,63 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
         const uint4* wk = a.Wt + (long long)k * a.w_client_stride;
         if (a.resident && group != cur_group) {
           cur_group = group;
-          if (lane == 0) {
-            mbar_wait(&b_empty[0], (uint32_t)(wloads & 1) ^ 1u);
-            mbar_arrive_expect_tx(&b_full[0], a.wbytes);
-          }
-          __syncwarp();
-          if (nnb == 1) {
-            if (lane == 0) bulk_g2s(smB, wk, a.wbytes, &b_full[0]);            // [tap][plane][Cout][8] is contiguous
-          } else {
-            for (int tp = lane; tp < a.taps * planes; tp += 32)
-              bulk_g2s(smB + (size_t)tp * pitchB, wk + ((long long)tp * a.Cout + (long long)nb * a.NB), pitchB,
-                       &b_full[0]);
+          if (warp == 0) {
+            if (lane == 0) {
+              mbar_wait(&b_empty[0], (uint32_t)(wloads & 1) ^ 1u);
+              mbar_arrive_expect_tx(&b_full[0], a.wbytes);
+            }
+            __syncwarp();
+            if (nnb == 1) {
+              if (lane == 0) bulk_g2s(smB, wk, a.wbytes, &b_full[0]);            // [tap][plane][Cout][8] is contiguous
+            } else {
+              for (int tp = lane; tp < a.taps * planes; tp += 32)
+                bulk_g2s(smB + (size_t)tp * pitchB, wk + ((long long)tp * a.Cout + (long long)nb * a.NB), pitchB,
+                         &b_full[0]);
+            }
           }
           ++wloads;
         }
         const long long row0 = (long long)a.lead + (long long)pass * a.T * kTileM - a.halo;
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = pa.stage(a.SA);
-          DBG_T0();
-          if (lane == 0) {
-            mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
-            mbar_arrive_expect_tx(&a_full[sa], bytesA);
-          }
-          __syncwarp();
-          DBG_ADD(0);
-          for (int i = lane; i < npar * kc; i += 32) {
-            const int pp = i / kc, c = i - pp * kc;
-            const uint4* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0;
-            bulk_g2s(smA + (size_t)sa * bytesA + (size_t)i * pitchA, src, pitchA, &a_full[sa]);
+          if (warp == (kProd - 1 - sa % kProd)) {
+            DBG_T0();
+            if (lane == 0) {
+              mbar_wait(&a_empty[sa], pa.phase(a.SA) ^ 1u);
+              mbar_arrive_expect_tx(&a_full[sa], bytesA);
+            }
+            __syncwarp();
+            DBG_ADD(0);
+            for (int i = lane; i < npar * kc; i += 32) {
+              const int pp = i / kc, c = i - pp * kc;
+              const uint4* src = xk + (long long)(pp * planes + kb * kc + c) * a.x_plane_stride + row0;
+              bulk_g2s(smA + (size_t)sa * bytesA + (size_t)i * pitchA, src, pitchA, &a_full[sa]);
+            }
           }
           pa.advance(a.SA);
           if (a.resident) continue;
           for (int tap = 0; tap < a.taps; ++tap) {
             const int sb = pb.stage(a.SB);
-            if (lane == 0) {
-              mbar_wait(&b_empty[sb], pb.phase(a.SB) ^ 1u);
-              mbar_arrive_expect_tx(&b_full[sb], bytesB);
-            }
-            __syncwarp();
-            const uint4* wsrc = wk + (((long long)tap * planes + kb * kc) * a.Cout + (long long)nb * a.NB);
-            if (nnb == 1) {
-              if (lane == 0) bulk_g2s(smB + (size_t)sb * bytesB, wsrc, bytesB, &b_full[sb]);   // kc planes contiguous
-            } else if (lane < kc) {
-              bulk_g2s(smB + (size_t)sb * bytesB + (size_t)lane * pitchB, wsrc + (long long)lane * a.Cout, pitchB,
-                       &b_full[sb]);
+            if (warp == sb % kProd) {
+              if (lane == 0) {
+                mbar_wait(&b_empty[sb], pb.phase(a.SB) ^ 1u);
+                mbar_arrive_expect_tx(&b_full[sb], bytesB);
+              }
+              __syncwarp();
+              const uint4* wsrc = wk + (((long long)tap * planes + kb * kc) * a.Cout + (long long)nb * a.NB);
+              if (nnb == 1) {
+                if (lane == 0) bulk_g2s(smB + (size_t)sb * bytesB, wsrc, bytesB, &b_full[sb]);   // kc planes contiguous
+              } else if (lane < kc) {
+                bulk_g2s(smB + (size_t)sb * bytesB + (size_t)lane * pitchB, wsrc + (long long)lane * a.Cout, pitchB,
+                         &b_full[sb]);
+              }
             }
             pb.advance(a.SB);
           }
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // =============================================================== MMA issuer
     if (elect_one()) {
       Pipe pa, pb, pacc;
@@ -333,7 +358,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     // ================================================================= epilogue
     // 8 warps: warps e and e+4 share TMEM lane quadrant (e & 3) and split the pass' tiles (or, for single-tile
     // passes, its 32-channel groups) between them - with one warp per scheduler the epilogue is latency-bound.
-    const int ew = warp - 2;
+    const int ew = warp - kEpiWarp0;
     const int q = warp & 3;                       // TMEM lane quadrant this warp may access
     const int half = ew >> 2;                     // 0 / 1
     Pipe pacc;
@@ -349,7 +374,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       const int nb_ = grp % nnb, k_ = grp / nnb;
       float* g = a.stats + (long long)k_ * a.stats_stride + (long long)nb_ * a.NB * 2;
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      for (int i = threadIdx.x - 64; i < 2 * a.NB; i += 32 * kEpiWarps) {
+      for (int i = threadIdx.x - kEpiThread0; i < 2 * a.NB; i += 32 * kEpiWarps) {
         const float v = ss_s[i];
         if (v != 0.f) { atomicAdd(g + i, v); ss_s[i] = 0.f; }
       }
@@ -363,11 +388,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       if (group != cur_group) {
         if (a.stats && cur_group >= 0) flush_stats(cur_group);
         cur_group = group;
+        if (a.bn_y) {     // mean / rstd of the consuming BatchNorm layer for this (client, n-block)
+          const float* sv_ = a.bn_saved + (long long)k * a.bn_saved_stride + 2 * nb * a.NB;
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          for (int i = threadIdx.x - kEpiThread0; i < a.NB; i += 32 * kEpiWarps) {
+            mr_s[i] = sv_[2 * i];
+            mr_s[a.NB + i] = sv_[2 * i + 1];
+          }
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
         if (affine) {     // per-channel scale / shift of this (client, n-block) -> shared memory
           const float* gsc = a.scale ? a.scale + (long long)k * a.ss_stride + nb * a.NB : nullptr;
           const float* gsh = a.shift + (long long)k * a.ss_stride + nb * a.NB;
           asm volatile("bar.sync 1, 256;" ::: "memory");
-          for (int i = threadIdx.x - 64; i < a.NB; i += 32 * kEpiWarps) {
+          for (int i = threadIdx.x - kEpiThread0; i < a.NB; i += 32 * kEpiWarps) {
             ss_s[i] = gsc ? gsc[i] : 1.f;
             ss_s[a.NB + i] = gsh[i];
           }
@@ -412,6 +446,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
       tc_fence_after();
       uint4* yk = a.Y + (long long)k * a.y_client_stride;
       const uint4* rk = a.Res ? a.Res + (long long)k * a.res_client_stride : nullptr;
+      const uint4* bnyk = a.bn_y ? a.bn_y + (long long)k * a.y_client_stride : nullptr;
+      const uint4* bnak = a.bn_act ? a.bn_act + (long long)k * a.y_client_stride : nullptr;
       const bool gs = a.stats != nullptr;
       for (int c0 = c_first; c0 < a.NB; c0 += c_step) {
         // u1/u2 hold scale/shift (evaluation epilogue) or the running sum / sum of squares (training epilogue);
@@ -480,8 +516,25 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
               // statistics of the value as stored (bf16-rounded in bf16 mode), so BatchNorm normalises exactly what
               // it reads
               chunk_unpack<V>(pk, f);
+              if (bnyk) {       // sums of the BatchNorm backward that consumes this gradient
+                float yv[V];
+                chunk_unpack<V>(bnyk[obase + g * a.y_plane_stride], yv);
+                if (bnak) {
+                  float av[V];
+                  chunk_unpack<V>(bnak[obase + g * a.y_plane_stride], av);
 #pragma unroll
-              for (int j = 0; j < V; ++j) { u1[g * V + j] += f[j]; u2[g * V + j] += f[j] * f[j]; }
+                  for (int j = 0; j < V; ++j) f[j] = av[j] > 0.f ? f[j] : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < V; ++j) {
+                  const int c = c0 + g * V + j;
+                  u1[g * V + j] += f[j];
+                  u2[g * V + j] += f[j] * (yv[j] - mr_s[c]) * mr_s[a.NB + c];
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < V; ++j) { u1[g * V + j] += f[j]; u2[g * V + j] += f[j] * f[j]; }
+              }
             }
           }
         }
@@ -502,14 +555,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
     }
     if (a.stats && cur_group >= 0) flush_stats(cur_group);
   }
-  if (a.dbg && lane == 0 && warp <= 2) {      // [cta][role 0..2][4]; slot 3 = the role's whole lifetime
+  if (a.dbg && lane == 0 && (warp == kProd - 1 || warp == kMmaWarp || warp == kEpiWarp0)) {
+    // [cta][role 0..2][4]; slot 3 = the role's whole lifetime (producer = the warp that owns A stage 0)
+    const int role = warp == kProd - 1 ? 0 : warp == kMmaWarp ? 1 : 2;
     dbgacc[3] = clock64() - dbg_start;
-    for (int i = 0; i < 4; ++i) a.dbg[((long long)blockIdx.x * 3 + warp) * 4 + i] = dbgacc[i];
+    for (int i = 0; i < 4; ++i) a.dbg[((long long)blockIdx.x * 3 + role) * 4 + i] = dbgacc[i];
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
@@ -543,10 +598,18 @@ long long dba_conv_rows(int B, int H, int W) {
 // in_s2d / out_s2d: space-to-depth forms for stride-2 convolutions (see ConvArgs).  With in_s2d, (H, W) is the
 // OUTPUT grid of the stride-2 convolution (the grid X' lives on), X' has 4*Cin channels and sub must be 1.  With
 // out_s2d, Y gets 4*Cout channels on the (H/2, W/2) grid; Res (if any) stays a plain (H, W) tensor.
+struct ConvBnBwd {              // host-side description of the BatchNorm-backward sums mode (see ConvArgs::bn_y)
+  const void* y;
+  const void* act;
+  const float* saved;
+  long long saved_stride;
+};
+
 static int conv_launch(const void* X, const void* Wt, long long w_client_stride, void* Y, const void* Res,
                        const float* scale, const float* shift, long long ss_stride, float* stats,
                        long long stats_stride, int K, int B, int H, int W, int Cin, int Cout, int ksize, int sub,
-                       int relu, int x_shared, int in_s2d, int out_s2d, int vlo, int vhi, void* stream) {
+                       int relu, int x_shared, int in_s2d, int out_s2d, int vlo, int vhi, void* stream,
+                       const ConvBnBwd* bb = nullptr) {
   DBA_REQUIRE(K > 0 && B > 0 && H > 0 && W > 0, "dba_conv_tc: bad sizes K=%d B=%d H=%d W=%d", K, B, H, W);
   DBA_REQUIRE(ksize == 1 || ksize == 3 || ksize == 5 || (ksize == 2 && out_s2d == 3),
               "dba_conv_tc: ksize must be 1, 3 or 5 (2 with out mode 3), got %d", ksize);
@@ -592,6 +655,12 @@ static int conv_launch(const void* X, const void* Wt, long long w_client_stride,
   a.halo = ksize == 2 ? a.Wp + 1 : (ksize / 2) * (a.Wp + 1);
   a.ksz = ksize;
   a.vlo = vlo; a.vhi = vhi > 0 ? vhi : (H > W ? H : W);
+  if (bb) {
+    DBA_REQUIRE(stats && bb->y && bb->saved && sub == 1 && !in_s2d && !out_s2d && !shift && !relu,
+                "dba_conv_tc: the BatchNorm-backward sums mode is for plain stride-1 input-gradient convolutions");
+    a.bn_y = (const uint4*)bb->y; a.bn_act = (const uint4*)bb->act; a.bn_saved = bb->saved;
+    a.bn_saved_stride = bb->saved_stride;
+  }
   const int kc = a.KB / V;
   const long long body = (long long)B * a.S;
   // n-block and rows per pass: as many 128-row tiles as fit in TMEM (512 columns); when that leaves SMs idle, first
@@ -619,7 +688,7 @@ static int conv_launch(const void* X, const void* Wt, long long w_client_stride,
     a.T = T; a.NB = NB;
     a.rowsA = T * kTileM + (npar == 4 ? 1 : 2) * a.halo;      // parity-plane taps only reach up / left
     const size_t bytesA = (size_t)npar * kc * a.rowsA * 16, bytesB = (size_t)kc * NB * 16;
-    const size_t misc = 1024 + 2 * NB * sizeof(float) + 128;
+    const size_t misc = 1024 + 4 * NB * sizeof(float) + 128;
     a.NS = (2 * T * NB <= 512) ? 2 : 1;
     a.wbytes = (unsigned int)((size_t)a.taps * (Cin / V) * NB * 16);
     a.resident = a.wbytes <= 100 * 1024 && 2 * bytesA + a.wbytes + misc <= budget;
@@ -633,6 +702,7 @@ static int conv_launch(const void* X, const void* Wt, long long w_client_stride,
       const int sb_cap = kMaxSB;
       long long sb = budget > 2 * bytesA + misc ? (long long)((budget - 2 * bytesA - misc) / bytesB) : 0;
       a.SB = sb > sb_cap ? sb_cap : (int)sb;
+      if (a.SB >= kProd) a.SB -= a.SB % kProd;          // stages are dealt to the producer warps round-robin
       if (a.SB < 2) a.SB = 2;
       breg = a.SB * bytesB;
     }
@@ -706,6 +776,19 @@ int dba_conv_tc_strided(const void* X, const void* Wt, long long w_client_stride
                         int relu, int x_shared, void* stream) {
   return dba_conv_tc_ex(X, Wt, w_client_stride, Y, Res, scale, shift, ss_stride, stats, stats_stride, K, B, H, W, Cin,
                         Cout, ksize, sub, relu, x_shared, 0, 0, stream);
+}
+
+// Input-gradient convolution (same operands as dba_conv_tc_strided without affine / ReLU / sub-sampling) that ALSO
+// accumulates the reduction sums of the BatchNorm backward consuming its output g = conv(dY, Wt) (+ Res):
+//   sums[k][2c] += sum g',  sums[k][2c + 1] += sum g' * (bn_y - mean_c) * rstd_c,  g' = bn_act > 0 ? g : 0 (bn_act may be
+// null: no ReLU).  bn_y / bn_act have the output's geometry; saved = (mean, rstd) pairs of that layer, row stride
+// ld_saved; sums must be zero on entry.  dba_bn_backward_split(..., sums_ready = 1) then skips its reduce kernel.
+int dba_conv_tc_dgrad_bn(const void* dY, const void* Wt, long long w_client_stride, void* G, const void* Res,
+                         const void* bn_y, const void* bn_act, const float* saved, long long ld_saved, float* sums,
+                         long long ld_sums, int K, int B, int H, int W, int Cin, int Cout, int ksize, void* stream) {
+  const ConvBnBwd bb{bn_y, bn_act, saved, ld_saved};
+  return conv_launch(dY, Wt, w_client_stride, G, Res, nullptr, nullptr, 0, sums, ld_sums, K, B, H, W, Cin, Cout, ksize, 1,
+                     0, 0, 0, 0, 0, 0, stream, &bb);
 }
 
 // Dense-stride convenience form: Wt [K][taps][Cin/8][Cout][8], scale/shift [K][Cout], stats [K][Cout][2].

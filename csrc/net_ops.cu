@@ -38,8 +38,8 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
   // forward pack: one thread per (tap, ciV, co) 16-byte group
   const long long nf = (long long)ptaps * cinV * CoutP;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nf; i += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(i % cinV);
-    const int co = (int)((i / cinV) % CoutP);
+    const int co = (int)(i % CoutP);                    // out channel fastest: consecutive threads store consecutive chunks
+    const int cv = (int)((i / CoutP) % cinV);
     const int tap = (int)(i / ((long long)cinV * CoutP));
     float v[V];
 #pragma unroll
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 extern "C" int dba_pack_weights(const float* W, long long ldw, const int* table, int n_layers, int K, void* dst,
                                 long long dst_client_stride, void* stream) {
   DBA_REQUIRE(n_layers > 0 && K > 0, "dba_pack_weights: n_layers=%d K=%d", n_layers, K);
-  dim3 g(32, n_layers, K);
+  dim3 g(K >= 8 ? 32 : 128, n_layers, K);     // few clients: the widest layers (147k chunks each way) need the blocks
   // dst_client_stride counts elements (bf16 or fp32) of the caller's pack tensor
   if (g_dba_act_mode == 1) {
     DBA_REQUIRE(dst_client_stride % 4 == 0, "dba_pack_weights: client stride %lld %% 4", dst_client_stride);

@@ -52,6 +52,12 @@ struct WgArgs {
   // s2d: X is the space-to-depth form (4*Cin channels, parity-major, on dY's grid) of a 3x3 stride-2 convolution's input;
   // tap (dh, dw) reads parity plane (dh != 1, dw != 1) shifted by (dh == 0 ? -1 : 0, dw == 0 ? -1 : 0).
   int s2d;
+  // vs = 3 ("vertical stack", 3x3 convolutions with Cout <= 32): the M = 128 rows of the A operand hold THREE copies of
+  // the 32 output channels, copy dh loaded from dY shifted by -(dh - 1) image rows, so one MMA per horizontal tap dw
+  // (a +-1 row shift of the X view) yields the gradients of the three taps (dh, dw) in TMEM lanes 32*dh + co:
+  // 3 MMAs per k-step instead of 9.  (M cannot be smaller than 128 without halving the tensor rate, and the A fetch of
+  // 4 KB per MMA is what bounds the narrow layers - so the idle 96 rows are given work.)
+  int vs;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -132,20 +138,24 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       const __nv_bfloat16* dyk = a.dY + (long long)k * a.dy_client + (long long)(mb * 16) * a.dy_plane;
       const __nv_bfloat16* xk = a.X + (long long)k * a.x_client + (long long)(nbk * nplanes) * a.x_plane;
       for (int ch = c0; ch < c1; ++ch) {
+        const int mslots = a.vs ? a.vs * mreal : mreal;          // A planes filled per operand set
         if (lane == 0) {
           mbar_wait(&empty[st], ph ^ 1u);
-          mbar_arrive_expect_tx(&full[st], NSET * (uint32_t)mreal * pitchA + bytesB);
+          mbar_arrive_expect_tx(&full[st], NSET * (uint32_t)mslots * pitchA + bytesB);
         }
         __syncwarp();
         const long long row = (long long)a.lead + (long long)ch * kRowsK;
-        const int per_set = mreal + npar * nplanes;
+        const int per_set = mslots + npar * nplanes;
         for (int pp = lane; pp < NSET * per_set; pp += 32) {
           const int set = pp >= per_set ? 1 : 0, p = pp - set * per_set;           // 0 = hi (or the only) set, 1 = lo
-          if (p < mreal) {
-            bulk_g2s(smA + (size_t)st * bytesA + (size_t)set * setA + (size_t)p * pitchA,
-                     dyk + (long long)set * a.dy_lo + (long long)p * a.dy_plane + row * 8, pitchA, &full[st]);
+          if (p < mslots) {
+            const int dh = a.vs ? p / mreal : 1, pl = a.vs ? p - dh * mreal : p;   // copy dh: dY rows shifted by -(dh-1)*Wp
+            const int slot = a.vs ? dh * 4 + pl : p;               // copy dh starts at row 32*dh of the A operand
+            bulk_g2s(smA + (size_t)st * bytesA + (size_t)set * setA + (size_t)slot * pitchA,
+                     dyk + (long long)set * a.dy_lo + (long long)pl * a.dy_plane + (row - (long long)(dh - 1) * a.Wp) * 8,
+                     pitchA, &full[st]);
           } else {
-            const int q = p - mreal, par = q / nplanes, j = q - par * nplanes;       // parity group, plane inside it
+            const int q = p - mslots, par = q / nplanes, j = q - par * nplanes;      // parity group, plane inside it
             bulk_g2s(smB + (size_t)st * bytesB + (size_t)set * setB + (size_t)q * pitchB,
                      xk + (long long)set * a.x_lo + ((long long)par * (a.Cin >> 3) + j) * a.x_plane + (row - a.halo) * 8,
                      pitchB, &full[st]);
@@ -177,7 +187,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
           const uint64_t dB0 = umma_desc_noswz(smem_u32(smB + (size_t)s * bytesB), 128, pitchB) + (uint64_t)a.halo;
           const uint32_t acc0 = ch != c0 ? 1u : 0u;
           for (int tap = t0; tap < t1; ++tap) {
-            const int shift = tap_shift[tap];
+            const int shift = a.vs ? tap - 1 : tap_shift[tap];       // vs: "tap" = horizontal tap dw, all dh at once
             const uint32_t d_tmem = tmem_base + (uint32_t)((tap - t0) * a.N);
             const uint64_t dB1 = dB0 + (uint64_t)(int64_t)shift;
             umma_f16(d_tmem, dA0, dB1, idesc, acc0);
@@ -219,13 +229,17 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       const bool vec = ((a.cin_real | a.w_off) & 3) == 0 && (a.ldg & 3) == 0 && a.npos == 0;
       if (c1 > c0) {
         for (int tap = t0; tap < t1; ++tap) {
-          float* dst = gk + ((long long)co * a.taps + tap) * a.cin_real + nbk * a.N;
+          // vs: lane quadrant q holds vertical tap dh = q (rows 32*dh + co), accumulator `tap` is horizontal tap dw
+          const int cow = a.vs ? lane : co;
+          const int tapw = a.vs ? q * 3 + tap : tap;
+          if (a.vs && q >= a.vs) break;
+          float* dst = gk + ((long long)cow * a.taps + tapw) * a.cin_real + nbk * a.N;
           const int cin_left = a.cin_real - nbk * a.N;
           for (int n0 = 0; n0 < a.N; n0 += 16) {
             uint32_t v[16];
             tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tap - t0) * a.N + n0), v);
             tmem_ld_wait();
-            if (co < a.cout_real) {
+            if (cow < a.cout_real) {
               if (vec) {
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
@@ -270,6 +284,9 @@ extern "C" {
 // (R = dba_conv_rows(B,H,W)).  Adds the weight gradient of a ksize x ksize convolution (ksize 1 or 3, pad ksize/2) into
 // G[k*ldg + w_off + (co*taps + tap)*cin_real + ci] for co < cout_real, ci < cin_real (the gradient slab is zeroed by
 // the caller once per step).  Cin / Cout are the padded channel counts of the planar buffers.
+static int g_wgrad_vstack = 1;
+void dba_set_wgrad_vstack(int on) { g_wgrad_vstack = on ? 1 : 0; }     // A/B switch (tests compare both forms)
+
 static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, int w_off, int K, int B, int H, int W,
                         int Cin, int Cout, int cin_real, int cout_real, int ksize, int cgrp_pad, int cgrp_real,
                         int npos, void* stream, long long x_client_stride = 0, int s2d = 0) {
@@ -305,6 +322,9 @@ static int wgrad_launch(const void* dY, const void* X, float* G, long long ldg, 
   if (a.tpg > a.taps) a.tpg = a.taps;
   a.ngroups = (a.taps + a.tpg - 1) / a.tpg;
   a.tpg = (a.taps + a.ngroups - 1) / a.ngroups;            // balance the groups (e.g. 9 taps, 4 max -> 3+3+3)
+  // vertical stack (see WgArgs::vs): three shifted copies of <= 32 output channels fill the 128 rows of A
+  a.vs = (g_wgrad_vstack && ksize == 3 && !s2d && npos == 0 && Cout <= 32 && 3 * a.N <= 512) ? 3 : 0;
+  if (a.vs) { a.tpg = 3; a.ngroups = 1; }
   const int base_items = K * a.nmb * a.ngroups * a.nnblk;
   int nsplit = (2 * kNumSMs + base_items - 1) / base_items;
   if (nsplit > a.body_chunks) nsplit = a.body_chunks;

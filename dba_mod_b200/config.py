@@ -108,6 +108,8 @@ _DEFAULTS: Dict[str, Any] = {
     "native_s2d": True,           # stride-2 convolutions from space-to-depth operands (output pixels only)
     "nvls": "auto",               # fused collectives through NVSwitch multicast (multimem): auto = from 4 ranks on
     "overlap_wgrad": True,        # weight-gradient kernels on a side stream / parallel graph branch
+    "fuse_bn_sums": False,        # BatchNorm-backward sums in the epilogue of the producing input-gradient convolution
+                                  # (measured SLOWER: the epilogue's extra loads cost more than the reduce kernel)
     "prewarm": True,              # allocate slabs / capture step graphs for every batch width at start-up
     "compact_tail": True,         # clients that finished their local steps stop being computed (native trainer)
 }

@@ -14,6 +14,8 @@ so a forward pass is 20 convolution launches + input stage + head for ALL models
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -78,6 +80,13 @@ class NativeResNet(LockStepTrainer):
         self.eval_chunk = int(params.get("native_eval_chunk", 500))
         self.overlap_wgrad = bool(params.get("overlap_wgrad", True)) and device.type == "cuda"
         self._side = torch.cuda.Stream(device=device) if self.overlap_wgrad else None
+        # BatchNorm-backward reduction sums accumulated in the epilogue of the input-gradient convolution that produces
+        # the gradient (13 of the 20 layers of the CIFAR net: the stride-2 space-to-depth blocks keep the reduce kernel)
+        # Off by default: measured slower (K = 1: 1.57 vs 1.49 ms / step, K = 10: 6.78 vs 5.93) - the two extra 16-byte
+        # loads per stored chunk sit on the epilogue's dependent chain and cost more than the reduce kernel they save.
+        self.fuse_bn_sums = (bool(params.get("fuse_bn_sums", False)) or os.environ.get("DBA_FUSE_BN_SUMS") == "1") \
+            and os.environ.get("DBA_FUSE_BN_SUMS") != "0"
+        self._sums_ready = set()
         self._eval_bufs: Dict[Tuple[int, int], dict] = {}
         d = data
         self.trig_u8 = d.trigger_masks.to(torch.uint8).contiguous()
@@ -503,13 +512,14 @@ class NativeResNet(LockStepTrainer):
         e = self.spec.entries
         r = l.H // l.sub
         Gr = t["Gr"]
-        native.check(self.lib.dba_bn_backward_split(
+        ready = l.name in self._sums_ready        # accumulated by the convolution that produced g (see _dgrad)
+        native.check(self.lib.dba_bn_backward_ex(
             native.ptr(g), native.ptr(y), native.ptr(act), native.ptr(dy), native.ptr(t["split_of"].get(dy.data_ptr())),
             native.ptr(gmask), native.ptr(t["sums"]),
             t["sums"].stride(0), 2 * l.bn_off, native.ptr(t["saved"]), t["saved"].stride(0), 2 * l.bn_off,
             native.ptr(W), W.stride(0), native.ptr(Gr), Gr.stride(0), e[l.bn + ".weight"].offset,
             e[l.bn + ".bias"].offset, native.ptr(nvalid), K, l.cout_p, self.B, r, r, y.shape[2], int(up),
-            dy.shape[2], native.stream()))
+            dy.shape[2], int(ready), native.stream()))
 
     def _wgrad(self, l: ConvL, K, dy, x, t, s2d=False):
         Gr = t["Gr"]
@@ -544,8 +554,20 @@ class NativeResNet(LockStepTrainer):
         with torch.cuda.stream(self._side):
             launch()
 
-    def _dgrad(self, l: ConvL, K, dy, pack, out, res=None):
+    def _dgrad(self, l: ConvL, K, dy, pack, out, res=None, bn=None, t=None):
+        """Input gradient of layer l.  bn = (layer, y, act): the BatchNorm whose backward consumes ``out``; its
+        reduction sums are then accumulated in this convolution's epilogue (no bn_bwd_reduce launch for that layer)."""
         wt = self._wt(pack, l, transposed=True)
+        if bn is not None and self.fuse_bn_sums:
+            bl, by, ba = bn
+            sums, saved = t["sums"], t["saved"]
+            native.check(self.lib.dba_conv_tc_dgrad_bn(
+                native.ptr(dy), native.ptr(wt), pack.stride(0), native.ptr(out), native.ptr(res), native.ptr(by),
+                native.ptr(ba), native.ptr(saved[:, 2 * bl.bn_off:]), saved.stride(0),
+                native.ptr(sums[:, 2 * bl.bn_off:]), sums.stride(0), K, self.B, l.H, l.H, l.cout_p, l.cin_p, l.ks,
+                native.stream()))
+            self._sums_ready.add(bl.name)
+            return out
         native.check(self.lib.dba_conv_tc_strided(
             native.ptr(dy), native.ptr(wt), pack.stride(0), native.ptr(out), native.ptr(res), None, None, 0, None, 0,
             K, self.B, l.H, l.H, l.cout_p, l.cin_p, l.ks, 1, 0, 0, native.stream()))
@@ -564,8 +586,9 @@ class NativeResNet(LockStepTrainer):
         lv_g = {r: t[("g", r)] for r in self.ress}
         pack = self.pack_weights(W, t["pack"])
         t["stats"].zero_(); Gr.zero_()
-        if not lib.dba_get_bn_fused():          # only the two-kernel BatchNorm backward accumulates into scratch
+        if not lib.dba_get_bn_fused() or self.fuse_bn_sums:     # scratch of the BatchNorm-backward reduction sums
             t["sums"].zero_()
+        self._sums_ready = set()
         native.check(lib.dba_input_stage_image_split(
             native.ptr(d.train_x), native.ptr(d.train_y), native.ptr(t["st_idx"]), t["st_idx"].stride(0),
             native.ptr(self.trig_u8), native.ptr(t["trig_row"]), native.ptr(t["poison_n"]),
@@ -626,9 +649,15 @@ class NativeResNet(LockStepTrainer):
             pool_o = [b for b in lv_g[r_out] if b is not g]
             dz, da1 = pool_o[0], pool_o[1]
             dy2, dy1 = t[("dy", c2.name)], t[("dy", c1.name)]
+            # the BatchNorm that will consume this block's input gradient: the previous block's bn2 (or the stem's)
+            if bi > 0:
+                c2p = self.blocks[bi - 1][1]
+                cons = (c2p, t[("y", c2p.name)], t[("a", c2p.name)])
+            else:
+                cons = None if self.pool else (stem, y0, a0)
             self._bn_bwd(c2, K, g, t[("y", c2.name)], t[("a", c2.name)], dy2, dz, W, t, nvalid, up=False)
             self._wgrad(c2, K, dy2, t[("a", c1.name)], t)
-            self._dgrad(c2, K, dy2, pack, da1)
+            self._dgrad(c2, K, dy2, pack, da1, bn=(c1, t[("y", c1.name)], t[("a", c1.name)]), t=t)
             xs = t.get(("s2d", bi)) if c1.d2s else None
             self._bn_bwd(c1, K, da1, t[("y", c1.name)], t[("a", c1.name)], dy1, None, W, t, nvalid,
                          up=(c1.sub == 2 and xs is None))
@@ -639,7 +668,7 @@ class NativeResNet(LockStepTrainer):
             pool_i = [b for b in lv_g[r_in] if b is not g and b is not dz and b is not da1]
             dx = pool_i[0]
             if sc is None:
-                self._dgrad(c1, K, dy1, pack, dx, res=dz)
+                self._dgrad(c1, K, dy1, pack, dx, res=dz, bn=cons, t=t)
             else:
                 dx2 = pool_i[1]
                 dys = t[("dy", sc.name)]
@@ -664,7 +693,7 @@ class NativeResNet(LockStepTrainer):
                     self._dgrad(c1, K, dy1, pack, dx2)
                     self._bn_bwd(sc, K, dz, t[("y", sc.name)], None, dys, None, W, t, nvalid, up=True)
                     self._wgrad(sc, K, dys, xin_b, t)
-                    self._dgrad(sc, K, dys, pack, dx, res=dx2)
+                    self._dgrad(sc, K, dys, pack, dx, res=dx2, bn=cons, t=t)
             g = dx
         if self.pool:
             native.check(lib.dba_maxpool_bwd(native.ptr(a0), native.ptr(g), native.ptr(t["pool_g"]), K, self.widths[0], B,

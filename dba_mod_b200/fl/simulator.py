@@ -373,6 +373,8 @@ class Simulator:
             self.ckpt_writer.save_model(self.state_dict(), epoch, rep.poison_loss if p["is_poison"] else rep.global_loss)
             self.recorder.save_result_csv(epoch, p["is_poison"], self.folder_path)
             self.metrics.flush()
+        else:
+            self.recorder.flush_scale_row()
         rep.seconds = time.time() - t0
         logger.info(f"Done in {rep.seconds} sec.")
         return rep

@@ -51,6 +51,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_set_pdl", [I], None)
     _sig(lib, "dba_get_pdl", [], c_int)
     _sig(lib, "dba_set_bn_fused", [I], None)
+    _sig(lib, "dba_set_wgrad_vstack", [I], None)
     _sig(lib, "dba_get_bn_fused", [], c_int)
     _sig(lib, "dba_set_act_dtype", [I])
     _sig(lib, "dba_get_act_dtype", [], c_int)
@@ -89,6 +90,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_bn_apply_split", [P, P, P, P, L, P, P, P, L, I, P, L, I, P, L, I, I, I, I, P, P, I, I, I, I, I, L, I, F, F,
                                      P])
     _sig(lib, "dba_bn_backward_split", [P, P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
+    _sig(lib, "dba_bn_backward_ex", [P, P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, I, P])
+    _sig(lib, "dba_conv_tc_dgrad_bn", [P, P, L, P, P, P, P, P, L, P, L, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_maxpool_fwd_split", [P, P, P, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_input_stage_image_split", [P, P, P, L, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_bn_backward", [P, P, P, P, P, P, L, I, P, L, I, P, L, P, L, I, I, P, I, I, I, I, I, L, I, L, P])
@@ -108,7 +111,9 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_loan_eval", [P, L, I, P, P, P, L, P, P, I, P, P, P])
     if os.environ.get("DBA_PDL") is not None:      # A/B switch for programmatic dependent launch (default: on)
         lib.dba_set_pdl(int(os.environ["DBA_PDL"]))
-    if os.environ.get("DBA_BN_FUSED") is not None:  # A/B switch: cluster-fused BatchNorm backward (default: on)
+    if os.environ.get("DBA_WGRAD_VSTACK") is not None:   # A/B switch: tap-stacked weight gradient of the 32-channel layers
+        lib.dba_set_wgrad_vstack(int(os.environ["DBA_WGRAD_VSTACK"]))
+    if os.environ.get("DBA_BN_FUSED") is not None:  # A/B switch: cluster-fused BatchNorm backward (default: off)
         lib.dba_set_bn_fused(int(os.environ["DBA_BN_FUSED"]))
     _LIB = lib
     return lib

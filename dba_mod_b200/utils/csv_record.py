@@ -59,6 +59,15 @@ class Recorder:
         if len(self.scale_temp_one_row) > 0:
             self.scale_temp_one_row.append(round(float(global_acc), 4))
 
+    def flush_scale_row(self) -> bool:
+        """Move the round's pending scale row into ``scale_result`` (the reference does this inside save_result_csv,
+        utils/csv_record.py:52-56); also called by runs that keep the records in memory only."""
+        if len(self.scale_temp_one_row) == 0:
+            return False
+        self.scale_result.append(copy.deepcopy(self.scale_temp_one_row))
+        self.scale_temp_one_row.clear()
+        return True
+
     # -- writer -----------------------------------------------------------------------------------------------
     def save_result_csv(self, epoch: int, is_poison: bool, folder_path: str) -> None:
         def _write(name, header, rows):
@@ -72,9 +81,7 @@ class Recorder:
         _write("test_result.csv", TEST_HEADER, self.test_result)
         if len(self.weight_result) > 0:
             _write("weight_result.csv", None, self.weight_result)
-        if len(self.scale_temp_one_row) > 0:
-            self.scale_result.append(copy.deepcopy(self.scale_temp_one_row))
-            self.scale_temp_one_row.clear()
+        if self.flush_scale_row():
             _write("scale_result.csv", None, self.scale_result)
         if is_poison:
             _write("posiontest_result.csv", TEST_HEADER, self.posiontest_result)

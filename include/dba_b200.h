@@ -183,6 +183,20 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
                           float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
                           const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
                           void* stream);
+/* Same with sums_ready: non-zero = the reduction sums were accumulated by the convolution that produced g
+ * (dba_conv_tc_dgrad_bn), only the apply kernel runs. */
+int dba_bn_backward_ex(const void* g, const void* y, const void* act, void* dy, void* dy_split, void* gmask,
+                       float* sums, long long ld_sums, int sums_off, float* saved, long long ld_saved, int saved_off,
+                       float* Wflat, long long ldw, float* Gflat, long long ldg, int g_off, int b_off,
+                       const int* nvalid, int K, int C, int B, int H, int W, long long R, int up, long long Rup,
+                       int sums_ready, void* stream);
+/* Input-gradient convolution G = conv(dY, Wt) (+ Res) whose epilogue also accumulates the BatchNorm-backward sums of
+ * the layer consuming G (sum g', sum g' * xhat with g' = bn_act > 0 ? g : 0) into sums[k][2c], sums[k][2c + 1]; saved =
+ * that layer's (mean, rstd) pairs.  Pointers sums / saved are already offset to the layer.  Reference counterpart:
+ * cuDNN's BatchNorm backward inside autograd (image_train.py:91,209). */
+int dba_conv_tc_dgrad_bn(const void* dY, const void* Wt, long long w_client_stride, void* G, const void* Res,
+                         const void* bn_y, const void* bn_act, const float* saved, long long ld_saved, float* sums,
+                         long long ld_sums, int K, int B, int H, int W, int Cin, int Cout, int ksize, void* stream);
 int dba_maxpool_fwd_split(const void* x, void* y, void* y_split, int K, int C, int B, int H, int W, long long Rin,
                           long long Rout, void* stream);
 int dba_input_stage_image_split(const void* data, const long long* labels, const long long* idx, long long ld_idx,
@@ -198,8 +212,10 @@ int dba_set_act_dtype(int mode);
  * run their prologue, while its predecessor drains.  No counterpart in the reference. */
 void dba_set_pdl(int on);
 int dba_get_pdl(void);
-/* BatchNorm backward as one thread-block-cluster launch per layer (default on; partial sums exchanged through
- * distributed shared memory, `sums` scratch unused) or as reduce + apply kernels (0; `sums` must be zeroed). */
+/* BatchNorm backward as one thread-block-cluster launch per layer (1; partial sums exchanged through distributed
+ * shared memory, deterministic, `sums` scratch unused) or as reduce + apply kernels (0, default - measured faster;
+ * `sums` must be zeroed by the caller). */
+void dba_set_wgrad_vstack(int on);   /* 3x3 weight gradients with Cout <= 32: three vertical taps stacked along M (default on) */
 void dba_set_bn_fused(int on);
 int dba_get_bn_fused(void);
 int dba_get_act_dtype(void);

@@ -62,6 +62,45 @@ def test_conv_eval_epilogue_and_shared_input(native_lib, act):
     torch.testing.assert_close(got, ref, rtol=act.rtol, atol=1.5 * act.atol)
 
 
+@pytest.mark.parametrize("K,B,H,Cin,Cout,with_act,with_res", [(2, 3, 8, 32, 32, True, False), (1, 5, 4, 256, 256, True, True),
+                                                              (2, 4, 16, 64, 64, False, True), (1, 64, 32, 32, 32, True, True)])
+def test_dgrad_epilogue_accumulates_batchnorm_backward_sums(native_lib, act, K, B, H, Cin, Cout, with_act, with_res):
+    """dba_conv_tc_dgrad_bn: g = conv(dY, Wt) (+ Res) as usual, and sums[k][c] = (sum g', sum g' * xhat) of the BatchNorm
+    that consumes g (g' = g where the layer's ReLU output is > 0), compared against the same sums formed from the
+    kernel's own stored g."""
+    from dba_mod_b200.ops import layout, native
+    lib = native.load()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(7)
+    d = torch.device("cuda", 0)
+    x = torch.randn(K, B, Cin, H, H, device=d)
+    w = torch.randn(K, Cout, Cin, 3, 3, device=d) / (Cin * 9) ** 0.5
+    res = torch.randn(K, B, Cout, H, H, device=d) if with_res else None
+    bny = torch.randn(K, B, Cout, H, H, device=d) * 1.3 + 0.2
+    bna = F.relu(torch.randn(K, B, Cout, H, H, device=d)) if with_act else None
+    saved = torch.stack([torch.randn(K, Cout, device=d) * 0.3, torch.rand(K, Cout, device=d) + 0.5], -1).contiguous()
+    sums = torch.zeros(K, Cout, 2, device=d)
+    xp, wp = layout.to_planar(x, dtype=act.dtype), layout.pack_conv_weight(w, dtype=act.dtype)
+    rp = layout.to_planar(res, dtype=act.dtype) if with_res else None
+    yp = layout.to_planar(bny, dtype=act.dtype)
+    ap = layout.to_planar(bna, dtype=act.dtype) if with_act else None
+    out = torch.zeros(K, Cout // act.V, layout.Geom(B, H, H).rows, act.V, dtype=act.dtype, device=d)
+    native.set_act_dtype(act.name)
+    native.check(lib.dba_conv_tc_dgrad_bn(native.ptr(xp), native.ptr(wp), wp[0].numel(), native.ptr(out), native.ptr(rp),
+                                          native.ptr(yp), native.ptr(ap), native.ptr(saved), saved.stride(0),
+                                          native.ptr(sums), sums.stride(0), K, B, H, H, Cin, Cout, 3, native.stream()))
+    torch.cuda.synchronize()
+    got = layout.from_planar(out, B, H, H)
+    ref = _ref(x, w, 3, 1, act) + (act.store(res) if with_res else 0)
+    torch.testing.assert_close(got, ref, rtol=act.rtol, atol=1.5 * act.atol)
+    ys = layout.from_planar(yp, B, H, H)
+    gm = got * (layout.from_planar(ap, B, H, H) > 0) if with_act else got
+    mean, rstd = saved[..., 0][:, None, :, None, None], saved[..., 1][:, None, :, None, None]
+    torch.testing.assert_close(sums[..., 0], gm.sum(dim=(1, 3, 4)), rtol=2e-3, atol=2e-2)
+    torch.testing.assert_close(sums[..., 1], (gm * (ys - mean) * rstd).sum(dim=(1, 3, 4)), rtol=2e-3, atol=5e-2)
+    assert layout.halo_is_zero(out, B, H, H)
+
+
 def test_conv_stats(native_lib, act):
     from dba_mod_b200.ops import conv, layout
     torch.manual_seed(2)

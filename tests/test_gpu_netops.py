@@ -35,7 +35,9 @@ def _wgrad_operand(x, act):
 # ----------------------------------------------------------------------------------------------- weight gradient
 WG_SHAPES = [  # K, B, H, Cin, Cout, ksize, cin_real
     (2, 5, 8, 64, 128, 3, 64),
-    (1, 3, 32, 32, 32, 3, 32),
+    (1, 3, 32, 32, 32, 3, 32),           # Cout <= 32, 3x3: three vertical taps stacked along M (and the plain form)
+    (2, 9, 8, 64, 32, 3, 64),
+    (1, 5, 16, 32, 24, 3, 20),           # ragged real channel counts inside the padded planes
     (2, 64, 32, 32, 32, 1, 27),          # CIFAR stem as a folded 1x1 convolution over 27 (padded to 32) columns
     (1, 4, 4, 256, 256, 3, 256),
     (1, 3, 2, 512, 512, 3, 512),
@@ -44,10 +46,14 @@ WG_SHAPES = [  # K, B, H, Cin, Cout, ksize, cin_real
 ]
 
 
+@pytest.mark.parametrize("vstack", [1, 0], ids=["vstack", "plain"])
 @pytest.mark.parametrize("K,B,H,Cin,Cout,ks,cin_real", WG_SHAPES)
-def test_wgrad_matches_autograd(native_lib, act, K, B, H, Cin, Cout, ks, cin_real):
+def test_wgrad_matches_autograd(native_lib, act, K, B, H, Cin, Cout, ks, cin_real, vstack):
     from dba_mod_b200.ops import native
     lib = native.load()
+    if vstack == 0 and not (ks == 3 and Cout <= 32):
+        pytest.skip("the stacked form only exists for 3x3 layers with Cout <= 32")
+    lib.dba_set_wgrad_vstack(vstack)
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(0)
     # bf16 mode: operands are bf16 values; tf32 mode: arbitrary fp32 values carried as bf16 hi + lo (16 mantissa bits)
@@ -64,9 +70,12 @@ def test_wgrad_matches_autograd(native_lib, act, K, B, H, Cin, Cout, ks, cin_rea
     ld = (Cout * ks * ks * cin_real + 3) // 4 * 4 + 8
     G = torch.zeros(K, ld, device=DEV)
     dyp, xp = _wgrad_operand(dy, act), _wgrad_operand(x, act)      # keep the operands alive across the launch
-    native.check(lib.dba_wgrad_tc(native.ptr(dyp), native.ptr(xp), native.ptr(G), G.stride(0), 4, K, B, H, H, Cin, Cout,
-                                  cin_real, Cout, ks, native.stream()))
-    torch.cuda.synchronize()
+    try:
+        native.check(lib.dba_wgrad_tc(native.ptr(dyp), native.ptr(xp), native.ptr(G), G.stride(0), 4, K, B, H, H, Cin, Cout,
+                                      cin_real, Cout, ks, native.stream()))
+        torch.cuda.synchronize()
+    finally:
+        lib.dba_set_wgrad_vstack(1)
     got = G[:, 4:4 + Cout * ks * ks * cin_real].view(K, Cout, ks, ks, cin_real).permute(0, 1, 4, 2, 3)
     scale = ref.abs().max().item()
     tol = dict(rtol=1e-4, atol=2e-5 * scale) if act.name == "tf32" else dict(rtol=act.rtol, atol=act.atol * scale)

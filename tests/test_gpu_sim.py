@@ -52,13 +52,19 @@ def test_mnist_rounds_native_backend(native_lib):
     from dba_mod_b200.fl.simulator import Simulator
     raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "mnist_params.yaml")))
     raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=6000, synthetic_test_size=1000,
-               number_of_total_participants=20, adversary_list=[3, 7, 11, 15], internal_epochs=2, epochs=5, eta=1.0,
-               scale_weights_poison=5,
+               number_of_total_participants=20, adversary_list=[3, 7, 11, 15], internal_epochs=4, epochs=5, eta=1.0,
+               lr=0.05, batch_size=32, scale_weights_poison=5,
                **{"0_poison_epochs": [5], "1_poison_epochs": [5], "2_poison_epochs": [99], "3_poison_epochs": [99]})
     sim = Simulator(Params(raw), device=torch.device("cuda", 0), quiet=True, write_files=False)
     assert sim.backend.name == "cuda" and sim.backend.native_train and sim.backend.native_eval
     reps = sim.run()
     sim.close()
+    # the fp32 torch backend on this configuration: loss 2.30 -> 1.79 -> 1.18 -> 0.34, accuracy 11 -> 90 %, then the
+    # attack round: backdoor accuracy 0.9 -> 100 %  (with the shipped lr / batch / 2 epochs nothing is learnt in 4
+    # rounds from a random initialisation, by either backend)
     assert len(reps) == 5 and all(r.global_loss == r.global_loss for r in reps)
-    assert reps[3].global_loss < reps[0].global_loss - 0.02, [r.global_loss for r in reps]
+    # (native vs torch backend on the same GPU, three seeds: tools/gpu_mnist_compare.py, profiles/r2/mnist_compare.txt;
+    # single runs wobble - atomics and sample order - so the band is on the best of the benign rounds)
+    assert min(r.global_loss for r in reps[1:4]) < reps[0].global_loss - 0.6, [r.global_loss for r in reps]
+    assert max(r.global_acc for r in reps[1:4]) > 45.0, [r.global_acc for r in reps]
     assert reps[4].poison_acc > reps[3].poison_acc + 30.0, [r.poison_acc for r in reps]

@@ -39,8 +39,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 
 constexpr int kMaxStages = 16;
 
-__global__ void __launch_bounds__(64, 1) probe(const char* src, long long src_bytes, int piece, int stage_bytes, int stages,
-                                               long long total, long long* cycles) {
+// mode 0: one producer warp, ring of `stages` (full / empty mbarriers per stage)           [conv_tc's scheme]
+// mode 1: one barrier, expect_tx(total) once, every copy issued back to back, one wait      [what the copy engine can do]
+// mode 2: like 0, but stage s is produced by warp s % nprod (nprod producer warps)
+// mode 3: like 0, but the free-stage wait / expect_tx of stage it+1 is issued BEFORE the copies of stage it
+__global__ void __launch_bounds__(192, 1) probe(const char* src, long long src_bytes, int piece, int stage_bytes, int stages,
+                                                long long total, long long* cycles, int mode, int nprod) {
   extern __shared__ __align__(128) char smem[];
   __shared__ uint64_t full[kMaxStages], empty[kMaxStages];
   if (threadIdx.x == 0) {
@@ -51,24 +55,49 @@ __global__ void __launch_bounds__(64, 1) probe(const char* src, long long src_by
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_stage = (int)(total / stage_bytes), per = stage_bytes / piece;
   const long long t0 = clock64();
-  if (warp == 0) {
-    long long off = (long long)blockIdx.x * 4096 % src_bytes;
-    for (int it = 0; it < n_stage; ++it) {
+  const long long span = (long long)stage_bytes * 3;
+  const long long wrap = (src_bytes - 2 * span) / span;       // stages before the source offset wraps
+  if (mode == 1) {
+    if (warp == 0) {
+      if (lane == 0) mbar_expect(&full[0], (uint32_t)total);
+      __syncwarp();
+      for (int it = 0; it < n_stage; ++it) {
+        const long long off = (long long)(it % wrap) * span;
+        const int s = it % stages;
+        for (int i = lane; i < per; i += 32)
+          bulk_g2s(smem + (size_t)s * stage_bytes + (size_t)i * piece, src + off + (long long)i * piece * 3, (uint32_t)piece,
+                   &full[0]);
+      }
+      if (lane == 0) mbar_wait(&full[0], 0);
+    }
+  } else if (warp < nprod) {
+    const int first = mode == 2 ? warp : 0, step = mode == 2 ? nprod : 1;
+    if (mode == 3 && lane == 0) { mbar_wait(&empty[0], 1u); mbar_expect(&full[0], (uint32_t)stage_bytes); }
+    for (int it = first; it < n_stage; it += step) {
       const int s = it % stages;
       const uint32_t ph = (uint32_t)(it / stages) & 1u;
-      if (lane == 0) {
-        mbar_wait(&empty[s], ph ^ 1u);
-        mbar_expect(&full[s], (uint32_t)stage_bytes);
+      if (mode != 3) {
+        if (lane == 0) {
+          mbar_wait(&empty[s], ph ^ 1u);
+          mbar_expect(&full[s], (uint32_t)stage_bytes);
+        }
+        __syncwarp();
       }
-      __syncwarp();
-      for (int i = lane; i < per; i += 32) {
-        const long long o = off + (long long)i * piece * 3;  // pieces are strided in global memory (like n-block rows)
-        bulk_g2s(smem + (size_t)s * stage_bytes + (size_t)i * piece, src + o, (uint32_t)piece, &full[s]);
+      const long long off = (long long)(it % wrap) * span;
+      for (int i = lane; i < per; i += 32)
+        bulk_g2s(smem + (size_t)s * stage_bytes + (size_t)i * piece, src + off + (long long)i * piece * 3, (uint32_t)piece,
+                 &full[s]);
+      if (mode == 3) {
+        const int it2 = it + 1;
+        if (it2 < n_stage && lane == 0) {
+          const int s2 = it2 % stages;
+          mbar_wait(&empty[s2], ((uint32_t)(it2 / stages) & 1u) ^ 1u);
+          mbar_expect(&full[s2], (uint32_t)stage_bytes);
+        }
+        __syncwarp();
       }
-      off += (long long)stage_bytes * 3;
-      if (off + (long long)stage_bytes * 6 > src_bytes) off = 0;
     }
-  } else if (lane == 0) {
+  } else if (warp == 5 && lane == 0) {
     for (int it = 0; it < n_stage; ++it) {
       const int s = it % stages;
       const uint32_t ph = (uint32_t)(it / stages) & 1u;
@@ -88,34 +117,38 @@ int main() {
   CK(cudaMemset(src, 1, src_bytes));
   CK(cudaMalloc(&cyc, 148 * sizeof(long long)));
   CK(cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  const long long total = 2LL << 20;           // bytes streamed per CTA
-  printf("%6s %7s %7s %7s | %10s %12s %10s\n", "grid", "piece", "stageB", "stages", "cyc/req", "B/clk/SM", "us");
-  const int grids[] = {1, 52, 148};
-  const int pieces[] = {512, 1024, 2048, 4096, 8192, 16384, 32768};
-  for (int g : grids) {
-    for (int piece : pieces) {
+  printf("%5s %6s %5s %7s %7s %6s | %9s %10s %9s %8s\n", "mode", "nprod", "grid", "piece", "stageB", "stages", "cyc/req",
+         "cyc/stage", "B/clk/SM", "us");
+  struct Cfg { int mode, nprod; };
+  const Cfg cfgs[] = {{0, 1}, {1, 1}, {2, 2}, {2, 4}, {3, 1}};
+  const int grids[] = {1, 148};
+  const int pieces[] = {1024, 8192};
+  for (const Cfg& c : cfgs) {
+    for (int g : grids) {
       for (int stage_bytes : {8192, 32768}) {
-        if (stage_bytes < piece) continue;
-        for (int stages : {4, 6}) {
-          if ((long long)stages * stage_bytes > 196 * 1024) continue;
-          long long h[148];
-          cudaEvent_t e0, e1;
-          CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-          for (int rep = 0; rep < 2; ++rep) {
-            CK(cudaEventRecord(e0));
-            probe<<<g, 64, stages * stage_bytes>>>(src, src_bytes, piece, stage_bytes, stages, total, cyc);
-            CK(cudaEventRecord(e1));
-            CK(cudaDeviceSynchronize());
+        for (int piece : pieces) {
+          if (stage_bytes < piece) continue;
+          for (int stages : {4, 6}) {
+            const long long total = c.mode == 1 ? (512LL << 10) : (2LL << 20);   // tx-count limit of one barrier: 2^20 - 1
+            long long h[148];
+            cudaEvent_t e0, e1;
+            CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+            for (int rep = 0; rep < 2; ++rep) {
+              CK(cudaEventRecord(e0));
+              probe<<<g, 192, stages * stage_bytes>>>(src, src_bytes, piece, stage_bytes, stages, total, cyc, c.mode, c.nprod);
+              CK(cudaEventRecord(e1));
+              CK(cudaDeviceSynchronize());
+            }
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            CK(cudaMemcpy(h, cyc, g * sizeof(long long), cudaMemcpyDeviceToHost));
+            long long mx = 0;
+            for (int i = 0; i < g; ++i) mx = h[i] > mx ? h[i] : mx;
+            const double reqs = (double)total / piece, nst = (double)total / stage_bytes;
+            printf("%5d %6d %5d %7d %7d %6d | %9.1f %10.1f %9.1f %8.1f\n", c.mode, c.nprod, g, piece, stage_bytes, stages,
+                   mx / reqs, mx / nst, (double)total / mx, ms * 1000.0);
+            CK(cudaEventDestroy(e0)); CK(cudaEventDestroy(e1));
           }
-          float ms = 0;
-          CK(cudaEventElapsedTime(&ms, e0, e1));
-          CK(cudaMemcpy(h, cyc, g * sizeof(long long), cudaMemcpyDeviceToHost));
-          long long mx = 0;
-          for (int i = 0; i < g; ++i) mx = h[i] > mx ? h[i] : mx;
-          const double reqs = (double)total / piece;
-          printf("%6d %7d %7d %7d | %10.1f %12.1f %10.1f\n", g, piece, stage_bytes, stages, mx / reqs, (double)total / mx,
-                 ms * 1000.0);
-          CK(cudaEventDestroy(e0)); CK(cudaEventDestroy(e1));
         }
       }
     }
