@@ -55,7 +55,7 @@ def run_own(agg, seed, a):
     from dba_mod_b200.parallel.launcher import make_comm
     raw = params_for(agg, a.rounds, a.train, a.test, a.set)
     raw.update(synthetic_data=True, synthetic_train_size=a.train, synthetic_test_size=a.test,
-               synthetic_seed=1234 + seed, seed=1 + seed, compute_dtype=a.dtype)
+               synthetic_seed=1234 + seed, seed=a.fixed_seed if a.fixed_seed >= 0 else 1 + seed, compute_dtype=a.dtype)
     comm = make_comm()
     sim = Simulator(Params(raw), comm=comm, quiet=True, write_files=False)
     reps = sim.run()
@@ -320,6 +320,9 @@ if __name__ == "__main__":
     r.add_argument("--dtype", default="tf32", choices=["tf32", "bf16"])
     r.add_argument("--out", default="gpurun_out/parity_own.json")
     r.add_argument("--set", default="", help="key=value,... overrides of the shipped YAML, applied to both arms")
+    r.add_argument("--fixed-seed", type=int, default=-1, dest="fixed_seed",
+                   help="own arm: use this seed for partition / selection / batch order in every run (the reference "
+                        "hard-codes seed 1, so its runs differ by data set only; -1 = 1 + s)")
     o = sub.add_parser("_refone")
     o.add_argument("--agg"); o.add_argument("--seed", type=int); o.add_argument("--rounds", type=int)
     o.add_argument("--train", type=int); o.add_argument("--test", type=int); o.add_argument("--out")
@@ -335,6 +338,7 @@ if __name__ == "__main__":
     sw.add_argument("--test", type=int, default=2000)
     sw.add_argument("--dtype", default="tf32")
     sw.add_argument("--outdir", default="gpurun_out")
+    sw.add_argument("--fixed-seed", type=int, default=-1, dest="fixed_seed")
     tj = sub.add_parser("traj", help="per-run accuracy / ASR trajectories of result files, one line per run")
     tj.add_argument("files", nargs="+")
     a = ap.parse_args()
