@@ -48,8 +48,8 @@ def data_label(p) -> str:
 
 
 def dtype_label(p, be, cuda: bool) -> str:
-    """Compute dtype of the native executor that actually ran (LOAN is an fp32 CUDA-core MLP, MnistNet's executor is
-    bf16-only, the ResNets follow compute_dtype)."""
+    """Compute dtype of the native executor that actually ran (LOAN is an fp32 CUDA-core MLP, the image networks
+    follow compute_dtype)."""
     if not cuda:
         return "fp32"
     ex = getattr(be, "exec", None)

@@ -38,6 +38,54 @@ extern "C" void dba_add_launch_count(unsigned long long n) { DBA_COUNT_LAUNCH(n)
 
 using namespace dba;
 
+// ------------------------------------------------------------------------------------------ lock-step staging
+// One launch per training step instead of six indexed copies: row r of the step's slab receives the schedule entries
+// (sample indices, flip flags, valid count, active flag, log slot, learning rate) of client rows[r] (or r) at `step`.
+struct StageArgs {
+  const long long* idx;        // [K][T][B]
+  const unsigned char* flip;   // [K][T][B] or null
+  const int* nvalid;           // [K][T]
+  const unsigned char* active; // [K][T]
+  const long long* slot;       // [K][T]
+  const float* lr;             // [K][T]
+  const long long* rows;       // [n] or null
+  long long* st_idx;           // [n][B]
+  unsigned char* st_flip;      // [n][B] or null
+  int* st_nvalid;
+  unsigned char* st_active;
+  long long* st_slot;
+  float* st_lr;
+  int T, B, step;
+};
+__global__ void __launch_bounds__(128) stage_step_kernel(const StageArgs a) {
+  const int r = blockIdx.x;
+  const long long k = a.rows ? a.rows[r] : r;
+  const long long e = k * a.T + a.step;
+  for (int b = threadIdx.x; b < a.B; b += blockDim.x) {
+    a.st_idx[(long long)r * a.B + b] = a.idx[e * a.B + b];
+    if (a.st_flip) a.st_flip[(long long)r * a.B + b] = a.flip[e * a.B + b];
+  }
+  if (threadIdx.x == 0) {
+    a.st_nvalid[r] = a.nvalid[e];
+    a.st_active[r] = a.active[e];
+    a.st_slot[r] = a.slot[e];
+    a.st_lr[r] = a.lr[e];
+  }
+}
+extern "C" int dba_stage_step(const long long* idx, const unsigned char* flip, const int* nvalid,
+                              const unsigned char* active, const long long* slot, const float* lr,
+                              const long long* rows, int n, int T, int B, int step, long long* st_idx,
+                              unsigned char* st_flip, int* st_nvalid, unsigned char* st_active, long long* st_slot,
+                              float* st_lr, void* stream) {
+  DBA_REQUIRE(n > 0 && T > 0 && B > 0 && step >= 0 && step < T, "dba_stage_step: n=%d T=%d B=%d step=%d", n, T, B, step);
+  DBA_REQUIRE((flip == nullptr) == (st_flip == nullptr), "dba_stage_step: flip / st_flip must be given together");
+  StageArgs a{idx, flip, nvalid, active, slot, lr, rows, st_idx, st_flip, st_nvalid, st_active, st_slot, st_lr, T, B, step};
+  stage_step_kernel<<<n, 128, 0, (cudaStream_t)stream>>>(a);
+  DBA_COUNT_LAUNCH(1);
+  DBA_CHECK_LAUNCH();
+  return DBA_OK;
+}
+
 static inline int grid_for(long long work_items, int block, int max_waves = 8) {
   long long g = (work_items + block - 1) / block;
   long long cap = (long long)kNumSMs * max_waves;

@@ -160,14 +160,26 @@ class LockStepTrainer:
             return x[:, step] if rows is None else x[rows, step]
 
         n = K if rows is None else int(rows.numel())
+        ps = per_step
+        native_stage = ps["idx"].is_cuda and all(ps[k].is_contiguous() for k in ("idx", "nvalid", "active", "slot", "lr")) \
+            and (not with_flip or ps["flip"].is_contiguous())
+        T, B = int(ps["idx"].shape[1]), int(ps["idx"].shape[2])
         for step in range(lo, hi):
-            t["st_idx"][:n].copy_(pick(per_step["idx"], step))
-            t["st_nvalid"][:n].copy_(pick(per_step["nvalid"], step))
-            t["st_active"][:n].copy_(pick(per_step["active"], step))
-            t["st_slot"][:n].copy_(pick(per_step["slot"], step))
-            t["st_lr"][:n].copy_(pick(per_step["lr"], step))
-            if with_flip:
-                t["st_flip"][:n].copy_(pick(per_step["flip"], step))
+            if native_stage:          # one launch instead of six indexed copies
+                native.check(self.lib.dba_stage_step(
+                    native.ptr(ps["idx"]), native.ptr(ps["flip"]) if with_flip else None, native.ptr(ps["nvalid"]),
+                    native.ptr(ps["active"]), native.ptr(ps["slot"]), native.ptr(ps["lr"]), native.ptr(rows), n, T, B,
+                    step, native.ptr(t["st_idx"]), native.ptr(t["st_flip"]) if with_flip else None,
+                    native.ptr(t["st_nvalid"]), native.ptr(t["st_active"]), native.ptr(t["st_slot"]),
+                    native.ptr(t["st_lr"]), native.stream()))
+            else:
+                t["st_idx"][:n].copy_(pick(ps["idx"], step))
+                t["st_nvalid"][:n].copy_(pick(ps["nvalid"], step))
+                t["st_active"][:n].copy_(pick(ps["active"], step))
+                t["st_slot"][:n].copy_(pick(ps["slot"], step))
+                t["st_lr"][:n].copy_(pick(ps["lr"], step))
+                if with_flip:
+                    t["st_flip"][:n].copy_(pick(ps["flip"], step))
             self._replay(K, t, flags, use_graph)
 
     def _replay(self, K: int, t: dict, flags: tuple, use_graph: bool = True) -> None:

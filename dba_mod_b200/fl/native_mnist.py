@@ -36,7 +36,8 @@ class NativeMnist(LockStepTrainer):
             raise ImportError("NativeMnist covers the MNIST network only")
         self.params, self.spec, self.data, self.device = params, spec, data, device
         self.lib = native.load()
-        self.compute_dtype = "bf16"        # the MnistNet pooling kernels (csrc/mnist_ops.cu) exist in bf16 only
+        self.compute_dtype = str(params.get("compute_dtype", "tf32"))
+        self.adt, self.V = native.act_layout(self.compute_dtype)      # activation dtype, channels per 16-byte chunk
         self.B = int(params["batch_size"])
         self.label_swap = int(params["poison_label_swap"])
         self.mu, self.wd = float(params["momentum"]), float(params["decay"])
@@ -46,7 +47,7 @@ class NativeMnist(LockStepTrainer):
         self.supports_dist_loss = True
         e = spec.entries
         self.e = e
-        # pack layout (bf16 elements per client)
+        # pack layout (elements per client, bf16 or fp32)
         self.o1 = 0                                   # conv1 folded [1][32/8][32][8]
         self.o2 = self.o1 + 32 * 32                   # conv2 [25][32/8][64][8]
         self.o2t = self.o2 + 25 * 32 * 64             # conv2 transposed [25][64/8][32][8]
@@ -68,24 +69,37 @@ class NativeMnist(LockStepTrainer):
         self.boff = (0, 32, 96)
         self.trig_u8 = data.trigger_masks.to(torch.uint8).contiguous()
         self._train_bufs: Dict[int, dict] = {}
-        self._eval_bufs: Dict[Tuple[int, int], dict] = {}
+        self._eval_bufs: Dict[int, tuple] = {}
 
     # ------------------------------------------------------------------------------------------ helpers
     def _zbuf(self, K: int, C_: int, g: Geom, slack_rows: int = 0) -> torch.Tensor:
-        """Planar-8 zero buffer [K, C/8, R, 8]; slack_rows zero rows before the first and after the last plane (the
+        """Planar zero buffer [K, C/V, R, V]; slack_rows zero rows before the first and after the last plane (the
         5x5 operand blocks reach 2*(W+1)+2 rows beyond a pass, see dba_conv_tc_valid)."""
-        n = K * (C_ // 8) * g.rows * 8
+        V = self.V
+        n = K * (C_ // V) * g.rows * V
+        pad = slack_rows * V
+        base = torch.zeros(n + 2 * pad, dtype=self.adt, device=self.device)
+        v = base[pad:pad + n].view(K, C_ // V, g.rows, V)
+        v._dba_base = base          # keep the allocation alive
+        return v
+
+    def _zsplit(self, K: int, C_: int, g: Geom, slack_rows: int = 0):
+        """tf32 mode: the bf16 hi/lo split copy [K, 2, C/8, R, 8] of a tensor the weight-gradient kernel reads
+        (None in bf16 mode, where the tensor itself is the operand)."""
+        if self.compute_dtype != "tf32":
+            return None
+        n = K * 2 * (C_ // 8) * g.rows * 8
         pad = slack_rows * 8
         base = torch.zeros(n + 2 * pad, dtype=torch.bfloat16, device=self.device)
-        v = base[pad:pad + n].view(K, C_ // 8, g.rows, 8)
-        v._dba_base = base          # keep the allocation alive
+        v = base[pad:pad + n].view(K, 2, C_ // 8, g.rows, 8)
+        v._dba_base = base
         return v
 
     def pack_weights(self, W: torch.Tensor, out=None) -> torch.Tensor:
         self._enter()
         K = W.shape[0]
         if out is None:
-            out = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=self.device)
+            out = torch.zeros(K, self.pack_elems, dtype=self.adt, device=self.device)
         native.check(self.lib.dba_pack_weights(native.ptr(W), W.stride(0), native.ptr(self.pack_table), 3, K,
                                                native.ptr(out), out.stride(0), native.stream()))
         return out
@@ -111,17 +125,18 @@ class NativeMnist(LockStepTrainer):
         """Input stage ... fc1 activations into t['h'] (shared by training and evaluation)."""
         lib, d = self.lib, self.data
         g24, g12, g1 = self._geoms(B)
-        native.check(lib.dba_input_stage_image(
+        native.check(lib.dba_input_stage_image_split(
             native.ptr(d_x), native.ptr(d_y), native.ptr(idx), ld_idx, native.ptr(self.trig_u8), native.ptr(trow),
-            native.ptr(pn), native.ptr(flip) if flip is not None else None, native.ptr(t["xin"]), native.ptr(labels),
+            native.ptr(pn), native.ptr(flip) if flip is not None else None, native.ptr(t["xin"]),
+            native.ptr(t.get("xin_s")), native.ptr(labels),
             K, B, d.H, d.W, d.C, 5, 1, 0, 24, 24, 32, self.label_swap, g24.rows, native.stream()))
         self._conv(t["xin"], pack, self.o1, bias, self.boff[0], K, B, 24, 32, 32, 1, t["a1"], True, w_shared=w_shared)
-        native.check(lib.dba_maxpool2_fwd(native.ptr(t["a1"]), native.ptr(t["p1"]), K, 32, B, 24, 24, 0, 12, 12, 0,
-                                          g24.rows, g12.rows, native.stream()))
+        native.check(lib.dba_maxpool2_fwd_split(native.ptr(t["a1"]), native.ptr(t["p1"]), native.ptr(t.get("p1_s")), K,
+                                                32, B, 24, 24, 0, 12, 12, 0, g24.rows, g12.rows, native.stream()))
         self._conv(t["p1"], pack, self.o2, bias, self.boff[1], K, B, 12, 32, 64, 5, t["a2"], True, 2, 10,
                    w_shared=w_shared)
-        native.check(lib.dba_maxpool2_fwd(native.ptr(t["a2"]), native.ptr(t["f"]), K, 64, B, 12, 12, 2, 4, 4, 1,
-                                          g12.rows, g1.rows, native.stream()))
+        native.check(lib.dba_maxpool2_fwd_split(native.ptr(t["a2"]), native.ptr(t["f"]), native.ptr(t.get("f_s")), K,
+                                                64, B, 12, 12, 2, 4, 4, 1, g12.rows, g1.rows, native.stream()))
         self._conv(t["f"], pack, self.o3, bias, self.boff[2], K, B, 1, 1024, 512, 1, t["h"], True, w_shared=w_shared)
 
     def _act_bufs(self, K: int, B: int, train: bool) -> dict:
@@ -134,7 +149,16 @@ class NativeMnist(LockStepTrainer):
             t.update({"dh": self._zbuf(K, 512, g1), "dz3": self._zbuf(K, 512, g1), "df": self._zbuf(K, 1024, g1),
                       "dz2": self._zbuf(K, 64, g12, g12.Wp + 2), "dp1": self._zbuf(K, 32, g12),
                       "dz1": self._zbuf(K, 32, g24)})
+            # tf32 mode: split copies of the weight-gradient operands (None in bf16 mode)
+            t.update({"xin_s": self._zsplit(K, 32, g24), "p1_s": self._zsplit(K, 32, g12, g12.Wp + 2),
+                      "f_s": self._zsplit(K, 1024, g1), "dz3_s": self._zsplit(K, 512, g1),
+                      "dz2_s": self._zsplit(K, 64, g12, g12.Wp + 2), "dz1_s": self._zsplit(K, 32, g24)})
         return t
+
+    def _wop(self, t: dict, name: str) -> torch.Tensor:
+        """Weight-gradient operand form of tensor ``name``: the tensor itself (bf16 mode) or its split copy (tf32)."""
+        s = t.get(name + "_s")
+        return s if s is not None else t[name]
 
     # ---------------------------------------------------------------------------------------- evaluation
     @staticmethod
@@ -161,10 +185,15 @@ class NativeMnist(LockStepTrainer):
             if not w_shared:
                 models = models[torch.tensor(order, device=dev)]
         pack = self.pack_weights(models)
-        key = (J, Bt)
-        if key not in self._eval_bufs:
-            self._eval_bufs[key] = self._act_bufs(J, Bt, train=False)
-        t = self._eval_bufs[key]
+        # one set of activation buffers per pass size, with room for the largest job list seen so far (an attack round
+        # adds backdoor / per-trigger evaluations: allocating a new set per job count put 0.1 s of torch.zeros into that
+        # round); the kernels address rows [0, Js) only
+        ent = self._eval_bufs.get(Bt)
+        if ent is None or ent[0] < J:
+            cap = max(J, 24 if ent is None else 2 * ent[0])
+            ent = (cap, self._act_bufs(cap, Bt, train=False))
+            self._eval_bufs[Bt] = ent
+        t = ent[1]
         Mw = models.shape[0]
         bias = self._bias(models, t["bias"][:Mw])
         nmax = max(ns) if ns else 0
@@ -215,7 +244,7 @@ class NativeMnist(LockStepTrainer):
         dev, B, sp = self.device, self.B, self.spec
         t = self._act_bufs(K, B, train=True)
         ld = (sp.Dp + 3) // 4 * 4
-        t["pack"] = torch.zeros(K, self.pack_elems, dtype=torch.bfloat16, device=dev)
+        t["pack"] = torch.zeros(K, self.pack_elems, dtype=self.adt, device=dev)
         for key in ("Gr", "V", "gs", "anchor"):
             t[key] = torch.zeros(K, ld, device=dev)
         t["W"] = torch.zeros(K, (sp.Df + 3) // 4 * 4, device=dev)
@@ -255,25 +284,26 @@ class NativeMnist(LockStepTrainer):
                                   native.ptr(t["mf"]), native.ptr(t["mi"]), t["mf"].shape[1], native.ptr(t["nan"]), K, B,
                                   500, 512, 1, 1, 10, g1.rows, native.stream()))
         # fc1
-        native.check(lib.dba_relu_bwd_bias(native.ptr(t["dh"]), native.ptr(t["h"]), native.ptr(t["dz3"]),
-                                           native.ptr(Gr), ldg, e["fc1.bias"].offset, 500, K, 512, B, 1, 1, g1.rows,
-                                           native.stream()))
-        native.check(lib.dba_wgrad_linear_chw(native.ptr(t["dz3"]), native.ptr(t["f"]), native.ptr(Gr), ldg,
-                                              e["fc1.weight"].offset, K, B, 512, 500, 64, 50, 16, native.stream()))
+        native.check(lib.dba_relu_bwd_bias_split(native.ptr(t["dh"]), native.ptr(t["h"]), native.ptr(t["dz3"]),
+                                                 native.ptr(t.get("dz3_s")), native.ptr(Gr), ldg, e["fc1.bias"].offset,
+                                                 500, K, 512, B, 1, 1, g1.rows, native.stream()))
+        native.check(lib.dba_wgrad_linear_chw(native.ptr(self._wop(t, "dz3")), native.ptr(self._wop(t, "f")),
+                                              native.ptr(Gr), ldg, e["fc1.weight"].offset, K, B, 512, 500, 64, 50, 16,
+                                              native.stream()))
         self._conv(t["dz3"], pack, self.o3t, None, 0, K, B, 1, 512, 1024, 1, t["df"], False)
         # pool2 + conv2
-        native.check(lib.dba_maxpool2_bwd_relu_bias(native.ptr(t["df"]), native.ptr(t["a2"]), native.ptr(t["dz2"]),
-                                                    native.ptr(Gr), ldg, e["conv2.bias"].offset, 50, K, 64, B, 12, 12,
-                                                    2, 4, 4, 1, g12.rows, g1.rows, native.stream()))
-        native.check(lib.dba_wgrad_tc(native.ptr(t["dz2"]), native.ptr(t["p1"]), native.ptr(Gr), ldg,
-                                      e["conv2.weight"].offset, K, B, 12, 12, 32, 64, 20, 50, 5, native.stream()))
+        native.check(lib.dba_maxpool2_bwd_relu_bias_split(
+            native.ptr(t["df"]), native.ptr(t["a2"]), native.ptr(t["dz2"]), native.ptr(t.get("dz2_s")), native.ptr(Gr),
+            ldg, e["conv2.bias"].offset, 50, K, 64, B, 12, 12, 2, 4, 4, 1, g12.rows, g1.rows, native.stream()))
+        native.check(lib.dba_wgrad_tc(native.ptr(self._wop(t, "dz2")), native.ptr(self._wop(t, "p1")), native.ptr(Gr),
+                                      ldg, e["conv2.weight"].offset, K, B, 12, 12, 32, 64, 20, 50, 5, native.stream()))
         self._conv(t["dz2"], pack, self.o2t, None, 0, K, B, 12, 64, 32, 5, t["dp1"], False)
         # pool1 + conv1
-        native.check(lib.dba_maxpool2_bwd_relu_bias(native.ptr(t["dp1"]), native.ptr(t["a1"]), native.ptr(t["dz1"]),
-                                                    native.ptr(Gr), ldg, e["conv1.bias"].offset, 20, K, 32, B, 24, 24,
-                                                    0, 12, 12, 0, g24.rows, g12.rows, native.stream()))
-        native.check(lib.dba_wgrad_tc(native.ptr(t["dz1"]), native.ptr(t["xin"]), native.ptr(Gr), ldg,
-                                      e["conv1.weight"].offset, K, B, 24, 24, 32, 32, 25, 20, 1, native.stream()))
+        native.check(lib.dba_maxpool2_bwd_relu_bias_split(
+            native.ptr(t["dp1"]), native.ptr(t["a1"]), native.ptr(t["dz1"]), native.ptr(t.get("dz1_s")), native.ptr(Gr),
+            ldg, e["conv1.bias"].offset, 20, K, 32, B, 24, 24, 0, 12, 12, 0, g24.rows, g12.rows, native.stream()))
+        native.check(lib.dba_wgrad_tc(native.ptr(self._wop(t, "dz1")), native.ptr(self._wop(t, "xin")), native.ptr(Gr),
+                                      ldg, e["conv1.weight"].offset, K, B, 24, 24, 32, 32, 25, 20, 1, native.stream()))
         if use_dist:   # K11: distance-regularised poison loss (image_train.py:87-90)
             sc = t["dist_scratch"]
             native.check(lib.dba_rows_sqdist(native.ptr(W), W.stride(0), native.ptr(t["anchor"]), t["anchor"].stride(0),

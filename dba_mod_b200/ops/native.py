@@ -48,6 +48,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_launch_count", [], c_ulonglong)
     _sig(lib, "dba_reset_launch_count", [], None)
     _sig(lib, "dba_add_launch_count", [c_ulonglong], None)
+    _sig(lib, "dba_stage_step", [P, P, P, P, P, P, P, I, I, I, I, P, P, P, P, P, P, P])
     _sig(lib, "dba_set_pdl", [I], None)
     _sig(lib, "dba_get_pdl", [], c_int)
     _sig(lib, "dba_set_bn_fused", [I], None)
@@ -78,8 +79,11 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_wgrad_tc_s2d", [P, P, P, L, I, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_wgrad_linear_chw", [P, P, P, L, I, I, I, I, I, I, I, I, P])
     _sig(lib, "dba_maxpool2_fwd", [P, P, I, I, I, I, I, I, I, I, I, L, L, P])
+    _sig(lib, "dba_maxpool2_fwd_split", [P, P, P, I, I, I, I, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_maxpool2_bwd_relu_bias", [P, P, P, P, L, I, I, I, I, I, I, I, I, I, I, I, L, L, P])
+    _sig(lib, "dba_maxpool2_bwd_relu_bias_split", [P, P, P, P, P, L, I, I, I, I, I, I, I, I, I, I, I, L, L, P])
     _sig(lib, "dba_relu_bwd_bias", [P, P, P, P, L, I, I, I, I, I, I, I, L, P])
+    _sig(lib, "dba_relu_bwd_bias_split", [P, P, P, P, P, L, I, I, I, I, I, I, I, L, P])
     _sig(lib, "dba_pack_weights", [P, L, P, I, I, P, L, P])
     _sig(lib, "dba_bn_fold", [P, L, P, I, I, P, P, L, F, P])
     _sig(lib, "dba_input_stage_image", [P, P, P, L, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, L, P])

@@ -127,6 +127,14 @@ int dba_maxpool2_bwd_relu_bias(const void* g, const void* x, void* dz, float* G,
                                long long Ro, void* stream);
 int dba_relu_bwd_bias(const void* g, const void* act, void* dz, float* G, long long ldg, int b_off, int c_real, int K,
                       int C, int B, int H, int W, long long R, void* stream);
+/* The same three with an optional bf16 hi/lo split copy of the output (tf32 mode: the weight-gradient operand form). */
+int dba_maxpool2_fwd_split(const void* x, void* y, void* y_split, int K, int C, int B, int Hi, int Wi, int off, int Ho,
+                           int Wo, int flatten, long long Ri, long long Ro, void* stream);
+int dba_maxpool2_bwd_relu_bias_split(const void* g, const void* x, void* dz, void* dz_split, float* G, long long ldg,
+                                     int b_off, int c_real, int K, int C, int B, int Hi, int Wi, int off, int Ho, int Wo,
+                                     int flatten, long long Ri, long long Ro, void* stream);
+int dba_relu_bwd_bias_split(const void* g, const void* act, void* dz, void* dz_split, float* G, long long ldg, int b_off,
+                            int c_real, int K, int C, int B, int H, int W, long long R, void* stream);
 
 /* ---- network plumbing (csrc/net_ops.cu, csrc/bn_ops.cu) -------------------------------------------------------- */
 
@@ -210,6 +218,13 @@ int dba_input_stage_image_split(const void* data, const long long* labels, const
 int dba_set_act_dtype(int mode);
 /* Programmatic dependent launch between consecutive network kernels (default on): a kernel's blocks are scheduled, and
  * run their prologue, while its predecessor drains.  No counterpart in the reference. */
+/* Lock-step staging: one launch copies the schedule entries of `step` (sample indices [K][T][B], flip flags, valid
+ * count, active flag, log slot, learning rate [K][T]) of clients rows[0..n) (null = 0..n-1) into the step slab's
+ * st_* rows.  Reference counterpart: the per-batch DataLoader / scheduler bookkeeping of image_train.py:191-230. */
+int dba_stage_step(const long long* idx, const unsigned char* flip, const int* nvalid, const unsigned char* active,
+                   const long long* slot, const float* lr, const long long* rows, int n, int T, int B, int step,
+                   long long* st_idx, unsigned char* st_flip, int* st_nvalid, unsigned char* st_active,
+                   long long* st_slot, float* st_lr, void* stream);
 void dba_set_pdl(int on);
 int dba_get_pdl(void);
 /* BatchNorm backward as one thread-block-cluster launch per layer (1; partial sums exchanged through distributed
