@@ -93,6 +93,10 @@ def bench_params(warmup: int, steps: int, windows: int = 2, config: str = "cifar
         if f"{i}_poison_epochs" in p:
             p[f"{i}_poison_epochs"] = [warmup + w * steps + 3 + 2 * i for w in range(windows)
                                        if 3 + 2 * i <= steps]
+    # one attack inside the warm-up as well, so that the attacker-only paths (poisoned schedule, scaling, backdoor
+    # tests, their buffers) exist before the first timed round - in both arms, they share this schedule
+    if warmup >= 2 and "0_poison_epochs" in p:
+        p["0_poison_epochs"] = [2] + list(p["0_poison_epochs"])
     return p
 
 
@@ -164,6 +168,10 @@ def run_own(args) -> dict:
     W, K = args.warmup, args.steps
     raw = bench_params(W, K, config=args.config)
     raw["compute_dtype"] = args.dtype
+    if comm.world > 1:
+        # several GPUs: the training phase is launch-bound (one or two clients per GPU), so a round's global evaluations
+        # run on a side stream under the next round's training (Simulator.overlap_global_eval)
+        raw["overlap_global_eval"] = True
     if args.small:
         raw.update(synthetic_train_size=5000, synthetic_test_size=1000)
     params = Params(raw)
@@ -180,6 +188,7 @@ def run_own(args) -> dict:
     epoch = 1
     for _ in range(W):
         sim.run_round(epoch); epoch += 1
+    sim.flush_pending()
     sim.timer.resolve()
     sim.timer.reset()                   # phase_ms covers the timed windows only
 
@@ -198,6 +207,7 @@ def run_own(args) -> dict:
         reports = []
         for _ in range(K):
             reports.append(sim.run_round(epoch)); epoch += 1
+        sim.flush_pending()             # a deferred global evaluation of the last round belongs to the timed region
         if cuda:
             e1.record()
         sync()
@@ -226,7 +236,7 @@ def run_own(args) -> dict:
                    "per_client_eval": True, "backend": be.name,
                    "native_train": bool(getattr(be, "native_train", False)),
                    "native_eval": bool(getattr(be, "native_eval", False)),
-                   "collectives": sim.collective_path},
+                   "collectives": sim.collective_path, "overlap_global_eval": bool(sim.overlap_global_eval)},
         "e2e": {"value": K / (ms_e2e / 1e3), "unit": "rounds/s", "h2d_bytes_per_step": sim.h2d_bytes_last,
                 "d2h_bytes_per_step": sim.d2h_bytes_last, "ms_per_step": ms_e2e / K,
                 "wall_ms_per_step": wall_e2e / K},

@@ -40,6 +40,8 @@ struct BnArgs {
   float momentum, eps;
 };
 
+constexpr int kRowsInFlight = 4;     // rows (16-byte chunks per tensor) a thread loads before it uses the first one
+
 // grid (row blocks, C/V, K), 256 threads; each thread walks rows of one V-channel plane.
 template <int V>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
@@ -74,43 +76,63 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
   const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
   const int total = a.B * S;
-  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
-    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
-    if (h >= a.H || w >= a.W) continue;
-    const long long off = plane + lead + q;
-    float o[V];
-    if (b < nv) {
-      float v[V];
-      chunk_unpack<V>(a.y[off], v);
+  const int stride = gridDim.x * blockDim.x;
+  // kRowsInFlight rows per thread and iteration, all loads issued before the first use: one 16-byte load in flight per
+  // thread left these kernels at ~50 % of the HBM bandwidth (ncu: 3.4 TB/s, profiles/r2/ncu_full_train_step_k10_summary.txt)
+  for (int qb = blockIdx.x * blockDim.x + threadIdx.x; qb < total; qb += stride * kRowsInFlight) {
+    uint4 ry[kRowsInFlight], rr[kRowsInFlight];
+    bool ok[kRowsInFlight];
+    int bb[kRowsInFlight], hh[kRowsInFlight], ww[kRowsInFlight];
 #pragma unroll
-      for (int j = 0; j < V; ++j) o[j] = v[j] * s_scale[j] + s_shift[j];
-      if (a.res) {
-        float r[V];
-        chunk_unpack<V>(a.res[off], r);
-#pragma unroll
-        for (int j = 0; j < V; ++j) o[j] += r[j];
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      const int q = qb + u * stride;
+      const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+      bb[u] = b; hh[u] = h; ww[u] = w;
+      ok[u] = q < total && h < a.H && w < a.W;
+      if (ok[u] && b < nv) {
+        ry[u] = a.y[plane + lead + q];
+        if (a.res) rr[u] = a.res[plane + lead + q];
       }
-      if (a.relu) {
+    }
 #pragma unroll
-        for (int j = 0; j < V; ++j) o[j] = fmaxf(o[j], 0.f);
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      if (!ok[u]) continue;
+      const int q = qb + u * stride, b = bb[u], h = hh[u], w = ww[u];
+      const long long off = plane + lead + q;
+      float o[V];
+      if (b < nv) {
+        float v[V];
+        chunk_unpack<V>(ry[u], v);
+#pragma unroll
+        for (int j = 0; j < V; ++j) o[j] = v[j] * s_scale[j] + s_shift[j];
+        if (a.res) {
+          float r[V];
+          chunk_unpack<V>(rr[u], r);
+#pragma unroll
+          for (int j = 0; j < V; ++j) o[j] += r[j];
+        }
+        if (a.relu) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) o[j] = relu_nan(o[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < V; ++j) o[j] = 0.f;
       }
-    } else {
-#pragma unroll
-      for (int j = 0; j < V; ++j) o[j] = 0.f;
-    }
-    const uint4 pk = chunk_pack_operand<V>(o);         // the activation is the next convolution's operand
-    a.out[off] = pk;
-    if constexpr (V == 4) {
-      if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.R, chunk, lead + q, o);
-    }
-    if (a.out2) {
-      const int W2p = (a.W >> 1) + 1, S2 = ((a.H >> 1) + 1) * W2p, lead2 = W2p + 1;
-      const int par = ((h & 1) << 1) | (w & 1);
-      const long long plane2 = ((long long)k * 4 + par) * (a.C / V) + chunk;
-      const long long row2 = lead2 + (long long)b * S2 + (h >> 1) * W2p + (w >> 1);
-      a.out2[plane2 * a.R2 + row2] = pk;
+      const uint4 pk = chunk_pack_operand<V>(o);         // the activation is the next convolution's operand
+      a.out[off] = pk;
       if constexpr (V == 4) {
-        if (a.out2_split) store_split(a.out2_split, k, (4 * a.C) >> 3, a.R2, par * (a.C >> 2) + chunk, row2, o);
+        if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.R, chunk, lead + q, o);
+      }
+      if (a.out2) {
+        const int W2p = (a.W >> 1) + 1, S2 = ((a.H >> 1) + 1) * W2p, lead2 = W2p + 1;
+        const int par = ((h & 1) << 1) | (w & 1);
+        const long long plane2 = ((long long)k * 4 + par) * (a.C / V) + chunk;
+        const long long row2 = lead2 + (long long)b * S2 + (h >> 1) * W2p + (w >> 1);
+        a.out2[plane2 * a.R2 + row2] = pk;
+        if constexpr (V == 4) {
+          if (a.out2_split) store_split(a.out2_split, k, (4 * a.C) >> 3, a.R2, par * (a.C >> 2) + chunk, row2, o);
+        }
       }
     }
   }
@@ -135,23 +157,39 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   float sg[V], sgx[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) sg[j] = sgx[j] = 0.f;
-  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
-    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
-    if (h >= a.H || w >= a.W) continue;
-    const long long off = plane + lead + q;
-    float g[V], y[V];
-    chunk_unpack<V>(a.g[off], g);
-    chunk_unpack<V>(a.y[off], y);
-    if (a.act) {
-      float o[V];
-      chunk_unpack<V>(a.act[off], o);
+  const int stride = gridDim.x * blockDim.x;
+  for (int qb = blockIdx.x * blockDim.x + threadIdx.x; qb < total; qb += stride * kRowsInFlight) {
+    uint4 rg[kRowsInFlight], ry[kRowsInFlight], ro[kRowsInFlight];
+    bool ok[kRowsInFlight];
 #pragma unroll
-      for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      const int q = qb + u * stride;
+      const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+      ok[u] = q < total && h < a.H && w < a.W;
+      if (ok[u]) {
+        const long long off = plane + lead + q;
+        rg[u] = a.g[off];
+        ry[u] = a.y[off];
+        if (a.act) ro[u] = a.act[off];
+      }
     }
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      sg[j] += g[j];
-      sgx[j] += g[j] * (y[j] - mean[j]) * rstd[j];
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      if (!ok[u]) continue;
+      float g[V], y[V];
+      chunk_unpack<V>(rg[u], g);
+      chunk_unpack<V>(ry[u], y);
+      if (a.act) {
+        float o[V];
+        chunk_unpack<V>(ro[u], o);
+#pragma unroll
+        for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        sg[j] += g[j];
+        sgx[j] += g[j] * (y[j] - mean[j]) * rstd[j];
+      }
     }
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -204,40 +242,60 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
   const long long plane_up = ((long long)k * (a.C / V) + chunk) * a.Rup;
   const int total = a.B * S;
-  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
-    const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
-    if (h >= a.H || w >= a.W) continue;
-    const long long off = plane + lead + q;
-    float d[V], gm[V];
-    if (b < nv) {
-      float g[V], y[V];
-      chunk_unpack<V>(a.g[off], g);
-      chunk_unpack<V>(a.y[off], y);
-      if (a.act) {
-        float o[V];
-        chunk_unpack<V>(a.act[off], o);
+  const int stride = gridDim.x * blockDim.x;
+  for (int qb = blockIdx.x * blockDim.x + threadIdx.x; qb < total; qb += stride * kRowsInFlight) {
+    uint4 rg[kRowsInFlight], ry[kRowsInFlight], ro[kRowsInFlight];
+    bool ok[kRowsInFlight];
+    int bb[kRowsInFlight], hh[kRowsInFlight], ww[kRowsInFlight];
 #pragma unroll
-        for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      const int q = qb + u * stride;
+      const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+      bb[u] = b; hh[u] = h; ww[u] = w;
+      ok[u] = q < total && h < a.H && w < a.W;
+      if (ok[u] && b < nv) {
+        const long long off = plane + lead + q;
+        rg[u] = a.g[off];
+        ry[u] = a.y[off];
+        if (a.act) ro[u] = a.act[off];
       }
+    }
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const float xh = (y[j] - s_mean[j]) * s_rstd[j];
-        gm[j] = g[j];
-        d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      if (!ok[u]) continue;
+      const int q = qb + u * stride, b = bb[u], h = hh[u], w = ww[u];
+      const long long off = plane + lead + q;
+      float d[V], gm[V];
+      if (b < nv) {
+        float g[V], y[V];
+        chunk_unpack<V>(rg[u], g);
+        chunk_unpack<V>(ry[u], y);
+        if (a.act) {
+          float o[V];
+          chunk_unpack<V>(ro[u], o);
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float xh = (y[j] - s_mean[j]) * s_rstd[j];
+          gm[j] = g[j];
+          d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < V; ++j) d[j] = gm[j] = 0.f;
       }
-    } else {
-#pragma unroll
-      for (int j = 0; j < V; ++j) d[j] = gm[j] = 0.f;
-    }
-    if (a.gmask) a.gmask[off] = chunk_pack<V>(gm);
-    long long doff = off, drow = lead + q;
-    if (a.up) {
-      drow = leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w;
-      doff = plane_up + drow;
-    }
-    a.out[doff] = chunk_pack_operand<V>(d);            // dy is the input-gradient convolution's operand
-    if constexpr (V == 4) {
-      if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.up ? a.Rup : a.R, chunk, drow, d);
+      if (a.gmask) a.gmask[off] = chunk_pack<V>(gm);
+      long long doff = off, drow = lead + q;
+      if (a.up) {
+        drow = leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w;
+        doff = plane_up + drow;
+      }
+      a.out[doff] = chunk_pack_operand<V>(d);            // dy is the input-gradient convolution's operand
+      if constexpr (V == 4) {
+        if (a.out_split) store_split(a.out_split, k, a.C >> 3, a.up ? a.Rup : a.R, chunk, drow, d);
+      }
     }
   }
 }

@@ -92,6 +92,11 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 template <int V> __device__ __forceinline__ void chunk_unpack(const uint4 u, float (&f)[V]);
 template <int V> __device__ __forceinline__ uint4 chunk_pack(const float (&f)[V]);
 
+// ReLU that propagates NaN like torch.relu (fmaxf(NaN, 0) would return 0): a model broken by a x100 scaled update - a
+// negative running variance after extrapolation - must evaluate to NaN logits (arg-max = class 0) here as it does in the
+// reference, not to a silently repaired network.
+__device__ __forceinline__ float relu_nan(float v) { return v < 0.f ? 0.f : v; }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

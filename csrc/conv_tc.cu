@@ -502,7 +502,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvArgs a) 
           }
           if (a.relu) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) sv[j] = fmaxf(sv[j], 0.f);
+            for (int j = 0; j < 32; ++j) sv[j] = relu_nan(sv[j]);
           }
 #pragma unroll
           for (int g = 0; g < NG; ++g) {           // 32 channels -> NG coalesced 16-byte stores

@@ -250,12 +250,12 @@ __global__ void __launch_bounds__(256) loan_eval_kernel(const LoanEvalArgs a) {
     for (int j = 0; j < F1; ++j) {
       float acc = w[OFF_B1 + j];
       for (int f = 0; f < F0; ++f) acc += w[OFF_W1 + j * F0 + f] * xv[f];
-      h1v[j] = fmaxf(acc, 0.f);
+      h1v[j] = relu_nan(acc);
     }
     for (int j = 0; j < F2; ++j) {
       float acc = w[OFF_B2 + j];
       for (int f = 0; f < F1; ++f) acc += w[OFF_W2 + j * F1 + f] * h1v[f];
-      h2v[j] = fmaxf(acc, 0.f);
+      h2v[j] = relu_nan(acc);
     }
     float lg[F3], mx = -INFINITY;
     int arg = 0;

@@ -93,6 +93,8 @@ _DEFAULTS: Dict[str, Any] = {
     "data_dir": "./data",
     "seed": 1,                    # main.py:36-38,86 hard-code 1
     "client_eval": True,          # Q16: per-client full-test-set evaluation each round
+    "overlap_global_eval": False,  # enqueue a round's global evaluations on a side stream, read them after the next
+                                  # round's local training (records keep their order; log lines come one phase late)
     "backend": "auto",            # auto | torch | cuda
     # cuda backend, ResNet executors: 'tf32' = fp32 activations + tcgen05 kind::tf32 (the reference's precision class:
     # fp32 tensors, TF32 convolutions), 'bf16' = bf16 activations + kind::f16 (fast mode, half the bytes)

@@ -170,3 +170,14 @@ class CudaBackend(TorchBackend):
         if self.native_eval and hasattr(self.exec, "evaluate_jobs"):
             return self.exec.evaluate_jobs(model, jobs, shard=shard)
         return super().evaluate_jobs(model, jobs, shard=shard)
+
+    @property
+    def can_defer_eval(self) -> bool:
+        """The executor can enqueue an evaluation without reading its result (NativeResNet.finalize_eval)."""
+        return bool(self.native_eval and hasattr(self.exec, "finalize_eval"))
+
+    def evaluate_jobs_deferred(self, model, jobs, shard=None):
+        return self.exec.evaluate_jobs(model, jobs, shard=shard, defer=True)
+
+    def finalize_eval(self, handle):
+        return self.exec.finalize_eval(handle)

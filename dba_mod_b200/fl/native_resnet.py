@@ -260,12 +260,12 @@ class NativeResNet(LockStepTrainer):
         return ids[r * per:min(n, (r + 1) * per)]
 
     @torch.no_grad()
-    def evaluate_jobs(self, model: torch.Tensor, jobs, shard=None):
+    def evaluate_jobs(self, model: torch.Tensor, jobs, shard=None, defer: bool = False):
         """ONE model on several input sets at once: jobs = [(split, trig_row), ...] (e.g. the round's global clean /
         combined-trigger / per-trigger evaluations, main.py:198-231).  The J input sets take the place of the client
         dimension and all of them are convolved with the same packed weights (client stride 0).
         Returns [(loss_sum, correct, n)] per job (sums over this rank's shard of each split)."""
-        return self._eval_general(model.reshape(1, -1), jobs, True, shard)
+        return self._eval_general(model.reshape(1, -1), jobs, True, shard, defer)
 
     @torch.no_grad()
     def evaluate_pairs(self, models: torch.Tensor, jobs, shard=None):
@@ -274,7 +274,9 @@ class NativeResNet(LockStepTrainer):
         every client, the attackers' pre-/post-scaling backdoor tests and local-trigger tests) run together."""
         return self._eval_general(models, jobs, False, shard)
 
-    def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None):
+    def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None, defer: bool = False):
+        """defer=True: no host read - returns a handle for finalize_eval() (the kernels are only enqueued on the current
+        stream; the simulator uses this to overlap a round's global evaluations with the next round's training)."""
         self._enter()
         d, dev, lib = self.data, self.device, self.lib
         J = len(jobs)
@@ -319,8 +321,14 @@ class NativeResNet(LockStepTrainer):
                                       None, native.ptr(mf), native.ptr(mi), 1, None, Js, Bt, self.head_C, self.head_H,
                                       self.head_H, self.ncls, Geom(Bt, self.head_H, self.head_H).rows,
                                       native.stream()))
+        handle = (mf, mi, order, ns, (models, pack, scale, shift, idx_all, trow, pn))   # inputs kept alive until read
+        return handle if defer else self.finalize_eval(handle)
+
+    @staticmethod
+    def finalize_eval(handle):
+        mf, mi, order, ns, _keep = handle
         mf_c, mi_c = mf.cpu(), mi.cpu()
-        out = [None] * J
+        out = [None] * len(order)
         for pos, j in enumerate(order):
             out[j] = (float(mf_c[pos, 0]), int(mi_c[pos, 0, 0]), ns[pos])
         return out

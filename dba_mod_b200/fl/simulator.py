@@ -183,6 +183,14 @@ class Simulator:
         self._loan_local_epoch = self.start_epoch - 1
         self.stream_inputs = False          # bench end-to-end mode: re-upload the round's inputs from pinned host
         self._pinned = None
+        # overlap_global_eval: a round's global evaluations (main.py:195-231) are only ENQUEUED - on a side stream - and
+        # read back after the next round's local training, which they overlap; records / CSV rows keep the reference's
+        # order, log lines of the global tests appear one training phase late.  Pays when the training phase leaves SMs
+        # idle (one client per GPU: launch-bound K = 1 steps).
+        self.overlap_global_eval = (bool(self.params.get("overlap_global_eval", False)) and self.device.type == "cuda"
+                                    and bool(getattr(self.backend, "can_defer_eval", False)))
+        self._eval_stream = torch.cuda.Stream(device=self.device) if self.overlap_global_eval else None
+        self._pending_eval = None
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
 
@@ -217,6 +225,7 @@ class Simulator:
             self.G_cnt.copy_(cnt[: self.spec.n_counters].to(self.device))
 
     def close(self) -> None:
+        self.flush_pending()
         self.metrics.close()
         close_logger(self._log_handlers)
         self._log_handlers = []
@@ -274,6 +283,7 @@ class Simulator:
             if max_rounds is not None and i >= max_rounds:
                 break
             reports.append(self.run_round(epoch))
+        self.flush_pending()
         logger.info("Saving all the graphs.")
         logger.info(f"This run has a label: {p['current_time']}. Metrics stream: {self.metrics.path}")
         return reports
@@ -311,9 +321,14 @@ class Simulator:
             dev_rows = rows.to(self.device, non_blocking=True)
             d.train_x.index_copy_(0, idx, dev_rows)
             nbytes += rows.numel() * rows.element_size()
+        self._h2d_train = nbytes
+
+    def _stage_test_inputs(self) -> None:
+        """End-to-end mode, second half: the test split, uploaded right before the round's first evaluation (after a
+        deferred global evaluation of the previous round has stopped reading it)."""
+        d = self.data
         d.test_x.copy_(self._pinned["test"], non_blocking=True)
-        nbytes += d.test_x.numel() * d.test_x.element_size()
-        self.h2d_bytes_last = nbytes
+        self.h2d_bytes_last = self._h2d_train + d.test_x.numel() * d.test_x.element_size()
 
     def run_round(self, epoch: int) -> RoundReport:
         p, be, dev = self.params, self.backend, self.device
@@ -350,6 +365,9 @@ class Simulator:
                     sch = build_schedule(p, self.data, plans, seg_epoch, dev, self.sched_gen)
                 with self.timer.phase("train/local_steps"):
                     res = be.train(sch, W, cnt, anchor, use_fg, generator=self.torch_gen)
+                self.flush_pending()            # previous round's global evaluations (overlapped the training above)
+                if self.stream_inputs and seg_epoch == epoch:
+                    self._stage_test_inputs()
                 rep.steps += sch.T
                 if use_fg:
                     grad_sum = res.grad_sum     # "only works for aggr_epoch_interval=1" (image_train.py:24)
@@ -365,10 +383,17 @@ class Simulator:
 
         # ---------------- global evaluation (main.py:195-231)
         with self.timer.phase("global_eval"):
+            if self.overlap_global_eval:
+                self._launch_global_eval(epoch, rep, t0)
+                return rep                # completed (in place) by flush_pending() during the next round / at the end
             self._global_eval(epoch, rep)
+        self._end_of_round(epoch, rep, t0)
+        return rep
+
+    def _end_of_round(self, epoch: int, rep: RoundReport, t0: float) -> None:
+        p = self.params
         if hasattr(self.comm, "check"):
             self.comm.check()            # a timed-out cross-GPU barrier (dead peer) surfaces here, once per round
-
         if self.write_files:
             self.ckpt_writer.save_model(self.state_dict(), epoch, rep.poison_loss if p["is_poison"] else rep.global_loss)
             self.recorder.save_result_csv(epoch, p["is_poison"], self.folder_path)
@@ -377,7 +402,28 @@ class Simulator:
             self.recorder.flush_scale_row()
         rep.seconds = time.time() - t0
         logger.info(f"Done in {rep.seconds} sec.")
-        return rep
+
+    def _launch_global_eval(self, epoch: int, rep: RoundReport, t0: float) -> None:
+        """Enqueue the round's global evaluations on the side stream (they read self.G and the test split, both left
+        untouched until flush_pending())."""
+        jobs, tests = self._global_jobs()
+        shard = (self.rank, self.world) if self.world > 1 else None
+        side = self._eval_stream
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            handle = self.backend.evaluate_jobs_deferred(self.G, jobs, shard=shard)
+        self._pending_eval = (epoch, rep, t0, tests, handle)
+
+    def flush_pending(self) -> None:
+        """Read back and record a deferred global evaluation (no-op when none is pending)."""
+        pend, self._pending_eval = self._pending_eval, None
+        if pend is None:
+            return
+        epoch, rep, t0, tests, handle = pend
+        torch.cuda.current_stream().wait_stream(self._eval_stream)     # evaluation buffers are shared with the main stream
+        res = self.backend.finalize_eval(handle)
+        self._record_global_eval(epoch, rep, tests, self._reduce_eval_rows(res))
+        self._end_of_round(epoch, rep, t0)
 
     # -------------------------------------------------------------------------------------- local phase
     def _loan_adaptive_lr(self, my_names, seg_epoch, W) -> Optional[dict]:
@@ -729,7 +775,9 @@ class Simulator:
         """All global evaluations of a round in one batched pass; with several ranks every rank evaluates its shard
         of the test split and the three sums are all-reduced (R5)."""
         shard = (self.rank, self.world) if self.world > 1 else None
-        res = self.backend.evaluate_jobs(self.G, jobs, shard=shard)
+        return self._reduce_eval_rows(self.backend.evaluate_jobs(self.G, jobs, shard=shard))
+
+    def _reduce_eval_rows(self, res) -> List[Tuple[float, float, int, int]]:
         t = torch.tensor([[r[0], float(r[1]), float(r[2])] for r in res], dtype=torch.float64, device=self.device)
         if self.world > 1:
             self.comm.all_reduce_sum_(t)
@@ -740,8 +788,11 @@ class Simulator:
         return out
 
     def _global_eval(self, epoch: int, rep: RoundReport) -> None:
-        p, rec = self.params, self.recorder
-        tge = epoch + p["aggr_epoch_interval"] - 1
+        jobs, tests = self._global_jobs()
+        self._record_global_eval(epoch, rep, tests, self._eval_global_jobs(jobs))
+
+    def _global_jobs(self):
+        p = self.params
         jobs = [("clean", 0)]
         tests = []
         if p["is_poison"]:
@@ -752,7 +803,11 @@ class Simulator:
             else:
                 tests = [(f"global_in_{a}_trigger", p.adversary_index(a) + 1) for a in p["adversary_list"]]
             jobs += [("poison", row) for _, row in tests]
-        results = self._eval_global_jobs(jobs)
+        return jobs, tests
+
+    def _record_global_eval(self, epoch: int, rep: RoundReport, tests, results) -> None:
+        p, rec = self.params, self.recorder
+        tge = epoch + p["aggr_epoch_interval"] - 1
         loss, acc, corr, n = results[0]
         logger.info("___Test {} poisoned: {}, epoch: {}: Average loss: {:.4f}, Accuracy: {}/{} ({:.4f}%)".format(
             self.target_name, False, tge, loss, corr, n, acc))

@@ -68,3 +68,34 @@ def test_mnist_rounds_native_backend(native_lib):
     assert min(r.global_loss for r in reps[1:4]) < reps[0].global_loss - 0.6, [r.global_loss for r in reps]
     assert max(r.global_acc for r in reps[1:4]) > 45.0, [r.global_acc for r in reps]
     assert reps[4].poison_acc > reps[3].poison_acc + 30.0, [r.poison_acc for r in reps]
+
+
+def test_overlapped_global_evaluation_records_the_same_rounds(native_lib):
+    """overlap_global_eval: a round's global evaluations run on a side stream under the next round's training and are
+    read back later.  Every report must still be complete, the records keep the reference's order (a round's client
+    rows, then its global row), and the deferred numbers equal a synchronous evaluation of the same global model."""
+    import yaml
+    from dba_mod_b200.config import Params
+    from dba_mod_b200.fl.simulator import Simulator
+    raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "cifar_params.yaml")))
+    raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=3000, synthetic_test_size=600, epochs=3,
+               number_of_total_participants=20, no_models=4, adversary_list=[3, 7, 11, 15], overlap_global_eval=True,
+               **{"0_poison_epochs": [2], "1_poison_epochs": [99], "2_poison_epochs": [99], "3_poison_epochs": [99]})
+    sim = Simulator(Params(raw), device=torch.device("cuda", 0), quiet=True, write_files=False)
+    assert sim.overlap_global_eval
+    reps = [sim.run_round(e) for e in (1, 2, 3)]
+    assert reps[0].global_acc is not None and reps[1].global_acc is not None     # completed during rounds 2 and 3
+    assert sim._pending_eval is not None                                         # round 3 still in flight
+    sim.flush_pending()
+    assert sim._pending_eval is None and all(r.global_acc is not None and r.poison_acc is not None for r in reps)
+    jobs, _ = sim._global_jobs()
+    sync = sim._eval_global_jobs(jobs)                       # the same global model, evaluated synchronously
+    assert abs(sync[0][0] - reps[2].global_loss) < 1e-4 * max(1.0, abs(sync[0][0])) and sync[0][2] == round(
+        reps[2].global_acc * sync[0][3] / 100.0)
+    assert abs(sync[1][1] - reps[2].poison_acc) < 1e-6
+    rows = sim.recorder.test_result
+    glob = [i for i, r in enumerate(rows) if r[0] == "global"]
+    assert [rows[i][1] for i in glob] == [1, 2, 3]
+    per_round = [sum(1 for r in rows[(glob[k - 1] + 1 if k else 0):glob[k]] if r[0] != "global") for k in range(3)]
+    assert per_round[0] == per_round[2] == 4 and per_round[1] >= 4, per_round    # the attack round adds attacker tests
+    sim.close()

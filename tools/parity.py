@@ -220,7 +220,12 @@ def cmd_report(a):
         for x in arms:
             runs = [v for k, v in x["runs"].items() if k.startswith(agg + "/")]
             if runs:
-                label = "reference" if x["arm"] == "reference" else f"own {x['dtype']} x{x.get('world', 1)} GPU"
+                if x["arm"] == "reference":
+                    label = f"reference (n={len(runs)})"
+                elif "backend=torch" in (x.get("overrides") or ""):
+                    label = f"own fp32 torch backend (n={len(runs)})"
+                else:
+                    label = f"own {x['dtype']} x{x.get('world', 1)} GPU (n={len(runs)})"
                 cols.append((label, runs, x["arm"]))
         if not cols:
             continue
@@ -339,6 +344,9 @@ if __name__ == "__main__":
     sw.add_argument("--dtype", default="tf32")
     sw.add_argument("--outdir", default="gpurun_out")
     sw.add_argument("--fixed-seed", type=int, default=-1, dest="fixed_seed")
+    mg = sub.add_parser("merge", help="merge the runs of result files of one arm / configuration (more seeds)")
+    mg.add_argument("files", nargs="+")
+    mg.add_argument("--out", required=True)
     tj = sub.add_parser("traj", help="per-run accuracy / ASR trajectories of result files, one line per run")
     tj.add_argument("files", nargs="+")
     a = ap.parse_args()
@@ -346,6 +354,15 @@ if __name__ == "__main__":
         json.dump(_ref_one(a.agg, a.seed, a), open(a.out, "w"))
     elif a.cmd == "run":
         cmd_run(a)
+    elif a.cmd == "merge":
+        xs = [json.load(open(f)) for f in a.files]
+        out = dict(xs[0])
+        out["runs"] = {}
+        for x in xs:
+            assert x["arm"] == xs[0]["arm"] and x.get("overrides", "") == xs[0].get("overrides", ""), "different arms / configurations"
+            out["runs"].update(x["runs"])
+        out["rounds"] = min(x["rounds"] for x in xs)
+        json.dump(out, open(a.out, "w"))
     elif a.cmd == "sweep":
         cmd_sweep(a)
     elif a.cmd == "traj":
