@@ -40,10 +40,11 @@ struct BnArgs {
   float momentum, eps;
 };
 
-constexpr int kRowsInFlight = 4;     // rows (16-byte chunks per tensor) a thread loads before it uses the first one
 
-// grid (row blocks, C/V, K), 256 threads; each thread walks rows of one V-channel plane.
-template <int V>
+// grid (row blocks, C/V, K), 256 threads; each thread walks rows of one V-channel plane, kRowsInFlight rows per iteration
+// with all loads issued before the first use.  Small grids (one or two clients per GPU) are latency-bound and take 4
+// (K = 1 step: 1.43 -> 1.37 ms); big grids lose occupancy with 4 (K = 10: 5.62 -> 5.95 ms) and take 1.
+template <int V, int kRowsInFlight>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   __shared__ float s_scale[V], s_shift[V];
   pdl_trigger();
@@ -77,8 +78,6 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   const long long plane = ((long long)k * (a.C / V) + chunk) * a.R;
   const int total = a.B * S;
   const int stride = gridDim.x * blockDim.x;
-  // kRowsInFlight rows per thread and iteration, all loads issued before the first use: one 16-byte load in flight per
-  // thread left these kernels at ~50 % of the HBM bandwidth (ncu: 3.4 TB/s, profiles/r2/ncu_full_train_step_k10_summary.txt)
   for (int qb = blockIdx.x * blockDim.x + threadIdx.x; qb < total; qb += stride * kRowsInFlight) {
     uint4 ry[kRowsInFlight], rr[kRowsInFlight];
     bool ok[kRowsInFlight];
@@ -138,7 +137,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   }
 }
 
-template <int V>
+template <int V, int kRowsInFlight>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   __shared__ float red[2][8][V];
   pdl_trigger();
@@ -211,7 +210,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   }
 }
 
-template <int V>
+template <int V, int kRowsInFlight>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   __shared__ float s_sc[V], s_mg[V], s_mgx[V], s_mean[V], s_rstd[V];
   pdl_trigger();
@@ -611,8 +610,9 @@ inline dim3 bn_grid(int B, int H, int W, int C, int K) {
   int rb = (total + 1023) / 1024;
   if (rb < 1) rb = 1;
   if (rb > 64) rb = 64;
-  return dim3(rb, C / act_v(), K);
+  return dim3(rb, C / act_v(), K);     // (fewer, longer row blocks for big grids were measured: K = 10 step 5.62 -> 5.86 ms)
 }
+inline bool bn_small(const dim3& g) { return (long long)g.x * g.y * g.z <= 1100; }
 
 }  // namespace
 
@@ -661,8 +661,15 @@ int dba_bn_apply_split(const void* y, const void* res, void* out, void* out_s2d,
   a.ld_stats = ld_stats; a.ld_saved = ld_saved; a.ldw = ldw; a.R = R;
   a.stats_off = stats_off; a.saved_off = saved_off; a.g_off = g_off; a.b_off = b_off; a.rm_off = rm_off; a.rv_off = rv_off;
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.relu = relu; a.momentum = momentum; a.eps = eps;
-  if (act_v() == 4) launch_pdl(bn_apply_kernel<4>, bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream, a);
-  else launch_pdl(bn_apply_kernel<8>, bn_grid(B, H, W, C, K), 256, 0, (cudaStream_t)stream, a);
+  const dim3 grid = bn_grid(B, H, W, C, K);
+  const cudaStream_t st = (cudaStream_t)stream;
+  if (act_v() == 4) {
+    if (bn_small(grid)) launch_pdl(bn_apply_kernel<4, 4>, grid, 256, 0, st, a);
+    else launch_pdl(bn_apply_kernel<4, 1>, grid, 256, 0, st, a);
+  } else {
+    if (bn_small(grid)) launch_pdl(bn_apply_kernel<8, 4>, grid, 256, 0, st, a);
+    else launch_pdl(bn_apply_kernel<8, 1>, grid, 256, 0, st, a);
+  }
   DBA_COUNT_LAUNCH(1);
   DBA_CHECK_LAUNCH();
   return DBA_OK;
@@ -714,12 +721,22 @@ int dba_bn_backward_ex(const void* g, const void* y, const void* act, void* dy, 
     DBA_CHECK_LAUNCH();
     return DBA_OK;
   }
+  const cudaStream_t st = (cudaStream_t)stream;
+  const bool small = bn_small(grid);
   if (act_v() == 4) {
-    if (!sums_ready) launch_pdl(bn_bwd_reduce_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
-    launch_pdl(bn_bwd_apply_kernel<4>, grid, 256, 0, (cudaStream_t)stream, a);
+    if (!sums_ready) {
+      if (small) launch_pdl(bn_bwd_reduce_kernel<4, 4>, grid, 256, 0, st, a);
+      else launch_pdl(bn_bwd_reduce_kernel<4, 1>, grid, 256, 0, st, a);
+    }
+    if (small) launch_pdl(bn_bwd_apply_kernel<4, 4>, grid, 256, 0, st, a);
+    else launch_pdl(bn_bwd_apply_kernel<4, 1>, grid, 256, 0, st, a);
   } else {
-    if (!sums_ready) launch_pdl(bn_bwd_reduce_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
-    launch_pdl(bn_bwd_apply_kernel<8>, grid, 256, 0, (cudaStream_t)stream, a);
+    if (!sums_ready) {
+      if (small) launch_pdl(bn_bwd_reduce_kernel<8, 4>, grid, 256, 0, st, a);
+      else launch_pdl(bn_bwd_reduce_kernel<8, 1>, grid, 256, 0, st, a);
+    }
+    if (small) launch_pdl(bn_bwd_apply_kernel<8, 4>, grid, 256, 0, st, a);
+    else launch_pdl(bn_bwd_apply_kernel<8, 1>, grid, 256, 0, st, a);
   }
   DBA_COUNT_LAUNCH(sums_ready ? 1 : 2);
   DBA_CHECK_LAUNCH();

@@ -25,7 +25,11 @@ using namespace dba;
 
 namespace {
 
-constexpr int kThreadsW = 192;
+// Two producer warps (a warp has one bulk-copy instruction in flight): stage s is loaded by warp
+// s % kProdW.  Warps: kProdW producers, one MMA issuer, four epilogue warps (one per TMEM lane quadrant, warp & 3).
+constexpr int kProdW = 2;
+constexpr int kMmaWarpW = kProdW;
+constexpr int kThreadsW = 32 * (kProdW + 1 + 4);
 
 struct WgArgs {
   const __nv_bfloat16* dY;     // [K][Cout/8][R][8]  (zero on halo rows and on padding samples)
@@ -88,8 +92,8 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   uint64_t* acc_empty = acc_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
   int* tap_shift = reinterpret_cast<int*>(tmem_slot + 4);    // [taps] row shift of every tap, computed once
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + a.taps) {
-    const int tap = threadIdx.x - 64;
+  if (threadIdx.x >= 96 && threadIdx.x < 96 + a.taps) {
+    const int tap = threadIdx.x - 96;
     int shift = 0;
     if (a.taps > 1) {
       const int th = tap / a.ksz;
@@ -110,7 +114,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
     mbar_fence_init();
   }
   pdl_trigger();
-  if (warp == 1) {
+  if (warp == kMmaWarpW) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
@@ -123,8 +127,9 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   const int items = a.K * a.nmb * a.ngroups * a.nnblk * a.nsplit;
   // real planes of dY available for this M block (the rest of the 16 planes stays unloaded: rows >= Cout of D are
   // never read back)
-  if (warp == 0) {
-    // whole warp: lane 0 waits for the free stage and posts the byte count, all lanes issue the plane copies
+  if (warp < kProdW) {
+    // every producer warp walks all stages and loads the ones it owns; lane 0 waits for the free stage and posts the
+    // byte count, all lanes issue the plane copies
     int st = 0;
     uint32_t ph = 0;
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
@@ -139,6 +144,10 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
       const __nv_bfloat16* xk = a.X + (long long)k * a.x_client + (long long)(nbk * nplanes) * a.x_plane;
       for (int ch = c0; ch < c1; ++ch) {
         const int mslots = a.vs ? a.vs * mreal : mreal;          // A planes filled per operand set
+        if (st % kProdW != warp) {                               // another producer warp's stage
+          if (++st == a.stages) { st = 0; ph ^= 1u; }
+          continue;
+        }
         if (lane == 0) {
           mbar_wait(&empty[st], ph ^ 1u);
           mbar_arrive_expect_tx(&full[st], NSET * (uint32_t)mslots * pitchA + bytesB);
@@ -164,7 +173,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
         if (++st == a.stages) { st = 0; ph ^= 1u; }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarpW) {
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(128, a.N, 1, 1);       // both operands MN-major
       int st = 0, acc_it = 0;
@@ -270,7 +279,7 @@ __global__ void __launch_bounds__(kThreadsW, 1) wgrad_tc_kernel(const WgArgs a) 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == kMmaWarpW) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
