@@ -93,6 +93,7 @@ _DEFAULTS: Dict[str, Any] = {
     "data_dir": "./data",
     "seed": 1,                    # main.py:36-38,86 hard-code 1
     "client_eval": True,          # Q16: per-client full-test-set evaluation each round
+    "overlap_client_eval": False,  # with overlap_global_eval: defer the per-client tests too (measured: no net gain)
     "overlap_global_eval": False,  # enqueue a round's global evaluations on a side stream, read them after the next
                                   # round's local training (records keep their order; log lines come one phase late)
     "backend": "auto",            # auto | torch | cuda

@@ -268,11 +268,20 @@ class NativeResNet(LockStepTrainer):
         return self._eval_general(model.reshape(1, -1), jobs, True, shard, defer)
 
     @torch.no_grad()
-    def evaluate_pairs(self, models: torch.Tensor, jobs, shard=None):
+    def evaluate_pairs(self, models: torch.Tensor, jobs, shard=None, defer: bool = False):
         """P (model, input set) pairs in one batched pass: models [P, Df], jobs = [(split, trig_row)] * P.  This is
         how all per-client evaluations that follow local training (image_train.py:148-164,268-295: clean test of
         every client, the attackers' pre-/post-scaling backdoor tests and local-trigger tests) run together."""
-        return self._eval_general(models, jobs, False, shard)
+        return self._eval_general(models, jobs, False, shard, defer)
+
+    def _h2d(self, values, dtype) -> torch.Tensor:
+        """Small host list -> device tensor without blocking the host on the current stream (torch.tensor(list,
+        device=...) is a synchronous copy: a deferred evaluation on the side stream would wait for everything queued
+        there before the next round could be enqueued)."""
+        t = torch.tensor(values, dtype=dtype)
+        if self.device.type != "cuda":
+            return t.to(self.device)
+        return t.pin_memory().to(self.device, non_blocking=True)
 
     def _eval_general(self, models: torch.Tensor, jobs, w_shared: bool, shard=None, defer: bool = False):
         """defer=True: no host read - returns a handle for finalize_eval() (the kernels are only enqueued on the current
@@ -292,7 +301,7 @@ class NativeResNet(LockStepTrainer):
             id_sets = [id_sets[j] for j in order]
             ns = [ns[j] for j in order]
             if not w_shared:
-                models = models[torch.tensor(order, device=dev)]
+                models = models[self._h2d(order, torch.long)]
         pack = self.pack_weights(models)
         scale = torch.empty(Mw, self.bn_total, device=dev)
         shift = torch.empty(Mw, self.bn_total, device=dev)
@@ -304,8 +313,8 @@ class NativeResNet(LockStepTrainer):
         bufs = self._ebufs(J, Bt, per_job_input=True)
         mf = torch.zeros(J, 1, device=dev)
         mi = torch.zeros(J, 1, 2, dtype=torch.int32, device=dev)
-        trow = torch.tensor([max(tr, 0) for _, tr in jobs], dtype=torch.long, device=dev)
-        pn = torch.tensor([Bt if sp == "poison" else 0 for sp, _ in jobs], dtype=torch.long, device=dev)
+        trow = self._h2d([max(tr, 0) for _, tr in jobs], torch.long)
+        pn = self._h2d([Bt if sp == "poison" else 0 for sp, _ in jobs], torch.long)
         idx_all = torch.full((J, (nmax + Bt - 1) // Bt * Bt if nmax else Bt), -1, dtype=torch.long, device=dev)
         for j, t in enumerate(id_sets):
             idx_all[j, :t.numel()] = t

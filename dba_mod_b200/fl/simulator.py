@@ -183,6 +183,8 @@ class Simulator:
         self._loan_local_epoch = self.start_epoch - 1
         self.stream_inputs = False          # bench end-to-end mode: re-upload the round's inputs from pinned host
         self._pinned = None
+        self._test_rows = None
+        self._host_idx = {}
         # overlap_global_eval: a round's global evaluations (main.py:195-231) are only ENQUEUED - on a side stream - and
         # read back after the next round's local training, which they overlap; records / CSV rows keep the reference's
         # order, log lines of the global tests appear one training phase late.  Pays when the training phase leaves SMs
@@ -191,6 +193,8 @@ class Simulator:
                                     and bool(getattr(self.backend, "can_defer_eval", False)))
         self._eval_stream = torch.cuda.Stream(device=self.device) if self.overlap_global_eval else None
         self._pending_eval = None
+        self._pending_client = None         # deferred per-client evaluations of the same round (image data only)
+        self._pending_rows = None
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
 
@@ -307,7 +311,12 @@ class Simulator:
         idx = torch.cat([d.client_index_tensor(n) for n in names]) if names else None
         nbytes = 0
         if idx is not None and idx.numel():
-            host_idx = idx.cpu()
+            # host copies of the clients' index lists are kept (a .cpu() per round would stall the host on the stream)
+            cache = self._host_idx
+            for n in names:
+                if n not in cache:
+                    cache[n] = d.client_index_tensor(n).cpu()
+            host_idx = torch.cat([cache[n] for n in names])
             n = int(host_idx.numel())
             stage = self._pinned.get("stage")
             if stage is None or stage.shape[0] < n:
@@ -327,6 +336,27 @@ class Simulator:
         """End-to-end mode, second half: the test split, uploaded right before the round's first evaluation (after a
         deferred global evaluation of the previous round has stopped reading it)."""
         d = self.data
+        if self.world > 1 and self.params["type"] in C.IMAGE_TYPES:
+            # several ranks: a rank evaluates its slice of the clean and of the backdoor test set (the executors' _shard:
+            # contiguous slices of ceil(n / world) indices) - those rows are this rank's inputs
+            if self._test_rows is None:
+                def part(ids):
+                    n = int(ids.numel())
+                    per = (n + self.world - 1) // self.world
+                    return ids[self.rank * per:min(n, (self.rank + 1) * per)]
+                rows = torch.unique(torch.cat([part(d.all_test_idx), part(d.poison_test_idx)]))
+                self._test_rows = (rows, rows.cpu())
+                stage = torch.empty((int(rows.numel()),) + tuple(self._pinned["test"].shape[1:]),
+                                    dtype=self._pinned["test"].dtype)
+                self._pinned["test_stage"] = stage.pin_memory() if self.device.type == "cuda" else stage
+                # the test split never changes: its shard is gathered into the pinned staging buffer once, every round
+                # then pays the host->device copy only
+                torch.index_select(self._pinned["test"], 0, self._test_rows[1], out=self._pinned["test_stage"])
+            rows_dev, rows_host = self._test_rows
+            stage = self._pinned["test_stage"]
+            d.test_x.index_copy_(0, rows_dev, stage.to(self.device, non_blocking=True))
+            self.h2d_bytes_last = self._h2d_train + stage.numel() * stage.element_size()
+            return
         d.test_x.copy_(self._pinned["test"], non_blocking=True)
         self.h2d_bytes_last = self._h2d_train + d.test_x.numel() * d.test_x.element_size()
 
@@ -375,7 +405,10 @@ class Simulator:
                     self._after_training(seg_epoch, plans, my_slots, sch, res, W, cnt, anchor, anchor_cnt,
                                          rows_local, num_samples, rep)
         # emit per-client rows in the reference's order (client by client)
-        self._emit_rows(rows_local, counts)
+        if self._pending_client is not None:
+            self._pending_rows = (rows_local, counts)          # completed and emitted by flush_pending()
+        else:
+            self._emit_rows(rows_local, counts)
 
         # ---------------- aggregation (main.py:172-191)
         with self.timer.phase("aggregate"):
@@ -384,6 +417,7 @@ class Simulator:
         # ---------------- global evaluation (main.py:195-231)
         with self.timer.phase("global_eval"):
             if self.overlap_global_eval:
+                self._enqueue_client_evals()
                 self._launch_global_eval(epoch, rep, t0)
                 return rep                # completed (in place) by flush_pending() during the next round / at the end
             self._global_eval(epoch, rep)
@@ -421,6 +455,12 @@ class Simulator:
             return
         epoch, rep, t0, tests, handle = pend
         torch.cuda.current_stream().wait_stream(self._eval_stream)     # evaluation buffers are shared with the main stream
+        pc, self._pending_client = self._pending_client, None
+        if pc is not None:              # the round's per-client tests first: their rows precede the global rows
+            c_epoch, plans, my_slots, rows, chandle = pc
+            self._record_client_evals(c_epoch, plans, my_slots, rows, self._finish_eval_jobs(chandle))
+            (rows_local, counts), self._pending_rows = self._pending_rows, None
+            self._emit_rows(rows_local, counts)
         res = self.backend.finalize_eval(handle)
         self._record_global_eval(epoch, rep, tests, self._reduce_eval_rows(res))
         self._end_of_round(epoch, rep, t0)
@@ -532,7 +572,14 @@ class Simulator:
         for split, trig, k, tag in self._eval_job_meta(plans):
             row = pre[pre_of[k]] if tag.startswith("pre_") else W[k]
             jobs.append((split, trig, row, k, tag))
-        results = self._run_eval_jobs(jobs, epoch)
+        if self._defer_client_eval():
+            # enqueue only: the rows of these tests are recorded by flush_pending(), after the next round's local phase
+            self._pending_client = (epoch, plans, list(my_slots), rows, self._launch_eval_jobs(jobs, epoch))
+            return
+        self._record_client_evals(epoch, plans, my_slots, rows, self._run_eval_jobs(jobs, epoch))
+
+    def _record_client_evals(self, epoch, plans, my_slots, rows, results) -> None:
+        p = self.params
         order_tags = ["pre_clean", "pre_poison", "clean", "poison", "agent"]
         for k, pl in enumerate(plans):
             slot = my_slots[k]
@@ -606,6 +653,55 @@ class Simulator:
                 out[(k, tag)] = (float(loss[j]) / n if n else 0, acc, int(correct[j]), n)
         return out
 
+    def _defer_client_eval(self) -> bool:
+        """overlap_client_eval (off by default, needs overlap_global_eval): the per-client tests of a round are deferred
+        the same way.  Measured at 8 GPUs: 18.7 ms of tests disappear from the round, the overlapped training phase gets
+        7.4 ms longer, host-side scheduling 2.7 ms - 82.5 -> 81.4 ms per round device-timed, but end to end 89.9 -> 92.6:
+        not worth it by default (the evaluation passes keep every SM busy for 50-100 us at a time and the launch-bound
+        training kernels queue behind them)."""
+        return (self.overlap_global_eval and bool(self.params.get("overlap_client_eval", False))
+                and self.params["type"] in C.IMAGE_TYPES and int(self.params["aggr_epoch_interval"]) == 1)
+
+    def _launch_eval_jobs(self, jobs, epoch):
+        """Deferred form of _run_eval_jobs, first half: the inputs of the evaluation - a copy of the model rows, after the
+        exchange between ranks (a collective, so it happens now, on the main stream).  The kernels are enqueued by
+        _enqueue_client_evals() once the aggregation kernels are in the queue (an evaluation pass keeps every SM busy
+        for milliseconds; the cooperative aggregation kernels would wait behind it)."""
+        if self.world > 1:
+            prep = self._balanced_inputs(jobs, epoch)
+            if prep is None:
+                return ["none", None, jobs, None]
+            models_all, jobs_all, counts = prep
+            return ["balanced", (models_all, jobs_all), jobs, counts]
+        if not jobs:
+            return ["none", None, jobs, None]
+        return ["single", (torch.stack([j[2] for j in jobs]), [(j[0], max(j[1], 0)) for j in jobs]), jobs, None]
+
+    def _enqueue_client_evals(self) -> None:
+        if self._pending_client is None:
+            return
+        handle = self._pending_client[4]
+        if handle[0] == "none":
+            return
+        models, meta = handle[1]
+        side = self._eval_stream
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            shard = (self.rank, self.world) if handle[0] == "balanced" else None
+            handle[1] = self.backend.exec.evaluate_pairs(models, meta, shard=shard, defer=True)
+
+    def _finish_eval_jobs(self, handle):
+        kind, h, jobs, counts = handle
+        if kind == "none":
+            return {}
+        res = self.backend.finalize_eval(h)
+        if kind == "balanced":
+            return self._balanced_reduce(res, jobs, counts)
+        out = {}
+        for (split, trig, _, k, tag), (loss, corr, n) in zip(jobs, res):
+            out[(k, tag)] = (loss / n if n else 0, 100.0 * corr / n if n else 0, corr, n)
+        return out
+
     def _run_eval_jobs_balanced(self, jobs, pairs, epoch=None):
         """Several ranks: the client -> rank placement is uneven (10 clients on 8 GPUs, attackers with extra tests),
         so the models to evaluate are exchanged (~11 MB each over NVLink) and EVERY rank evaluates ALL
@@ -613,6 +709,16 @@ class Simulator:
         all-reduced and each rank keeps the rows of its own jobs.  Every rank derives all ranks' job lists from the
         round plan (no metadata exchange); with the peer-memory communicator the models are pulled over NVLink by a
         gather kernel and the sums go through the fused all-reduce - no NCCL call, no pickling."""
+        prep = self._balanced_inputs(jobs, epoch)
+        if prep is None:
+            return {}
+        models_all, jobs_all, counts = prep
+        res = pairs(models_all, jobs_all, shard=(self.rank, self.world))
+        if res is None:
+            return None
+        return self._balanced_reduce(res, jobs, counts)
+
+    def _balanced_inputs(self, jobs, epoch=None):
         names = self._round_names
         ep = self._round_epoch if epoch is None else epoch
         owner = self._placement(names, self._round_epoch)
@@ -625,7 +731,7 @@ class Simulator:
         counts = [len(g) for g in gathered]
         total = sum(counts)
         if total == 0:
-            return {}
+            return None
         Df = self.spec.Df
         mine = torch.stack([j[2][:Df] for j in jobs]) if jobs else torch.zeros(0, Df, device=self.device)
         if hasattr(self.comm, "gather_rows"):
@@ -633,9 +739,9 @@ class Simulator:
         else:
             models_all = self.comm.all_gather_rows(mine.contiguous(), counts)
         jobs_all = [m for g in gathered for m in g]
-        res = pairs(models_all, jobs_all, shard=(self.rank, self.world))
-        if res is None:
-            return None
+        return models_all, jobs_all, counts
+
+    def _balanced_reduce(self, res, jobs, counts):
         t = torch.tensor([[r[0], float(r[1]), float(r[2])] for r in res], dtype=torch.float64, device=self.device)
         self.comm.all_reduce_sum_(t)
         lo = sum(counts[: self.rank])

@@ -70,7 +70,8 @@ def test_mnist_rounds_native_backend(native_lib):
     assert reps[4].poison_acc > reps[3].poison_acc + 30.0, [r.poison_acc for r in reps]
 
 
-def test_overlapped_global_evaluation_records_the_same_rounds(native_lib):
+@pytest.mark.parametrize("clients_too", [False, True], ids=["global", "global+client"])
+def test_overlapped_global_evaluation_records_the_same_rounds(native_lib, clients_too):
     """overlap_global_eval: a round's global evaluations run on a side stream under the next round's training and are
     read back later.  Every report must still be complete, the records keep the reference's order (a round's client
     rows, then its global row), and the deferred numbers equal a synchronous evaluation of the same global model."""
@@ -80,7 +81,7 @@ def test_overlapped_global_evaluation_records_the_same_rounds(native_lib):
     raw = yaml.safe_load(open(os.path.join(ROOT, "utils", "cifar_params.yaml")))
     raw.update(resumed_model=False, synthetic_data=True, synthetic_train_size=3000, synthetic_test_size=600, epochs=3,
                number_of_total_participants=20, no_models=4, adversary_list=[3, 7, 11, 15], overlap_global_eval=True,
-               scale_weights_poison=4,
+               scale_weights_poison=4, overlap_client_eval=clients_too,
                **{"0_poison_epochs": [2], "1_poison_epochs": [99], "2_poison_epochs": [99], "3_poison_epochs": [99]})
     sim = Simulator(Params(raw), device=torch.device("cuda", 0), quiet=True, write_files=False)
     assert sim.overlap_global_eval
