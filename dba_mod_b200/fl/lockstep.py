@@ -30,6 +30,12 @@ class LockStepTrainer:
 
     compute_dtype = "bf16"
 
+    def _metric_slots(self) -> int:
+        """Per-internal-epoch metric slots of a slab: the longest local schedule the configuration can produce (the
+        reference logs one line per internal epoch, image_train.py:121-133), at least 16."""
+        p = self.params
+        return max(16, int(p.get("internal_epochs", 1)), int(p.get("internal_poison_epochs", 1)))
+
     def _enter(self) -> None:
         """Selects this executor's activation element mode in the native library (library-wide switch)."""
         native.set_act_dtype(self.compute_dtype)
@@ -93,7 +99,8 @@ class LockStepTrainer:
         E = max(sch.E_max, 1)
         t = self._tbufs(K)
         if E > t["mf"].shape[1]:
-            raise NotImplementedError(f"more than {t['mf'].shape[1]} internal epochs")
+            raise ValueError(f"schedule with {E} internal epochs, slabs were sized for {t['mf'].shape[1]} "
+                             "(internal_epochs / internal_poison_epochs changed after the executor was built?)")
         # persistent slabs (their addresses are baked into the captured step graph)
         t["W"][:, :Df].copy_(W[:, :Df])
         if cnt.numel():

@@ -249,9 +249,9 @@ class NativeMnist(LockStepTrainer):
             t[key] = torch.zeros(K, ld, device=dev)
         t["W"] = torch.zeros(K, (sp.Df + 3) // 4 * 4, device=dev)
         t["cnt"] = torch.zeros(K, sp.n_counters, dtype=torch.long, device=dev)
-        t["mf"] = torch.zeros(K, 16, device=dev)
-        t["mf_dist"] = torch.zeros(K, 16, device=dev)
-        t["mi"] = torch.zeros(K, 16, 2, dtype=torch.int32, device=dev)
+        t["mf"] = torch.zeros(K, self._metric_slots(), device=dev)
+        t["mf_dist"] = torch.zeros(K, self._metric_slots(), device=dev)
+        t["mi"] = torch.zeros(K, self._metric_slots(), 2, dtype=torch.int32, device=dev)
         t["nan"] = torch.zeros(K, dtype=torch.uint8, device=dev)
         t["dist"] = torch.zeros(K, dtype=torch.float64, device=dev)
         t["dist_scratch"] = torch.zeros(int(self.lib.dba_rows_sqdist_scratch_elems(max(K, 1))), dtype=torch.float64,

@@ -490,13 +490,13 @@ class NativeResNet(LockStepTrainer):
         t["gs"] = torch.zeros_like(t["Gr"])
         t["W"] = torch.zeros(K, (self.spec.Df + 3) // 4 * 4, device=dev)
         t["cnt"] = torch.zeros(K, self.spec.n_counters, dtype=torch.long, device=dev)
-        t["mf"] = torch.zeros(K, 16, device=dev)
-        t["mf_dist"] = torch.zeros(K, 16, device=dev)
+        t["mf"] = torch.zeros(K, self._metric_slots(), device=dev)
+        t["mf_dist"] = torch.zeros(K, self._metric_slots(), device=dev)
         t["anchor"] = torch.zeros(K, (self.spec.Dp + 3) // 4 * 4, device=dev)
         t["dist"] = torch.zeros(K, dtype=torch.float64, device=dev)
         t["dist_scratch"] = torch.zeros(int(self.lib.dba_rows_sqdist_scratch_elems(max(K, 1))), dtype=torch.float64,
                                         device=dev)
-        t["mi"] = torch.zeros(K, 16, 2, dtype=torch.int32, device=dev)
+        t["mi"] = torch.zeros(K, self._metric_slots(), 2, dtype=torch.int32, device=dev)
         t["nan"] = torch.zeros(K, dtype=torch.uint8, device=dev)
         t["st_idx"] = torch.full((K, B), -1, dtype=torch.long, device=dev)
         t["st_flip"] = torch.zeros(K, B, dtype=torch.uint8, device=dev)
