@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1"
-timeout 120 $TR --master-port 29551 bench.py --gpus 8 --steps 5 --warmup 3 --config tiny_foolsgold > gpurun_out/bench_tiny_foolsgold_8gpu.json 2> gpurun_out/bench_tiny_foolsgold_8gpu.err; tail -c 500 gpurun_out/bench_tiny_foolsgold_8gpu.json; echo; grep -v "Warning\|return func\|^\*\|OMP" gpurun_out/bench_tiny_foolsgold_8gpu.err | tail -n 5
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke_final.log 2>&1; echo "smoke rc=$?"; tail -n 4 gpurun_out/smoke_final.log
+timeout 600 python -m pytest tests/test_gpu_resnet.py -m gpu -q > gpurun_out/pytest_gpu15.log 2>&1; echo "pytest rc=$?"; tail -n 3 gpurun_out/pytest_gpu15.log
