@@ -137,6 +137,125 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
   }
 }
 
+// tf32 mode with split copies: ONE thread handles the two 4-channel chunks that make up an 8-channel plane of the bf16
+// hi/lo split tensor, so the split rows leave as full 16-byte stores (a thread of bn_apply_kernel<4> writes 8 bytes at a
+// 16-byte stride: half-filled sectors, the kernel stayed at 48 % of the HBM copy bandwidth while the other BatchNorm
+// kernels reach 67-70 %).  grid (row blocks, C/8, K).
+__device__ __forceinline__ void split_pair_store(uint4* base, long long row16, long long lo_off16, const float (&o)[8]) {
+  uint4 ph, pl;
+  ph.x = pack_bf16x2(o[0], o[1]); ph.y = pack_bf16x2(o[2], o[3]); ph.z = pack_bf16x2(o[4], o[5]); ph.w = pack_bf16x2(o[6], o[7]);
+  pl.x = pack_bf16x2(o[0] - bf16lo(ph.x), o[1] - bf16hi(ph.x));
+  pl.y = pack_bf16x2(o[2] - bf16lo(ph.y), o[3] - bf16hi(ph.y));
+  pl.z = pack_bf16x2(o[4] - bf16lo(ph.z), o[5] - bf16hi(ph.z));
+  pl.w = pack_bf16x2(o[6] - bf16lo(ph.w), o[7] - bf16hi(ph.w));
+  base[row16] = ph;
+  base[row16 + lo_off16] = pl;
+}
+
+template <int kRowsInFlight>
+__global__ void __launch_bounds__(256) bn_apply_pair_kernel(const BnArgs a) {
+  __shared__ float s_scale[8], s_shift[8];
+  pdl_trigger();
+  pdl_wait();
+  const int p8 = blockIdx.y, k = blockIdx.z;
+  const int nv = a.nvalid[k];
+  const float n = (float)nv * (float)(a.H * a.W);
+  if (threadIdx.x < 8) {
+    const int c = p8 * 8 + threadIdx.x;
+    float* w = a.Wflat + (long long)k * a.ldw;
+    const float s1 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c];
+    const float s2 = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
+    const float mean = n > 0.f ? s1 / n : 0.f;
+    const float var = n > 0.f ? fmaxf(s2 / n - mean * mean, 0.f) : 0.f;
+    const float rstd = 1.f / sqrtf(var + a.eps);
+    const float sc = w[a.g_off + c] * rstd;
+    s_scale[threadIdx.x] = sc;
+    s_shift[threadIdx.x] = w[a.b_off + c] - mean * sc;
+    if (blockIdx.x == 0) {
+      a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c] = mean;
+      a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c + 1] = rstd;
+      if (nv > 0 && (!a.active || a.active[k])) {
+        const float unb = n > 1.f ? var * n / (n - 1.f) : var;
+        w[a.rm_off + c] = (1.f - a.momentum) * w[a.rm_off + c] + a.momentum * mean;
+        w[a.rv_off + c] = (1.f - a.momentum) * w[a.rv_off + c] + a.momentum * unb;
+      }
+    }
+  }
+  __syncthreads();
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const int C4 = a.C >> 2, C8 = a.C >> 3;
+  const long long plane0 = ((long long)k * C4 + 2 * p8) * a.R, plane1 = plane0 + a.R;
+  uint4* split = reinterpret_cast<uint4*>(a.out_split);
+  uint4* split2 = reinterpret_cast<uint4*>(a.out2_split);
+  const long long sp_base = ((long long)k * 2 * C8 + p8) * a.R, sp_lo = (long long)C8 * a.R;
+  const int total = a.B * S;
+  const int stride = gridDim.x * blockDim.x;
+  for (int qb = blockIdx.x * blockDim.x + threadIdx.x; qb < total; qb += stride * kRowsInFlight) {
+    uint4 ry0[kRowsInFlight], ry1[kRowsInFlight], rr0[kRowsInFlight], rr1[kRowsInFlight];
+    bool ok[kRowsInFlight];
+    int bb[kRowsInFlight], hh[kRowsInFlight], ww[kRowsInFlight];
+#pragma unroll
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      const int q = qb + u * stride;
+      const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+      bb[u] = b; hh[u] = h; ww[u] = w;
+      ok[u] = q < total && h < a.H && w < a.W;
+      if (ok[u] && b < nv) {
+        ry0[u] = a.y[plane0 + lead + q];
+        ry1[u] = a.y[plane1 + lead + q];
+        if (a.res) { rr0[u] = a.res[plane0 + lead + q]; rr1[u] = a.res[plane1 + lead + q]; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      if (!ok[u]) continue;
+      const int q = qb + u * stride, b = bb[u], h = hh[u], w = ww[u];
+      float o[8];
+      if (b < nv) {
+        float v0[4], v1[4];
+        chunk_unpack<4>(ry0[u], v0);
+        chunk_unpack<4>(ry1[u], v1);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          o[j] = v0[j] * s_scale[j] + s_shift[j];
+          o[4 + j] = v1[j] * s_scale[4 + j] + s_shift[4 + j];
+        }
+        if (a.res) {
+          float r0[4], r1[4];
+          chunk_unpack<4>(rr0[u], r0);
+          chunk_unpack<4>(rr1[u], r1);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { o[j] += r0[j]; o[4 + j] += r1[j]; }
+        }
+        if (a.relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = relu_nan(o[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = 0.f;
+      }
+      const float o0[4] = {o[0], o[1], o[2], o[3]}, o1[4] = {o[4], o[5], o[6], o[7]};
+      const uint4 pk0 = chunk_pack_operand<4>(o0), pk1 = chunk_pack_operand<4>(o1);
+      a.out[plane0 + lead + q] = pk0;
+      a.out[plane1 + lead + q] = pk1;
+      if (split) split_pair_store(split, sp_base + lead + q, sp_lo, o);
+      if (a.out2) {
+        const int W2p = (a.W >> 1) + 1, S2 = ((a.H >> 1) + 1) * W2p, lead2 = W2p + 1;
+        const int par = ((h & 1) << 1) | (w & 1);
+        const long long p2 = (((long long)k * 4 + par) * C4 + 2 * p8) * a.R2;
+        const long long row2 = lead2 + (long long)b * S2 + (h >> 1) * W2p + (w >> 1);
+        a.out2[p2 + row2] = pk0;
+        a.out2[p2 + a.R2 + row2] = pk1;
+        if (split2) {       // [K][2][4C/8][R2][8]: plane8 of the space-to-depth tensor = par * C/8 + p8
+          const long long s2 = ((long long)k * 2 * (4 * C8) + (long long)par * C8 + p8) * a.R2;
+          split_pair_store(split2, s2 + row2, (long long)(4 * C8) * a.R2, o);
+        }
+      }
+    }
+  }
+}
+
 template <int V, int kRowsInFlight>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   __shared__ float red[2][8][V];
@@ -582,6 +701,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const PoolArgs a) {
   }
 }
 
+int g_bn_pair = 1;     // tf32 mode: bn_apply on 8-channel planes (A/B switch dba_set_bn_pair)
 int g_bn_fused = 0;   // measured slower than reduce + apply (K = 1: 1.65 vs 1.59 ms / step, K = 10: 6.36 vs 5.96)
 
 template <typename... KArgs, typename... Args>
@@ -663,7 +783,12 @@ int dba_bn_apply_split(const void* y, const void* res, void* out, void* out_s2d,
   a.K = K; a.C = C; a.B = B; a.H = H; a.W = W; a.relu = relu; a.momentum = momentum; a.eps = eps;
   const dim3 grid = bn_grid(B, H, W, C, K);
   const cudaStream_t st = (cudaStream_t)stream;
-  if (act_v() == 4) {
+  if (act_v() == 4 && g_bn_pair && a.out_split && (a.out2 == nullptr || a.out2_split)) {
+    // 8-channel planes per thread: full 16-byte stores of the split copies
+    dim3 gp(grid.x, C / 8, K);
+    if (bn_small(gp)) launch_pdl(bn_apply_pair_kernel<4>, gp, 256, 0, st, a);
+    else launch_pdl(bn_apply_pair_kernel<1>, gp, 256, 0, st, a);
+  } else if (act_v() == 4) {
     if (bn_small(grid)) launch_pdl(bn_apply_kernel<4, 4>, grid, 256, 0, st, a);
     else launch_pdl(bn_apply_kernel<4, 1>, grid, 256, 0, st, a);
   } else {
@@ -754,6 +879,7 @@ int dba_bn_backward_split(const void* g, const void* y, const void* act, void* d
 // 1: BatchNorm backward = one cluster launch per layer; 0 (default): the two-kernel form (reduce with atomics into the
 // caller-zeroed `sums` scratch, then apply).  Both produce the same dy; the fused form needs no zeroed scratch and is
 // deterministic, but clusters of <= 8 CTAs walk long row slices twice and lose to 64 row blocks x 2 launches.
+void dba_set_bn_pair(int on) { g_bn_pair = on ? 1 : 0; }
 void dba_set_bn_fused(int on) { g_bn_fused = on ? 1 : 0; }
 int dba_get_bn_fused() { return g_bn_fused; }
 

@@ -52,6 +52,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "dba_set_pdl", [I], None)
     _sig(lib, "dba_get_pdl", [], c_int)
     _sig(lib, "dba_set_bn_fused", [I], None)
+    _sig(lib, "dba_set_bn_pair", [I], None)
     _sig(lib, "dba_set_wgrad_vstack", [I], None)
     _sig(lib, "dba_get_bn_fused", [], c_int)
     _sig(lib, "dba_set_act_dtype", [I])
@@ -117,6 +118,8 @@ def load() -> ctypes.CDLL:
         lib.dba_set_pdl(int(os.environ["DBA_PDL"]))
     if os.environ.get("DBA_WGRAD_VSTACK") is not None:   # A/B switch: tap-stacked weight gradient of the 32-channel layers
         lib.dba_set_wgrad_vstack(int(os.environ["DBA_WGRAD_VSTACK"]))
+    if os.environ.get("DBA_BN_PAIR") is not None:       # A/B switch: BatchNorm apply on 8-channel planes in tf32 mode
+        lib.dba_set_bn_pair(int(os.environ["DBA_BN_PAIR"]))
     if os.environ.get("DBA_BN_FUSED") is not None:  # A/B switch: cluster-fused BatchNorm backward (default: off)
         lib.dba_set_bn_fused(int(os.environ["DBA_BN_FUSED"]))
     _LIB = lib

@@ -231,6 +231,7 @@ int dba_get_pdl(void);
  * shared memory, deterministic, `sums` scratch unused) or as reduce + apply kernels (0, default - measured faster;
  * `sums` must be zeroed by the caller). */
 void dba_set_wgrad_vstack(int on);   /* 3x3 weight gradients with Cout <= 32: three vertical taps stacked along M (default on) */
+void dba_set_bn_pair(int on);        /* tf32 mode: BatchNorm apply handles 8-channel planes per thread (default on) */
 void dba_set_bn_fused(int on);
 int dba_get_bn_fused(void);
 int dba_get_act_dtype(void);
