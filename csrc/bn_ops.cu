@@ -418,6 +418,110 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   }
 }
 
+// bn_bwd_apply on 8-channel planes (tf32 mode with a split copy of dy): see bn_apply_pair_kernel.
+template <int kRowsInFlight>
+__global__ void __launch_bounds__(256) bn_bwd_apply_pair_kernel(const BnArgs a) {
+  __shared__ float s_sc[8], s_mg[8], s_mgx[8], s_mean[8], s_rstd[8];
+  pdl_trigger();
+  pdl_wait();
+  const int p8 = blockIdx.y, k = blockIdx.z;
+  const int nv = a.nvalid[k];
+  const float n = (float)nv * (float)(a.H * a.W);
+  if (threadIdx.x < 8) {
+    const int c = p8 * 8 + threadIdx.x;
+    const float sg = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c];
+    const float sgx = a.stats[(long long)k * a.ld_stats + a.stats_off + 2 * c + 1];
+    const float mean = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c];
+    const float rstd = a.saved[(long long)k * a.ld_saved + a.saved_off + 2 * c + 1];
+    const float gamma = a.Wflat[(long long)k * a.ldw + a.g_off + c];
+    s_sc[threadIdx.x] = gamma * rstd;
+    s_mg[threadIdx.x] = n > 0.f ? sg / n : 0.f;
+    s_mgx[threadIdx.x] = n > 0.f ? sgx / n : 0.f;
+    s_mean[threadIdx.x] = mean;
+    s_rstd[threadIdx.x] = rstd;
+    if (blockIdx.x == 0 && a.Gflat) {
+      a.Gflat[(long long)k * a.ldg + a.g_off + c] = sgx;   // d gamma
+      a.Gflat[(long long)k * a.ldg + a.b_off + c] = sg;    // d beta
+    }
+  }
+  __syncthreads();
+  const int Wp = a.W + 1, S = (a.H + 1) * Wp, lead = Wp + 1;
+  const int Wpu = 2 * a.W + 1, Su = (2 * a.H + 1) * Wpu, leadu = Wpu + 1;
+  const int C4 = a.C >> 2, C8 = a.C >> 3;
+  const long long plane0 = ((long long)k * C4 + 2 * p8) * a.R, plane1 = plane0 + a.R;
+  const long long Rd = a.up ? a.Rup : a.R;                       // rows of a dy plane
+  const long long dplane0 = ((long long)k * C4 + 2 * p8) * Rd, dplane1 = dplane0 + Rd;
+  uint4* split = reinterpret_cast<uint4*>(a.out_split);
+  const long long sp_base = ((long long)k * 2 * C8 + p8) * Rd, sp_lo = (long long)C8 * Rd;
+  const int total = a.B * S;
+  const int stride = gridDim.x * blockDim.x;
+  for (int qb = blockIdx.x * blockDim.x + threadIdx.x; qb < total; qb += stride * kRowsInFlight) {
+    uint4 rg0[kRowsInFlight], rg1[kRowsInFlight], ry0[kRowsInFlight], ry1[kRowsInFlight], ro0[kRowsInFlight],
+        ro1[kRowsInFlight];
+    bool ok[kRowsInFlight];
+    int bb[kRowsInFlight], hh[kRowsInFlight], ww[kRowsInFlight];
+#pragma unroll
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      const int q = qb + u * stride;
+      const int b = q / S, rem = q - b * S, h = rem / Wp, w = rem - h * Wp;
+      bb[u] = b; hh[u] = h; ww[u] = w;
+      ok[u] = q < total && h < a.H && w < a.W;
+      if (ok[u] && b < nv) {
+        const long long o0 = plane0 + lead + q, o1 = plane1 + lead + q;
+        rg0[u] = a.g[o0]; rg1[u] = a.g[o1];
+        ry0[u] = a.y[o0]; ry1[u] = a.y[o1];
+        if (a.act) { ro0[u] = a.act[o0]; ro1[u] = a.act[o1]; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kRowsInFlight; ++u) {
+      if (!ok[u]) continue;
+      const int q = qb + u * stride, b = bb[u], h = hh[u], w = ww[u];
+      float d[8], gm[8];
+      if (b < nv) {
+        float g[8], y[8];
+        {
+          float t0[4], t1[4];
+          chunk_unpack<4>(rg0[u], t0); chunk_unpack<4>(rg1[u], t1);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { g[j] = t0[j]; g[4 + j] = t1[j]; }
+          chunk_unpack<4>(ry0[u], t0); chunk_unpack<4>(ry1[u], t1);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { y[j] = t0[j]; y[4 + j] = t1[j]; }
+          if (a.act) {
+            chunk_unpack<4>(ro0[u], t0); chunk_unpack<4>(ro1[u], t1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              g[j] = t0[j] > 0.f ? g[j] : 0.f;
+              g[4 + j] = t1[j] > 0.f ? g[4 + j] : 0.f;
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = (y[j] - s_mean[j]) * s_rstd[j];
+          gm[j] = g[j];
+          d[j] = s_sc[j] * (g[j] - s_mg[j] - xh * s_mgx[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] = gm[j] = 0.f;
+      }
+      if (a.gmask) {
+        const float m0[4] = {gm[0], gm[1], gm[2], gm[3]}, m1[4] = {gm[4], gm[5], gm[6], gm[7]};
+        a.gmask[plane0 + lead + q] = chunk_pack<4>(m0);
+        a.gmask[plane1 + lead + q] = chunk_pack<4>(m1);
+      }
+      long long drow = lead + q;
+      if (a.up) drow = leadu + (long long)b * Su + (2 * h) * Wpu + 2 * w;
+      const float d0[4] = {d[0], d[1], d[2], d[3]}, d1[4] = {d[4], d[5], d[6], d[7]};
+      a.out[dplane0 + drow] = chunk_pack_operand<4>(d0);          // dy is the input-gradient convolution's operand
+      a.out[dplane1 + drow] = chunk_pack_operand<4>(d1);
+      split_pair_store(split, sp_base + drow, sp_lo, d);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ fused backward
 // Reduce + apply in ONE launch: the row blocks of a (client, channel-plane) pair form a thread-block cluster; every CTA
 // reduces its slice, the partial sums are exchanged through distributed shared memory (fixed summation order, no
@@ -853,8 +957,15 @@ int dba_bn_backward_ex(const void* g, const void* y, const void* act, void* dy, 
       if (small) launch_pdl(bn_bwd_reduce_kernel<4, 4>, grid, 256, 0, st, a);
       else launch_pdl(bn_bwd_reduce_kernel<4, 1>, grid, 256, 0, st, a);
     }
-    if (small) launch_pdl(bn_bwd_apply_kernel<4, 4>, grid, 256, 0, st, a);
-    else launch_pdl(bn_bwd_apply_kernel<4, 1>, grid, 256, 0, st, a);
+    if (g_bn_pair && a.out_split) {       // 8-channel planes per thread: 16-byte stores of the split copy of dy
+      const dim3 gp(grid.x, C / 8, K);
+      if (bn_small(gp)) launch_pdl(bn_bwd_apply_pair_kernel<2>, gp, 256, 0, st, a);   // <4> needs 176 registers
+      else launch_pdl(bn_bwd_apply_pair_kernel<1>, gp, 256, 0, st, a);
+    } else if (small) {
+      launch_pdl(bn_bwd_apply_kernel<4, 4>, grid, 256, 0, st, a);
+    } else {
+      launch_pdl(bn_bwd_apply_kernel<4, 1>, grid, 256, 0, st, a);
+    }
   } else {
     if (!sums_ready) {
       if (small) launch_pdl(bn_bwd_reduce_kernel<8, 4>, grid, 256, 0, st, a);
